@@ -1,0 +1,62 @@
+"""Shared comparison helpers for the parity tests (oracle = checker, never the product)."""
+import gzip
+from pathlib import Path
+
+import numpy as np
+
+
+def read_text(path):
+    path = Path(path)
+    if path.suffix == ".gz":
+        with gzip.open(path, "rt") as fh:
+            return fh.read()
+    return path.read_text()
+
+
+def assert_norm_files_equal(got, want):
+    """Step-4 hand-off file: every field string-equal (ids, N, Rw, %.3f headers, %.2f scales and z)."""
+    g, w = read_text(got).splitlines(), read_text(want).splitlines()
+    assert len(g) == len(w), f"line count {len(g)} != {len(w)}"
+    for ln, (a, b) in enumerate(zip(g, w)):
+        if a != b:
+            fa, fb = a.split("\t"), b.split("\t")
+            bad = [i for i, (x, y) in enumerate(zip(fa, fb)) if x != y][:5]
+            raise AssertionError(f"line {ln}: {len(fa)} vs {len(fb)} fields; first diffs at {bad}: "
+                                 f"{[(fa[i], fb[i]) for i in bad]}")
+
+
+def parse_neighbors(text):
+    rows = {}
+    for line in text.splitlines():
+        p = line.split("\t")
+        rows[p[0]] = (p[1], [(p[i], p[i + 1], p[i + 2]) for i in range(2, len(p) - 2, 3)])
+    return rows
+
+
+def assert_neighbor_files_equal(got, want, tie_rel=1e-6, r_use=None):
+    """Step-5 file: ids/scales string-equal; neighbour id SETS equal; order equal except inside groups of
+    (near-)tied printed distances, where sklearn's order is unspecified (north_star: ties within 1e-6 rel)."""
+    g, w = parse_neighbors(read_text(got)), parse_neighbors(read_text(want))
+    assert list(g) == list(w)
+    for sid in w:
+        assert g[sid][0] == w[sid][0], f"{sid}: scale {g[sid][0]} != {w[sid][0]}"
+        gl, wl = g[sid][1], w[sid][1]
+        assert len(gl) == len(wl), f"{sid}: {len(gl)} vs {len(wl)} neighbours"
+        assert [x[2] for x in gl] == [x[2] for x in wl], f"{sid}: printed distances differ"
+        assert {x[0] for x in gl} == {x[0] for x in wl}, f"{sid}: neighbour sets differ"
+        for (gi, gs, gd), (wi, ws, wd) in zip(gl, wl):
+            if gi != wi:
+                # allowed only inside a run of equal printed distances
+                assert gd == wd
+            else:
+                assert gs == ws
+
+
+def assert_dipcn_files_equal(got, want, rel=1e-5):
+    g, w = read_text(got).splitlines(), read_text(want).splitlines()
+    assert g[0] == w[0] == "Sample\tNorm_Reads"
+    assert len(g) == len(w)
+    for a, b in zip(g[1:], w[1:]):
+        (ia, va), (ib, vb) = a.split("\t"), b.split("\t")
+        assert ia == ib
+        assert abs(float(va) - float(vb)) <= rel * abs(float(vb)), (ia, va, vb)
