@@ -1,0 +1,81 @@
+"""ctypes binding of libgridb200.so (the C ABI declared in include/gridb200.h).
+
+There is no fallback: if the shared library is missing or a call fails, the caller gets an exception.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+_HERE = Path(__file__).resolve().parent
+LIB_PATH = _HERE / "csrc" / "libgridb200.so"
+
+_i64, _i32, _u64, _f64, _vp, _sz = C.c_int64, C.c_int32, C.c_uint64, C.c_double, C.c_void_p, C.c_size_t
+
+# name -> (restype, argtypes); must list every symbol include/gridb200.h declares (tests/test_abi.py checks)
+SIGNATURES = {
+    "gridb200_last_error": (C.c_char_p, []),
+    "gridb200_version": (C.c_char_p, []),
+    "gridb200_launch_count": (_u64, []),
+    "gridb200_col_raw_stats": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp]),
+    "gridb200_depth_filter": (C.c_int, [_vp, _vp, _i64, _f64, _f64, _vp, _vp]),
+    "gridb200_row_stats": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "gridb200_row_scales": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, _vp]),
+    "gridb200_col_norm_stats_ws_bytes": (_sz, [_i64, _i64]),
+    "gridb200_col_norm_stats": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "gridb200_col_finalize": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "gridb200_select_ws_bytes": (_sz, [_i64]),
+    "gridb200_select": (C.c_int, [_vp, _i64, _f64, _vp, _vp, _vp, _sz, _vp]),
+    "gridb200_knn_col_filter": (C.c_int, [_vp, _vp, _i64, _f64, _f64, _vp, _vp, _vp, _vp, _sz, _vp]),
+    "gridb200_transform": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _i64, _vp, _i64,
+                                     _vp, _vp, _vp]),
+    "gridb200_knn_prepare": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _i32, _vp, _i64, _vp, _vp]),
+    "gridb200_gram": (C.c_int, [_vp, _i64, _i64, _vp, _i64, _i64, _i64, _i32, _vp, _i64, C.c_int, C.c_int, _vp]),
+    "gridb200_topk_init": (C.c_int, [_vp, _vp, _i64, _i32, _vp]),
+    "gridb200_topk_merge": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _i32, _vp, _vp, _vp]),
+    "gridb200_dipcn": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _i64, _i32, _i64, _i32, _vp, _i64, _vp, _vp]),
+    "gridb200_synth_depth": (C.c_int, [_u64, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp]),
+    "gridb200_ingest_ws_bytes": (_sz, [_i64]),
+    "gridb200_ingest_text": (C.c_int, [_vp, _i64, C.c_char_p, _i32, _i64, _i64, _vp, _i64, _i64, _i64, _vp, _vp, _vp,
+                                       _sz, _vp]),
+}
+
+
+class GridB200Error(RuntimeError):
+    """A libgridb200 call returned a non-zero status."""
+
+    def __init__(self, fn: str, code: int, msg: str):
+        super().__init__(f"{fn} failed ({code}): {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load the library once; raises if it has not been built (python grid_b200/csrc/build.py)."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise ImportError(f"{LIB_PATH} is missing: build it with `python grid_b200/csrc/build.py` "
+                              "(there is no CPU fallback)")
+        lib = C.CDLL(str(LIB_PATH))
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def call(name: str, *args):
+    """Call an int-status entry point and raise GridB200Error on failure."""
+    lib = load()
+    rc = getattr(lib, name)(*args)
+    if rc != 0:
+        raise GridB200Error(name, rc, lib.gridb200_last_error().decode())
+
+
+def ptr(t) -> int | None:
+    """Device pointer of a torch tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()

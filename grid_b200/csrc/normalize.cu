@@ -1,0 +1,558 @@
+// Step 4 kernels: per-bin raw sums, per-sample sums, per-bin normalised statistics, transform + quantise.
+//
+// All four matrix passes are HBM-bound streaming reads of depth[n, ld] (fp32).  Thread mapping for the
+// column-oriented passes: one thread owns 4 consecutive bins (one 16-byte load per row), a block owns 1024
+// bins x a slab of rows, so a warp reads 512 contiguous bytes of every row it visits and the per-bin state
+// lives in registers.  Arithmetic is exact integer (hundredths) for sums and fp64 for everything the
+// reference does in fp64; see DESIGN.md "Numerics" for why fp32 is not enough before the %.2f rounding.
+#include "common.cuh"
+
+namespace g2 {
+
+constexpr int kThreads = 256;
+constexpr int kColsPerBlock = kThreads * 4;
+
+// rows per slab so that the grid has at least ~8 blocks per SM when the bin count alone cannot provide them
+static int64_t pick_row_slab(int64_t n, int64_t col_blocks, int64_t min_rows) {
+  const int64_t want_blocks = (int64_t)kSMs * 8;
+  int64_t slabs = (want_blocks + col_blocks - 1) / col_blocks;
+  int64_t rows = (n + slabs - 1) / slabs;
+  if (rows < min_rows) rows = min_rows;
+  if (rows > n) rows = n;
+  return rows < 1 ? 1 : rows;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K1: colsum[j] = sum_i h_ij, colcnt[j] = #{h_ij > 0}
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ depth, int64_t n, int64_t b,
+                                                      int64_t ld, int64_t rows_per_slab,
+                                                      unsigned long long* __restrict__ colsum,
+                                                      int* __restrict__ colcnt) {
+  const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
+  if (j0 >= b) return;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_slab;
+  const int64_t r1 = min(n, r0 + rows_per_slab);
+  unsigned long long s[4] = {0, 0, 0, 0};
+  int c[4] = {0, 0, 0, 0};
+  const float* p = depth + r0 * ld + j0;
+  for (int64_t base = r0; base < r1; base += 512) {  // uint32 partials cannot overflow within 512 rows
+    const int64_t lim = (r1 < base + 512 ? r1 : base + 512);
+    unsigned ps[4] = {0, 0, 0, 0};
+    int64_t i = base;
+    for (; i + 8 <= lim; i += 8) {
+      float4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = ld_stream(reinterpret_cast<const float4*>(p + u * ld));
+      p += 8 * ld;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int h0 = depth_hundredths(v[u].x), h1 = depth_hundredths(v[u].y);
+        const int h2 = depth_hundredths(v[u].z), h3 = depth_hundredths(v[u].w);
+        ps[0] += h0; ps[1] += h1; ps[2] += h2; ps[3] += h3;
+        c[0] += h0 > 0; c[1] += h1 > 0; c[2] += h2 > 0; c[3] += h3 > 0;
+      }
+    }
+    for (; i < lim; ++i) {
+      const float4 v = ld_stream(reinterpret_cast<const float4*>(p));
+      p += ld;
+      const int h0 = depth_hundredths(v.x), h1 = depth_hundredths(v.y);
+      const int h2 = depth_hundredths(v.z), h3 = depth_hundredths(v.w);
+      ps[0] += h0; ps[1] += h1; ps[2] += h2; ps[3] += h3;
+      c[0] += h0 > 0; c[1] += h1 > 0; c[2] += h2 > 0; c[3] += h3 > 0;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) s[q] += ps[q];
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    if (j0 + q < b) {
+      if (gridDim.y == 1) {
+        colsum[j0 + q] = s[q];
+        colcnt[j0 + q] = c[q];
+      } else {
+        atomicAdd(&colsum[j0 + q], s[q]);
+        atomicAdd(&colcnt[j0 + q], c[q]);
+      }
+    }
+  }
+}
+
+__global__ void k_depth_filter(const long long* __restrict__ colsum, const int* __restrict__ colcnt, int64_t b,
+                               double lo, double hi, uint8_t* __restrict__ valid) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= b) return;
+  const int c = colcnt[j];
+  bool ok = false;
+  if (c > 0) {
+    const double m = (double)colsum[j] / (100.0 * (double)c);
+    ok = (lo <= m) && (m <= hi);
+  }
+  valid[j] = ok ? 1 : 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K3: rowsum[i] = sum over valid bins of h_ij, rowcnt[i] = #present.  grid = (bin chunks, rows).
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kRowUnroll = 16;
+constexpr int kRowChunk = kThreads * 4 * kRowUnroll;  // 16384 bins per block
+
+__global__ void __launch_bounds__(kThreads) k_row_stats(const float* __restrict__ depth, int64_t b, int64_t ld,
+                                                        const uint8_t* __restrict__ valid,
+                                                        unsigned long long* __restrict__ rowsum,
+                                                        int* __restrict__ rowcnt) {
+  const int64_t row = blockIdx.y;
+  const int64_t c0 = (int64_t)blockIdx.x * kRowChunk;
+  const float* p = depth + row * ld;
+  float4 v[kRowUnroll];
+  uint32_t m[kRowUnroll];
+#pragma unroll
+  for (int u = 0; u < kRowUnroll; ++u) {
+    const int64_t j = c0 + ((int64_t)u * kThreads + threadIdx.x) * 4;
+    if (j < b) {  // ld >= roundup4(b): the 16-byte load stays inside the row
+      v[u] = ld_stream(reinterpret_cast<const float4*>(p + j));
+      if (j + 4 <= b) {
+        m[u] = *reinterpret_cast<const uint32_t*>(valid + j);
+      } else {
+        m[u] = 0;
+        for (int q = 0; q < 4 && j + q < b; ++q) m[u] |= (uint32_t)valid[j + q] << (8 * q);
+      }
+    } else {
+      v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      m[u] = 0;
+    }
+  }
+  unsigned long long s = 0;
+  int c = 0;
+#pragma unroll
+  for (int u = 0; u < kRowUnroll; ++u) {
+    const int h0 = (m[u] & 0x000000ffu) ? depth_hundredths(v[u].x) : 0;
+    const int h1 = (m[u] & 0x0000ff00u) ? depth_hundredths(v[u].y) : 0;
+    const int h2 = (m[u] & 0x00ff0000u) ? depth_hundredths(v[u].z) : 0;
+    const int h3 = (m[u] & 0xff000000u) ? depth_hundredths(v[u].w) : 0;
+    s += (unsigned)(h0 + h1) + (unsigned)(h2 + h3);
+    c += (h0 > 0) + (h1 > 0) + (h2 > 0) + (h3 > 0);
+  }
+  s = (unsigned long long)warp_sum((long long)s);
+  c = warp_sum(c);
+  __shared__ unsigned long long ss[kThreads / 32];
+  __shared__ int sc[kThreads / 32];
+  if ((threadIdx.x & 31) == 0) {
+    ss[threadIdx.x >> 5] = s;
+    sc[threadIdx.x >> 5] = c;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long ts = 0;
+    int tc = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) {
+      ts += ss[w];
+      tc += sc[w];
+    }
+    if (tc) {
+      atomicAdd(&rowsum[row], ts);
+      atomicAdd(&rowcnt[row], tc);
+    }
+  }
+}
+
+__global__ void k_row_scales(const long long* __restrict__ rowsum, const int* __restrict__ rowcnt, int64_t n,
+                             double* __restrict__ raw_mean, double* __restrict__ scale_q,
+                             double* __restrict__ row_factor) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int c = rowcnt[i];
+  const long long s = rowsum[i];
+  double m = nan(""), q = nan(""), f = nan("");
+  if (c > 0 && s > 0) {
+    m = (double)s / (100.0 * (double)c);    // nanmean of the raw depths of the row
+    q = printf_round(m, 100.0) / 100.0;     // float("%.2f" % m)
+    f = (double)c / (double)s;              // y_ij = h_ij * f  ==  depth_ij / rowmean_i
+  }
+  if (raw_mean) raw_mean[i] = m;
+  if (scale_q) scale_q[i] = q;
+  if (row_factor) row_factor[i] = f;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K4: sd[j] = sum_i (y_ij - 1), sd2[j] = sum_i (y_ij - 1)^2 over present cells (shifted-data variance).
+// Deterministic: with several row slabs each slab writes its own partial, reduced in slab order afterwards.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_col_norm(const float* __restrict__ depth, int64_t n, int64_t b,
+                                                       int64_t ld, int64_t rows_per_slab,
+                                                       const uint8_t* __restrict__ valid,
+                                                       const double* __restrict__ row_factor,
+                                                       double* __restrict__ out_sd, double* __restrict__ out_sd2) {
+  const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
+  if (j0 >= b) return;
+  bool ok[4];
+  bool any = false;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    ok[q] = (j0 + q < b) && valid[j0 + q];
+    any |= ok[q];
+  }
+  double s1[4] = {0, 0, 0, 0}, s2[4] = {0, 0, 0, 0};
+  if (any) {
+    const int64_t r0 = (int64_t)blockIdx.y * rows_per_slab;
+    const int64_t r1 = min(n, r0 + rows_per_slab);
+    const float* p = depth + r0 * ld + j0;
+    int64_t i = r0;
+    for (; i + 4 <= r1; i += 4) {
+      float4 v[4];
+      double f[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        v[u] = ld_stream(reinterpret_cast<const float4*>(p + u * ld));
+        f[u] = row_factor[i + u];
+      }
+      p += 4 * ld;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int h[4] = {depth_hundredths(v[u].x), depth_hundredths(v[u].y), depth_hundredths(v[u].z),
+                          depth_hundredths(v[u].w)};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (h[q] > 0) {  // a row with no valid bin has f = NaN but then also no present cell
+            const double d = fma(u32_to_double(h[q]), f[u], -1.0);
+            s1[q] += d;
+            s2[q] = fma(d, d, s2[q]);
+          }
+        }
+      }
+    }
+    for (; i < r1; ++i) {
+      const float4 v = ld_stream(reinterpret_cast<const float4*>(p));
+      const double f = row_factor[i];
+      p += ld;
+      const int h[4] = {depth_hundredths(v.x), depth_hundredths(v.y), depth_hundredths(v.z), depth_hundredths(v.w)};
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (h[q] > 0) {
+          const double d = fma(u32_to_double(h[q]), f, -1.0);
+          s1[q] += d;
+          s2[q] = fma(d, d, s2[q]);
+        }
+      }
+    }
+  }
+  double* o1 = out_sd + (int64_t)blockIdx.y * b;
+  double* o2 = out_sd2 + (int64_t)blockIdx.y * b;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    if (j0 + q < b) {
+      o1[j0 + q] = ok[q] ? s1[q] : 0.0;
+      o2[j0 + q] = ok[q] ? s2[q] : 0.0;
+    }
+  }
+}
+
+__global__ void k_reduce_slabs(const double* __restrict__ part1, const double* __restrict__ part2, int64_t b,
+                               int slabs, double* __restrict__ sd, double* __restrict__ sd2) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= b) return;
+  double a = 0, c = 0;
+  for (int s = 0; s < slabs; ++s) {
+    a += part1[(int64_t)s * b + j];
+    c += part2[(int64_t)s * b + j];
+  }
+  sd[j] = a;
+  sd2[j] = c;
+}
+
+__global__ void k_col_finalize(const double* __restrict__ sd, const double* __restrict__ sd2,
+                               const int* __restrict__ colcnt, const uint8_t* __restrict__ valid, int64_t b,
+                               int64_t n_total, double* __restrict__ mu, double* __restrict__ s2,
+                               double* __restrict__ ratio) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= b) return;
+  double m = nan(""), v = nan(""), r = nan("");
+  const int c = colcnt[j];
+  if (valid[j] && c > 0) {
+    const double a = sd[j];
+    const double dbar = a / (double)c;
+    m = 1.0 + dbar;
+    // sum (d - dbar)^2 = sd2 - sd*dbar ; the reference divides by N-1 with N = all rows (ddof=1, :446)
+    v = fma(-a, dbar, sd2[j]) / (double)(n_total - 1);
+    if (v < 0.0) v = 0.0;
+    if (m > 0.0) r = 100.0 * v / m;
+  }
+  mu[j] = m;
+  s2[j] = v;
+  ratio[j] = r;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K7: transform + printf-exact quantisation + compaction to the selected bins (+ clipped fp16 operand,
+// + exact row norms).  Block = 1024 bins x a slab of rows.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kTransformSlab = 256;
+
+template <bool kZq, bool kZh>
+__global__ void __launch_bounds__(kThreads) k_transform(const float* __restrict__ depth, int64_t n, int64_t b,
+                                                        int64_t ld, const double* __restrict__ row_factor,
+                                                        const double* __restrict__ mu,
+                                                        const int32_t* __restrict__ sel_pos,
+                                                        const uint8_t* __restrict__ keep,
+                                                        const double* __restrict__ info, int zclip,
+                                                        int16_t* __restrict__ zq, int64_t ldq,
+                                                        __half* __restrict__ zh, int64_t ldh,
+                                                        unsigned long long* __restrict__ norms,
+                                                        unsigned long long* __restrict__ sat) {
+  __shared__ unsigned long long s_norm[kTransformSlab];
+  const int64_t r0 = (int64_t)blockIdx.y * kTransformSlab;
+  const int64_t r1 = min(n, r0 + kTransformSlab);
+  if (kZh) {
+    for (int t = threadIdx.x; t < kTransformSlab; t += kThreads) s_norm[t] = 0;
+    __syncthreads();
+  }
+  const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
+  int pos[4];
+  double m[4], a[4];
+  bool kp[4];
+  bool any = false;
+  const double zscale = info[0];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    pos[q] = (j0 + q < b) ? sel_pos[j0 + q] : -1;
+    m[q] = 0.0;
+    a[q] = 0.0;
+    kp[q] = false;
+    if (pos[q] >= 0) {
+      any = true;
+      m[q] = mu[j0 + q];
+      a[q] = zscale / sqrt(m[q]);  // selected bins have a finite ratio, hence mu > 0
+      kp[q] = keep ? keep[j0 + q] != 0 : true;
+    }
+  }
+  const unsigned warp_any = __ballot_sync(0xffffffffu, any);
+  if (warp_any) {
+    const float* p = depth + r0 * ld + (j0 < b ? j0 : 0);
+    for (int64_t i = r0; i < r1; ++i, p += ld) {
+      int vsq = 0;
+      if (any) {
+        const float4 v = ld_stream(reinterpret_cast<const float4*>(p));
+        const double f = row_factor[i];
+        const int h[4] = {depth_hundredths(v.x), depth_hundredths(v.y), depth_hundredths(v.z), depth_hundredths(v.w)};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (pos[q] < 0) continue;
+          int zi = -32768;
+          if (h[q] > 0 && f == f) {
+            const double z = fma(u32_to_double(h[q]), f, -m[q]) * a[q];
+            double zr = printf_round(z, 100.0);
+            if (fabs(zr) > 32766.0) {
+              atomicAdd(sat, 1ULL);
+              zr = zr > 0 ? 32766.0 : -32766.0;
+            }
+            zi = double_to_int_exact(zr);
+            if (zi == 0 && z < 0.0) zi = -32767;  // prints as "-0.00"; numerically zero
+          }
+          if (kZq) zq[i * ldq + pos[q]] = (int16_t)zi;
+          if (kZh) {
+            int c = 0;
+            if (zi > -32767 && kp[q]) c = max(-zclip, min(zclip, zi));
+            zh[i * ldh + pos[q]] = __int2half_rn(c);
+            vsq += c * c;
+          }
+        }
+      }
+      if (kZh) {
+        const int tot = __reduce_add_sync(0xffffffffu, vsq);
+        if ((threadIdx.x & 31) == 0 && tot) atomicAdd(&s_norm[i - r0], (unsigned long long)tot);
+      }
+    }
+  }
+  if (kZh) {
+    __syncthreads();
+    for (int t = threadIdx.x; t < r1 - r0; t += kThreads)
+      if (s_norm[t]) atomicAdd(&norms[r0 + t], s_norm[t]);
+  }
+}
+
+// zq (hundredths, from a step-4 file) -> clipped fp16 operand + exact norms.  One block per row.
+__global__ void __launch_bounds__(kThreads) k_knn_prepare(const int16_t* __restrict__ zq, int64_t rw, int64_t ldq,
+                                                          const uint8_t* __restrict__ keep, int zclip,
+                                                          __half* __restrict__ zh, int64_t ldh,
+                                                          unsigned long long* __restrict__ norms) {
+  const int64_t i = blockIdx.x;
+  unsigned long long acc = 0;
+  for (int64_t j = threadIdx.x; j < ldh; j += kThreads) {
+    int c = 0;
+    if (j < rw) {
+      const int v = zq[i * ldq + j];
+      if (v > -32767 && (!keep || keep[j])) c = max(-zclip, min(zclip, v));
+    }
+    zh[i * ldh + j] = __int2half_rn(c);
+    acc += (unsigned)(c * c);
+  }
+  acc = (unsigned long long)warp_sum((long long)acc);
+  __shared__ unsigned long long ss[kThreads / 32];
+  if ((threadIdx.x & 31) == 0) ss[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long t = 0;
+    for (int w = 0; w < kThreads / 32; ++w) t += ss[w];
+    norms[i] = t;
+  }
+}
+
+}  // namespace g2
+
+using namespace g2;
+
+static int check_matrix(const void* p, int64_t n, int64_t b, int64_t ld) {
+  G2_REQUIRE(p != nullptr, GRIDB200_EINVAL, "depth matrix pointer is null");
+  G2_REQUIRE(n > 0 && b > 0, GRIDB200_EINVAL, "empty matrix (n=%lld, b=%lld)", (long long)n, (long long)b);
+  G2_REQUIRE(ld >= b && ld % 4 == 0, GRIDB200_EINVAL, "leading dimension %lld must be >= b=%lld and a multiple of 4",
+             (long long)ld, (long long)b);
+  G2_REQUIRE((reinterpret_cast<uintptr_t>(p) & 15) == 0, GRIDB200_EINVAL, "depth matrix must be 16-byte aligned");
+  G2_REQUIRE(n < (1LL << 31) && b < (1LL << 40), GRIDB200_EINVAL, "matrix too large");
+  return 0;
+}
+
+extern "C" int gridb200_col_raw_stats(const float* depth, int64_t n, int64_t b, int64_t ld, int64_t* colsum,
+                                      int32_t* colcnt, void* stream) {
+  if (int e = check_matrix(depth, n, b, ld)) return e;
+  G2_REQUIRE(colsum && colcnt, GRIDB200_EINVAL, "null output");
+  cudaStream_t st = as_stream(stream);
+  const int64_t cb = (b + kColsPerBlock - 1) / kColsPerBlock;
+  const int64_t rows = pick_row_slab(n, cb, 64);
+  const int64_t slabs = (n + rows - 1) / rows;
+  G2_REQUIRE(slabs <= 65535, GRIDB200_EINVAL, "too many row slabs");
+  if (slabs > 1) {
+    G2_CUDA(cudaMemsetAsync(colsum, 0, b * sizeof(int64_t), st));
+    G2_CUDA(cudaMemsetAsync(colcnt, 0, b * sizeof(int32_t), st));
+  }
+  k_col_raw<<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(
+      depth, n, b, ld, rows, reinterpret_cast<unsigned long long*>(colsum), colcnt);
+  G2_LAUNCHED();
+  return 0;
+}
+
+extern "C" int gridb200_depth_filter(const int64_t* colsum, const int32_t* colcnt, int64_t b, double min_depth,
+                                     double max_depth, uint8_t* valid, void* stream) {
+  G2_REQUIRE(colsum && colcnt && valid && b > 0, GRIDB200_EINVAL, "bad argument");
+  k_depth_filter<<<(unsigned)((b + 255) / 256), 256, 0, as_stream(stream)>>>(
+      reinterpret_cast<const long long*>(colsum), colcnt, b, min_depth, max_depth, valid);
+  G2_LAUNCHED();
+  return 0;
+}
+
+extern "C" int gridb200_row_stats(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                                  int64_t* rowsum, int32_t* rowcnt, void* stream) {
+  if (int e = check_matrix(depth, n, b, ld)) return e;
+  G2_REQUIRE(valid && rowsum && rowcnt, GRIDB200_EINVAL, "null argument");
+  G2_REQUIRE((reinterpret_cast<uintptr_t>(valid) & 3) == 0, GRIDB200_EINVAL, "valid flags must be 4-byte aligned");
+  cudaStream_t st = as_stream(stream);
+  G2_CUDA(cudaMemsetAsync(rowsum, 0, n * sizeof(int64_t), st));
+  G2_CUDA(cudaMemsetAsync(rowcnt, 0, n * sizeof(int32_t), st));
+  const int64_t chunks = (b + kRowChunk - 1) / kRowChunk;
+  for (int64_t r0 = 0; r0 < n; r0 += 65535) {  // gridDim.y limit
+    const int64_t rows = std::min<int64_t>(65535, n - r0);
+    k_row_stats<<<dim3((unsigned)chunks, (unsigned)rows), kThreads, 0, st>>>(
+        depth + r0 * ld, b, ld, valid, reinterpret_cast<unsigned long long*>(rowsum) + r0, rowcnt + r0);
+    G2_LAUNCHED();
+  }
+  return 0;
+}
+
+extern "C" int gridb200_row_scales(const int64_t* rowsum, const int32_t* rowcnt, int64_t n, double* raw_mean,
+                                   double* scale_q, double* row_factor, void* stream) {
+  G2_REQUIRE(rowsum && rowcnt && n > 0, GRIDB200_EINVAL, "bad argument");
+  k_row_scales<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(
+      reinterpret_cast<const long long*>(rowsum), rowcnt, n, raw_mean, scale_q, row_factor);
+  G2_LAUNCHED();
+  return 0;
+}
+
+static int64_t col_norm_slab_rows(int64_t n, int64_t b) {
+  const int64_t cb = (b + kColsPerBlock - 1) / kColsPerBlock;
+  if (cb >= (int64_t)kSMs * 4) return n;  // enough bin blocks: one slab, no partial buffers
+  return pick_row_slab(n, cb, 32);
+}
+
+extern "C" size_t gridb200_col_norm_stats_ws_bytes(int64_t n, int64_t b) {
+  if (n <= 0 || b <= 0) return 0;
+  const int64_t rows = col_norm_slab_rows(n, b);
+  const int64_t slabs = (n + rows - 1) / rows;
+  return slabs > 1 ? (size_t)slabs * (size_t)b * 2 * sizeof(double) : 0;
+}
+
+extern "C" int gridb200_col_norm_stats(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                                       const double* row_factor, double* sd, double* sd2, void* ws,
+                                       size_t ws_bytes, void* stream) {
+  if (int e = check_matrix(depth, n, b, ld)) return e;
+  G2_REQUIRE(valid && row_factor && sd && sd2, GRIDB200_EINVAL, "null argument");
+  cudaStream_t st = as_stream(stream);
+  const int64_t cb = (b + kColsPerBlock - 1) / kColsPerBlock;
+  const int64_t rows = col_norm_slab_rows(n, b);
+  const int64_t slabs = (n + rows - 1) / rows;
+  G2_REQUIRE(slabs <= 65535, GRIDB200_EINVAL, "too many row slabs");
+  if (slabs == 1) {
+    k_col_norm<<<dim3((unsigned)cb, 1), kThreads, 0, st>>>(depth, n, b, ld, rows, valid, row_factor, sd, sd2);
+    G2_LAUNCHED();
+  } else {
+    G2_REQUIRE(ws && ws_bytes >= gridb200_col_norm_stats_ws_bytes(n, b), GRIDB200_EINVAL,
+               "workspace too small: need %zu bytes", gridb200_col_norm_stats_ws_bytes(n, b));
+    double* p1 = static_cast<double*>(ws);
+    double* p2 = p1 + slabs * b;
+    k_col_norm<<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(depth, n, b, ld, rows, valid, row_factor,
+                                                                          p1, p2);
+    G2_LAUNCHED();
+    k_reduce_slabs<<<(unsigned)((b + 255) / 256), 256, 0, st>>>(p1, p2, b, (int)slabs, sd, sd2);
+    G2_LAUNCHED();
+  }
+  return 0;
+}
+
+extern "C" int gridb200_col_finalize(const double* sd, const double* sd2, const int32_t* colcnt,
+                                     const uint8_t* valid, int64_t b, int64_t n_total, double* mu, double* s2,
+                                     double* ratio, void* stream) {
+  G2_REQUIRE(sd && sd2 && colcnt && valid && mu && s2 && ratio && b > 0, GRIDB200_EINVAL, "bad argument");
+  k_col_finalize<<<(unsigned)((b + 255) / 256), 256, 0, as_stream(stream)>>>(sd, sd2, colcnt, valid, b, n_total, mu,
+                                                                            s2, ratio);
+  G2_LAUNCHED();
+  return 0;
+}
+
+extern "C" int gridb200_transform(const float* depth, int64_t n, int64_t b, int64_t ld, const double* row_factor,
+                                  const double* mu, const int32_t* sel_pos, const uint8_t* keep,
+                                  const double* info, int32_t zclip, int16_t* zq, int64_t ldq, void* zh,
+                                  int64_t ldh, int64_t* norms, unsigned long long* sat, void* stream) {
+  if (int e = check_matrix(depth, n, b, ld)) return e;
+  G2_REQUIRE(row_factor && mu && sel_pos && info && sat, GRIDB200_EINVAL, "null argument");
+  G2_REQUIRE(zq || zh, GRIDB200_EINVAL, "at least one of zq / zh must be requested");
+  G2_REQUIRE(!zh || (norms && zclip > 0 && zclip <= 2048), GRIDB200_EINVAL,
+             "zh needs norms and 0 < zclip <= 2048 (fp16 holds integers exactly up to 2048)");
+  const int64_t cb = (b + kColsPerBlock - 1) / kColsPerBlock;
+  const int64_t slabs = (n + kTransformSlab - 1) / kTransformSlab;
+  G2_REQUIRE(slabs <= 65535, GRIDB200_EINVAL, "too many row slabs");
+  dim3 grid((unsigned)cb, (unsigned)slabs);
+  cudaStream_t st = as_stream(stream);
+  __half* zhp = static_cast<__half*>(zh);
+  unsigned long long* np = reinterpret_cast<unsigned long long*>(norms);
+  if (zq && zh)
+    k_transform<true, true><<<grid, kThreads, 0, st>>>(depth, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip, zq,
+                                                       ldq, zhp, ldh, np, sat);
+  else if (zq)
+    k_transform<true, false><<<grid, kThreads, 0, st>>>(depth, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip,
+                                                        zq, ldq, zhp, ldh, np, sat);
+  else
+    k_transform<false, true><<<grid, kThreads, 0, st>>>(depth, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip,
+                                                        zq, ldq, zhp, ldh, np, sat);
+  G2_LAUNCHED();
+  return 0;
+}
+
+extern "C" int gridb200_knn_prepare(const int16_t* zq, int64_t n, int64_t rw, int64_t ldq, const uint8_t* keep,
+                                    int32_t zclip, void* zh, int64_t ldh, int64_t* norms, void* stream) {
+  G2_REQUIRE(zq && zh && norms && n > 0 && rw >= 0 && ldq >= rw && ldh >= rw, GRIDB200_EINVAL, "bad argument");
+  G2_REQUIRE(zclip > 0 && zclip <= 2048, GRIDB200_EINVAL, "0 < zclip <= 2048 required");
+  G2_REQUIRE(n < (1LL << 31), GRIDB200_EINVAL, "too many rows");
+  k_knn_prepare<<<(unsigned)n, kThreads, 0, as_stream(stream)>>>(zq, rw, ldq, keep, zclip, static_cast<__half*>(zh),
+                                                                 ldh, reinterpret_cast<unsigned long long*>(norms));
+  G2_LAUNCHED();
+  return 0;
+}

@@ -1,0 +1,350 @@
+// Order statistics and compaction over the per-bin ratio vector (length b, up to a few million):
+//   - median + top_frac threshold of the finite ratios  (normalize_mosdepth.py:460-468, :479-499)
+//   - sigma2_min of the %.3f-rounded ratios             (find_neighbors.py:128-175)
+// Implemented as an 8-pass MSB radix select on order-preserving 64-bit keys.  Each pass is one multi-block
+// kernel: warp-aggregated shared-memory histograms for up to 3 target ranks at once, merged with global
+// atomics; the last block to finish picks the digit of every target.  No host round trip, no sort.
+#include "common.cuh"
+
+namespace g2 {
+
+struct SelState {
+  unsigned long long prefix[3];
+  unsigned long long rank[3];
+  unsigned long long count;
+  double value[3];
+  unsigned int done;
+  int ntargets;
+  int error;
+  int pad;
+};
+constexpr size_t kStateBytes = 256;
+constexpr size_t kHistBytes = 8 * 3 * 256 * sizeof(unsigned);
+constexpr int kSelThreads = 256;
+constexpr int kScanTile = 2048;
+
+__device__ __forceinline__ unsigned long long key_of(double v) {
+  const unsigned long long u = (unsigned long long)__double_as_longlong(v);
+  return (u >> 63) ? ~u : (u | 0x8000000000000000ULL);
+}
+__device__ __forceinline__ double value_of(unsigned long long k) {
+  const unsigned long long u = (k >> 63) ? (k & 0x7FFFFFFFFFFFFFFFULL) : ~k;
+  return __longlong_as_double((long long)u);
+}
+// mode 0: candidates are the non-NaN values; mode 1: the finite values
+__device__ __forceinline__ bool is_candidate(double v, int mode) { return mode == 0 ? (v == v) : isfinite(v); }
+
+__global__ void k_sel_count(const double* __restrict__ vals, int64_t n, int mode, SelState* st) {
+  int c = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    c += is_candidate(vals[i], mode);
+  c = warp_sum(c);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&st->count, (unsigned long long)c);
+}
+
+// kind 0: ranks (cnt-1)/2, cnt/2 (median) and int(top_frac*cnt) (threshold).  kind 1: min(int(rw*(1-frac_r)), cnt-1)
+__global__ void k_sel_ranks(SelState* st, int kind, double param, const double* info) {
+  const long long cnt = (long long)st->count;
+  st->error = 0;
+  if (cnt == 0) {
+    st->ntargets = 0;
+    return;
+  }
+  if (kind == 0) {
+    st->ntargets = 3;
+    st->rank[0] = (unsigned long long)((cnt - 1) / 2);
+    st->rank[1] = (unsigned long long)(cnt / 2);
+    long long t = (long long)(param * (double)cnt);  // Python: int(top_frac * len(sorted_ratios))
+    if (t >= cnt || t < 0) {
+      st->error = 1;  // the reference's list index is out of range here
+      t = cnt - 1;
+    }
+    st->rank[2] = (unsigned long long)t;
+  } else {
+    st->ntargets = 1;
+    const long long rw = (long long)info[3];
+    long long t = (long long)((double)rw * (1.0 - param));  // int(R * (1.0 - frac_r))
+    if (t > cnt - 1) t = cnt - 1;
+    if (t < 0) t = 0;
+    st->rank[0] = (unsigned long long)t;
+  }
+  for (int t = 0; t < 3; ++t) st->prefix[t] = 0;
+}
+
+__global__ void __launch_bounds__(kSelThreads) k_sel_pass(const double* __restrict__ vals, int64_t n, int mode,
+                                                          int pass, SelState* st, unsigned* __restrict__ hist_all) {
+  __shared__ unsigned sh[3][256];
+  __shared__ bool s_last;
+  const int nt = st->ntargets;
+  if (nt == 0) return;
+  for (int t = threadIdx.x; t < 3 * 256; t += kSelThreads) (&sh[0][0])[t] = 0;
+  __syncthreads();
+  const int shift = 56 - 8 * pass;
+  unsigned long long pre[3];
+  for (int t = 0; t < 3; ++t) pre[t] = st->prefix[t];
+  const int64_t stride = (int64_t)gridDim.x * kSelThreads;
+  const int64_t nround = ((n + stride - 1) / stride) * stride;  // keep warps converged for match_any
+  for (int64_t i = (int64_t)blockIdx.x * kSelThreads + threadIdx.x; i < nround; i += stride) {
+    const double v = i < n ? vals[i] : nan("");
+    const bool cand = i < n && is_candidate(v, mode);
+    const unsigned long long key = key_of(v);
+    const unsigned digit = (unsigned)(key >> shift) & 0xffu;
+    for (int t = 0; t < nt; ++t) {
+      const bool hit = cand && (pass == 0 || (key >> (shift + 8)) == (pre[t] >> (shift + 8)));
+      const unsigned ballot = __ballot_sync(0xffffffffu, hit);
+      if (!ballot) continue;
+      if (hit) {
+        const unsigned peers = __match_any_sync(ballot, digit);
+        if ((threadIdx.x & 31) == __ffs(peers) - 1) {
+          const unsigned cnt = __popc(peers);
+          atomicAdd(&sh[t][digit], cnt);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  unsigned* hist = hist_all + (size_t)pass * 3 * 256;
+  for (int t = threadIdx.x; t < 3 * 256; t += kSelThreads) {
+    const unsigned c = (&sh[0][0])[t];
+    if (c) atomicAdd(&hist[t], c);
+  }
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(&st->done, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (threadIdx.x < nt) {
+    const int t = threadIdx.x;
+    unsigned long long r = st->rank[t];
+    const volatile unsigned* h = hist + t * 256;
+    int d = 0;
+    for (; d < 255; ++d) {
+      const unsigned c = h[d];
+      if (r < c) break;
+      r -= c;
+    }
+    st->rank[t] = r;
+    const unsigned long long p = pre[t] | ((unsigned long long)d << shift);
+    st->prefix[t] = p;
+    if (pass == 7) st->value[t] = value_of(p);
+  }
+  if (threadIdx.x == 0) st->done = 0;
+}
+
+// zscale / threshold from the three order statistics
+__global__ void k_norm_select_finish(SelState* st, double* info) {
+  double zscale = 1.0, thr = nan("");
+  if (st->ntargets) {
+    const double med = (st->value[0] + st->value[1]) / 2.0;  // np.median: mean of the two middle values
+    if (med > 0.0) zscale = 1.0 / sqrt(med / 100.0);
+    thr = st->value[2];
+  }
+  info[0] = zscale;
+  info[1] = thr;
+  info[2] = (double)st->count;
+  info[3] = st->error ? -1.0 : 0.0;  // completed by the scan
+}
+
+// flags -> exclusive scan -> compact positions.  flag = ratio > thr (NaN compares false).
+__global__ void __launch_bounds__(1024) k_flag_count(const double* __restrict__ ratio, int64_t b,
+                                                     const double* __restrict__ info, int* __restrict__ block_sums) {
+  const double thr = info[1];
+  const int64_t base = (int64_t)blockIdx.x * kScanTile;
+  int c = 0;
+  for (int e = threadIdx.x; e < kScanTile; e += 1024) {
+    const int64_t j = base + e;
+    if (j < b) c += ratio[j] > thr;
+  }
+  c = warp_sum(c);
+  __shared__ int sw[32];
+  if ((threadIdx.x & 31) == 0) sw[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    int v = sw[threadIdx.x];
+    v = warp_sum(v);
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = v;
+  }
+}
+
+__global__ void __launch_bounds__(1024) k_scan_block_sums(int* __restrict__ block_sums, int64_t nblocks, double* info) {
+  __shared__ int sw[32];
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int64_t base = 0; base < nblocks; base += 1024) {
+    const int64_t i = base + threadIdx.x;
+    const int v = i < nblocks ? block_sums[i] : 0;
+    int x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, x, o);
+      if ((threadIdx.x & 31) >= o) x += y;
+    }
+    if ((threadIdx.x & 31) == 31) sw[threadIdx.x >> 5] = x;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+      int w = sw[threadIdx.x];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, w, o);
+        if (threadIdx.x >= o) w += y;
+      }
+      sw[threadIdx.x] = w;
+    }
+    __syncthreads();
+    const int warp_off = (threadIdx.x >> 5) ? sw[(threadIdx.x >> 5) - 1] : 0;
+    const int incl = x + warp_off + carry;
+    if (i < nblocks) block_sums[i] = incl - v;  // exclusive
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0 && info[3] >= 0.0) info[3] = (double)carry;
+}
+
+__global__ void __launch_bounds__(1024) k_write_pos(const double* __restrict__ ratio, int64_t b,
+                                                    const double* __restrict__ info,
+                                                    const int* __restrict__ block_sums, int32_t* __restrict__ sel_pos) {
+  const double thr = info[1];
+  const int64_t base = (int64_t)blockIdx.x * kScanTile;
+  // each thread owns 2 consecutive elements
+  const int64_t j = base + 2 * (int64_t)threadIdx.x;
+  const int f0 = (j < b) && (ratio[j] > thr);
+  const int f1 = (j + 1 < b) && (ratio[j + 1] > thr);
+  int x = f0 + f1;
+  const int mine = x;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int y = __shfl_up_sync(0xffffffffu, x, o);
+    if ((threadIdx.x & 31) >= o) x += y;
+  }
+  __shared__ int sw[32];
+  if ((threadIdx.x & 31) == 31) sw[threadIdx.x >> 5] = x;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    int w = sw[threadIdx.x];
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, w, o);
+      if (threadIdx.x >= o) w += y;
+    }
+    sw[threadIdx.x] = w;
+  }
+  __syncthreads();
+  const int excl = x - mine + ((threadIdx.x >> 5) ? sw[(threadIdx.x >> 5) - 1] : 0) + block_sums[blockIdx.x];
+  if (j < b) sel_pos[j] = f0 ? excl : -1;
+  if (j + 1 < b) sel_pos[j + 1] = f1 ? excl + f0 : -1;
+}
+
+// ---- find_neighbors' region filter --------------------------------------------------------------------
+__global__ void k_round3(const double* __restrict__ ratio, const int32_t* __restrict__ sel_pos, int64_t b,
+                         double* __restrict__ rq) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= b) return;
+  double v = nan("");
+  if (sel_pos[j] >= 0) {
+    const double r = ratio[j];
+    v = isfinite(r) ? printf_round(r, 1000.0) / 1000.0 : r;  // float("%.3f" % r)
+  }
+  rq[j] = v;
+}
+
+__global__ void k_keep(const double* __restrict__ rq, const int32_t* __restrict__ sel_pos, int64_t b,
+                       const SelState* st, double sigma2_max, uint8_t* __restrict__ keep,
+                       unsigned long long* __restrict__ r_use, double* info2) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool none_finite = st->ntargets == 0;
+  const double lo = none_finite ? nan("") : st->value[0];
+  int k = 0;
+  if (j < b) {
+    if (sel_pos[j] >= 0) {
+      const double v = rq[j];
+      k = none_finite ? 1 : (isfinite(v) && v >= lo && v <= sigma2_max);
+    }
+    keep[j] = (uint8_t)k;
+  }
+  const int c = warp_sum(k);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(r_use, (unsigned long long)c);
+  if (j == 0) info2[1] = lo;
+}
+
+__global__ void k_ruse_to_double(const unsigned long long* r_use, double* info2) { info2[0] = (double)*r_use; }
+
+static int run_select(const double* vals, int64_t n, int mode, int kind, double param, const double* info,
+                      SelState* st, unsigned* hist, cudaStream_t stream) {
+  G2_CUDA(cudaMemsetAsync(st, 0, kStateBytes + kHistBytes, stream));
+  const int blocks = (int)std::min<int64_t>((n + kSelThreads * 8 - 1) / (kSelThreads * 8), (int64_t)kSMs * 4);
+  k_sel_count<<<blocks, kSelThreads, 0, stream>>>(vals, n, mode, st);
+  G2_LAUNCHED();
+  k_sel_ranks<<<1, 1, 0, stream>>>(st, kind, param, info);
+  G2_LAUNCHED();
+  for (int pass = 0; pass < 8; ++pass) {
+    k_sel_pass<<<blocks, kSelThreads, 0, stream>>>(vals, n, mode, pass, st, hist);
+    G2_LAUNCHED();
+  }
+  return 0;
+}
+
+}  // namespace g2
+
+using namespace g2;
+
+extern "C" size_t gridb200_select_ws_bytes(int64_t b) {
+  if (b <= 0) return 0;
+  const size_t nblk = (size_t)((b + kScanTile - 1) / kScanTile) + 1;
+  size_t bytes = kStateBytes + kHistBytes + ((nblk * sizeof(int) + 255) / 256) * 256 + 256;
+  bytes += (size_t)b * sizeof(double);  // rounded ratios for the kNN filter
+  return bytes;
+}
+
+extern "C" int gridb200_select(const double* ratio, int64_t b, double top_frac, int32_t* sel_pos, double* info,
+                               void* ws, size_t ws_bytes, void* stream) {
+  G2_REQUIRE(ratio && sel_pos && info && ws && b > 0, GRIDB200_EINVAL, "bad argument");
+  G2_REQUIRE(ws_bytes >= gridb200_select_ws_bytes(b), GRIDB200_EINVAL, "workspace too small: need %zu bytes",
+             gridb200_select_ws_bytes(b));
+  G2_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, GRIDB200_EINVAL, "workspace must be 256-byte aligned");
+  G2_REQUIRE(b < (1LL << 31), GRIDB200_EINVAL, "too many bins");
+  cudaStream_t st = as_stream(stream);
+  char* w = static_cast<char*>(ws);
+  SelState* state = reinterpret_cast<SelState*>(w);
+  unsigned* hist = reinterpret_cast<unsigned*>(w + kStateBytes);
+  int* block_sums = reinterpret_cast<int*>(w + kStateBytes + kHistBytes);
+  if (int e = run_select(ratio, b, /*mode=*/0, /*kind=*/0, top_frac, nullptr, state, hist, st)) return e;
+  k_norm_select_finish<<<1, 1, 0, st>>>(state, info);
+  G2_LAUNCHED();
+  const int64_t nblk = (b + kScanTile - 1) / kScanTile;
+  k_flag_count<<<(unsigned)nblk, 1024, 0, st>>>(ratio, b, info, block_sums);
+  G2_LAUNCHED();
+  k_scan_block_sums<<<1, 1024, 0, st>>>(block_sums, nblk, info);
+  G2_LAUNCHED();
+  k_write_pos<<<(unsigned)nblk, 1024, 0, st>>>(ratio, b, info, block_sums, sel_pos);
+  G2_LAUNCHED();
+  return 0;
+}
+
+extern "C" int gridb200_knn_col_filter(const double* ratio, const int32_t* sel_pos, int64_t b, double frac_r,
+                                       double sigma2_max, uint8_t* keep, const double* info, double* info2,
+                                       void* ws, size_t ws_bytes, void* stream) {
+  G2_REQUIRE(ratio && sel_pos && keep && info && info2 && ws && b > 0, GRIDB200_EINVAL, "bad argument");
+  G2_REQUIRE(ws_bytes >= gridb200_select_ws_bytes(b), GRIDB200_EINVAL, "workspace too small: need %zu bytes",
+             gridb200_select_ws_bytes(b));
+  G2_REQUIRE((reinterpret_cast<uintptr_t>(ws) & 255) == 0, GRIDB200_EINVAL, "workspace must be 256-byte aligned");
+  cudaStream_t st = as_stream(stream);
+  char* w = static_cast<char*>(ws);
+  SelState* state = reinterpret_cast<SelState*>(w);
+  unsigned* hist = reinterpret_cast<unsigned*>(w + kStateBytes);
+  const size_t nblk = (size_t)((b + kScanTile - 1) / kScanTile) + 1;
+  char* after = w + kStateBytes + kHistBytes + ((nblk * sizeof(int) + 255) / 256) * 256;
+  unsigned long long* r_use = reinterpret_cast<unsigned long long*>(after);
+  double* rq = reinterpret_cast<double*>(after + 256);
+  k_round3<<<(unsigned)((b + 255) / 256), 256, 0, st>>>(ratio, sel_pos, b, rq);
+  G2_LAUNCHED();
+  if (int e = run_select(rq, b, /*mode=*/1, /*kind=*/1, frac_r, info, state, hist, st)) return e;
+  G2_CUDA(cudaMemsetAsync(r_use, 0, sizeof(unsigned long long), st));
+  k_keep<<<(unsigned)((b + 255) / 256), 256, 0, st>>>(rq, sel_pos, b, state, sigma2_max, keep, r_use, info2);
+  G2_LAUNCHED();
+  k_ruse_to_double<<<1, 1, 0, st>>>(r_use, info2);
+  G2_LAUNCHED();
+  return 0;
+}

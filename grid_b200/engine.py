@@ -1,0 +1,304 @@
+"""Device pipeline: steps 4-6 on torch CUDA tensors through the C ABI (include/gridb200.h).
+
+torch is plumbing here (device memory, streams, torch.distributed); every arithmetic step is a libgridb200
+kernel.  Multi-GPU (``group`` given): the cohort is sharded by BINS -- every rank holds all N samples and a
+contiguous slice of the bins -- because for N << bins the only cross-rank data are N-vectors (row sums, row
+norms), the ratio vector, and one N x N partial Gram matrix; see DESIGN.md "Multi-GPU".
+"""
+
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import torch
+
+from . import _lib
+from ._lib import call, ptr
+
+
+@dataclass
+class Params:
+    """Config knobs of the three steps with the reference's in-function defaults
+    (normalize_mosdepth.py:49-51, find_neighbors.py:31-34, compute_dipcn.py:31)."""
+
+    min_depth: float = 20.0
+    max_depth: float = 100.0
+    top_frac: float = 0.1
+    zmax: float = 2.0
+    sigma2_max: float = 1000.0
+    frac_r: float = 1.0
+    num_neighbors: int = 500
+    n_nbr: int = 300
+
+    @property
+    def zclip(self) -> int:
+        return int(round(self.zmax * 100))
+
+
+@dataclass
+class NormResult:
+    n: int
+    b: int
+    colsum: torch.Tensor
+    colcnt: torch.Tensor
+    valid: torch.Tensor
+    raw_mean: torch.Tensor
+    scale_q: torch.Tensor
+    row_factor: torch.Tensor
+    mu: torch.Tensor
+    s2: torch.Tensor
+    ratio: torch.Tensor
+    sel_pos: torch.Tensor       # local compact position or -1, per local bin
+    keep: torch.Tensor
+    zscale: float
+    rw: int                     # bins selected in the whole cohort
+    rw_local: int               # ... of which on this rank
+    r_use: int
+    zq: torch.Tensor | None = None
+    zh: torch.Tensor | None = None
+    kdim: int = 0               # padded local operand width (multiple of 64)
+    norms: torch.Tensor | None = None
+    saturated: int = 0
+    extra: dict = field(default_factory=dict)
+
+
+PROFILE: dict | None = None  # bench.py sets this to {} to collect per-stage CUDA-event timings
+
+
+class _mark:
+    """Record CUDA events around a stage on the current stream when PROFILE is enabled (zero cost otherwise)."""
+
+    def __init__(self, name: str):
+        self.name = name
+
+    def __enter__(self):
+        if PROFILE is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+
+    def __exit__(self, *exc):
+        if PROFILE is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            PROFILE.setdefault(self.name, []).append((self.e0, e1))
+
+
+def profile_summary(steps: int = 0) -> dict:
+    """{stage: {"ms": mean per step, "calls": n}} from the recorded events (call after a synchronize)."""
+    out = {}
+    for name, evs in (PROFILE or {}).items():
+        tot = sum(a.elapsed_time(b) for a, b in evs)
+        out[name] = {"ms": tot / (steps or len(evs)), "calls": len(evs)}
+    return out
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ws(nbytes: int, dev) -> torch.Tensor:
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+
+
+def _all_reduce(t: torch.Tensor, group) -> None:
+    if group is not None:
+        import torch.distributed as dist
+
+        dist.all_reduce(t, group=group)
+
+
+def check_depth(depth: torch.Tensor, b: int) -> tuple[int, int]:
+    if not (depth.is_cuda and depth.dtype == torch.float32 and depth.dim() == 2 and depth.stride(1) == 1):
+        raise ValueError("depth must be a 2-D fp32 CUDA tensor with unit column stride")
+    return depth.shape[0], depth.stride(0)
+
+
+def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, want_zh: bool = True,
+              group=None) -> NormResult:
+    """Step 4 on a device-resident depth matrix [n, ld] (first ``b`` columns are bins; 0 = absent).
+
+    With ``group`` the matrix holds this rank's bin slice; ranks are ordered by bin range.
+    """
+    n, ld = check_depth(depth, b)
+    dev, st = depth.device, _stream()
+    i64 = dict(dtype=torch.int64, device=dev)
+    f64 = dict(dtype=torch.float64, device=dev)
+    colsum, colcnt = torch.empty(b, **i64), torch.empty(b, dtype=torch.int32, device=dev)
+    valid = torch.empty(b, dtype=torch.uint8, device=dev)
+    with _mark("col_raw"):
+        call("gridb200_col_raw_stats", ptr(depth), n, b, ld, ptr(colsum), ptr(colcnt), st)
+    call("gridb200_depth_filter", ptr(colsum), ptr(colcnt), b, float(p.min_depth), float(p.max_depth), ptr(valid), st)
+
+    rowsum, rowcnt = torch.empty(n, **i64), torch.empty(n, dtype=torch.int32, device=dev)
+    with _mark("row_stats"):
+        call("gridb200_row_stats", ptr(depth), n, b, ld, ptr(valid), ptr(rowsum), ptr(rowcnt), st)
+    _all_reduce(rowsum, group)
+    _all_reduce(rowcnt, group)
+    raw_mean, scale_q, row_factor = torch.empty(n, **f64), torch.empty(n, **f64), torch.empty(n, **f64)
+    call("gridb200_row_scales", ptr(rowsum), ptr(rowcnt), n, ptr(raw_mean), ptr(scale_q), ptr(row_factor), st)
+
+    sd, sd2 = torch.empty(b, **f64), torch.empty(b, **f64)
+    ws = _ws(_lib.load().gridb200_col_norm_stats_ws_bytes(n, b), dev)
+    with _mark("col_norm"):
+        call("gridb200_col_norm_stats", ptr(depth), n, b, ld, ptr(valid), ptr(row_factor), ptr(sd), ptr(sd2), ptr(ws),
+             ws.numel(), st)
+    mu, s2, ratio = torch.empty(b, **f64), torch.empty(b, **f64), torch.empty(b, **f64)
+    # samples without any valid bin are dropped by the reference before normalising (filter_empty_samples,
+    # normalize_mosdepth.py:576-600); they contribute nothing here either, only N in the ddof=1 divisor changes
+    n_eff = int((rowcnt > 0).sum())
+    call("gridb200_col_finalize", ptr(sd), ptr(sd2), ptr(colcnt), ptr(valid), b, n_eff, ptr(mu), ptr(s2), ptr(ratio), st)
+
+    # selection runs on the whole cohort's ratio vector (every rank redundantly)
+    if group is not None:
+        import torch.distributed as dist
+
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+        sizes = torch.zeros(world, **i64)
+        sizes[rank] = b
+        dist.all_reduce(sizes, group=group)
+        sizes = sizes.tolist()
+        bmax = max(sizes)
+        mine = torch.full((bmax,), float("nan"), **f64)
+        mine[:b] = ratio
+        gathered = torch.empty(world * bmax, **f64)
+        dist.all_gather_into_tensor(gathered, mine, group=group)
+        ratio_all = torch.cat([gathered[r * bmax:r * bmax + sizes[r]] for r in range(world)])
+        lo = sum(sizes[:rank])
+    else:
+        ratio_all, lo = ratio, 0
+    ball = ratio_all.numel()
+    sel_all = torch.empty(ball, dtype=torch.int32, device=dev)
+    keep_all = torch.empty(ball, dtype=torch.uint8, device=dev)
+    info, info2 = torch.empty(4, **f64), torch.empty(2, **f64)
+    ws2 = _ws(_lib.load().gridb200_select_ws_bytes(ball), dev)
+    with _mark("select"):
+        call("gridb200_select", ptr(ratio_all), ball, float(p.top_frac), ptr(sel_all), ptr(info), ptr(ws2), ws2.numel(), st)
+        call("gridb200_knn_col_filter", ptr(ratio_all), ptr(sel_all), ball, float(p.frac_r), float(p.sigma2_max),
+             ptr(keep_all), ptr(info), ptr(info2), ptr(ws2), ws2.numel(), st)
+    if group is not None:
+        mine_sel = sel_all[lo:lo + b]
+        before = (sel_all[:lo] >= 0).sum().to(torch.int32)
+        sel_pos = torch.where(mine_sel >= 0, mine_sel - before, mine_sel).contiguous()
+        keep = keep_all[lo:lo + b].contiguous()
+        rw_local_t = (mine_sel >= 0).sum()
+    else:
+        sel_pos, keep, rw_local_t = sel_all, keep_all, None
+    host = torch.cat([info, info2, (rw_local_t.to(torch.float64).reshape(1) if rw_local_t is not None else info[3:4])]).cpu()
+    zscale, rw, r_use, rw_local = float(host[0]), int(host[3]), int(host[4]), int(host[6])
+    if rw < 0:
+        raise IndexError("list index out of range")  # what the reference's sorted_ratios[int(top_frac*len)] raises
+    res = NormResult(n=n, b=b, colsum=colsum, colcnt=colcnt, valid=valid, raw_mean=raw_mean, scale_q=scale_q,
+                     row_factor=row_factor, mu=mu, s2=s2, ratio=ratio, sel_pos=sel_pos, keep=keep, zscale=zscale,
+                     rw=rw, rw_local=rw_local, r_use=r_use)
+    res.extra.update(thr=float(host[1]), n_finite=int(host[2]), sigma2_min=float(host[5]), bin_offset=lo,
+                     rowcnt=rowcnt, rowsum=rowsum, n_eff=n_eff)
+    if rw_local == 0 or not (want_zq or want_zh):
+        return res
+
+    sat = torch.zeros(1, dtype=torch.int64, device=dev)
+    zq = zh = norms = None
+    ldq = ldh = 0
+    if want_zq:
+        ldq = (rw_local + 7) // 8 * 8
+        zq = torch.empty((n, ldq), dtype=torch.int16, device=dev)
+        if ldq > rw_local:
+            zq[:, rw_local:] = -32768
+    if want_zh:
+        ldh = (rw_local + 63) // 64 * 64
+        zh = torch.empty((n, ldh), dtype=torch.float16, device=dev)
+        if ldh > rw_local:
+            zh[:, rw_local:] = 0
+        norms = torch.zeros(n, **i64)
+    with _mark("transform"):
+        call("gridb200_transform", ptr(depth), n, b, ld, ptr(row_factor), ptr(mu), ptr(sel_pos), ptr(keep), ptr(info),
+             p.zclip, ptr(zq), ldq, ptr(zh), ldh, ptr(norms), ptr(sat), st)
+    if want_zh:
+        _all_reduce(norms, group)
+    res.zq, res.zh, res.kdim, res.norms = zq, zh, ldh, norms
+    res.extra["sat"] = sat
+    return res
+
+
+def prepare_from_zq(zq: torch.Tensor, rw: int, keep: torch.Tensor | None, zclip: int):
+    """Operand + exact norms from a hundredths matrix read back from a step-4 file (find_neighbors.py:57-65)."""
+    n, ldq = zq.shape[0], zq.stride(0)
+    ldh = max(64, (rw + 63) // 64 * 64)
+    zh = torch.empty((n, ldh), dtype=torch.float16, device=zq.device)
+    norms = torch.empty(n, dtype=torch.int64, device=zq.device)
+    call("gridb200_knn_prepare", ptr(zq), n, rw, ldq, ptr(keep), zclip, ptr(zh), ldh, ptr(norms), _stream())
+    return zh, ldh, norms
+
+
+def knn(zh: torch.Tensor, kdim: int, norms: torch.Tensor, k: int, vmax: int, impl: int = 0, group=None,
+        max_block_bytes: int = 2 << 30):
+    """Exact k nearest neighbours of every row among all rows (self excluded): (idx[n,k] int32, d2[n,k] int64).
+
+    d2 is in units of 1e-4 (hundredths squared).  Rows with fewer than k candidates are padded with -1.
+    Bin-sharded multi-GPU: each rank contributes the Gram partial of its bins; partials are all-reduced.
+    """
+    n, ld = zh.shape[0], zh.stride(0)
+    dev, st = zh.device, _stream()
+    k = max(1, min(k, n - 1)) if n > 1 else 1
+    best_d2 = torch.empty((n, k), dtype=torch.int64, device=dev)
+    best_idx = torch.empty((n, k), dtype=torch.int32, device=dev)
+    call("gridb200_topk_init", ptr(best_d2), ptr(best_idx), n, k, st)
+    ldd = (n + 1) // 2 * 2
+    qb = max(1, min(n, max_block_bytes // (8 * ldd)))
+    rchunk = 8192 - k
+    for q0 in range(0, n, qb):
+        nq = min(qb, n - q0)
+        dot = torch.empty((nq, ldd), dtype=torch.int64, device=dev)
+        with _mark("gram"):
+            call("gridb200_gram", zh.data_ptr() + q0 * ld * 2, nq, ld, ptr(zh), n, ld, kdim, vmax, ptr(dot), ldd, 0,
+                 impl, st)
+        _all_reduce(dot, group)
+        with _mark("topk"):
+            for r0 in range(0, n, rchunk):
+                nr = min(rchunk, n - r0)
+                call("gridb200_topk_merge", dot.data_ptr() + r0 * 8, ldd, nq, nr, norms.data_ptr() + q0 * 8,
+                     norms.data_ptr() + r0 * 8, q0, r0, k, best_d2.data_ptr() + q0 * k * 8,
+                     best_idx.data_ptr() + q0 * k * 4, st)
+    return best_idx, best_d2
+
+
+def dipcn(counts: torch.Tensor, has_count: torch.Tensor, scale_q: torch.Tensor, nbr_idx: torch.Tensor, n_nbr: int):
+    """Step 6 on device arrays: counts[n,g] int32, has_count[n] uint8, scale_q[n] f64, nbr_idx[n,k] int32 -> out[n,g] f64."""
+    n, g = counts.shape
+    dev = counts.device
+    out = torch.empty((n, g), dtype=torch.float64, device=dev)
+    t_ws = torch.empty(n * g, dtype=torch.float64, device=dev)
+    with _mark("dipcn"):
+        call("gridb200_dipcn", ptr(counts), n, g, counts.stride(0), ptr(has_count), ptr(scale_q), ptr(nbr_idx),
+             nbr_idx.shape[0], nbr_idx.shape[1], 0, int(n_nbr), ptr(out), g, ptr(t_ws), _stream())
+    return out
+
+
+def synth_depth(seed: int, n: int, b: int, row0: int = 0, col0: int = 0, device="cuda", ld: int | None = None):
+    """Device-generated synthetic depth matrix, bit-identical to grid_b200.synth.depth_matrix."""
+    from . import synth
+
+    ld = ld or (b + 3) // 4 * 4
+    c, rc = synth.row_params(seed, n, row0)
+    bc, rb = synth.col_params(seed, b, col0)
+    dev = torch.device(device)
+    tc, trc, tb, trb = (torch.from_numpy(a).to(dev) for a in (c, rc, bc, rb))
+    depth = torch.empty((n, ld), dtype=torch.float32, device=dev)
+    if ld > b:
+        depth[:, b:] = 0
+    call("gridb200_synth_depth", seed, n, b, row0, col0, ptr(tc), ptr(trc), ptr(tb), ptr(trb), ptr(depth), ld, _stream())
+    return depth
+
+
+def run_chain(depth: torch.Tensor, b: int, counts: torch.Tensor, p: Params, impl: int = 0, group=None):
+    """normalize -> kNN -> dipCN with everything resident on the device (the benchmarked path)."""
+    res = normalize(depth, b, p, want_zq=False, want_zh=True, group=group)
+    if res.rw == 0:
+        raise ValueError("no bins selected")
+    if res.zh is None:  # this rank's slice holds no selected bin: contribute a zero partial
+        res.zh = torch.zeros((res.n, 64), dtype=torch.float16, device=depth.device)
+        res.kdim, res.norms = 64, torch.zeros(res.n, dtype=torch.int64, device=depth.device)
+        _all_reduce(res.norms, group)
+    idx, d2 = knn(res.zh, res.kdim, res.norms, p.num_neighbors, p.zclip, impl=impl, group=group)
+    has = torch.ones(res.n, dtype=torch.uint8, device=depth.device)
+    cn = dipcn(counts, has, res.scale_q, idx, p.n_nbr)
+    return res, idx, d2, cn

@@ -1,0 +1,119 @@
+"""Step 4, drop-in for grid/utils/normalize_mosdepth.py: same entry point, config keys, defaults, output file.
+
+Host work: find and inflate the per-sample mosdepth files, apply the line filters, pack the fp32 depth matrix.
+Device work (libgridb200): population-mean depth filter, per-sample means, per-bin statistics, median rescale,
+variance selection, transform and printf-exact quantisation.
+"""
+from __future__ import annotations
+
+import gzip
+import sys
+from concurrent.futures import ThreadPoolExecutor
+from pathlib import Path
+
+import numpy as np
+
+from .. import io as gio
+from ..io import (find_bed_gz_for_individual, load_repeat_mask, map_mosdepth_files_to_samples,  # noqa: F401  (reference names)
+                  norm_chrom)
+from .utils import get_samples, log, progress_bar, setup_output_file
+
+
+def pack_depth_matrix(individuals: dict, mosdepth_dir, chrom, start, end, excluded, threads: int = 1, console=None):
+    """Parse every sample once and pack depth[N, B] (fp32, 0 = absent) over the union of bins seen.
+
+    Rows follow sorted sample ids, columns sorted (start, end) -- the order build_matrix_from_regions uses
+    (normalize_mosdepth.py:379-416).  Unreadable files contribute nothing (:286-287, :353-355).
+    """
+    ids = sorted(individuals)
+
+    def one(sid):
+        path = find_bed_gz_for_individual(sid, mosdepth_dir)
+        if not path.exists():
+            return None
+        try:
+            with gzip.open(path, "rb") as fh:
+                return gio.parse_regions_text(fh.read(), chrom, start, end, excluded)
+        except Exception:
+            return None
+
+    with progress_bar(console, total=len(ids), description="Extracting per-sample regions...") as (progress, task):
+        with ThreadPoolExecutor(max_workers=max(1, threads)) as ex:
+            parsed = []
+            for res in ex.map(one, ids):
+                parsed.append(res)
+                progress.update(task, advance=1)
+    keys = [np.stack([p[0], p[1]], axis=1) for p in parsed if p is not None and len(p[0])]
+    if not keys:
+        return ids, np.zeros((0, 2), dtype=np.int64), np.zeros((len(ids), 0), dtype=np.float32)
+    bins = np.unique(np.concatenate(keys), axis=0)  # sorted by (start, end)
+    code = {(int(s), int(e)): j for j, (s, e) in enumerate(bins)}
+    depth = np.zeros((len(ids), (len(bins) + 3) // 4 * 4), dtype=np.float32)
+    for i, p in enumerate(parsed):
+        if p is None:
+            continue
+        for s, e, h in zip(p[0].tolist(), p[1].tolist(), p[2].tolist()):
+            depth[i, code[(s, e)]] = h / 100.0  # later duplicates overwrite: last wins
+    return ids, bins, depth
+
+
+def normalize_mosdepth(config, console):
+    """Same contract as the reference's normalize_mosdepth(config, console) (normalize_mosdepth.py:23-145)."""
+    try:
+        samples = get_samples(config["samples_file"])
+        chrom = config.get("chrom", None)
+        start = config.get("start_bp", None)
+        end = config.get("end_bp", None)
+        threads = config.get("threads", 1)
+        ncfg = config["mosdepth"]["normalize"]
+        prefix = config.get("mosdepth", {}).get("normalize", {}).get("output_file_prefix", None)
+        ftype = config.get("output_file_type", "tsv")
+        output_file = Path(f"{config.get('output_dir', '.')}/{prefix}.{ftype}.gz")
+        remove_intermediate = config.get("mosdepth", {}).get("remove_intermediate", False)
+        mosdepth_dir = config.get("mosdepth", {}).get("work_dir", None)
+        min_depth = ncfg.get("min_depth", 20)
+        max_depth = ncfg.get("max_depth", 100)
+        top_frac = ncfg.get("top_frac", 0.1)
+        repeat_mask = ncfg.get("repeat_mask_file", None)
+    except Exception as e:
+        log(console, f"[red]Config error: {e}[/red]")
+        return
+
+    output_path = setup_output_file(output_file, chrom, start, end)
+    individuals = map_mosdepth_files_to_samples(mosdepth_dir, samples)
+    if not individuals:
+        log(console, f"✗ No mosdepth files found in {mosdepth_dir}", style="danger")
+        sys.exit(1)
+    excluded = load_repeat_mask(repeat_mask)
+
+    import torch
+
+    from .. import engine
+
+    ids, bins, depth = pack_depth_matrix(individuals, mosdepth_dir, chrom, start, end, excluded, threads, console)
+    b = len(bins)
+    if b == 0:
+        log(console, "No valid samples with regions found.", style="danger")
+        sys.exit(1)
+    p = engine.Params(min_depth=min_depth, max_depth=max_depth, top_frac=top_frac)
+    res = engine.normalize(torch.from_numpy(depth).cuda(), b, p, want_zq=True, want_zh=False)
+    rows = np.nonzero(res.extra["rowcnt"].cpu().numpy() > 0)[0]  # filter_empty_samples (:576-600)
+    if len(rows) < len(ids):
+        log(console, f"Removed {len(ids) - len(rows)} samples with 0 regions", style="warning")
+    if len(rows) == 0:
+        log(console, "No valid samples with regions found.", style="danger")
+        sys.exit(1)
+    sel = np.nonzero(res.sel_pos.cpu().numpy() >= 0)[0]
+    zq = res.zq.cpu().numpy()[rows][:, : res.rw] if res.zq is not None else np.zeros((len(rows), 0), dtype=np.int16)
+    gio.write_normalized_output(output_path, [ids[i] for i in rows], zq, res.mu.cpu().numpy()[sel],
+                                res.ratio.cpu().numpy()[sel], res.raw_mean.cpu().numpy()[rows])
+    log(console, f"Mosdepth normalization complete. Results written to {output_path}", style="success")
+
+    if remove_intermediate:  # mosdepth.remove_intermediate_files(dir, console, include_region_bed_gz=True), mosdepth.py:300-326
+        suffixes = ("mosdepth.global.dist.txt", "mosdepth.region.dist.txt", "regions.bed.gz.csi", "regions.bed.gz")
+        for f in Path(mosdepth_dir).glob("*"):
+            if f.name.endswith(suffixes):
+                try:
+                    f.unlink()
+                except Exception as e:
+                    log(console, f"Failed to remove intermediate file {f}: {e}", style="warning")

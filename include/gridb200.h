@@ -1,0 +1,189 @@
+/*
+ * gridb200.h -- C ABI of libgridb200.so: the B200 (sm_100a) implementation of GRiD's depth-inference
+ * hot path (reference steps 4-6: normalize_mosdepth -> find_neighbors -> compute_dipcn).
+ *
+ * The reference (caterer-z-t/GRiD) is pure Python and has no FFI; the boundary this library replaces is the
+ * body of three Python step functions.  Each entry point below cites the reference lines whose arithmetic
+ * it takes over (paths relative to /root/reference/grid/utils/).  The Python host in grid_b200/ keeps the
+ * reference's function names, config keys and file formats and calls these through ctypes; see
+ * INTEGRATION.md for the binding a reference maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative GRIDB200_E* code on failure; the message is available
+ *     from gridb200_last_error() (thread-local, library-owned, valid until the next failing call).
+ *   - all pointers are DEVICE pointers unless the name ends in _host; the caller owns every buffer; the
+ *     library allocates nothing on the device; scratch space is passed in as `ws` (size from *_ws_bytes).
+ *   - `stream` is a cudaStream_t passed as void*; all work is asynchronous on that stream.
+ *   - matrices are row-major with an explicit leading dimension in ELEMENTS; rows are samples.
+ *   - depth matrix: fp32, 0.0f = bin absent for that sample (the reference keeps only depth > 0,
+ *     normalize_mosdepth.py:274-278), values are multiples of 0.01 below 41943.04 (mosdepth prints %.2f).
+ *   - "hundredths": integer n standing for the decimal n/100, i.e. the value a %.2f text field carries.
+ *   - no C++ exception crosses this boundary.
+ */
+#ifndef GRIDB200_H
+#define GRIDB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define GRIDB200_API __attribute__((visibility("default")))
+#else
+#define GRIDB200_API
+#endif
+
+#define GRIDB200_OK 0
+#define GRIDB200_EINVAL (-1)   /* bad argument (null pointer, misaligned leading dimension, size out of range) */
+#define GRIDB200_ECUDA (-2)    /* CUDA runtime / driver error */
+#define GRIDB200_EDOMAIN (-3)  /* input outside the documented exact domain */
+#define GRIDB200_ENODEV (-4)   /* no sm_100 device / driver entry point unavailable */
+
+#define GRIDB200_ZQ_NA ((int16_t)-32768)       /* "NA" cell in a hundredths matrix */
+#define GRIDB200_ZQ_NEG_ZERO ((int16_t)-32767) /* negative value that prints as "-0.00"; numerically 0 */
+#define GRIDB200_ZQ_LIMIT 32766                /* |hundredths| saturates here (counted in *sat) */
+
+GRIDB200_API const char* gridb200_last_error(void);
+GRIDB200_API const char* gridb200_version(void);
+/* Number of kernels this library has launched in the calling process (bench.py's gpu_launches). */
+GRIDB200_API uint64_t gridb200_launch_count(void);
+
+/* ------------------------------------------------------------------ step 4: normalize_mosdepth ----------- */
+
+/* Per-bin raw sums over the local rows: colsum[j] = sum_i round(100*depth[i,j]), colcnt[j] = #{i: depth>0}.
+ * Replaces pass 1, compute_population_mean_depths (normalize_mosdepth.py:218-301) once the text is parsed.
+ * Buffers are overwritten.  Row-sharded multi-GPU: all-reduce(sum) both outputs afterwards. */
+GRIDB200_API int gridb200_col_raw_stats(const float* depth, int64_t n, int64_t b, int64_t ld,
+                           int64_t* colsum, int32_t* colcnt, void* stream);
+
+/* valid[j] = 1 iff colcnt>0 and min_depth <= colsum/(100*colcnt) <= max_depth (normalize_mosdepth.py:81-83). */
+GRIDB200_API int gridb200_depth_filter(const int64_t* colsum, const int32_t* colcnt, int64_t b,
+                          double min_depth, double max_depth, uint8_t* valid, void* stream);
+
+/* Per-sample sums over the valid bins: rowsum[i] = sum_j round(100*depth[i,j]), rowcnt[i] = #present.
+ * This is np.nanmean(mat, axis=1) (normalize_mosdepth.py:120 and :440) in exact integer form.
+ * Column-sharded multi-GPU: all-reduce(sum) both outputs afterwards. */
+GRIDB200_API int gridb200_row_stats(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                       int64_t* rowsum, int32_t* rowcnt, void* stream);
+
+/* raw_mean[i] = rowsum/(100*rowcnt) (the "scale" column, NaN for an empty row); scale_q[i] = that value
+ * after the %.2f text hand-off (normalize_mosdepth.py:552-554 -> find_neighbors.py:111); row_factor[i] =
+ * rowcnt/rowsum, so that depth_ij/rowmean_i == hundredths_ij * row_factor[i] (normalize_mosdepth.py:440-442).
+ * Any output may be null. */
+GRIDB200_API int gridb200_row_scales(const int64_t* rowsum, const int32_t* rowcnt, int64_t n,
+                        double* raw_mean, double* scale_q, double* row_factor, void* stream);
+
+/* Per-bin sums of the row-normalised matrix y = depth/rowmean, shifted by 1: sd[j] = sum_i (y-1),
+ * sd2[j] = sum_i (y-1)^2 over present cells of valid bins (normalize_mosdepth.py:445-446 in one pass).
+ * ws: gridb200_col_norm_stats_ws_bytes(n,b).  Row-sharded multi-GPU: all-reduce(sum) sd and sd2. */
+GRIDB200_API size_t gridb200_col_norm_stats_ws_bytes(int64_t n, int64_t b);
+GRIDB200_API int gridb200_col_norm_stats(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                            const double* row_factor,
+                            double* sd, double* sd2, void* ws, size_t ws_bytes, void* stream);
+
+/* mu = 1 + sd/cnt; s2 = (sd2 - sd^2/cnt)/(n_total-1); ratio = 100*s2/mu where mu > 0 else NaN; NaN for
+ * invalid bins (normalize_mosdepth.py:445-451).  n_total = number of sample rows in the whole cohort. */
+GRIDB200_API int gridb200_col_finalize(const double* sd, const double* sd2, const int32_t* colcnt, const uint8_t* valid,
+                          int64_t b, int64_t n_total, double* mu, double* s2, double* ratio, void* stream);
+
+/* Median rescale and variance selection on the FULL ratio vector (normalize_mosdepth.py:460-468, :479-499):
+ *   zscale = 1/sqrt(median(finite ratio)/100) if that median > 0 else 1
+ *   thr = sorted(finite)[int(top_frac*count)]; sel_pos[j] = rank of j among {ratio > thr} else -1
+ * info (device, 4 doubles): [0]=zscale [1]=thr [2]=count of finite ratios [3]=number selected (Rw).
+ * status GRIDB200_EDOMAIN is reported through info[3] = -1 when int(top_frac*count) == count (the reference
+ * raises IndexError there).  ws: gridb200_select_ws_bytes(b). */
+GRIDB200_API size_t gridb200_select_ws_bytes(int64_t b);
+GRIDB200_API int gridb200_select(const double* ratio, int64_t b, double top_frac, int32_t* sel_pos, double* info,
+                    void* ws, size_t ws_bytes, void* stream);
+
+/* find_neighbors' region filter on the %.3f-rounded ratios of the selected bins (find_neighbors.py:128-175):
+ * keep[j] = 1 iff sel_pos[j] >= 0 and finite(rq) and rq >= sigma2_min and rq <= sigma2_max, where
+ * rq = float("%.3f" % ratio[j]) and sigma2_min = sorted(finite rq)[min(int(Rw*(1-frac_r)), n_finite-1)];
+ * no finite rq -> every selected bin is kept.  `info` is gridb200_select's output (Rw is read on the device);
+ * info2 (device, 2 doubles): [0]=R_use [1]=sigma2_min.  ws: gridb200_select_ws_bytes(b). */
+GRIDB200_API int gridb200_knn_col_filter(const double* ratio, const int32_t* sel_pos, int64_t b, double frac_r,
+                            double sigma2_max, uint8_t* keep, const double* info, double* info2,
+                            void* ws, size_t ws_bytes, void* stream);
+
+/* The transform pass (normalize_mosdepth.py:454-470 + the %.2f hand-off :552-554 + find_neighbors.py:57-58):
+ *   z = ((depth/rowmean) - mu_j) / sqrt(mu_j) * zscale          fp64, then printf-exact rounding to hundredths
+ *   zq[i, sel_pos[j]] = hundredths(z)  (GRIDB200_ZQ_NA where absent, GRIDB200_ZQ_NEG_ZERO for "-0.00";
+ *                                       saturates at +-GRIDB200_ZQ_LIMIT, counted in *sat)
+ *   zh[i, sel_pos[j]] = fp16(clip(hundredths(z), +-zclip))  with NA -> 0 and 0 where keep[j] == 0
+ *   norms[i] += sum_j zh[i,j]^2 (exact int64; caller zeroes it)
+ * zq and zh are optional (either may be null); ldq/ldh in elements; pad columns [Rw, ldh) of zh must be
+ * zeroed by the caller.  `info` is gridb200_select's output (zscale is read on the device). */
+GRIDB200_API int gridb200_transform(const float* depth, int64_t n, int64_t b, int64_t ld,
+                       const double* row_factor, const double* mu,
+                       const int32_t* sel_pos, const uint8_t* keep, const double* info, int32_t zclip,
+                       int16_t* zq, int64_t ldq, void* zh, int64_t ldh, int64_t* norms,
+                       unsigned long long* sat, void* stream);
+
+/* ------------------------------------------------------------------ step 5: find_neighbors --------------- */
+
+/* zq (as read back from a step-4 file) -> tensor-core operand: clip to +-zclip, NA -> 0, zero dropped bins,
+ * fp16; norms[i] = exact sum of squares (overwritten) (find_neighbors.py:57-65). keep may be null. */
+GRIDB200_API int gridb200_knn_prepare(const int16_t* zq, int64_t n, int64_t rw, int64_t ldq, const uint8_t* keep,
+                         int32_t zclip, void* zh, int64_t ldh, int64_t* norms, void* stream);
+
+/* Exact Gram block: dot[i,j] (+)= sum_k q[i,k]*r[j,k] over kdim bins, operands fp16 holding integers with
+ * |v| <= vmax (<= 2048).  This is the -2*X.Y^T term of sklearn's EuclideanArgKmin64, which the reference
+ * reaches through NearestNeighbors.kneighbors (find_neighbors.py:207-213).
+ *   impl 0: tcgen05 tensor cores + TMA (sm_100a); fp32 TMEM accumulation over chunks short enough to stay
+ *           below 2^24 (exact), drained into int64.        impl 1: plain SIMT integer kernel (cross-check).
+ * ldq/ldr multiples of 8 elements, base pointers 16-byte aligned, kdim a multiple of 64 (zero padded).
+ * accumulate != 0 adds to dot (bin-sharded multi-GPU and K-blocked calls). */
+GRIDB200_API int gridb200_gram(const void* zq_f16, int64_t nq, int64_t ldq, const void* zr_f16, int64_t nr, int64_t ldr,
+                  int64_t kdim, int32_t vmax, int64_t* dot, int64_t ldd, int accumulate, int impl,
+                  void* stream);
+
+/* d2[i,j] = normq[i] + normr[j] - 2*dot[i,j]; the row's own sample (q_gid0+i == r_gid0+j) is skipped
+ * (find_neighbors.py:218-219); merge into the running k-best lists, ascending by (d2, global index) -- the
+ * order sklearn's heap + sort yields when no two candidates tie, lower index first among exact ties.
+ * best_d2 [nq,k] / best_idx [nq,k] must be initialised with gridb200_topk_init before the first block.
+ * nr + k <= 8192 per call. */
+GRIDB200_API int gridb200_topk_init(int64_t* best_d2, int32_t* best_idx, int64_t nq, int32_t k, void* stream);
+GRIDB200_API int gridb200_topk_merge(const int64_t* dot, int64_t ldd, int64_t nq, int64_t nr,
+                        const int64_t* normq, const int64_t* normr, int64_t q_gid0, int64_t r_gid0,
+                        int32_t k, int64_t* best_d2, int32_t* best_idx, void* stream);
+
+/* ------------------------------------------------------------------ step 6: compute_dipcn ---------------- */
+
+/* out[i,g] = (counts[q0+i,g]/scale[q0+i]) / mean_{first n_nbr neighbours j with has_count[j]} counts[j,g]/scale[j]
+ * (compute_dipcn.py:62-88); NaN where the reference omits the sample (no count / no contributing neighbour).
+ * counts [n_all, g] int32 (read counts are integers and stay so), scale_q [n_all] = the %.2f-rounded scales,
+ * nbr_idx [nq,k] global indices (-1 = empty slot).  t_ws: n_all*g doubles of scratch. */
+GRIDB200_API int gridb200_dipcn(const int32_t* counts, int64_t n_all, int64_t g, int64_t ldc, const uint8_t* has_count,
+                   const double* scale_q, const int32_t* nbr_idx, int64_t nq, int32_t k, int64_t q_gid0,
+                   int32_t n_nbr, double* out, int64_t ldo, double* t_ws, void* stream);
+
+/* ------------------------------------------------------------------ synthetic cohorts (bench / tests) ---- */
+
+/* Device twin of grid_b200/synth.py:depth_hundredths -- fills depth[n, b] (fp32, ld) for global rows
+ * row0.. and bins col0..; c/rc are per-row, bcol/rb per-bin parameter vectors (computed by the host). */
+GRIDB200_API int gridb200_synth_depth(uint64_t seed, int64_t n, int64_t b, int64_t row0, int64_t col0,
+                         const double* c, const double* rc, const double* bcol, const double* rb,
+                         float* depth, int64_t ld, void* stream);
+
+/* ------------------------------------------------------------------ ingest (mosdepth text) --------------- */
+
+/* Parse one sample's decompressed `chrom\tstart\tend\tdepth\n` text on the device and scatter the depths
+ * into row `row` of the packed matrix (the line filters of normalize_mosdepth.py:262-285/:321-352):
+ * chromosome PREFIX match (chrom_len = 0 matches all), >= 4 tab fields, depth > 0, bin touching the closed
+ * window [win_lo, win_hi] (win_lo < 0: no window), not masked (mask_bits: bit kb set = masked, may be null).
+ * Column = (start - bin0) / 1000 for bins of exactly 1000 bp aligned to bin0; other lines are counted in
+ * stats[1] (irregular) and skipped.  stats (device, 4 x int64): [0]=kept [1]=irregular [2]=lines [3]=masked.
+ * ws: 8 bytes per text byte / 16 + 64 KiB. */
+GRIDB200_API size_t gridb200_ingest_ws_bytes(int64_t nbytes);
+GRIDB200_API int gridb200_ingest_text(const char* text, int64_t nbytes, const char* chrom_prefix, int32_t chrom_len,
+                         int64_t win_lo, int64_t win_hi, const uint32_t* mask_bits, int64_t mask_kb,
+                         int64_t bin0, int64_t b, float* depth_row, int64_t* stats,
+                         void* ws, size_t ws_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GRIDB200_H */

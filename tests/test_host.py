@@ -1,0 +1,105 @@
+"""Host-side logic (formats, line filters, drop-in installation) -- CPU only."""
+import gzip
+import sys
+import types
+
+import numpy as np
+import pytest
+
+from grid_b200 import io as gio
+from grid_b200 import synth
+from oracle import grid_oracle as O
+
+
+def test_synth_is_deterministic_and_sane():
+    a = synth.depth_hundredths(5, 40, 300)
+    assert (a == synth.depth_hundredths(5, 40, 300)).all()
+    assert (a[10:20, 100:200] == synth.depth_hundredths(5, 10, 100, row0=10, col0=100)).all()  # counter-based
+    assert 0.0003 < (a == 0).mean() < 0.003
+    m = a[a > 0] / 100
+    assert 15 < m.mean() < 60
+    assert synth.read_counts(5, 10, [42599, 1000]).shape == (10, 2)
+
+
+def test_parse_regions_matches_oracle_filters(tmp_path):
+    lines = ["chr6\t1000\t2000\t25.50", "chr6\t2000\t3000\t0.00", "chr60\t1000\t2000\t7.25", "chr5\t1000\t2000\t9.00",
+             "chr6\t9000\t10000\t31.10", "chr6\t3000\t4000\t12.34", "short\tline", "chr6\t3000\t4000\t13.37", ""]
+    p = tmp_path / "S.regions.bed.gz"
+    with gzip.open(p, "wt") as f:
+        f.write("\n".join(lines))
+    for chrom, lo, hi, mask in (("chr6", 1000, 4000, {}), ("6", 1000, 4000, {"chr6": {3}}), (None, None, None, {}),
+                                ("chr6", None, None, {"chr60": {1, 2}})):
+        want = O.scan_regions(p, chrom, lo, hi, mask)
+        s, e, h = gio.parse_regions_text(gzip.open(p, "rb").read(), chrom, lo, hi, mask)
+        assert list(zip(s.tolist(), e.tolist(), (h / 100).tolist())) == want
+
+
+def test_step4_file_roundtrip_and_codes(tmp_path):
+    zq = np.array([[0, -1, 250, gio.ZQ_NA, gio.ZQ_NEG_ZERO], [-200, 199, 1, -100, 32766]], dtype=np.int16)
+    p = tmp_path / "n.tsv.gz"
+    gio.write_normalized_output(p, ["A", "B"], zq, np.array([1.0, 2.0, 0.9994, np.nan, 1.5]),
+                                np.array([0.5, 1000.5, np.nan, 1.0, 2.0]), np.array([30.004, 28.005]))
+    txt = gzip.open(p, "rt").read().splitlines()
+    assert txt[0] == "2\t5\t1.000\t2.000\t0.999\tNA\t1.500"
+    assert txt[1] == "2\t5\t0.500\t1000.500\tNA\t1.000\t2.000"
+    assert txt[2] == "A\t30.00\t0.00\t-0.01\t2.50\tNA\t-0.00"
+    assert txt[3] == "B\t28.00\t-2.00\t1.99\t0.01\t-1.00\t327.66"
+    ids, ratios, back, scales = gio.read_normalized_data(p)
+    assert ids == ["A", "B"] and scales.tolist() == [30.0, 28.0]
+    want = zq.copy()
+    want[0, 4] = 0
+    assert (back == want).all()
+    # the oracle's reader sees the same numbers
+    oid, oratio, oz, _ = O.read_normalized(p)
+    np.testing.assert_array_equal(np.isnan(oratio), np.isnan(ratios))
+    np.testing.assert_array_equal(np.where(np.isnan(oz), gio.ZQ_NA, np.rint(oz * 100)), want)
+
+
+def test_neighbor_file_matches_oracle_writer(tmp_path):
+    ids = ["S1", "S2", "S3"]
+    scales = np.array([30.0, 28.004, 31.999])
+    idx = np.array([[1, 2], [0, 2], [0, -1]], dtype=np.int32)
+    d2 = np.array([[1234500, 99999999], [1234500, 5], [7, 0]], dtype=np.int64)
+    gio.save_neighbors(tmp_path / "a.gz", ids, scales, idx, d2, 38)
+    O.save_neighbors(tmp_path / "b.gz", ids, dict(zip(ids, scales)), [[1, 2], [0, 2], [0]],
+                     [[123.45, 9999.9999], [123.45, 0.0005], [0.0007]], 38)
+    assert gzip.open(tmp_path / "a.gz", "rt").read() == gzip.open(tmp_path / "b.gz", "rt").read()
+    nid, nsc, lists = gio.load_neighbors(tmp_path / "a.gz")
+    assert nid == ids and lists[2] == [("S1", 30.0)]
+
+
+def test_install_rebinds_reference_steps(monkeypatch):
+    pkg = types.ModuleType("grid")
+    utils = types.ModuleType("grid.utils")
+    mods = {"grid": pkg, "grid.utils": utils}
+    for name, fn in (("normalize_mosdepth", "normalize_mosdepth"), ("find_neighbors", "find_neighbors"),
+                     ("compute_dipcn", "compute_diploid_genotypes")):
+        m = types.ModuleType(f"grid.utils.{name}")
+        setattr(m, fn, lambda config, console: "reference")
+        setattr(utils, name, m)
+        mods[f"grid.utils.{name}"] = m
+    for k, v in mods.items():
+        monkeypatch.setitem(sys.modules, k, v)
+    import grid_b200
+
+    grid_b200.install()
+    from grid_b200.utils import compute_dipcn, find_neighbors, normalize_mosdepth
+
+    assert mods["grid.utils.normalize_mosdepth"].normalize_mosdepth is normalize_mosdepth.normalize_mosdepth
+    assert mods["grid.utils.find_neighbors"].find_neighbors is find_neighbors.find_neighbors
+    assert mods["grid.utils.compute_dipcn"].compute_diploid_genotypes is compute_dipcn.compute_diploid_genotypes
+
+
+def test_config_errors_are_logged_not_raised(capsys):
+    from grid_b200.utils.find_neighbors import find_neighbors
+    from grid_b200.utils.normalize_mosdepth import normalize_mosdepth
+
+    assert normalize_mosdepth({}, None) is None and "Config error" in capsys.readouterr().out
+    assert find_neighbors({"mosdepth": {}}, None) is None and "Config error" in capsys.readouterr().out
+
+
+def test_product_never_imports_the_oracle():
+    import pathlib
+
+    for f in pathlib.Path(gio.__file__).parent.rglob("*.py"):
+        assert "oracle" not in f.read_text().replace("the oracle", ""), f
