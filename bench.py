@@ -60,7 +60,7 @@ def cpu_sample_step(a, bins):
     from grid_b200 import synth
     from oracle import grid_oracle as O
 
-    depth = synth.depth_matrix(SEED, a.samples, bins)
+    depth = synth.depth_hundredths(SEED, a.samples, bins) / 100.0  # the decimals the reference would parse
     counts = synth.read_counts(SEED, a.samples, [LPA_LEN])
     t0 = time.perf_counter()
     O.chain_arrays(depth, counts, num_neighbors=a.k, n_nbr=a.n_nbr, exact_knn=False)

@@ -1,7 +1,342 @@
-// placeholder until the tcgen05 kernel lands (next commit)
+// Exact Gram block on Blackwell tensor cores:  dot[i,j] += sum_k Q[i,k] * R[j,k]
+//
+// Operands are fp16 holding small integers (clipped z-scores in hundredths, |v| <= vmax), so every product is
+// exact and an fp32 accumulator stays an exact integer while its magnitude is below 2^24.  The K loop is cut into
+// chunks of ck k-blocks with ck*64*vmax^2 < 2^24; each chunk accumulates in TMEM (tcgen05.mma, fp32), is drained
+// with tcgen05.ld, converted to int32 and added into per-thread int32 registers; those are flushed to the int64
+// result with red.global.add before they can overflow.  Nothing is ever rounded: the result is the exact integer
+// dot product, whatever K is.
+//
+// Structure (one CTA per SM, persistent over work items = (128x128 output tile, K split)):
+//   warp 0      TMA producer   cp.async.bulk.tensor 2D, 128B swizzle, 6-stage mbarrier ring of 64-wide k-blocks
+//   warp 1      MMA issuer     one elected lane, tcgen05.mma cta_group::1 kind::f16 M128 N128 K16, 2 TMEM stages
+//   warp 2      TMEM allocator
+//   warps 4-11  epilogue       lane quarter = warp%4, column half = (warp-4)/4: 64 accumulators per thread
+#include <cuda.h>
+
 #include "common.cuh"
-int gridb200_gram_tc(const void*, int64_t, int64_t, const void*, int64_t, int64_t, int64_t, int32_t, int64_t*, int64_t,
-                     int, void*) {
-  g2::set_error("tcgen05 Gram kernel not built");
-  return GRIDB200_ENODEV;
+
+namespace g2 {
+namespace tc {
+
+constexpr int BM = 128, BN = 128, BK = 64, UMMA_K = 16;
+constexpr int STAGES = 6;
+constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int ACC_STAGES = 2;
+constexpr int TMEM_COLS = ACC_STAGES * BN;  // 256 fp32 columns
+constexpr int NUM_THREADS = 384;
+constexpr int EPI_WARP0 = 4, EPI_WARPS = 8;
+constexpr int EPI_COLS = BN / 2;            // columns per epilogue thread
+constexpr int CHECK_EVERY = 16;             // chunks between int32 overflow checks
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+
+// kind::f16 instruction descriptor: D=f32 (bit 4), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24
+constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+struct Work {
+  int tiles_m, tiles_n, ntiles, ksplits, kb_total, kb_per_split, ck, group_m;
+  int64_t nq, nr, ldd;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t da, uint64_t db, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(da), "l"(db), "r"(IDESC), "r"(accumulate)
+      : "memory");
+}
+// K-major operand tile, 128-byte swizzle: 8-row groups 1024 B apart (SBO), LBO = 1 (ignored), version 1 (sm_100)
+__device__ __forceinline__ uint64_t smem_desc(uint32_t addr) {
+  return (uint64_t)((addr >> 4) & 0x3FFF) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void red_add_s64(long long* p, long long v) {
+  asm volatile("red.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// item -> (k split, tile m, tile n): k-split major so concurrent CTAs stream the same K window through L2;
+// within a split, tiles are walked in bands of group_m tile-rows so concurrent tiles share operand rows.
+__device__ __forceinline__ void decode_item(const Work& w, int item, int& ks, int& tm, int& tn) {
+  ks = item / w.ntiles;
+  const int t = item - ks * w.ntiles;
+  const int per_group = w.group_m * w.tiles_n;
+  const int g = t / per_group;
+  const int first_m = g * w.group_m;
+  const int gsize = min(w.tiles_m - first_m, w.group_m);
+  const int r = t - g * per_group;
+  tm = first_m + r % gsize;
+  tn = r / gsize;
+}
+
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+k_gram_tc(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_r, const Work w,
+          long long* __restrict__ dot) {
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // 128B-swizzle atoms need 1024-byte alignment
+  const uint32_t bars = base + STAGES * STAGE_BYTES;
+  const uint32_t full0 = bars, empty0 = bars + 8 * STAGES, tfull0 = bars + 16 * STAGES, tempty0 = tfull0 + 8 * ACC_STAGES;
+  const uint32_t tmem_slot = tempty0 + 8 * ACC_STAGES;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nitems = w.ntiles * w.ksplits;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, 1);
+    }
+    for (int a = 0; a < ACC_STAGES; ++a) {
+      mbar_init(tfull0 + 8 * a, 1);
+      mbar_init(tempty0 + 8 * a, EPI_WARPS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    // ===================================== TMA producer =====================================
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_r) : "memory");
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+        int ks, tm, tn;
+        decode_item(w, item, ks, tm, tn);
+        const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty0 + 8 * stage, phase ^ 1);
+          const uint32_t fb = full0 + 8 * stage;
+          mbar_expect_tx(fb, STAGE_BYTES);
+          const uint32_t sa = base + stage * STAGE_BYTES;
+          tma_load_2d(sa, &map_q, fb, kb * BK, tm * BM);
+          tma_load_2d(sa + A_BYTES, &map_r, fb, kb * BK, tn * BN);
+          if (++stage == STAGES) stage = 0, phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================== MMA issuer =======================================
+    if (lane == 0) {
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+        int ks, tm, tn;
+        decode_item(w, item, ks, tm, tn);
+        const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
+        for (int c0 = kb0; c0 < kb1; c0 += w.ck) {
+          const int c1 = min(kb1, c0 + w.ck);
+          mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);  // epilogue has drained this accumulator stage
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+          for (int kb = c0; kb < c1; ++kb) {
+            mbar_wait(full0 + 8 * stage, phase);
+            tc_fence_after();
+            const uint32_t sa = base + stage * STAGE_BYTES;
+            const uint64_t da = smem_desc(sa), db = smem_desc(sa + A_BYTES);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)  // +32 bytes (2 x 16 B) per K16 step inside the swizzle atom
+              tc_mma(d_tmem, da + 2 * k, db + 2 * k, (kb > c0 || k > 0) ? 1u : 0u);
+            tc_commit(empty0 + 8 * stage);  // smem slot is free once these MMAs have read it
+            if (++stage == STAGES) stage = 0, phase ^= 1;
+          }
+          tc_commit(tfull0 + 8 * acc);  // chunk complete in TMEM
+          if (++acc == ACC_STAGES) acc = 0, acc_phase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= EPI_WARP0) {
+    // ===================================== epilogue =========================================
+    const int quarter = warp & 3, half = (warp - EPI_WARP0) >> 2;
+    int acc32[EPI_COLS];
+#pragma unroll
+    for (int i = 0; i < EPI_COLS; ++i) acc32[i] = 0;
+    int acc = 0, since_check = 0;
+    uint32_t acc_phase = 0;
+    for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
+      int ks, tm, tn;
+      decode_item(w, item, ks, tm, tn);
+      const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
+      const int64_t row = (int64_t)tm * BM + quarter * 32 + lane;
+      const int64_t col0 = (int64_t)tn * BN + half * EPI_COLS;
+      long long* out = dot + row * w.ldd + col0;
+      const bool row_ok = row < w.nq;
+      for (int c0 = kb0; c0 < kb1; c0 += w.ck) {
+        mbar_wait(tfull0 + 8 * acc, acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + half * EPI_COLS);
+        uint32_t v[EPI_COLS];
+#pragma unroll
+        for (int c = 0; c < EPI_COLS / 16; ++c) tmem_ld16(taddr + c * 16, v + c * 16);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty0 + 8 * acc);  // TMEM stage may be overwritten
+        if (++acc == ACC_STAGES) acc = 0, acc_phase ^= 1;
+#pragma unroll
+        for (int i = 0; i < EPI_COLS; ++i) acc32[i] += __float2int_rn(__uint_as_float(v[i]));
+        if (++since_check == CHECK_EVERY) {  // keep |acc32| + 16 more chunks (< 2^24 each) below 2^31
+          since_check = 0;
+#pragma unroll
+          for (int i = 0; i < EPI_COLS; ++i) {
+            if ((unsigned)(acc32[i] + 0x70000000) > 0xE0000000u) {
+              if (row_ok && col0 + i < w.nr) red_add_s64(out + i, (long long)acc32[i]);
+              acc32[i] = 0;
+            }
+          }
+        }
+      }
+      since_check = 0;
+#pragma unroll
+      for (int i = 0; i < EPI_COLS; ++i) {
+        if (row_ok && col0 + i < w.nr && acc32[i] != 0) red_add_s64(out + i, (long long)acc32[i]);
+        acc32[i] = 0;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
+// ---- host side ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+static int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t kdim, int64_t ld, int box_rows) {
+  EncodeTiledFn enc = get_encode();
+  G2_REQUIRE(enc != nullptr, GRIDB200_ENODEV, "cuTensorMapEncodeTiled is not available from this driver");
+  const cuuint64_t dims[2] = {(cuuint64_t)kdim, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  G2_REQUIRE(r == CUDA_SUCCESS, GRIDB200_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return 0;
+}
+
+}  // namespace tc
+}  // namespace g2
+
+int gridb200_gram_tc(const void* zq, int64_t nq, int64_t ldq, const void* zr, int64_t nr, int64_t ldr, int64_t kdim,
+                     int32_t vmax, int64_t* dot, int64_t ldd, int accumulate, void* stream) {
+  using namespace g2;
+  using namespace g2::tc;
+  // largest chunk (in 64-wide k-blocks) whose partial sums stay strictly below 2^24
+  const int64_t ck = ((1LL << 24) - 1) / ((int64_t)vmax * vmax * BK);
+  G2_REQUIRE(ck >= 1, GRIDB200_EDOMAIN,
+             "vmax=%d: one 64-wide k-block can exceed 2^24 in fp32; the tensor-core path needs vmax <= 511 (use impl=1)",
+             vmax);
+  G2_REQUIRE(nq < (1LL << 31) && nr < (1LL << 31) && kdim < (1LL << 31), GRIDB200_EINVAL, "shape exceeds int32");
+  cudaStream_t st = as_stream(stream);
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    G2_CUDA(cudaGetDevice(&dev));
+    cudaDeviceProp prop;
+    G2_CUDA(cudaGetDeviceProperties(&prop, dev));
+    G2_REQUIRE(prop.major == 10, GRIDB200_ENODEV, "tcgen05 path needs an sm_100 device (found sm_%d%d)", prop.major,
+               prop.minor);
+    G2_CUDA(cudaFuncSetAttribute(k_gram_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    sms = prop.multiProcessorCount;
+  }
+  CUtensorMap mq, mr;
+  if (int e = make_map(&mq, zq, nq, kdim, ldq, BM)) return e;
+  if (int e = make_map(&mr, zr, nr, kdim, ldr, BN)) return e;
+
+  Work w;
+  w.nq = nq, w.nr = nr, w.ldd = ldd;
+  w.tiles_m = (int)((nq + BM - 1) / BM);
+  w.tiles_n = (int)((nr + BN - 1) / BN);
+  w.ntiles = w.tiles_m * w.tiles_n;
+  w.kb_total = (int)(kdim / BK);
+  w.ck = (int)std::min<int64_t>(ck, w.kb_total);
+  w.group_m = 8;
+  // K splits: best wave efficiency over the SMs, each split at least 4 chunks long
+  const int chunks = (w.kb_total + w.ck - 1) / w.ck;
+  int best_s = 1;
+  double best_eff = 0.0;
+  for (int s = 1; s <= 64 && s * 4 <= std::max(chunks, 4); ++s) {
+    const int cps = (chunks + s - 1) / s;          // chunks per split
+    const int real_s = (chunks + cps - 1) / cps;   // splits actually needed
+    const long long items = (long long)w.ntiles * real_s;
+    const double eff = (double)items / (double)(((items + sms - 1) / sms) * sms);
+    if (eff > best_eff + 1e-9) best_eff = eff, best_s = real_s;
+  }
+  const int cps = (chunks + best_s - 1) / best_s;
+  w.kb_per_split = cps * w.ck;
+  w.ksplits = (w.kb_total + w.kb_per_split - 1) / w.kb_per_split;
+  if (!accumulate) G2_CUDA(cudaMemset2DAsync(dot, ldd * sizeof(int64_t), 0, nr * sizeof(int64_t), nq, st));
+  const long long items = (long long)w.ntiles * w.ksplits;
+  const int grid = (int)std::min<long long>(items, sms);
+  k_gram_tc<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, reinterpret_cast<long long*>(dot));
+  G2_LAUNCHED();
+  return 0;
 }

@@ -238,6 +238,8 @@ def knn(zh: torch.Tensor, kdim: int, norms: torch.Tensor, k: int, vmax: int, imp
     """
     n, ld = zh.shape[0], zh.stride(0)
     dev, st = zh.device, _stream()
+    if impl == 0 and vmax > 511:
+        impl = 1  # |v| > 511: a 64-wide fp32 chunk is no longer exact; the integer SIMT kernel takes over (still GPU)
     k = max(1, min(k, n - 1)) if n > 1 else 1
     best_d2 = torch.empty((n, k), dtype=torch.int64, device=dev)
     best_idx = torch.empty((n, k), dtype=torch.int32, device=dev)

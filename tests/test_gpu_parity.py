@@ -76,12 +76,13 @@ def test_synth_device_equals_numpy(eng):
 
 
 def _array_case(seed, n, b, holes=0.0, **kw):
-    depth = synth.depth_matrix(seed, n, b)
+    """(fp32 matrix for the device, the same depths as the decimals the reference would parse, counts)."""
+    h = synth.depth_hundredths(seed, n, b)
     if holes:
         rng = np.random.default_rng(seed)
-        depth[rng.random(depth.shape) < holes] = 0
+        h[rng.random(h.shape) < holes] = 0
     counts = synth.read_counts(seed, n, [42599, 1500, 900000])
-    return depth, counts
+    return (h / 100.0).astype(np.float32), h / 100.0, counts
 
 
 @pytest.mark.parametrize("seed,n,b,holes,params", [
@@ -91,8 +92,8 @@ def _array_case(seed, n, b, holes=0.0, **kw):
     (4, 33, 1030, 0.0, dict(top_frac=0.0, frac_r=0.5, sigma2_max=0.9, num_neighbors=5, n_nbr=5)),
 ])
 def test_array_chain_matches_oracle(seed, n, b, holes, params, eng):
-    depth, counts = _array_case(seed, n, b, holes)
-    want = O.chain_arrays(depth, counts, **params)
+    depth, decimals, counts = _array_case(seed, n, b, holes)
+    want = O.chain_arrays(decimals, counts, **params)
     p = eng.Params(**params)
     ld = (b + 3) // 4 * 4
     dd = np.zeros((n, ld), dtype=np.float32)
@@ -131,7 +132,9 @@ def test_array_chain_matches_oracle(seed, n, b, holes, params, eng):
 
 def test_gram_tensor_core_is_exact_at_extremes(eng):
     """All-(+-vmax) rows are the worst case for fp32 accumulation: the chunked drain must stay exact."""
-    for vmax, n, k in ((200, 300, 8192), (2048, 140, 4096), (1, 129, 64)):
+    from grid_b200._lib import GridB200Error, call, ptr
+
+    for vmax, n, k, impls in ((200, 300, 8192, (1, 0)), (511, 140, 4096, (1, 0)), (1, 129, 64, (1, 0)), (2048, 70, 512, (1,))):
         rng = np.random.default_rng(vmax)
         a = rng.choice([-vmax, vmax], size=(n, k)).astype(np.int64)
         a[0] = vmax
@@ -139,12 +142,36 @@ def test_gram_tensor_core_is_exact_at_extremes(eng):
         a[2, ::2] = 0
         t = torch.from_numpy(a.astype(np.float16)).cuda()
         want = a @ a.T
-        for impl in (1, 0):
-            dot = torch.empty((n, n + (n % 2)), dtype=torch.int64, device="cuda")
-            from grid_b200._lib import call, ptr
+        for impl in impls:
+            dot = torch.full((n, n + (n % 2)), -7, dtype=torch.int64, device="cuda")
             call("gridb200_gram", ptr(t), n, k, ptr(t), n, k, k, vmax, ptr(dot), dot.stride(0), 0, impl,
                  torch.cuda.current_stream().cuda_stream)
             np.testing.assert_array_equal(dot.cpu().numpy()[:, :n], want)
+            call("gridb200_gram", ptr(t), n, k, ptr(t), n, k, k, vmax, ptr(dot), dot.stride(0), 1, impl,
+                 torch.cuda.current_stream().cuda_stream)                    # accumulate
+            np.testing.assert_array_equal(dot.cpu().numpy()[:, :n], 2 * want)
+    with pytest.raises(GridB200Error, match="vmax"):                          # fp32 chunks cannot be exact there
+        call("gridb200_gram", ptr(t), 70, 512, ptr(t), 70, 512, 512, 2048, ptr(dot), dot.stride(0), 0, 0,
+             torch.cuda.current_stream().cuda_stream)
+
+
+def test_gram_rectangular_blocks_and_long_k(eng):
+    """Query block != reference block (the blocked / ring schedule), ragged edges, and a K long enough for many
+    chunk drains, int32 overflow flushes and K splits."""
+    from grid_b200._lib import call, ptr
+
+    rng = np.random.default_rng(5)
+    nq, nr, k = 200, 333, 64 * 700
+    q = rng.integers(-200, 201, size=(nq, k)).astype(np.int64)
+    r = rng.integers(-200, 201, size=(nr, k)).astype(np.int64)
+    q[3] = 200
+    r[5] = 200                                                               # 200*200*44800 = 1.8e9 > 2^30
+    r[6] = -200
+    tq, tr = torch.from_numpy(q.astype(np.float16)).cuda(), torch.from_numpy(r.astype(np.float16)).cuda()
+    dot = torch.empty((nq, nr + 1), dtype=torch.int64, device="cuda")
+    call("gridb200_gram", ptr(tq), nq, k, ptr(tr), nr, k, k, 200, ptr(dot), dot.stride(0), 0, 0,
+         torch.cuda.current_stream().cuda_stream)
+    np.testing.assert_array_equal(dot.cpu().numpy()[:, :nr], q @ r.T)
 
 
 def test_knn_properties_at_scale(eng):
