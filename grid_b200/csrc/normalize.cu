@@ -285,9 +285,38 @@ __global__ void k_col_finalize(const double* __restrict__ sd, const double* __re
 
 // ---------------------------------------------------------------------------------------------------------
 // K7: transform + printf-exact quantisation + compaction to the selected bins (+ clipped fp16 operand,
-// + exact row norms).  Block = 1024 bins x a slab of rows.
+// + exact row norms).  Block = 1024 bins x a slab of rows, processed in batches of 8 rows:
+//   1. every thread issues its 8 row loads (16 B each) before touching any of them,
+//   2. computes z in fp64, rounds exactly, and drops the 2-byte results into a shared staging row at the
+//      compacted position (selected bins of one block are contiguous in the output),
+//   3. the block copies each staged row out with ALIGNED 16-byte stores (element stores only on the two
+//      ragged ends, which belong to neighbouring blocks).
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kTransformSlab = 256;
+constexpr int kTB = 8;                       // rows per batch
+constexpr int kStageRow = kColsPerBlock + 8;  // halves per staged row (+8: alignment shift)
+
+template <typename T>
+__device__ __forceinline__ void copy_out_rows(const T* __restrict__ stage, T* __restrict__ out, int64_t ld_out,
+                                              int64_t row0, int nrows, int p0, int len) {
+  // stage[r][shift + e] holds output element p0 + e of row row0 + r, shift = p0 % 8, so 16-byte chunk q of the
+  // staged row lines up with the aligned global chunk starting at element (p0 - shift) + 8q.
+  const int shift = p0 & 7;
+  const int nchunk = (shift + len + 7) >> 3;
+  for (int w = threadIdx.x; w < nrows * nchunk; w += kThreads) {
+    const int r = w / nchunk, q = w - r * nchunk;
+    const T* src = stage + r * kStageRow + 8 * q;
+    T* dst = out + (row0 + r) * ld_out + (p0 - shift) + 8 * q;
+    const int e0 = 8 * q - shift;  // first element of this chunk relative to p0
+    if (e0 >= 0 && e0 + 8 <= len) {
+      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+    } else {
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        if (e0 + e >= 0 && e0 + e < len) dst[e] = src[e];
+    }
+  }
+}
 
 template <bool kZq, bool kZh>
 __global__ void __launch_bounds__(kThreads) k_transform(const float* __restrict__ depth, int64_t n, int64_t b,
@@ -300,44 +329,69 @@ __global__ void __launch_bounds__(kThreads) k_transform(const float* __restrict_
                                                         __half* __restrict__ zh, int64_t ldh,
                                                         unsigned long long* __restrict__ norms,
                                                         unsigned long long* __restrict__ sat) {
+  __shared__ __align__(16) int16_t s_zq[kZq ? kTB * kStageRow : 8];
+  __shared__ __align__(16) __half s_zh[kZh ? kTB * kStageRow : 8];
+  __shared__ double s_f[kTransformSlab];
   __shared__ unsigned long long s_norm[kTransformSlab];
+  __shared__ int s_lo, s_hi;
   const int64_t r0 = (int64_t)blockIdx.y * kTransformSlab;
-  const int64_t r1 = min(n, r0 + kTransformSlab);
-  if (kZh) {
-    for (int t = threadIdx.x; t < kTransformSlab; t += kThreads) s_norm[t] = 0;
-    __syncthreads();
+  const int nrow = (int)(n - r0 < kTransformSlab ? n - r0 : (int64_t)kTransformSlab);
+  for (int t = threadIdx.x; t < kTransformSlab; t += kThreads) {
+    s_norm[t] = 0;
+    s_f[t] = t < nrow ? row_factor[r0 + t] : nan("");
   }
+  if (threadIdx.x == 0) s_lo = 0x7fffffff, s_hi = -1;
+  __syncthreads();
   const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
   int pos[4];
   double m[4], a[4];
   bool kp[4];
-  bool any = false;
+  int lo = 0x7fffffff, hi = -1;
   const double zscale = info[0];
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
     pos[q] = (j0 + q < b) ? sel_pos[j0 + q] : -1;
-    m[q] = 0.0;
-    a[q] = 0.0;
-    kp[q] = false;
+    m[q] = 0.0, a[q] = 0.0, kp[q] = false;
     if (pos[q] >= 0) {
-      any = true;
+      lo = min(lo, pos[q]), hi = max(hi, pos[q]);
       m[q] = mu[j0 + q];
       a[q] = zscale / sqrt(m[q]);  // selected bins have a finite ratio, hence mu > 0
       kp[q] = keep ? keep[j0 + q] != 0 : true;
     }
   }
-  const unsigned warp_any = __ballot_sync(0xffffffffu, any);
-  if (warp_any) {
-    const float* p = depth + r0 * ld + (j0 < b ? j0 : 0);
-    for (int64_t i = r0; i < r1; ++i, p += ld) {
+  const bool any = hi >= 0;
+  lo = __reduce_min_sync(0xffffffffu, lo);
+  hi = __reduce_max_sync(0xffffffffu, hi);
+  if ((threadIdx.x & 31) == 0 && hi >= 0) {
+    atomicMin(&s_lo, lo);
+    atomicMax(&s_hi, hi);
+  }
+  __syncthreads();
+  const int p0 = s_lo, len = s_hi - s_lo + 1;  // this block's contiguous output range
+  if (s_hi < 0) return;                        // no selected bin in these 1024 columns (block-uniform)
+  const int shift = p0 & 7;
+  int off[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) off[q] = pos[q] >= 0 ? pos[q] - p0 + shift : -1;
+  const float* colp = depth + (j0 < b ? j0 : 0);
+
+  for (int rb = 0; rb < nrow; rb += kTB) {
+    const int nr = min(kTB, nrow - rb);
+    float4 v[kTB];
+    if (any) {
+#pragma unroll
+      for (int u = 0; u < kTB; ++u)
+        v[u] = u < nr ? ld_stream(reinterpret_cast<const float4*>(colp + (r0 + rb + u) * ld)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < kTB; ++u) {
       int vsq = 0;
-      if (any) {
-        const float4 v = ld_stream(reinterpret_cast<const float4*>(p));
-        const double f = row_factor[i];
-        const int h[4] = {depth_hundredths(v.x), depth_hundredths(v.y), depth_hundredths(v.z), depth_hundredths(v.w)};
+      if (any && u < nr) {
+        const double f = s_f[rb + u];
+        const int h[4] = {depth_hundredths(v[u].x), depth_hundredths(v[u].y), depth_hundredths(v[u].z), depth_hundredths(v[u].w)};
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          if (pos[q] < 0) continue;
+          if (off[q] < 0) continue;
           int zi = -32768;
           if (h[q] > 0 && f == f) {
             const double z = fma(u32_to_double(h[q]), f, -m[q]) * a[q];
@@ -349,24 +403,27 @@ __global__ void __launch_bounds__(kThreads) k_transform(const float* __restrict_
             zi = double_to_int_exact(zr);
             if (zi == 0 && z < 0.0) zi = -32767;  // prints as "-0.00"; numerically zero
           }
-          if (kZq) zq[i * ldq + pos[q]] = (int16_t)zi;
+          if (kZq) s_zq[u * kStageRow + off[q]] = (int16_t)zi;
           if (kZh) {
             int c = 0;
             if (zi > -32767 && kp[q]) c = max(-zclip, min(zclip, zi));
-            zh[i * ldh + pos[q]] = __int2half_rn(c);
+            s_zh[u * kStageRow + off[q]] = __int2half_rn(c);
             vsq += c * c;
           }
         }
       }
-      if (kZh) {
+      if (kZh && u < nr) {
         const int tot = __reduce_add_sync(0xffffffffu, vsq);
-        if ((threadIdx.x & 31) == 0 && tot) atomicAdd(&s_norm[i - r0], (unsigned long long)tot);
+        if ((threadIdx.x & 31) == 0 && tot) atomicAdd(&s_norm[rb + u], (unsigned long long)tot);
       }
     }
+    __syncthreads();
+    if (kZq) copy_out_rows<int16_t>(s_zq, zq, ldq, r0 + rb, nr, p0, len);
+    if (kZh) copy_out_rows<__half>(s_zh, zh, ldh, r0 + rb, nr, p0, len);
+    __syncthreads();
   }
   if (kZh) {
-    __syncthreads();
-    for (int t = threadIdx.x; t < r1 - r0; t += kThreads)
+    for (int t = threadIdx.x; t < nrow; t += kThreads)
       if (s_norm[t]) atomicAdd(&norms[r0 + t], s_norm[t]);
   }
 }
@@ -526,6 +583,10 @@ extern "C" int gridb200_transform(const float* depth, int64_t n, int64_t b, int6
   G2_REQUIRE(zq || zh, GRIDB200_EINVAL, "at least one of zq / zh must be requested");
   G2_REQUIRE(!zh || (norms && zclip > 0 && zclip <= 2048), GRIDB200_EINVAL,
              "zh needs norms and 0 < zclip <= 2048 (fp16 holds integers exactly up to 2048)");
+  G2_REQUIRE(!zq || (ldq % 8 == 0 && (reinterpret_cast<uintptr_t>(zq) & 15) == 0), GRIDB200_EINVAL,
+             "zq must be 16-byte aligned with ldq a multiple of 8");
+  G2_REQUIRE(!zh || (ldh % 8 == 0 && (reinterpret_cast<uintptr_t>(zh) & 15) == 0), GRIDB200_EINVAL,
+             "zh must be 16-byte aligned with ldh a multiple of 8");
   const int64_t cb = (b + kColsPerBlock - 1) / kColsPerBlock;
   const int64_t slabs = (n + kTransformSlab - 1) / kTransformSlab;
   G2_REQUIRE(slabs <= 65535, GRIDB200_EINVAL, "too many row slabs");
