@@ -13,6 +13,7 @@
 //   warp 2      TMEM allocator
 //   warps 4-11  epilogue       lane quarter = warp%4, column half = (warp-4)/4: 64 accumulators per thread
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -251,6 +252,227 @@ k_gram_tc(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUt
   }
 }
 
+
+// =========================================================================================================
+// CTA-pair version (cta_group::2): one 256 x 256 output tile per pair of SMs.  Each CTA stages its own 128
+// query rows and 128 of the 256 reference rows per k-block (32 KB, as before) but the pair performs four times
+// the MMA work on them, which is what lifts the kernel off the L2-bandwidth ceiling.  The leader CTA issues
+// tcgen05.mma.cta_group::2 (M=256, N=256); each CTA's TMEM holds its 128 x 256 half of the accumulator, drained
+// by that CTA's own 8 epilogue warps (128 int32 accumulators per thread).
+//   warp 0      TMA producer (both CTAs; transaction bytes land on the LEADER's full barrier) + TMEM allocator
+//   warp 1      MMA issuer (leader CTA only); commits are multicast to both CTAs' barriers
+//   warps 2-9   epilogue: lane quarter = warp%4, column half = (warp-2)/4
+// =========================================================================================================
+namespace pair {
+
+constexpr int TM = 256, TN = 256;           // tile of the pair
+constexpr int CTA_ROWS = 128;               // query rows / reference rows staged per CTA
+constexpr int NUM_THREADS = 384;            // warpgroup 0 = {TMA, MMA, 2 idle warps}, warpgroups 1-2 = epilogue
+constexpr int EPI_WARP0 = 4, EPI_WARPS = 8;
+constexpr int REGS_CTRL = 40, REGS_EPI = 232;  // setmaxnreg: 128*40 + 256*232 = 64512 <= 65536
+constexpr int EPI_COLS = TN / 2;            // 128 columns per epilogue thread
+constexpr int TMEM_COLS = ACC_STAGES * TN;  // 512: all of TMEM
+constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, uint32_t leader_bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(map), "r"(leader_bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {  // arrive on this barrier in BOTH CTAs
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+               "h"((uint16_t)3)
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma_pair(uint32_t d_tmem, uint64_t da, uint64_t db, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(da), "l"(db), "r"(IDESC), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr));
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_r, const Work w,
+               long long* __restrict__ dot) {
+  extern __shared__ unsigned char smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bars = base + STAGES * STAGE_BYTES;
+  const uint32_t full0 = bars, empty0 = bars + 8 * STAGES, tfull0 = bars + 16 * STAGES, tempty0 = tfull0 + 8 * ACC_STAGES;
+  const uint32_t tmem_slot = tempty0 + 8 * ACC_STAGES;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();
+  const int pair_id = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  const int nitems = w.ntiles * w.ksplits;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full0 + 8 * s, 2);   // leader's expect_tx arrive + the peer's remote arrive
+      mbar_init(empty0 + 8 * s, 1);  // one multicast commit
+    }
+    for (int a = 0; a < ACC_STAGES; ++a) {
+      mbar_init(tfull0 + 8 * a, 1);                // one multicast commit
+      mbar_init(tempty0 + 8 * a, 2 * EPI_WARPS);   // every epilogue warp of both CTAs (leader's copy is used)
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp < EPI_WARP0) asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS_CTRL));
+  if (warp == 0) {
+    // ===================================== TMA producer (both CTAs) =========================
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_r) : "memory");
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = pair_id; item < nitems; item += npairs) {
+        int ks, tm, tn;
+        decode_item(w, item, ks, tm, tn);
+        const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
+        const int qrow = tm * TM + (int)rank * CTA_ROWS, rrow = tn * TN + (int)rank * CTA_ROWS;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty0 + 8 * stage, phase ^ 1);
+          const uint32_t leader_full = map_to_cta(full0 + 8 * stage, 0);
+          if (rank == 0) mbar_expect_tx(full0 + 8 * stage, 2 * STAGE_BYTES);  // bytes of both CTAs
+          else mbar_arrive_cluster(leader_full);
+          const uint32_t sa = base + stage * STAGE_BYTES;
+          tma_load_2d_pair(sa, &map_q, leader_full, kb * BK, qrow);
+          tma_load_2d_pair(sa + A_BYTES, &map_r, leader_full, kb * BK, rrow);
+          if (++stage == STAGES) stage = 0, phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================== MMA issuer (leader only) =========================
+    if (rank == 0 && lane == 0) {
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int item = pair_id; item < nitems; item += npairs) {
+        int ks, tm, tn;
+        decode_item(w, item, ks, tm, tn);
+        const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
+        for (int c0 = kb0; c0 < kb1; c0 += w.ck) {
+          const int c1 = min(kb1, c0 + w.ck);
+          mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TN);
+          for (int kb = c0; kb < c1; ++kb) {
+            mbar_wait(full0 + 8 * stage, phase);
+            tc_fence_after();
+            const uint32_t sa = base + stage * STAGE_BYTES;
+            const uint64_t da = smem_desc(sa), db = smem_desc(sa + A_BYTES);
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              tc_mma_pair(d_tmem, da + 2 * k, db + 2 * k, (kb > c0 || k > 0) ? 1u : 0u);
+            tc_commit_pair(empty0 + 8 * stage);
+            if (++stage == STAGES) stage = 0, phase ^= 1;
+          }
+          tc_commit_pair(tfull0 + 8 * acc);
+          if (++acc == ACC_STAGES) acc = 0, acc_phase ^= 1;
+        }
+      }
+    }
+  } else if (warp >= EPI_WARP0) {
+    // ===================================== epilogue (both CTAs) =============================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_EPI));
+    const int quarter = warp & 3, half = (warp - EPI_WARP0) >> 2;
+    int acc32[EPI_COLS];
+#pragma unroll
+    for (int i = 0; i < EPI_COLS; ++i) acc32[i] = 0;
+    int acc = 0, since_check = 0;
+    uint32_t acc_phase = 0;
+    for (int item = pair_id; item < nitems; item += npairs) {
+      int ks, tm, tn;
+      decode_item(w, item, ks, tm, tn);
+      const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
+      const int64_t row = (int64_t)tm * TM + rank * CTA_ROWS + quarter * 32 + lane;
+      const int64_t col0 = (int64_t)tn * TN + half * EPI_COLS;
+      long long* out = dot + row * w.ldd + col0;
+      const bool row_ok = row < w.nq;
+      for (int c0 = kb0; c0 < kb1; c0 += w.ck) {
+        mbar_wait(tfull0 + 8 * acc, acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * TN + half * EPI_COLS);
+#pragma unroll
+        for (int c = 0; c < EPI_COLS / 16; ++c) {
+          uint32_t v[16];
+          tmem_ld16(taddr + c * 16, v);
+          tmem_ld_wait();
+          if (c == EPI_COLS / 16 - 1) {  // everything is in registers: hand the TMEM stage back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(map_to_cta(tempty0 + 8 * acc, 0));
+          }
+#pragma unroll
+          for (int i = 0; i < 16; ++i) acc32[c * 16 + i] += __float2int_rn(__uint_as_float(v[i]));
+        }
+        if (++acc == ACC_STAGES) acc = 0, acc_phase ^= 1;
+        if (++since_check == CHECK_EVERY) {
+          since_check = 0;
+#pragma unroll
+          for (int i = 0; i < EPI_COLS; ++i) {
+            if ((unsigned)(acc32[i] + 0x70000000) > 0xE0000000u) {
+              if (row_ok && col0 + i < w.nr) red_add_s64(out + i, (long long)acc32[i]);
+              acc32[i] = 0;
+            }
+          }
+        }
+      }
+      since_check = 0;
+#pragma unroll
+      for (int i = 0; i < EPI_COLS; ++i) {
+        if (row_ok && col0 + i < w.nr && acc32[i] != 0) red_add_s64(out + i, (long long)acc32[i]);
+        acc32[i] = 0;
+      }
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();  // the peer's TMEM and barriers stay alive until the leader's last MMA/commit has landed
+  if (warp == 0) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+  }
+}
+
+}  // namespace pair
+
 // ---- host side ------------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -311,15 +533,25 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t ldq, const void* zr, in
   if (int e = make_map(&mq, zq, nq, kdim, ldq, BM)) return e;
   if (int e = make_map(&mr, zr, nr, kdim, ldr, BN)) return e;
 
+  // GRIDB200_GRAM_1CTA=1 selects the single-CTA kernel (debugging aid); the CTA-pair kernel is the product path
+  static int use_pair = -1;
+  if (use_pair < 0) {
+    const char* e = getenv("GRIDB200_GRAM_1CTA");
+    use_pair = (e && e[0] == '1') ? 0 : 1;
+    if (use_pair)
+      G2_CUDA(cudaFuncSetAttribute(pair::k_gram_tc_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+  }
+  const int tile_m = use_pair ? pair::TM : BM, tile_n = use_pair ? pair::TN : BN;
+  const int workers = use_pair ? sms / 2 : sms;
   Work w;
   w.nq = nq, w.nr = nr, w.ldd = ldd;
-  w.tiles_m = (int)((nq + BM - 1) / BM);
-  w.tiles_n = (int)((nr + BN - 1) / BN);
+  w.tiles_m = (int)((nq + tile_m - 1) / tile_m);
+  w.tiles_n = (int)((nr + tile_n - 1) / tile_n);
   w.ntiles = w.tiles_m * w.tiles_n;
   w.kb_total = (int)(kdim / BK);
   w.ck = (int)std::min<int64_t>(ck, w.kb_total);
-  w.group_m = 8;
-  // K splits: best wave efficiency over the SMs, each split at least 4 chunks long
+  w.group_m = use_pair ? 4 : 8;
+  // K splits: best wave efficiency over the workers, each split at least 4 chunks long
   const int chunks = (w.kb_total + w.ck - 1) / w.ck;
   int best_s = 1;
   double best_eff = 0.0;
@@ -327,7 +559,7 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t ldq, const void* zr, in
     const int cps = (chunks + s - 1) / s;          // chunks per split
     const int real_s = (chunks + cps - 1) / cps;   // splits actually needed
     const long long items = (long long)w.ntiles * real_s;
-    const double eff = (double)items / (double)(((items + sms - 1) / sms) * sms);
+    const double eff = (double)items / (double)(((items + workers - 1) / workers) * workers);
     if (eff > best_eff + 1e-9) best_eff = eff, best_s = real_s;
   }
   const int cps = (chunks + best_s - 1) / best_s;
@@ -335,8 +567,11 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t ldq, const void* zr, in
   w.ksplits = (w.kb_total + w.kb_per_split - 1) / w.kb_per_split;
   if (!accumulate) G2_CUDA(cudaMemset2DAsync(dot, ldd * sizeof(int64_t), 0, nr * sizeof(int64_t), nq, st));
   const long long items = (long long)w.ntiles * w.ksplits;
-  const int grid = (int)std::min<long long>(items, sms);
-  k_gram_tc<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, reinterpret_cast<long long*>(dot));
+  const int nwork = (int)std::min<long long>(items, workers);
+  if (use_pair)
+    pair::k_gram_tc_pair<<<2 * nwork, pair::NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, reinterpret_cast<long long*>(dot));
+  else
+    k_gram_tc<<<nwork, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, reinterpret_cast<long long*>(dot));
   G2_LAUNCHED();
   return 0;
 }
