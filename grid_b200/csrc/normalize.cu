@@ -293,8 +293,9 @@ __global__ void k_col_finalize(const double* __restrict__ sd, const double* __re
 //      ragged ends, which belong to neighbouring blocks).
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kTransformSlab = 256;
-constexpr int kTB = 8;                       // rows per batch
-constexpr int kStageRow = kColsPerBlock + 8;  // halves per staged row (+8: alignment shift)
+constexpr int kTB = 8;                        // rows per batch
+constexpr int kStageRow = kColsPerBlock + 16;  // halves per staged row (+8 alignment shift, +8 dump slots)
+constexpr int kDump = kStageRow - 1;          // where unselected bins drop their (ignored) result
 
 template <typename T>
 __device__ __forceinline__ void copy_out_rows(const T* __restrict__ stage, T* __restrict__ out, int64_t ld_out,
@@ -303,19 +304,38 @@ __device__ __forceinline__ void copy_out_rows(const T* __restrict__ stage, T* __
   // staged row lines up with the aligned global chunk starting at element (p0 - shift) + 8q.
   const int shift = p0 & 7;
   const int nchunk = (shift + len + 7) >> 3;
-  for (int w = threadIdx.x; w < nrows * nchunk; w += kThreads) {
-    const int r = w / nchunk, q = w - r * nchunk;
-    const T* src = stage + r * kStageRow + 8 * q;
-    T* dst = out + (row0 + r) * ld_out + (p0 - shift) + 8 * q;
+  for (int q = threadIdx.x; q < nchunk; q += kThreads) {
     const int e0 = 8 * q - shift;  // first element of this chunk relative to p0
-    if (e0 >= 0 && e0 + 8 <= len) {
-      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
-    } else {
+    const bool whole = e0 >= 0 && e0 + 8 <= len;
+    const T* src = stage + 8 * q;
+    T* dst = out + row0 * ld_out + (p0 - shift) + 8 * q;
+    for (int r = 0; r < nrows; ++r, src += kStageRow, dst += ld_out) {
+      if (whole) {
+        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+      } else {
 #pragma unroll
-      for (int e = 0; e < 8; ++e)
-        if (e0 + e >= 0 && e0 + e < len) dst[e] = src[e];
+        for (int e = 0; e < 8; ++e)
+          if (e0 + e >= 0 && e0 + e < len) dst[e] = src[e];
+      }
     }
   }
+}
+
+// Rare path of the quantiser: t = w*a100 landed exactly on k+0.5 (the exact residual decides, as printf would on the
+// exact value) or |t| is beyond the int16 code range (saturate and count).
+__device__ __noinline__ int quantise_slow(double w, double a100, unsigned long long* sat) {
+  const double t = w * a100;
+  double q = round_even(t);
+  if (fabs(t - q) == 0.5) {
+    const double r = fma(w, a100, -t);
+    if (r > 0.0) q = t + 0.5;
+    else if (r < 0.0) q = t - 0.5;
+  }
+  if (fabs(q) > 32766.0) {
+    atomicAdd(sat, 1ULL);
+    q = q > 0 ? 32766.0 : -32766.0;
+  }
+  return double_to_int_exact(q);
 }
 
 template <bool kZq, bool kZh>
@@ -344,19 +364,20 @@ __global__ void __launch_bounds__(kThreads) k_transform(const float* __restrict_
   __syncthreads();
   const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
   int pos[4];
-  double m[4], a[4];
-  bool kp[4];
+  double negmu[4], a100[4];  // t = (h*f - mu) * (100*zscale/sqrt(mu))
+  int zc[4];                 // clip bound of the fp16 operand; 0 for bins the kNN filter drops
   int lo = 0x7fffffff, hi = -1;
   const double zscale = info[0];
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
     pos[q] = (j0 + q < b) ? sel_pos[j0 + q] : -1;
-    m[q] = 0.0, a[q] = 0.0, kp[q] = false;
+    negmu[q] = 0.0, a100[q] = 0.0, zc[q] = 0;
     if (pos[q] >= 0) {
       lo = min(lo, pos[q]), hi = max(hi, pos[q]);
-      m[q] = mu[j0 + q];
-      a[q] = zscale / sqrt(m[q]);  // selected bins have a finite ratio, hence mu > 0
-      kp[q] = keep ? keep[j0 + q] != 0 : true;
+      const double m = mu[j0 + q];
+      negmu[q] = -m;
+      a100[q] = 100.0 * (zscale / sqrt(m));  // selected bins have a finite ratio, hence mu > 0
+      zc[q] = (keep ? keep[j0 + q] != 0 : true) ? zclip : 0;
     }
   }
   const bool any = hi >= 0;
@@ -372,7 +393,7 @@ __global__ void __launch_bounds__(kThreads) k_transform(const float* __restrict_
   const int shift = p0 & 7;
   int off[4];
 #pragma unroll
-  for (int q = 0; q < 4; ++q) off[q] = pos[q] >= 0 ? pos[q] - p0 + shift : -1;
+  for (int q = 0; q < 4; ++q) off[q] = pos[q] >= 0 ? pos[q] - p0 + shift : kDump - q;
   const float* colp = depth + (j0 < b ? j0 : 0);
 
   for (int rb = 0; rb < nrow; rb += kTB) {
@@ -388,25 +409,39 @@ __global__ void __launch_bounds__(kThreads) k_transform(const float* __restrict_
       int vsq = 0;
       if (any && u < nr) {
         const double f = s_f[rb + u];
-        const int h[4] = {depth_hundredths(v[u].x), depth_hundredths(v[u].y), depth_hundredths(v[u].z), depth_hundredths(v[u].w)};
+        const bool row_ok = f == f;
+        const float vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+        int zi[4];
+        bool rare = false;
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          if (off[q] < 0) continue;
-          int zi = -32768;
-          if (h[q] > 0 && f == f) {
-            const double z = fma(u32_to_double(h[q]), f, -m[q]) * a[q];
-            double zr = printf_round(z, 100.0);
-            if (fabs(zr) > 32766.0) {
-              atomicAdd(sat, 1ULL);
-              zr = zr > 0 ? 32766.0 : -32766.0;
+          const int h = depth_hundredths(vv[q]);
+          const double w = fma(u32_to_double(h), f, negmu[q]);
+          const double t = w * a100[q];
+          const double tm = t + kRoundMagic;       // low word = round-half-even(t) as int32
+          const double d = t - (tm - kRoundMagic);
+          zi[q] = __double2loint(tm);
+          // exactly on .5 after rounding, or beyond the int16 code range: settle in the slow path
+          rare |= (fabs(d) == 0.5) | ((__double2hiint(t) & 0x7fffffff) >= 0x40DFFF00);
+          if (kZq && zi[q] == 0 && __double2hiint(t) < 0) zi[q] = -32767;  // prints as "-0.00"
+          if (!(h > 0 && row_ok)) zi[q] = -32768;
+        }
+        if (rare) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int h = depth_hundredths(vv[q]);
+            if (h > 0 && row_ok && off[q] < kDump - 3) {
+              const double w = fma(u32_to_double(h), f, negmu[q]);
+              const int z = quantise_slow(w, a100[q], sat);
+              zi[q] = (kZq && z == 0 && w * a100[q] < 0.0) ? -32767 : z;
             }
-            zi = double_to_int_exact(zr);
-            if (zi == 0 && z < 0.0) zi = -32767;  // prints as "-0.00"; numerically zero
           }
-          if (kZq) s_zq[u * kStageRow + off[q]] = (int16_t)zi;
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (kZq) s_zq[u * kStageRow + off[q]] = (int16_t)zi[q];
           if (kZh) {
-            int c = 0;
-            if (zi > -32767 && kp[q]) c = max(-zclip, min(zclip, zi));
+            const int c = zi[q] > -32767 ? max(-zc[q], min(zc[q], zi[q])) : 0;
             s_zh[u * kStageRow + off[q]] = __int2half_rn(c);
             vsq += c * c;
           }

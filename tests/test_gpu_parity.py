@@ -198,6 +198,28 @@ def test_knn_properties_at_scale(eng):
     assert all(look[(j, i)] == d for (i, j), d in look.items() if (j, i) in look)
 
 
+def test_transform_saturation_and_negative_zero(eng):
+    """An absurd outlier saturates the int16 code (counted, clamped) without disturbing any other cell; values in
+    (-0.005, 0) keep their sign in the text code."""
+    n, b = 48, 256
+    h = synth.depth_hundredths(8, n, b)
+    h[7, 100] = 4_000_000                       # 40000x coverage in one bin
+    dec = h / 100.0
+    want = O.chain_arrays(dec, synth.read_counts(8, n, [1000]), num_neighbors=5, n_nbr=5)
+    res = eng.normalize(torch.from_numpy(dec.astype(np.float32)).cuda(), b, eng.Params(), want_zq=True, want_zh=True)
+    zq = res.zq.cpu().numpy()[:, :res.rw].astype(np.int64)
+    exp = want["zq"].copy()
+    big = np.abs(exp) > 32766
+    big &= exp != -32768
+    assert big.sum() >= 1 and int(res.extra["sat"].item()) == int(big.sum())
+    np.testing.assert_array_equal(zq[big], np.sign(exp[big]) * 32766)
+    negzero = zq == -32767
+    zq[negzero] = 0
+    np.testing.assert_array_equal(zq[~big], exp[~big])
+    z = O.normalize_matrix(np.where(dec[:, want["valid"]] > 0, dec[:, want["valid"]], np.nan))[0][:, want["sel"]]
+    np.testing.assert_array_equal(negzero, (np.signbit(z) & (exp == 0)))
+
+
 def test_errors_surface_as_exceptions(eng):
     from grid_b200._lib import GridB200Error
 
