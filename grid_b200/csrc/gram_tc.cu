@@ -7,35 +7,65 @@
 // result with red.global.add before they can overflow.  Nothing is ever rounded: the result is the exact integer
 // dot product, whatever K is.
 //
-// Structure (one CTA per SM, persistent over work items = (128x128 output tile, K split)):
-//   warp 0      TMA producer   cp.async.bulk.tensor 2D, 128B swizzle, 6-stage mbarrier ring of 64-wide k-blocks
-//   warp 1      MMA issuer     one elected lane, tcgen05.mma cta_group::1 kind::f16 M128 N128 K16, 2 TMEM stages
-//   warp 2      TMEM allocator
-//   warps 4-11  epilogue       lane quarter = warp%4, column half = (warp-4)/4: 64 accumulators per thread
+// Operand layout ("k-blocked"): element (row i, bin k) lives at  base + ((k/64)*slab + i)*64 + k%64  (fp16), i.e.
+// every 64-bin k-block is one contiguous slab of `slab` rows x 128 B.  A 128-row operand box of one k-block is a
+// single contiguous 16 KB read (the row-major layout this replaces cost one DRAM page and one TLB entry per row).
+//
+// One CTA PAIR (cluster 2x1x1, tcgen05 cta_group::2) per 256 x 256 output tile, persistent over work items =
+// (tile, K split).  Each CTA stages its own 128 query rows and 128 of the 256 reference rows per k-block; the
+// leader issues M=256 N=256 K=16 MMAs; each CTA's TMEM holds its 128 x 256 half of the accumulator (two stages:
+// chunk c+1 accumulates while chunk c drains).
+//   warp 0      TMA producer (both CTAs; transaction bytes land on the LEADER's full barrier) + TMEM allocator
+//               + L2 pacing (below)
+//   warp 1      MMA issuer (leader CTA only); commits are multicast to both CTAs' barriers
+//   warps 4-11  epilogue: lane quarter = warp%4, column half = (warp-4)/4, 128 int32 accumulators per thread
+//
+// L2 pacing.  K is millions of bins long, so free-running pairs drift apart along K until nothing a pair loads is
+// still in L2 when the next pair wants it (ncu, first version: 335 GB of DRAM reads for a 16.7 GB operand, 33 %
+// L2 hits).  The producers therefore publish their k-block step in a global table and do not run more than
+// `window` steps ahead of the slowest pair, which keeps the union of all in-flight operand slabs inside L2.
+// Pacing is a performance hint only: a wait that exceeds its time-out is abandoned and pacing is switched off for
+// the rest of that CTA's life, so no forward-progress assumption about other CTAs is ever needed.
+//
+// Symmetric mode (Q and R are the same matrix): only tiles on or above the diagonal are computed; a small
+// transpose kernel then copies them below the diagonal (dot[j,i] = dot[i,j]).
 #include <cuda.h>
 #include <stdlib.h>
+
+#include <algorithm>
 
 #include "common.cuh"
 
 namespace g2 {
 namespace tc {
 
-constexpr int BM = 128, BN = 128, BK = 64, UMMA_K = 16;
+constexpr int BK = 64, UMMA_K = 16;
 constexpr int STAGES = 6;
-constexpr int A_BYTES = BM * BK * 2, B_BYTES = BN * BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int TM = 256, TN = 256;           // tile of the pair
+constexpr int CTA_ROWS = 128;               // query rows / reference rows staged per CTA
+constexpr int A_BYTES = CTA_ROWS * BK * 2, B_BYTES = CTA_ROWS * BK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int ACC_STAGES = 2;
-constexpr int TMEM_COLS = ACC_STAGES * BN;  // 256 fp32 columns
-constexpr int NUM_THREADS = 384;
+constexpr int TMEM_COLS = ACC_STAGES * TN;  // 512: all of TMEM
+constexpr int NUM_THREADS = 384;            // warpgroup 0 = {TMA, MMA, 2 idle warps}, warpgroups 1-2 = epilogue
 constexpr int EPI_WARP0 = 4, EPI_WARPS = 8;
-constexpr int EPI_COLS = BN / 2;            // columns per epilogue thread
+constexpr int REGS_CTRL = 40, REGS_EPI = 232;  // setmaxnreg: 128*40 + 256*232 = 64512 <= 65536
+constexpr int EPI_COLS = TN / 2;            // 128 columns per epilogue thread
 constexpr int CHECK_EVERY = 16;             // chunks between int32 overflow checks
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int PACE = 16;                    // k-block steps between pacing checks
+constexpr long long PACE_TIMEOUT = 400000;  // cycles a producer will wait for the slowest pair (~0.2 ms)
+constexpr int MAX_PAIRS = 128;
 
 // kind::f16 instruction descriptor: D=f32 (bit 4), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24
-constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+
+// progress table of the pacing scheme: (launch epoch << 32) | k-block step, one entry per CTA pair
+__device__ unsigned long long g_pace[MAX_PAIRS];
 
 struct Work {
   int tiles_m, tiles_n, ntiles, ksplits, kb_total, kb_per_split, ck, group_m;
+  int symmetric, window;
+  unsigned epoch;
   int64_t nq, nr, ldd;
 };
 
@@ -46,9 +76,6 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 }
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done;
@@ -62,218 +89,15 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "memory");
   } while (!done);
 }
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
-      "l"(map), "r"(bar), "r"(c0), "r"(c1)
-      : "memory");
-}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t da, uint64_t db, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
-      "l"(da), "l"(db), "r"(IDESC), "r"(accumulate)
-      : "memory");
-}
 // K-major operand tile, 128-byte swizzle: 8-row groups 1024 B apart (SBO), LBO = 1 (ignored), version 1 (sm_100)
 __device__ __forceinline__ uint64_t smem_desc(uint32_t addr) {
   return (uint64_t)((addr >> 4) & 0x3FFF) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t* v) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-      : "r"(taddr));
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void red_add_s64(long long* p, long long v) {
   asm volatile("red.global.add.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
-
-// item -> (k split, tile m, tile n): k-split major so concurrent CTAs stream the same K window through L2;
-// within a split, tiles are walked in bands of group_m tile-rows so concurrent tiles share operand rows.
-__device__ __forceinline__ void decode_item(const Work& w, int item, int& ks, int& tm, int& tn) {
-  ks = item / w.ntiles;
-  const int t = item - ks * w.ntiles;
-  const int per_group = w.group_m * w.tiles_n;
-  const int g = t / per_group;
-  const int first_m = g * w.group_m;
-  const int gsize = min(w.tiles_m - first_m, w.group_m);
-  const int r = t - g * per_group;
-  tm = first_m + r % gsize;
-  tn = r / gsize;
-}
-
-__global__ void __launch_bounds__(NUM_THREADS, 1)
-k_gram_tc(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_r, const Work w,
-          long long* __restrict__ dot) {
-  extern __shared__ unsigned char smem_raw[];
-  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // 128B-swizzle atoms need 1024-byte alignment
-  const uint32_t bars = base + STAGES * STAGE_BYTES;
-  const uint32_t full0 = bars, empty0 = bars + 8 * STAGES, tfull0 = bars + 16 * STAGES, tempty0 = tfull0 + 8 * ACC_STAGES;
-  const uint32_t tmem_slot = tempty0 + 8 * ACC_STAGES;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nitems = w.ntiles * w.ksplits;
-
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) {
-      mbar_init(full0 + 8 * s, 1);
-      mbar_init(empty0 + 8 * s, 1);
-    }
-    for (int a = 0; a < ACC_STAGES; ++a) {
-      mbar_init(tfull0 + 8 * a, 1);
-      mbar_init(tempty0 + 8 * a, EPI_WARPS);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  if (warp == 2) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  uint32_t tmem_base;
-  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
-
-  if (warp == 0) {
-    // ===================================== TMA producer =====================================
-    if (lane == 0) {
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
-      asm volatile("prefetch.tensormap [%0];" ::"l"(&map_r) : "memory");
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
-        int ks, tm, tn;
-        decode_item(w, item, ks, tm, tn);
-        const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
-        for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(empty0 + 8 * stage, phase ^ 1);
-          const uint32_t fb = full0 + 8 * stage;
-          mbar_expect_tx(fb, STAGE_BYTES);
-          const uint32_t sa = base + stage * STAGE_BYTES;
-          tma_load_2d(sa, &map_q, fb, kb * BK, tm * BM);
-          tma_load_2d(sa + A_BYTES, &map_r, fb, kb * BK, tn * BN);
-          if (++stage == STAGES) stage = 0, phase ^= 1;
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===================================== MMA issuer =======================================
-    if (lane == 0) {
-      int stage = 0, acc = 0;
-      uint32_t phase = 0, acc_phase = 0;
-      for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
-        int ks, tm, tn;
-        decode_item(w, item, ks, tm, tn);
-        const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
-        for (int c0 = kb0; c0 < kb1; c0 += w.ck) {
-          const int c1 = min(kb1, c0 + w.ck);
-          mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);  // epilogue has drained this accumulator stage
-          tc_fence_after();
-          const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
-          for (int kb = c0; kb < c1; ++kb) {
-            mbar_wait(full0 + 8 * stage, phase);
-            tc_fence_after();
-            const uint32_t sa = base + stage * STAGE_BYTES;
-            const uint64_t da = smem_desc(sa), db = smem_desc(sa + A_BYTES);
-#pragma unroll
-            for (int k = 0; k < BK / UMMA_K; ++k)  // +32 bytes (2 x 16 B) per K16 step inside the swizzle atom
-              tc_mma(d_tmem, da + 2 * k, db + 2 * k, (kb > c0 || k > 0) ? 1u : 0u);
-            tc_commit(empty0 + 8 * stage);  // smem slot is free once these MMAs have read it
-            if (++stage == STAGES) stage = 0, phase ^= 1;
-          }
-          tc_commit(tfull0 + 8 * acc);  // chunk complete in TMEM
-          if (++acc == ACC_STAGES) acc = 0, acc_phase ^= 1;
-        }
-      }
-    }
-  } else if (warp >= EPI_WARP0) {
-    // ===================================== epilogue =========================================
-    const int quarter = warp & 3, half = (warp - EPI_WARP0) >> 2;
-    int acc32[EPI_COLS];
-#pragma unroll
-    for (int i = 0; i < EPI_COLS; ++i) acc32[i] = 0;
-    int acc = 0, since_check = 0;
-    uint32_t acc_phase = 0;
-    for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
-      int ks, tm, tn;
-      decode_item(w, item, ks, tm, tn);
-      const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
-      const int64_t row = (int64_t)tm * BM + quarter * 32 + lane;
-      const int64_t col0 = (int64_t)tn * BN + half * EPI_COLS;
-      long long* out = dot + row * w.ldd + col0;
-      const bool row_ok = row < w.nq;
-      for (int c0 = kb0; c0 < kb1; c0 += w.ck) {
-        mbar_wait(tfull0 + 8 * acc, acc_phase);
-        tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + half * EPI_COLS);
-        uint32_t v[EPI_COLS];
-#pragma unroll
-        for (int c = 0; c < EPI_COLS / 16; ++c) tmem_ld16(taddr + c * 16, v + c * 16);
-        tmem_ld_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(tempty0 + 8 * acc);  // TMEM stage may be overwritten
-        if (++acc == ACC_STAGES) acc = 0, acc_phase ^= 1;
-#pragma unroll
-        for (int i = 0; i < EPI_COLS; ++i) acc32[i] += __float2int_rn(__uint_as_float(v[i]));
-        if (++since_check == CHECK_EVERY) {  // keep |acc32| + 16 more chunks (< 2^24 each) below 2^31
-          since_check = 0;
-#pragma unroll
-          for (int i = 0; i < EPI_COLS; ++i) {
-            if ((unsigned)(acc32[i] + 0x70000000) > 0xE0000000u) {
-              if (row_ok && col0 + i < w.nr) red_add_s64(out + i, (long long)acc32[i]);
-              acc32[i] = 0;
-            }
-          }
-        }
-      }
-      since_check = 0;
-#pragma unroll
-      for (int i = 0; i < EPI_COLS; ++i) {
-        if (row_ok && col0 + i < w.nr && acc32[i] != 0) red_add_s64(out + i, (long long)acc32[i]);
-        acc32[i] = 0;
-      }
-    }
-  }
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 2) {
-    tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
-  }
-}
-
-
-// =========================================================================================================
-// CTA-pair version (cta_group::2): one 256 x 256 output tile per pair of SMs.  Each CTA stages its own 128
-// query rows and 128 of the 256 reference rows per k-block (32 KB, as before) but the pair performs four times
-// the MMA work on them, which is what lifts the kernel off the L2-bandwidth ceiling.  The leader CTA issues
-// tcgen05.mma.cta_group::2 (M=256, N=256); each CTA's TMEM holds its 128 x 256 half of the accumulator, drained
-// by that CTA's own 8 epilogue warps (128 int32 accumulators per thread).
-//   warp 0      TMA producer (both CTAs; transaction bytes land on the LEADER's full barrier) + TMEM allocator
-//   warp 1      MMA issuer (leader CTA only); commits are multicast to both CTAs' barriers
-//   warps 2-9   epilogue: lane quarter = warp%4, column half = (warp-2)/4
-// =========================================================================================================
-namespace pair {
-
-constexpr int TM = 256, TN = 256;           // tile of the pair
-constexpr int CTA_ROWS = 128;               // query rows / reference rows staged per CTA
-constexpr int NUM_THREADS = 384;            // warpgroup 0 = {TMA, MMA, 2 idle warps}, warpgroups 1-2 = epilogue
-constexpr int EPI_WARP0 = 4, EPI_WARPS = 8;
-constexpr int REGS_CTRL = 40, REGS_EPI = 232;  // setmaxnreg: 128*40 + 256*232 = 64512 <= 65536
-constexpr int EPI_COLS = TN / 2;            // 128 columns per epilogue thread
-constexpr int TMEM_COLS = ACC_STAGES * TN;  // 512: all of TMEM
-constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
-
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
@@ -290,10 +114,11 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
-__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, uint32_t leader_bar, int c0, int c1) {
+// one k-block (c2) x 128 rows starting at c1 x all 64 bins of the block
+__device__ __forceinline__ void tma_load_pair(uint32_t dst, const CUtensorMap* map, uint32_t leader_bar, int row, int kb) {
   asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
-      "l"(map), "r"(leader_bar), "r"(c0), "r"(c1)
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+      "l"(map), "r"(leader_bar), "r"(0), "r"(row), "r"(kb)
       : "memory");
 }
 __device__ __forceinline__ void tc_commit_pair(uint32_t bar) {  // arrive on this barrier in BOTH CTAs
@@ -319,12 +144,74 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
         "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
       : "r"(taddr));
 }
+// tcgen05.wait::ld that also tells the compiler the 32 registers of the pending load are (re)defined here, so no
+// use of them can be scheduled above the wait.
+__device__ __forceinline__ void tmem_ld_wait32(uint32_t* v) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+                 "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]),
+                 "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]),
+                 "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]),
+                 "+r"(v[30]), "+r"(v[31])
+               :
+               : "memory");
+}
+
+// item -> (k split, tile m, tile n).  K-split major, so that the pairs of one wave stream the same K window.
+// General mode: tiles walked in bands of group_m tile-rows so concurrent tiles share operand rows.
+// Symmetric mode: the tiles_m*(tiles_m+1)/2 tiles with tn >= tm, row by row.
+__device__ __forceinline__ void decode_item(const Work& w, int item, int& ks, int& tm, int& tn) {
+  ks = item / w.ntiles;
+  int t = item - ks * w.ntiles;
+  if (w.symmetric) {
+    int rowlen = w.tiles_n;
+    tm = 0;
+    while (t >= rowlen) t -= rowlen, --rowlen, ++tm;
+    tn = tm + t;
+    return;
+  }
+  const int per_group = w.group_m * w.tiles_n;
+  const int g = t / per_group;
+  const int first_m = g * w.group_m;
+  const int gsize = min(w.tiles_m - first_m, w.group_m);
+  const int r = t - g * per_group;
+  tm = first_m + r % gsize;
+  tn = r / gsize;
+}
+
+// Whole warp 0.  Publish this pair's step, then hold the producer until the slowest pair is within `window` steps.
+__device__ __forceinline__ void pace(const Work& w, int pair_id, int npairs, uint32_t rank, int lane, unsigned step,
+                                     bool& enabled) {
+  if (rank == 0 && lane == 0)
+    *reinterpret_cast<volatile unsigned long long*>(&g_pace[pair_id]) = ((unsigned long long)w.epoch << 32) | step;
+  if (!enabled || step < (unsigned)w.window) return;
+  const unsigned need = step - (unsigned)w.window;
+  const long long t0 = clock64();
+  for (;;) {
+    unsigned m = 0xffffffffu;
+    for (int p = lane; p < npairs; p += 32) {
+      const unsigned long long v = *reinterpret_cast<volatile unsigned long long*>(&g_pace[p]);
+      const unsigned e = (unsigned)(v >> 32);
+      // an older epoch = that pair has not started in this launch; a newer one = a later launch owns the table
+      const unsigned s = e == w.epoch ? (unsigned)v : (e < w.epoch ? 0u : 0xffffffffu);
+      m = min(m, s);
+    }
+    m = __reduce_min_sync(0xffffffffu, m);
+    if (m >= need) return;
+    if (clock64() - t0 > PACE_TIMEOUT) {  // warp-uniform enough: every lane sees a similar clock; decide by lane 0
+      enabled = false;
+    }
+    enabled = __shfl_sync(0xffffffffu, (int)enabled, 0) != 0;
+    if (!enabled) return;
+    __nanosleep(200);
+  }
+}
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_r, const Work w,
                long long* __restrict__ dot) {
   extern __shared__ unsigned char smem_raw[];
-  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // 128B-swizzle atoms need 1024-byte alignment
   const uint32_t bars = base + STAGES * STAGE_BYTES;
   const uint32_t full0 = bars, empty0 = bars + 8 * STAGES, tfull0 = bars + 16 * STAGES, tempty0 = tfull0 + 8 * ACC_STAGES;
   const uint32_t tmem_slot = tempty0 + 8 * ACC_STAGES;
@@ -360,25 +247,35 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
     if (lane == 0) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_q) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_r) : "memory");
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int item = pair_id; item < nitems; item += npairs) {
-        int ks, tm, tn;
-        decode_item(w, item, ks, tm, tn);
-        const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
-        const int qrow = tm * TM + (int)rank * CTA_ROWS, rrow = tn * TN + (int)rank * CTA_ROWS;
-        for (int kb = kb0; kb < kb1; ++kb) {
+    }
+    int stage = 0;
+    uint32_t phase = 0;
+    unsigned step = 0;
+    bool pacing = w.window > 0 && npairs > 1;
+    for (int item = pair_id; item < nitems; item += npairs) {
+      int ks, tm, tn;
+      decode_item(w, item, ks, tm, tn);
+      const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
+      const int qrow = tm * TM + (int)rank * CTA_ROWS, rrow = tn * TN + (int)rank * CTA_ROWS;
+      for (int kb = kb0; kb < kb1; ++kb, ++step) {
+        if (step % PACE == 0) {
+          pace(w, pair_id, npairs, rank, lane, step, pacing);
+          __syncwarp();
+        }
+        if (lane == 0) {
           mbar_wait(empty0 + 8 * stage, phase ^ 1);
           const uint32_t leader_full = map_to_cta(full0 + 8 * stage, 0);
           if (rank == 0) mbar_expect_tx(full0 + 8 * stage, 2 * STAGE_BYTES);  // bytes of both CTAs
           else mbar_arrive_cluster(leader_full);
           const uint32_t sa = base + stage * STAGE_BYTES;
-          tma_load_2d_pair(sa, &map_q, leader_full, kb * BK, qrow);
-          tma_load_2d_pair(sa + A_BYTES, &map_r, leader_full, kb * BK, rrow);
-          if (++stage == STAGES) stage = 0, phase ^= 1;
+          tma_load_pair(sa, &map_q, leader_full, qrow, kb);
+          tma_load_pair(sa + A_BYTES, &map_r, leader_full, rrow, kb);
         }
+        if (++stage == STAGES) stage = 0, phase ^= 1;
       }
     }
+    if (rank == 0 && lane == 0)  // finished: never hold anybody back
+      *reinterpret_cast<volatile unsigned long long*>(&g_pace[pair_id]) = ((unsigned long long)w.epoch << 32) | 0xffffffffu;
   } else if (warp == 1) {
     // ===================================== MMA issuer (leader only) =========================
     if (rank == 0 && lane == 0) {
@@ -390,7 +287,7 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
         for (int c0 = kb0; c0 < kb1; c0 += w.ck) {
           const int c1 = min(kb1, c0 + w.ck);
-          mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
+          mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);  // both CTAs' epilogues have drained this TMEM stage
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + (uint32_t)(acc * TN);
           for (int kb = c0; kb < c1; ++kb) {
@@ -399,12 +296,12 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
             const uint32_t sa = base + stage * STAGE_BYTES;
             const uint64_t da = smem_desc(sa), db = smem_desc(sa + A_BYTES);
 #pragma unroll
-            for (int k = 0; k < BK / UMMA_K; ++k)
+            for (int k = 0; k < BK / UMMA_K; ++k)  // +32 bytes (2 x 16 B) per K16 step inside the swizzle atom
               tc_mma_pair(d_tmem, da + 2 * k, db + 2 * k, (kb > c0 || k > 0) ? 1u : 0u);
-            tc_commit_pair(empty0 + 8 * stage);
+            tc_commit_pair(empty0 + 8 * stage);  // smem slot is free (in both CTAs) once these MMAs have read it
             if (++stage == STAGES) stage = 0, phase ^= 1;
           }
-          tc_commit_pair(tfull0 + 8 * acc);
+          tc_commit_pair(tfull0 + 8 * acc);  // chunk complete in TMEM
           if (++acc == ACC_STAGES) acc = 0, acc_phase ^= 1;
         }
       }
@@ -424,27 +321,35 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
       const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
       const int64_t row = (int64_t)tm * TM + rank * CTA_ROWS + quarter * 32 + lane;
       const int64_t col0 = (int64_t)tn * TN + half * EPI_COLS;
-      long long* out = dot + row * w.ldd + col0;
+      long long* out = dot + row * w.ldd + col0;           // dot[row, col0 + i]
       const bool row_ok = row < w.nq;
       for (int c0 = kb0; c0 < kb1; c0 += w.ck) {
         mbar_wait(tfull0 + 8 * acc, acc_phase);
         tc_fence_after();
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * TN + half * EPI_COLS);
+        uint32_t va[32], vb[32];
+        tmem_ld32(taddr, va);
+        tmem_ld_wait32(va);
+        tmem_ld32(taddr + 32, vb);
 #pragma unroll
-        for (int c = 0; c < EPI_COLS / 16; ++c) {
-          uint32_t v[16];
-          tmem_ld16(taddr + c * 16, v);
-          tmem_ld_wait();
-          if (c == EPI_COLS / 16 - 1) {  // everything is in registers: hand the TMEM stage back to the MMA warp
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive_cluster(map_to_cta(tempty0 + 8 * acc, 0));
-          }
+        for (int i = 0; i < 32; ++i) acc32[i] += __float2int_rn(__uint_as_float(va[i]));
+        tmem_ld_wait32(vb);
+        tmem_ld32(taddr + 64, va);
 #pragma unroll
-          for (int i = 0; i < 16; ++i) acc32[c * 16 + i] += __float2int_rn(__uint_as_float(v[i]));
-        }
+        for (int i = 0; i < 32; ++i) acc32[32 + i] += __float2int_rn(__uint_as_float(vb[i]));
+        tmem_ld_wait32(va);
+        tmem_ld32(taddr + 96, vb);
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc32[64 + i] += __float2int_rn(__uint_as_float(va[i]));
+        tmem_ld_wait32(vb);
+        // everything is in registers: hand the TMEM stage back to the MMA warp
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(map_to_cta(tempty0 + 8 * acc, 0));
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc32[96 + i] += __float2int_rn(__uint_as_float(vb[i]));
         if (++acc == ACC_STAGES) acc = 0, acc_phase ^= 1;
-        if (++since_check == CHECK_EVERY) {
+        if (++since_check == CHECK_EVERY) {  // keep |acc32| + 16 more chunks (< 2^24 each) below 2^31
           since_check = 0;
 #pragma unroll
           for (int i = 0; i < EPI_COLS; ++i) {
@@ -471,7 +376,23 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
   }
 }
 
-}  // namespace pair
+// dot[j,i] = dot[i,j] for every element of the 256 x 256 tiles strictly above the tile diagonal (symmetric mode).
+// Block = one 32 x 32 patch, transposed through shared memory so both the read and the write are coalesced.
+__global__ void __launch_bounds__(256) k_mirror_upper(long long* __restrict__ dot, int64_t n, int64_t ldd) {
+  __shared__ long long t[32][33];
+  const int bi = blockIdx.y, bj = blockIdx.x;           // 32-row / 32-column patch indices
+  if ((bj * 32) / TN <= (bi * 32) / TM) return;         // on or below the tile diagonal: already complete
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t i = (int64_t)bi * 32 + r, j = (int64_t)bj * 32 + tx;
+    if (i < n && j < n) t[r][tx] = dot[i * ldd + j];
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const int64_t j = (int64_t)bj * 32 + r, i = (int64_t)bi * 32 + tx;
+    if (i < n && j < n) dot[j * ldd + i] = t[tx][r];
+  }
+}
 
 // ---- host side ------------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -490,14 +411,15 @@ static EncodeTiledFn get_encode() {
   return fn;
 }
 
-static int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t kdim, int64_t ld, int box_rows) {
+// 3-D view of a k-blocked operand: (bin in block: 64) x (row: rows) x (k-block: nkb); rows beyond `rows` read as 0
+static int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t nkb, int64_t slab) {
   EncodeTiledFn enc = get_encode();
   G2_REQUIRE(enc != nullptr, GRIDB200_ENODEV, "cuTensorMapEncodeTiled is not available from this driver");
-  const cuuint64_t dims[2] = {(cuuint64_t)kdim, (cuuint64_t)rows};
-  const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
-  const cuuint32_t estr[2] = {1, 1};
-  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+  const cuuint64_t dims[3] = {(cuuint64_t)BK, (cuuint64_t)rows, (cuuint64_t)nkb};
+  const cuuint64_t strides[2] = {(cuuint64_t)BK * 2, (cuuint64_t)slab * BK * 2};
+  const cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)CTA_ROWS, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(ptr), dims, strides, box, estr,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   G2_REQUIRE(r == CUDA_SUCCESS, GRIDB200_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
@@ -507,8 +429,8 @@ static int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t kdi
 }  // namespace tc
 }  // namespace g2
 
-int gridb200_gram_tc(const void* zq, int64_t nq, int64_t ldq, const void* zr, int64_t nr, int64_t ldr, int64_t kdim,
-                     int32_t vmax, int64_t* dot, int64_t ldd, int accumulate, void* stream) {
+int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, int64_t nr, int64_t slabr,
+                     int64_t kdim, int32_t vmax, int64_t* dot, int64_t ldd, int accumulate, void* stream) {
   using namespace g2;
   using namespace g2::tc;
   // largest chunk (in 64-wide k-blocks) whose partial sums stay strictly below 2^24
@@ -526,31 +448,31 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t ldq, const void* zr, in
     G2_CUDA(cudaGetDeviceProperties(&prop, dev));
     G2_REQUIRE(prop.major == 10, GRIDB200_ENODEV, "tcgen05 path needs an sm_100 device (found sm_%d%d)", prop.major,
                prop.minor);
-    G2_CUDA(cudaFuncSetAttribute(k_gram_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    G2_CUDA(cudaFuncSetAttribute(k_gram_tc_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     sms = prop.multiProcessorCount;
   }
+  const int64_t nkb = kdim / BK;
   CUtensorMap mq, mr;
-  if (int e = make_map(&mq, zq, nq, kdim, ldq, BM)) return e;
-  if (int e = make_map(&mr, zr, nr, kdim, ldr, BN)) return e;
+  if (int e = make_map(&mq, zq, nq, nkb, slabq)) return e;
+  if (int e = make_map(&mr, zr, nr, nkb, slabr)) return e;
 
-  // GRIDB200_GRAM_1CTA=1 selects the single-CTA kernel (debugging aid); the CTA-pair kernel is the product path
-  static int use_pair = -1;
-  if (use_pair < 0) {
-    const char* e = getenv("GRIDB200_GRAM_1CTA");
-    use_pair = (e && e[0] == '1') ? 0 : 1;
-    if (use_pair)
-      G2_CUDA(cudaFuncSetAttribute(pair::k_gram_tc_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+  static int no_sym = -1, no_pace = -1;  // debugging switches
+  if (no_sym < 0) {
+    const char* e = getenv("GRIDB200_GRAM_NOSYM");
+    no_sym = (e && e[0] == '1') ? 1 : 0;
+    e = getenv("GRIDB200_GRAM_NOPACE");
+    no_pace = (e && e[0] == '1') ? 1 : 0;
   }
-  const int tile_m = use_pair ? pair::TM : BM, tile_n = use_pair ? pair::TN : BN;
-  const int workers = use_pair ? sms / 2 : sms;
+  const int workers = std::min(sms / 2, MAX_PAIRS);
   Work w;
   w.nq = nq, w.nr = nr, w.ldd = ldd;
-  w.tiles_m = (int)((nq + tile_m - 1) / tile_m);
-  w.tiles_n = (int)((nr + tile_n - 1) / tile_n);
-  w.ntiles = w.tiles_m * w.tiles_n;
-  w.kb_total = (int)(kdim / BK);
+  w.symmetric = (!no_sym && zq == zr && nq == nr && slabq == slabr) ? 1 : 0;
+  w.tiles_m = (int)((nq + TM - 1) / TM);
+  w.tiles_n = (int)((nr + TN - 1) / TN);
+  w.ntiles = w.symmetric ? w.tiles_m * (w.tiles_m + 1) / 2 : w.tiles_m * w.tiles_n;
+  w.kb_total = (int)nkb;
   w.ck = (int)std::min<int64_t>(ck, w.kb_total);
-  w.group_m = use_pair ? 4 : 8;
+  w.group_m = 4;
   // K splits: best wave efficiency over the workers, each split at least 4 chunks long
   const int chunks = (w.kb_total + w.ck - 1) / w.ck;
   int best_s = 1;
@@ -565,13 +487,26 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t ldq, const void* zr, in
   const int cps = (chunks + best_s - 1) / best_s;
   w.kb_per_split = cps * w.ck;
   w.ksplits = (w.kb_total + w.kb_per_split - 1) / w.kb_per_split;
+  // pacing window: the operand rows one wave touches, times `window` k-blocks, should stay near 32 MB
+  {
+    const int64_t wave_rows = w.symmetric ? nq
+                                          : std::min<int64_t>(nq, (int64_t)w.group_m * TM) +
+                                                std::min<int64_t>(nr, (int64_t)(workers / w.group_m + 1) * TN);
+    int64_t win = (32LL << 20) / (wave_rows * BK * 2);
+    win = std::max<int64_t>(2 * PACE, std::min<int64_t>(win, 16 * PACE)) / PACE * PACE;
+    w.window = no_pace ? 0 : (int)win;
+  }
+  static std::atomic<unsigned> epoch{0};
+  w.epoch = epoch.fetch_add(1) + 1;
   if (!accumulate) G2_CUDA(cudaMemset2DAsync(dot, ldd * sizeof(int64_t), 0, nr * sizeof(int64_t), nq, st));
   const long long items = (long long)w.ntiles * w.ksplits;
   const int nwork = (int)std::min<long long>(items, workers);
-  if (use_pair)
-    pair::k_gram_tc_pair<<<2 * nwork, pair::NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, reinterpret_cast<long long*>(dot));
-  else
-    k_gram_tc<<<nwork, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, reinterpret_cast<long long*>(dot));
+  k_gram_tc_pair<<<2 * nwork, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, reinterpret_cast<long long*>(dot));
   G2_LAUNCHED();
+  if (w.symmetric && w.tiles_m > 1) {
+    const unsigned nb = (unsigned)((nq + 31) / 32);
+    k_mirror_upper<<<dim3(nb, nb), 256, 0, st>>>(reinterpret_cast<long long*>(dot), nq, ldd);
+    G2_LAUNCHED();
+  }
   return 0;
 }

@@ -26,8 +26,9 @@ __global__ void __launch_bounds__(256) k_gram_simt(const __half* __restrict__ q,
     for (int e = threadIdx.x; e < kTile * kKT; e += 256) {
       const int row = e / kKT, kk = e % kKT;
       const int64_t k = k0 + kk;
-      sq[row][kk] = (i0 + row < nq && k < kdim) ? __half2int_rn(q[(i0 + row) * ldq + k]) : 0;
-      sr[row][kk] = (j0 + row < nr && k < kdim) ? __half2int_rn(r[(j0 + row) * ldr + k]) : 0;
+      // k-blocked operands: element (row, k) at ((k/64)*slab + row)*64 + k%64
+      sq[row][kk] = (i0 + row < nq && k < kdim) ? __half2int_rn(q[((k >> 6) * ldq + i0 + row) * 64 + (k & 63)]) : 0;
+      sr[row][kk] = (j0 + row < nr && k < kdim) ? __half2int_rn(r[((k >> 6) * ldr + j0 + row) * 64 + (k & 63)]) : 0;
     }
     __syncthreads();
 #pragma unroll 8
@@ -73,9 +74,10 @@ extern "C" int gridb200_gram(const void* zq, int64_t nq, int64_t ldq, const void
   using namespace g2;
   G2_REQUIRE(zq && zr && dot, GRIDB200_EINVAL, "null pointer");
   G2_REQUIRE(nq > 0 && nr > 0 && kdim > 0 && ldd >= nr, GRIDB200_EINVAL, "bad shape");
-  G2_REQUIRE(ldq >= kdim && ldr >= kdim && ldq % 8 == 0 && ldr % 8 == 0 && kdim % 64 == 0, GRIDB200_EINVAL,
-             "kdim must be a multiple of 64 and the leading dimensions multiples of 8 (got kdim=%lld ldq=%lld ldr=%lld)",
-             (long long)kdim, (long long)ldq, (long long)ldr);
+  G2_REQUIRE(ldq >= nq && ldr >= nr && kdim % 64 == 0, GRIDB200_EINVAL,
+             "kdim must be a multiple of 64 and each k-block slab must hold its rows (got kdim=%lld nq=%lld slabq=%lld "
+             "nr=%lld slabr=%lld)",
+             (long long)kdim, (long long)nq, (long long)ldq, (long long)nr, (long long)ldr);
   G2_REQUIRE(((reinterpret_cast<uintptr_t>(zq) | reinterpret_cast<uintptr_t>(zr)) & 15) == 0, GRIDB200_EINVAL,
              "operands must be 16-byte aligned");
   G2_REQUIRE(vmax > 0 && vmax <= 2048, GRIDB200_EDOMAIN, "vmax=%d outside (0, 2048]: fp16 cannot hold it exactly",

@@ -297,7 +297,10 @@ constexpr int kTB = 8;                        // rows per batch
 constexpr int kStageRow = kColsPerBlock + 16;  // halves per staged row (+8 alignment shift, +8 dump slots)
 constexpr int kDump = kStageRow - 1;          // where unselected bins drop their (ignored) result
 
-template <typename T>
+// kBlocked = false: row-major output, element (r, p) at out[r*ld_out + p].
+// kBlocked = true : k-blocked operand layout of the Gram kernel, element (r, p) at out[((p/64)*ld_out + r)*64 + p%64]
+//                   (ld_out = rows per 64-bin slab); an aligned 8-element chunk never straddles two k-blocks.
+template <typename T, bool kBlocked>
 __device__ __forceinline__ void copy_out_rows(const T* __restrict__ stage, T* __restrict__ out, int64_t ld_out,
                                               int64_t row0, int nrows, int p0, int len) {
   // stage[r][shift + e] holds output element p0 + e of row row0 + r, shift = p0 % 8, so 16-byte chunk q of the
@@ -308,8 +311,10 @@ __device__ __forceinline__ void copy_out_rows(const T* __restrict__ stage, T* __
     const int e0 = 8 * q - shift;  // first element of this chunk relative to p0
     const bool whole = e0 >= 0 && e0 + 8 <= len;
     const T* src = stage + 8 * q;
-    T* dst = out + row0 * ld_out + (p0 - shift) + 8 * q;
-    for (int r = 0; r < nrows; ++r, src += kStageRow, dst += ld_out) {
+    const int64_t pe = (int64_t)(p0 - shift) + 8 * q;  // first element of the chunk in the output row
+    T* dst = kBlocked ? out + ((pe >> 6) * ld_out + row0) * 64 + (pe & 63) : out + row0 * ld_out + pe;
+    const int64_t step = kBlocked ? 64 : ld_out;
+    for (int r = 0; r < nrows; ++r, src += kStageRow, dst += step) {
       if (whole) {
         *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
       } else {
@@ -453,8 +458,8 @@ __global__ void __launch_bounds__(kThreads) k_transform(const float* __restrict_
       }
     }
     __syncthreads();
-    if (kZq) copy_out_rows<int16_t>(s_zq, zq, ldq, r0 + rb, nr, p0, len);
-    if (kZh) copy_out_rows<__half>(s_zh, zh, ldh, r0 + rb, nr, p0, len);
+    if (kZq) copy_out_rows<int16_t, false>(s_zq, zq, ldq, r0 + rb, nr, p0, len);
+    if (kZh) copy_out_rows<__half, true>(s_zh, zh, ldh, r0 + rb, nr, p0, len);
     __syncthreads();
   }
   if (kZh) {
@@ -470,13 +475,14 @@ __global__ void __launch_bounds__(kThreads) k_knn_prepare(const int16_t* __restr
                                                           unsigned long long* __restrict__ norms) {
   const int64_t i = blockIdx.x;
   unsigned long long acc = 0;
-  for (int64_t j = threadIdx.x; j < ldh; j += kThreads) {
+  const int64_t kdim = (rw + 63) / 64 * 64;  // zero padded to whole k-blocks
+  for (int64_t j = threadIdx.x; j < kdim; j += kThreads) {
     int c = 0;
     if (j < rw) {
       const int v = zq[i * ldq + j];
       if (v > -32767 && (!keep || keep[j])) c = max(-zclip, min(zclip, v));
     }
-    zh[i * ldh + j] = __int2half_rn(c);
+    zh[((j >> 6) * ldh + i) * 64 + (j & 63)] = __int2half_rn(c);  // k-blocked, ldh = rows per slab
     acc += (unsigned)(c * c);
   }
   acc = (unsigned long long)warp_sum((long long)acc);
@@ -620,8 +626,8 @@ extern "C" int gridb200_transform(const float* depth, int64_t n, int64_t b, int6
              "zh needs norms and 0 < zclip <= 2048 (fp16 holds integers exactly up to 2048)");
   G2_REQUIRE(!zq || (ldq % 8 == 0 && (reinterpret_cast<uintptr_t>(zq) & 15) == 0), GRIDB200_EINVAL,
              "zq must be 16-byte aligned with ldq a multiple of 8");
-  G2_REQUIRE(!zh || (ldh % 8 == 0 && (reinterpret_cast<uintptr_t>(zh) & 15) == 0), GRIDB200_EINVAL,
-             "zh must be 16-byte aligned with ldh a multiple of 8");
+  G2_REQUIRE(!zh || (ldh >= n && (reinterpret_cast<uintptr_t>(zh) & 15) == 0), GRIDB200_EINVAL,
+             "zh must be 16-byte aligned with at least n rows per k-block slab");
   const int64_t cb = (b + kColsPerBlock - 1) / kColsPerBlock;
   const int64_t slabs = (n + kTransformSlab - 1) / kTransformSlab;
   G2_REQUIRE(slabs <= 65535, GRIDB200_EINVAL, "too many row slabs");
@@ -644,7 +650,7 @@ extern "C" int gridb200_transform(const float* depth, int64_t n, int64_t b, int6
 
 extern "C" int gridb200_knn_prepare(const int16_t* zq, int64_t n, int64_t rw, int64_t ldq, const uint8_t* keep,
                                     int32_t zclip, void* zh, int64_t ldh, int64_t* norms, void* stream) {
-  G2_REQUIRE(zq && zh && norms && n > 0 && rw >= 0 && ldq >= rw && ldh >= rw, GRIDB200_EINVAL, "bad argument");
+  G2_REQUIRE(zq && zh && norms && n > 0 && rw >= 0 && ldq >= rw && ldh >= n, GRIDB200_EINVAL, "bad argument");
   G2_REQUIRE(zclip > 0 && zclip <= 2048, GRIDB200_EINVAL, "0 < zclip <= 2048 required");
   G2_REQUIRE(n < (1LL << 31), GRIDB200_EINVAL, "too many rows");
   k_knn_prepare<<<(unsigned)n, kThreads, 0, as_stream(stream)>>>(zq, rw, ldq, keep, zclip, static_cast<__half*>(zh),

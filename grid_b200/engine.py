@@ -205,13 +205,13 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
             zq[:, rw_local:] = -32768
     if want_zh:
         ldh = (rw_local + 63) // 64 * 64
-        zh = torch.empty((n, ldh), dtype=torch.float16, device=dev)
+        zh = torch.empty((ldh // 64, n, 64), dtype=torch.float16, device=dev)  # k-blocked: [k-block, row, bin]
         if ldh > rw_local:
-            zh[:, rw_local:] = 0
+            zh[-1, :, rw_local % 64:] = 0
         norms = torch.zeros(n, **i64)
     with _mark("transform"):
         call("gridb200_transform", ptr(depth), n, b, ld, ptr(row_factor), ptr(mu), ptr(sel_pos), ptr(keep), ptr(info),
-             p.zclip, ptr(zq), ldq, ptr(zh), ldh, ptr(norms), ptr(sat), st)
+             p.zclip, ptr(zq), ldq, ptr(zh), n, ptr(norms), ptr(sat), st)
     if want_zh:
         _all_reduce(norms, group)
     res.zq, res.zh, res.kdim, res.norms = zq, zh, ldh, norms
@@ -223,20 +223,27 @@ def prepare_from_zq(zq: torch.Tensor, rw: int, keep: torch.Tensor | None, zclip:
     """Operand + exact norms from a hundredths matrix read back from a step-4 file (find_neighbors.py:57-65)."""
     n, ldq = zq.shape[0], zq.stride(0)
     ldh = max(64, (rw + 63) // 64 * 64)
-    zh = torch.empty((n, ldh), dtype=torch.float16, device=zq.device)
+    zh = torch.zeros((ldh // 64, n, 64), dtype=torch.float16, device=zq.device)
     norms = torch.empty(n, dtype=torch.int64, device=zq.device)
-    call("gridb200_knn_prepare", ptr(zq), n, rw, ldq, ptr(keep), zclip, ptr(zh), ldh, ptr(norms), _stream())
+    call("gridb200_knn_prepare", ptr(zq), n, rw, ldq, ptr(keep), zclip, ptr(zh), n, ptr(norms), _stream())
     return zh, ldh, norms
+
+
+def zh_rowmajor(zh: torch.Tensor) -> torch.Tensor:
+    """[n, kdim] view-copy of a k-blocked operand (tests and debugging)."""
+    return zh.permute(1, 0, 2).reshape(zh.shape[1], zh.shape[0] * 64)
 
 
 def knn(zh: torch.Tensor, kdim: int, norms: torch.Tensor, k: int, vmax: int, impl: int = 0, group=None,
         max_block_bytes: int = 2 << 30):
     """Exact k nearest neighbours of every row among all rows (self excluded): (idx[n,k] int32, d2[n,k] int64).
 
+    zh is the k-blocked operand [kdim/64, n, 64] written by gridb200_transform / gridb200_knn_prepare.
     d2 is in units of 1e-4 (hundredths squared).  Rows with fewer than k candidates are padded with -1.
     Bin-sharded multi-GPU: each rank contributes the Gram partial of its bins; partials are all-reduced.
     """
-    n, ld = zh.shape[0], zh.stride(0)
+    assert zh.dim() == 3 and zh.shape[2] == 64 and zh.is_contiguous() and zh.shape[0] * 64 == kdim, "zh is [kdim/64, n, 64]"
+    n = zh.shape[1]
     dev, st = zh.device, _stream()
     if impl == 0 and vmax > 511:
         impl = 1  # |v| > 511: a 64-wide fp32 chunk is no longer exact; the integer SIMT kernel takes over (still GPU)
@@ -251,7 +258,7 @@ def knn(zh: torch.Tensor, kdim: int, norms: torch.Tensor, k: int, vmax: int, imp
         nq = min(qb, n - q0)
         dot = torch.empty((nq, ldd), dtype=torch.int64, device=dev)
         with _mark("gram"):
-            call("gridb200_gram", zh.data_ptr() + q0 * ld * 2, nq, ld, ptr(zh), n, ld, kdim, vmax, ptr(dot), ldd, 0,
+            call("gridb200_gram", zh.data_ptr() + q0 * 64 * 2, nq, n, ptr(zh), n, n, kdim, vmax, ptr(dot), ldd, 0,
                  impl, st)
         _all_reduce(dot, group)
         with _mark("topk"):
@@ -297,7 +304,7 @@ def run_chain(depth: torch.Tensor, b: int, counts: torch.Tensor, p: Params, impl
     if res.rw == 0:
         raise ValueError("no bins selected")
     if res.zh is None:  # this rank's slice holds no selected bin: contribute a zero partial
-        res.zh = torch.zeros((res.n, 64), dtype=torch.float16, device=depth.device)
+        res.zh = torch.zeros((1, res.n, 64), dtype=torch.float16, device=depth.device)
         res.kdim, res.norms = 64, torch.zeros(res.n, dtype=torch.int64, device=depth.device)
         _all_reduce(res.norms, group)
     idx, d2 = knn(res.zh, res.kdim, res.norms, p.num_neighbors, p.zclip, impl=impl, group=group)

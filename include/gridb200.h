@@ -112,31 +112,38 @@ GRIDB200_API int gridb200_knn_col_filter(const double* ratio, const int32_t* sel
  *   z = ((depth/rowmean) - mu_j) / sqrt(mu_j) * zscale          fp64, then printf-exact rounding to hundredths
  *   zq[i, sel_pos[j]] = hundredths(z)  (GRIDB200_ZQ_NA where absent, GRIDB200_ZQ_NEG_ZERO for "-0.00";
  *                                       saturates at +-GRIDB200_ZQ_LIMIT, counted in *sat)
- *   zh[i, sel_pos[j]] = fp16(clip(hundredths(z), +-zclip))  with NA -> 0 and 0 where keep[j] == 0
- *   norms[i] += sum_j zh[i,j]^2 (exact int64; caller zeroes it)
- * zq and zh are optional (either may be null); ldq/ldh in elements; pad columns [Rw, ldh) of zh must be
- * zeroed by the caller.  `info` is gridb200_select's output (zscale is read on the device). */
+ *   zh(i, sel_pos[j]) = fp16(clip(hundredths(z), +-zclip))  with NA -> 0 and 0 where keep[j] == 0
+ *   norms[i] += sum_j zh(i,j)^2 (exact int64; caller zeroes it)
+ * zq and zh are optional (either may be null).  zq is row-major with ldq in elements.  zh is the K-BLOCKED
+ * operand of gridb200_gram: element (row i, compact bin p) lives at zh[((p/64)*zh_slab + i)*64 + p%64], i.e.
+ * each 64-bin k-block is one contiguous slab of zh_slab (>= n) rows x 128 bytes; the pad bins [Rw, ceil64(Rw))
+ * of the last k-block must be zeroed by the caller.  `info` is gridb200_select's output (zscale is read on
+ * the device). */
 GRIDB200_API int gridb200_transform(const float* depth, int64_t n, int64_t b, int64_t ld,
                        const double* row_factor, const double* mu,
                        const int32_t* sel_pos, const uint8_t* keep, const double* info, int32_t zclip,
-                       int16_t* zq, int64_t ldq, void* zh, int64_t ldh, int64_t* norms,
+                       int16_t* zq, int64_t ldq, void* zh, int64_t zh_slab, int64_t* norms,
                        unsigned long long* sat, void* stream);
 
 /* ------------------------------------------------------------------ step 5: find_neighbors --------------- */
 
 /* zq (as read back from a step-4 file) -> tensor-core operand: clip to +-zclip, NA -> 0, zero dropped bins,
- * fp16; norms[i] = exact sum of squares (overwritten) (find_neighbors.py:57-65). keep may be null. */
+ * fp16 in the k-blocked layout described at gridb200_transform (all ceil64(rw) bins are written, pad = 0);
+ * norms[i] = exact sum of squares (overwritten) (find_neighbors.py:57-65). keep may be null. */
 GRIDB200_API int gridb200_knn_prepare(const int16_t* zq, int64_t n, int64_t rw, int64_t ldq, const uint8_t* keep,
-                         int32_t zclip, void* zh, int64_t ldh, int64_t* norms, void* stream);
+                         int32_t zclip, void* zh, int64_t zh_slab, int64_t* norms, void* stream);
 
 /* Exact Gram block: dot[i,j] (+)= sum_k q[i,k]*r[j,k] over kdim bins, operands fp16 holding integers with
  * |v| <= vmax (<= 2048).  This is the -2*X.Y^T term of sklearn's EuclideanArgKmin64, which the reference
  * reaches through NearestNeighbors.kneighbors (find_neighbors.py:207-213).
  *   impl 0: tcgen05 tensor cores + TMA (sm_100a); fp32 TMEM accumulation over chunks short enough to stay
  *           below 2^24 (exact), drained into int64.        impl 1: plain SIMT integer kernel (cross-check).
- * ldq/ldr multiples of 8 elements, base pointers 16-byte aligned, kdim a multiple of 64 (zero padded).
- * accumulate != 0 adds to dot (bin-sharded multi-GPU and K-blocked calls). */
-GRIDB200_API int gridb200_gram(const void* zq_f16, int64_t nq, int64_t ldq, const void* zr_f16, int64_t nr, int64_t ldr,
+ * Operands are K-BLOCKED (see gridb200_transform): element (i,k) at base[((k/64)*slab + i)*64 + k%64]; a block
+ * of rows starting at row q0 of a larger operand is passed as base + q0*64 with the same slab.  Base pointers
+ * 16-byte aligned, kdim a multiple of 64 (zero padded), slabq >= nq, slabr >= nr.
+ * When both operands are the same matrix (same pointer, rows and slab) impl 0 computes only the tiles on or
+ * above the diagonal and mirrors them.  accumulate != 0 adds to dot (bin-sharded multi-GPU, K-blocked calls). */
+GRIDB200_API int gridb200_gram(const void* zq_f16, int64_t nq, int64_t slabq, const void* zr_f16, int64_t nr, int64_t slabr,
                   int64_t kdim, int32_t vmax, int64_t* dot, int64_t ldd, int accumulate, int impl,
                   void* stream);
 

@@ -54,6 +54,6 @@ def test_bad_arguments_are_reported_not_crashed(lib_path):
     with pytest.raises(_lib.GridB200Error, match="multiple of 4"):
         _lib.call("gridb200_col_raw_stats", 4096, 4, 5, 5, 4096, 4096, None)
     with pytest.raises(_lib.GridB200Error, match="kdim"):
-        _lib.call("gridb200_gram", 4096, 4, 72, 4096, 4, 72, 70, 200, 4096, 4, 0, 1, None)
+        _lib.call("gridb200_gram", 4096, 4, 4, 4096, 4, 4, 70, 200, 4096, 4, 0, 1, None)
     with pytest.raises(_lib.GridB200Error, match="vmax"):
-        _lib.call("gridb200_gram", 4096, 4, 64, 4096, 4, 64, 64, 5000, 4096, 4, 0, 1, None)
+        _lib.call("gridb200_gram", 4096, 4, 4, 4096, 4, 4, 64, 5000, 4096, 4, 0, 1, None)

@@ -116,7 +116,7 @@ def test_array_chain_matches_oracle(seed, n, b, holes, params, eng):
     zq[zq == -32767] = 0
     np.testing.assert_array_equal(zq, want["zq"])                              # every %.2f field, exactly
     # tensor-core operand = clipped, NA->0, dropped bins zeroed; norms exact
-    zh = res.zh.cpu().numpy()[:, :res.rw].astype(np.int64)
+    zh = eng.zh_rowmajor(res.zh).cpu().numpy()[:, :res.rw].astype(np.int64)
     np.testing.assert_array_equal(zh[:, want["keep"]], want["zc"])
     assert (np.delete(zh, want["keep"], axis=1) == 0).all()
     np.testing.assert_array_equal(res.norms.cpu().numpy(), (want["zc"] ** 2).sum(axis=1))
@@ -130,6 +130,12 @@ def test_array_chain_matches_oracle(seed, n, b, holes, params, eng):
     np.testing.assert_allclose(cn.cpu().numpy(), want["dipcn"], rtol=DIPCN_REL)
 
 
+def _kblocked(a: np.ndarray) -> torch.Tensor:
+    """[n, k] integer matrix -> the k-blocked fp16 operand [k/64, n, 64] gridb200_gram reads."""
+    n, k = a.shape
+    return torch.from_numpy(np.ascontiguousarray(a.astype(np.float16).reshape(n, k // 64, 64).transpose(1, 0, 2))).cuda()
+
+
 def test_gram_tensor_core_is_exact_at_extremes(eng):
     """All-(+-vmax) rows are the worst case for fp32 accumulation: the chunked drain must stay exact."""
     from grid_b200._lib import GridB200Error, call, ptr
@@ -140,18 +146,18 @@ def test_gram_tensor_core_is_exact_at_extremes(eng):
         a[0] = vmax
         a[1] = -vmax
         a[2, ::2] = 0
-        t = torch.from_numpy(a.astype(np.float16)).cuda()
+        t = _kblocked(a)
         want = a @ a.T
         for impl in impls:
             dot = torch.full((n, n + (n % 2)), -7, dtype=torch.int64, device="cuda")
-            call("gridb200_gram", ptr(t), n, k, ptr(t), n, k, k, vmax, ptr(dot), dot.stride(0), 0, impl,
+            call("gridb200_gram", ptr(t), n, n, ptr(t), n, n, k, vmax, ptr(dot), dot.stride(0), 0, impl,
                  torch.cuda.current_stream().cuda_stream)
             np.testing.assert_array_equal(dot.cpu().numpy()[:, :n], want)
-            call("gridb200_gram", ptr(t), n, k, ptr(t), n, k, k, vmax, ptr(dot), dot.stride(0), 1, impl,
+            call("gridb200_gram", ptr(t), n, n, ptr(t), n, n, k, vmax, ptr(dot), dot.stride(0), 1, impl,
                  torch.cuda.current_stream().cuda_stream)                    # accumulate
             np.testing.assert_array_equal(dot.cpu().numpy()[:, :n], 2 * want)
     with pytest.raises(GridB200Error, match="vmax"):                          # fp32 chunks cannot be exact there
-        call("gridb200_gram", ptr(t), 70, 512, ptr(t), 70, 512, 512, 2048, ptr(dot), dot.stride(0), 0, 0,
+        call("gridb200_gram", ptr(t), 70, 70, ptr(t), 70, 70, 512, 2048, ptr(dot), dot.stride(0), 0, 0,
              torch.cuda.current_stream().cuda_stream)
 
 
@@ -167,11 +173,38 @@ def test_gram_rectangular_blocks_and_long_k(eng):
     q[3] = 200
     r[5] = 200                                                               # 200*200*44800 = 1.8e9 > 2^30
     r[6] = -200
-    tq, tr = torch.from_numpy(q.astype(np.float16)).cuda(), torch.from_numpy(r.astype(np.float16)).cuda()
+    tq, tr = _kblocked(q), _kblocked(r)
     dot = torch.empty((nq, nr + 1), dtype=torch.int64, device="cuda")
-    call("gridb200_gram", ptr(tq), nq, k, ptr(tr), nr, k, k, 200, ptr(dot), dot.stride(0), 0, 0,
+    call("gridb200_gram", ptr(tq), nq, nq, ptr(tr), nr, nr, k, 200, ptr(dot), dot.stride(0), 0, 0,
          torch.cuda.current_stream().cuda_stream)
     np.testing.assert_array_equal(dot.cpu().numpy()[:, :nr], q @ r.T)
+    # a query block in the middle of the reference operand (what engine.knn passes for blocked queries)
+    q0, nqb = 70, 150
+    dot2 = torch.empty((nqb, nr + 1), dtype=torch.int64, device="cuda")
+    call("gridb200_gram", tr.data_ptr() + q0 * 64 * 2, nqb, nr, ptr(tr), nr, nr, k, 200, ptr(dot2), dot2.stride(0), 0, 0,
+         torch.cuda.current_stream().cuda_stream)
+    np.testing.assert_array_equal(dot2.cpu().numpy()[:, :nr], r[q0:q0 + nqb] @ r.T)
+
+
+def test_gram_symmetric_many_tiles(eng):
+    """Same-operand call with several 256-row tiles: only the upper triangle is computed and then mirrored; the
+    result must equal the general (two-operand) path bit for bit, with and without accumulation."""
+    from grid_b200._lib import call, ptr
+
+    rng = np.random.default_rng(11)
+    n, k = 1100, 64 * 90
+    a = rng.integers(-200, 201, size=(n, k)).astype(np.int64)
+    t = _kblocked(a)
+    want = a @ a.T
+    dot = torch.full((n, n), 3, dtype=torch.int64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    call("gridb200_gram", ptr(t), n, n, ptr(t), n, n, k, 200, ptr(dot), n, 0, 0, st)
+    np.testing.assert_array_equal(dot.cpu().numpy(), want)
+    call("gridb200_gram", ptr(t), n, n, ptr(t), n, n, k, 200, ptr(dot), n, 1, 0, st)
+    np.testing.assert_array_equal(dot.cpu().numpy(), 2 * want)
+    t2 = t.clone()                                                            # different pointer: general path
+    call("gridb200_gram", ptr(t), n, n, ptr(t2), n, n, k, 200, ptr(dot), n, 0, 0, st)
+    np.testing.assert_array_equal(dot.cpu().numpy(), want)
 
 
 def test_knn_properties_at_scale(eng):
@@ -184,7 +217,7 @@ def test_knn_properties_at_scale(eng):
     idx, d2 = eng.knn(res.zh, res.kdim, res.norms, 50, p.zclip)
     idx, d2 = idx.cpu().numpy(), d2.cpu().numpy()
     assert (np.diff(d2, axis=1) >= 0).all() and (idx != np.arange(n)[:, None]).all() and (idx >= 0).all()
-    zh = res.zh.cpu().numpy().astype(np.int64)
+    zh = eng.zh_rowmajor(res.zh).cpu().numpy().astype(np.int64)
     rows = np.random.default_rng(0).choice(n, 40, replace=False)
     full = ((zh[rows, None, :] - zh[None, :, :]) ** 2).sum(axis=2) if n * b * 40 < 2e8 else None
     for t, i in enumerate(rows):
@@ -205,8 +238,9 @@ def test_transform_saturation_and_negative_zero(eng):
     h = synth.depth_hundredths(8, n, b)
     h[7, 100] = 4_000_000                       # 40000x coverage in one bin
     dec = h / 100.0
-    want = O.chain_arrays(dec, synth.read_counts(8, n, [1000]), num_neighbors=5, n_nbr=5)
-    res = eng.normalize(torch.from_numpy(dec.astype(np.float32)).cuda(), b, eng.Params(), want_zq=True, want_zh=True)
+    want = O.chain_arrays(dec, synth.read_counts(8, n, [1000]), num_neighbors=5, n_nbr=5, max_depth=1e9)
+    res = eng.normalize(torch.from_numpy(dec.astype(np.float32)).cuda(), b, eng.Params(max_depth=1e9), want_zq=True,
+                        want_zh=True)
     zq = res.zq.cpu().numpy()[:, :res.rw].astype(np.int64)
     exp = want["zq"].copy()
     big = np.abs(exp) > 32766
@@ -229,5 +263,5 @@ def test_errors_surface_as_exceptions(eng):
     with pytest.raises(ValueError):
         eng.normalize(depth.double(), 64, eng.Params())
     with pytest.raises(GridB200Error):
-        eng.knn(torch.zeros((4, 64), dtype=torch.float16, device="cuda"), 64, torch.zeros(4, dtype=torch.int64, device="cuda"),
+        eng.knn(torch.zeros((1, 4, 64), dtype=torch.float16, device="cuda"), 64, torch.zeros(4, dtype=torch.int64, device="cuda"),
                 2, 5000)
