@@ -157,6 +157,30 @@ __device__ __forceinline__ void tmem_ld_wait32(uint32_t* v) {
                : "memory");
 }
 
+// acc += (int)x for an integer-valued float |x| < 2^24, two ways, so that the work is split between two pipes:
+//   add_exact_xu : F2I (XU pipe, 16 lanes/clk/SM -- ncu showed this pipe 82 % busy when it did all the work)
+//   add_exact_fma: FFMA/FADD/IMAD/IADD3 only.  With M = 1.5*2^23: t = x/4096 + M has bits(M) + hi, hi = rint(x/4096);
+//                  lo = x - 4096*hi is exact and |lo| <= 2048, so bits(lo + M) = bits(M) + lo; x = 4096*hi + lo.
+__device__ __forceinline__ void add_exact_xu(int& acc, uint32_t xbits) { acc += __float2int_rn(__uint_as_float(xbits)); }
+__device__ __forceinline__ void add_exact_fma(int& acc, uint32_t xbits) {
+  constexpr float M = 12582912.0f;                                // 0x4B400000
+  constexpr uint32_t K = 0u - (0x4B400000u * 4096u + 0x4B400000u);  // removes both biases (mod 2^32)
+  const float x = __uint_as_float(xbits);
+  const float t = __fmaf_rn(x, 0.000244140625f, M);
+  const float hf = __fadd_rn(t, -M);
+  const float lo = __fmaf_rn(hf, -4096.0f, x);
+  const float u = __fadd_rn(lo, M);
+  acc = (int)((uint32_t)acc + (__float_as_uint(t) << 12) + (__float_as_uint(u) + K));
+}
+template <int kBase>
+__device__ __forceinline__ void drain32(int* acc32, const uint32_t* v) {
+#pragma unroll
+  for (int i = 0; i < 32; ++i) {
+    if (i & 1) add_exact_fma(acc32[kBase + i], v[i]);
+    else add_exact_xu(acc32[kBase + i], v[i]);
+  }
+}
+
 // item -> (k split, tile m, tile n).  K-split major, so that the pairs of one wave stream the same K window.
 // General mode: tiles walked in bands of group_m tile-rows so concurrent tiles share operand rows.
 // Symmetric mode: the tiles_m*(tiles_m+1)/2 tiles with tn >= tm, row by row.
@@ -331,23 +355,19 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         tmem_ld32(taddr, va);
         tmem_ld_wait32(va);
         tmem_ld32(taddr + 32, vb);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) acc32[i] += __float2int_rn(__uint_as_float(va[i]));
+        drain32<0>(acc32, va);
         tmem_ld_wait32(vb);
         tmem_ld32(taddr + 64, va);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) acc32[32 + i] += __float2int_rn(__uint_as_float(vb[i]));
+        drain32<32>(acc32, vb);
         tmem_ld_wait32(va);
         tmem_ld32(taddr + 96, vb);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) acc32[64 + i] += __float2int_rn(__uint_as_float(va[i]));
+        drain32<64>(acc32, va);
         tmem_ld_wait32(vb);
         // everything is in registers: hand the TMEM stage back to the MMA warp
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive_cluster(map_to_cta(tempty0 + 8 * acc, 0));
-#pragma unroll
-        for (int i = 0; i < 32; ++i) acc32[96 + i] += __float2int_rn(__uint_as_float(vb[i]));
+        drain32<96>(acc32, vb);
         if (++acc == ACC_STAGES) acc = 0, acc_phase ^= 1;
         if (++since_check == CHECK_EVERY) {  // keep |acc32| + 16 more chunks (< 2^24 each) below 2^31
           since_check = 0;

@@ -286,11 +286,12 @@ __global__ void k_col_finalize(const double* __restrict__ sd, const double* __re
 // ---------------------------------------------------------------------------------------------------------
 // K7: transform + printf-exact quantisation + compaction to the selected bins (+ clipped fp16 operand,
 // + exact row norms).  Block = 1024 bins x a slab of rows, processed in batches of 8 rows:
-//   1. every thread issues its 8 row loads (16 B each) before touching any of them,
-//   2. computes z in fp64, rounds exactly, and drops the 2-byte results into a shared staging row at the
-//      compacted position (selected bins of one block are contiguous in the output),
-//   3. the block copies each staged row out with ALIGNED 16-byte stores (element stores only on the two
-//      ragged ends, which belong to neighbouring blocks).
+//   1. compute z in fp64 for the batch already in registers, round exactly, drop the 2-byte results into a
+//      shared staging row at the compacted position (selected bins of one block are contiguous in the output),
+//   2. issue the 8 row loads (16 B each) of the NEXT batch, so they fly during steps 3-4,
+//   3. one __syncthreads (the staging buffer is double-buffered),
+//   4. copy the staged rows out with ALIGNED 16-byte stores, (chunk, row) pairs spread over all threads
+//      (element stores only on the two ragged ends, which belong to neighbouring blocks).
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kTransformSlab = 256;
 constexpr int kTB = 8;                        // rows per batch
@@ -300,28 +301,26 @@ constexpr int kDump = kStageRow - 1;          // where unselected bins drop thei
 // kBlocked = false: row-major output, element (r, p) at out[r*ld_out + p].
 // kBlocked = true : k-blocked operand layout of the Gram kernel, element (r, p) at out[((p/64)*ld_out + r)*64 + p%64]
 //                   (ld_out = rows per 64-bin slab); an aligned 8-element chunk never straddles two k-blocks.
+// stage[r][shift + e] holds output element p0 + e of row row0 + r, shift = p0 % 8, so 16-byte chunk q of the
+// staged row lines up with the aligned global chunk starting at element (p0 - shift) + 8q.
 template <typename T, bool kBlocked>
 __device__ __forceinline__ void copy_out_rows(const T* __restrict__ stage, T* __restrict__ out, int64_t ld_out,
                                               int64_t row0, int nrows, int p0, int len) {
-  // stage[r][shift + e] holds output element p0 + e of row row0 + r, shift = p0 % 8, so 16-byte chunk q of the
-  // staged row lines up with the aligned global chunk starting at element (p0 - shift) + 8q.
   const int shift = p0 & 7;
   const int nchunk = (shift + len + 7) >> 3;
-  for (int q = threadIdx.x; q < nchunk; q += kThreads) {
+  for (int w = threadIdx.x; w < nchunk * kTB; w += kThreads) {
+    const int r = w / nchunk, q = w - r * nchunk;  // consecutive threads -> consecutive chunks of one row
+    if (r >= nrows) break;
     const int e0 = 8 * q - shift;  // first element of this chunk relative to p0
-    const bool whole = e0 >= 0 && e0 + 8 <= len;
-    const T* src = stage + 8 * q;
+    const T* src = stage + r * kStageRow + 8 * q;
     const int64_t pe = (int64_t)(p0 - shift) + 8 * q;  // first element of the chunk in the output row
-    T* dst = kBlocked ? out + ((pe >> 6) * ld_out + row0) * 64 + (pe & 63) : out + row0 * ld_out + pe;
-    const int64_t step = kBlocked ? 64 : ld_out;
-    for (int r = 0; r < nrows; ++r, src += kStageRow, dst += step) {
-      if (whole) {
-        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
-      } else {
+    T* dst = kBlocked ? out + ((pe >> 6) * ld_out + row0 + r) * 64 + (pe & 63) : out + (row0 + r) * ld_out + pe;
+    if (e0 >= 0 && e0 + 8 <= len) {
+      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+    } else {
 #pragma unroll
-        for (int e = 0; e < 8; ++e)
-          if (e0 + e >= 0 && e0 + e < len) dst[e] = src[e];
-      }
+      for (int e = 0; e < 8; ++e)
+        if (e0 + e >= 0 && e0 + e < len) dst[e] = src[e];
     }
   }
 }
@@ -337,34 +336,31 @@ __device__ __noinline__ int quantise_slow(double w, double a100, unsigned long l
     else if (r < 0.0) q = t - 0.5;
   }
   if (fabs(q) > 32766.0) {
-    atomicAdd(sat, 1ULL);
+    if (sat) atomicAdd(sat, 1ULL);
     q = q > 0 ? 32766.0 : -32766.0;
   }
   return double_to_int_exact(q);
 }
 
 template <bool kZq, bool kZh>
-__global__ void __launch_bounds__(kThreads) k_transform(const float* __restrict__ depth, int64_t n, int64_t b,
-                                                        int64_t ld, const double* __restrict__ row_factor,
-                                                        const double* __restrict__ mu,
-                                                        const int32_t* __restrict__ sel_pos,
-                                                        const uint8_t* __restrict__ keep,
-                                                        const double* __restrict__ info, int zclip,
-                                                        int16_t* __restrict__ zq, int64_t ldq,
-                                                        __half* __restrict__ zh, int64_t ldh,
-                                                        unsigned long long* __restrict__ norms,
-                                                        unsigned long long* __restrict__ sat) {
-  __shared__ __align__(16) int16_t s_zq[kZq ? kTB * kStageRow : 8];
-  __shared__ __align__(16) __half s_zh[kZh ? kTB * kStageRow : 8];
+__global__ void __launch_bounds__(kThreads, 3) k_transform(const float* __restrict__ depth, int64_t n, int64_t b,
+                                                           int64_t ld, const double* __restrict__ row_factor,
+                                                           const double* __restrict__ mu,
+                                                           const int32_t* __restrict__ sel_pos,
+                                                           const uint8_t* __restrict__ keep,
+                                                           const double* __restrict__ info, int zclip,
+                                                           int16_t* __restrict__ zq, int64_t ldq,
+                                                           __half* __restrict__ zh, int64_t ldh,
+                                                           unsigned long long* __restrict__ norms,
+                                                           unsigned long long* __restrict__ sat) {
+  __shared__ __align__(16) int16_t s_zq[kZq ? 2 * kTB * kStageRow : 8];
+  __shared__ __align__(16) __half s_zh[kZh ? 2 * kTB * kStageRow : 8];
   __shared__ double s_f[kTransformSlab];
-  __shared__ unsigned long long s_norm[kTransformSlab];
+  __shared__ unsigned s_part[kZh ? (kThreads / 32) * kTransformSlab : 1];  // per-warp partial row norms
   __shared__ int s_lo, s_hi;
   const int64_t r0 = (int64_t)blockIdx.y * kTransformSlab;
   const int nrow = (int)(n - r0 < kTransformSlab ? n - r0 : (int64_t)kTransformSlab);
-  for (int t = threadIdx.x; t < kTransformSlab; t += kThreads) {
-    s_norm[t] = 0;
-    s_f[t] = t < nrow ? row_factor[r0 + t] : nan("");
-  }
+  for (int t = threadIdx.x; t < kTransformSlab; t += kThreads) s_f[t] = t < nrow ? row_factor[r0 + t] : nan("");
   if (threadIdx.x == 0) s_lo = 0x7fffffff, s_hi = -1;
   __syncthreads();
   const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
@@ -385,9 +381,9 @@ __global__ void __launch_bounds__(kThreads) k_transform(const float* __restrict_
       zc[q] = (keep ? keep[j0 + q] != 0 : true) ? zclip : 0;
     }
   }
-  const bool any = hi >= 0;
   lo = __reduce_min_sync(0xffffffffu, lo);
   hi = __reduce_max_sync(0xffffffffu, hi);
+  const bool any = hi >= 0;  // WARP-uniform (the batch loop contains warp collectives): some lane has a selected bin
   if ((threadIdx.x & 31) == 0 && hi >= 0) {
     atomicMin(&s_lo, lo);
     atomicMax(&s_hi, hi);
@@ -399,72 +395,91 @@ __global__ void __launch_bounds__(kThreads) k_transform(const float* __restrict_
   int off[4];
 #pragma unroll
   for (int q = 0; q < 4; ++q) off[q] = pos[q] >= 0 ? pos[q] - p0 + shift : kDump - q;
-  const float* colp = depth + (j0 < b ? j0 : 0);
+  const float* colp = depth + (j0 < b ? j0 : 0) + r0 * ld;
+  const int warp = threadIdx.x >> 5;
+  // the dump slots never reach global memory, but the 32-bit hi-word test below must not see NaN garbage there:
+  // unselected bins run with negmu = a100 = 0, i.e. t = 0 (or NaN for an empty row, which compares false)
 
-  for (int rb = 0; rb < nrow; rb += kTB) {
+  float4 v[kTB];
+  if (any) {
+#pragma unroll
+    for (int u = 0; u < kTB; ++u)
+      v[u] = u < nrow ? ld_stream(reinterpret_cast<const float4*>(colp + (int64_t)u * ld)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  int buf = 0;
+  for (int rb = 0; rb < nrow; rb += kTB, buf ^= 1) {
     const int nr = min(kTB, nrow - rb);
-    float4 v[kTB];
+    int16_t* const bq = s_zq + (kZq ? buf * kTB * kStageRow : 0);
+    __half* const bh = s_zh + (kZh ? buf * kTB * kStageRow : 0);
     if (any) {
 #pragma unroll
-      for (int u = 0; u < kTB; ++u)
-        v[u] = u < nr ? ld_stream(reinterpret_cast<const float4*>(colp + (r0 + rb + u) * ld)) : make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-#pragma unroll
-    for (int u = 0; u < kTB; ++u) {
-      int vsq = 0;
-      if (any && u < nr) {
-        const double f = s_f[rb + u];
-        const bool row_ok = f == f;
-        const float vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-        int zi[4];
-        bool rare = false;
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int h = depth_hundredths(vv[q]);
-          const double w = fma(u32_to_double(h), f, negmu[q]);
-          const double t = w * a100[q];
-          const double tm = t + kRoundMagic;       // low word = round-half-even(t) as int32
-          const double d = t - (tm - kRoundMagic);
-          zi[q] = __double2loint(tm);
-          // exactly on .5 after rounding, or beyond the int16 code range: settle in the slow path
-          rare |= (fabs(d) == 0.5) | ((__double2hiint(t) & 0x7fffffff) >= 0x40DFFF00);
-          if (kZq && zi[q] == 0 && __double2hiint(t) < 0) zi[q] = -32767;  // prints as "-0.00"
-          if (!(h > 0 && row_ok)) zi[q] = -32768;
-        }
-        if (rare) {
+      for (int u = 0; u < kTB; ++u) {
+        int vsq = 0;
+        if (u < nr) {
+          const double f = s_f[rb + u];
+          const float vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+          int zi[4];
+          bool rare = false;
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             const int h = depth_hundredths(vv[q]);
-            if (h > 0 && row_ok && off[q] < kDump - 3) {
-              const double w = fma(u32_to_double(h), f, negmu[q]);
-              const int z = quantise_slow(w, a100[q], sat);
-              zi[q] = (kZq && z == 0 && w * a100[q] < 0.0) ? -32767 : z;
+            const double w = fma(u32_to_double(h), f, negmu[q]);
+            const double t = w * a100[q];
+            const double tm = t + kRoundMagic;       // low word = round-half-even(t) as int32
+            const double d = t - (tm - kRoundMagic);
+            zi[q] = __double2loint(tm);
+            // exactly on .5 after rounding, or beyond the int16 code range: settle in the slow path
+            rare |= (fabs(d) == 0.5) | ((__double2hiint(t) & 0x7fffffff) >= 0x40DFFF00);
+            if (kZq && zi[q] == 0 && __double2hiint(t) < 0) zi[q] = -32767;  // prints as "-0.00"
+            if (h == 0) zi[q] = -32768;  // absent cell (a row without valid bins has no present cell either)
+          }
+          if (rare) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              const int h = depth_hundredths(vv[q]);
+              if (h > 0 && f == f && off[q] < kDump - 3) {
+                const double w = fma(u32_to_double(h), f, negmu[q]);
+                const int z = quantise_slow(w, a100[q], sat);
+                zi[q] = (kZq && z == 0 && w * a100[q] < 0.0) ? -32767 : z;
+              }
+            }
+          }
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (kZq) bq[u * kStageRow + off[q]] = (int16_t)zi[q];
+            if (kZh) {
+              const int c = zi[q] > -32767 ? max(-zc[q], min(zc[q], zi[q])) : 0;
+              bh[u * kStageRow + off[q]] = __int2half_rn(c);
+              vsq += c * c;
             }
           }
         }
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          if (kZq) s_zq[u * kStageRow + off[q]] = (int16_t)zi[q];
-          if (kZh) {
-            const int c = zi[q] > -32767 ? max(-zc[q], min(zc[q], zi[q])) : 0;
-            s_zh[u * kStageRow + off[q]] = __int2half_rn(c);
-            vsq += c * c;
-          }
+        if (kZh && u < nr) {
+          const int tot = __reduce_add_sync(0xffffffffu, vsq);  // <= 128 * 2048^2 = 2^29
+          if ((threadIdx.x & 31) == 0) s_part[warp * kTransformSlab + rb + u] = (unsigned)tot;
         }
       }
-      if (kZh && u < nr) {
-        const int tot = __reduce_add_sync(0xffffffffu, vsq);
-        if ((threadIdx.x & 31) == 0 && tot) atomicAdd(&s_norm[rb + u], (unsigned long long)tot);
-      }
+      // next batch: in flight during the barrier and the copy-out
+      const int rn = rb + kTB;
+#pragma unroll
+      for (int u = 0; u < kTB; ++u)
+        if (rn + u < nrow) v[u] = ld_stream(reinterpret_cast<const float4*>(colp + (int64_t)(rn + u) * ld));
+    } else if (kZh) {
+      for (int u = 0; u < nr; ++u)
+        if ((threadIdx.x & 31) == 0) s_part[warp * kTransformSlab + rb + u] = 0;
     }
     __syncthreads();
-    if (kZq) copy_out_rows<int16_t, false>(s_zq, zq, ldq, r0 + rb, nr, p0, len);
-    if (kZh) copy_out_rows<__half, true>(s_zh, zh, ldh, r0 + rb, nr, p0, len);
-    __syncthreads();
+    if (kZq) copy_out_rows<int16_t, false>(bq, zq, ldq, r0 + rb, nr, p0, len);
+    if (kZh) copy_out_rows<__half, true>(bh, zh, ldh, r0 + rb, nr, p0, len);
   }
   if (kZh) {
-    for (int t = threadIdx.x; t < nrow; t += kThreads)
-      if (s_norm[t]) atomicAdd(&norms[r0 + t], s_norm[t]);
+    __syncthreads();
+    for (int t = threadIdx.x; t < nrow; t += kThreads) {
+      unsigned long long tot = 0;
+#pragma unroll
+      for (int w = 0; w < kThreads / 32; ++w) tot += s_part[w * kTransformSlab + t];
+      if (tot) atomicAdd(&norms[r0 + t], tot);
+    }
   }
 }
 
@@ -635,15 +650,16 @@ extern "C" int gridb200_transform(const float* depth, int64_t n, int64_t b, int6
   cudaStream_t st = as_stream(stream);
   __half* zhp = static_cast<__half*>(zh);
   unsigned long long* np = reinterpret_cast<unsigned long long*>(norms);
-  if (zq && zh)
-    k_transform<true, true><<<grid, kThreads, 0, st>>>(depth, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip, zq,
-                                                       ldq, zhp, ldh, np, sat);
-  else if (zq)
+  // both outputs wanted (tests, small cohorts): two launches, so that one block's double-buffered staging stays
+  // inside the 48 KB static shared-memory limit; the second launch does not count saturations again
+  if (zq) {
     k_transform<true, false><<<grid, kThreads, 0, st>>>(depth, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip,
                                                         zq, ldq, zhp, ldh, np, sat);
-  else
+    if (zh) G2_LAUNCHED();
+  }
+  if (zh)
     k_transform<false, true><<<grid, kThreads, 0, st>>>(depth, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip,
-                                                        zq, ldq, zhp, ldh, np, sat);
+                                                        zq, ldq, zhp, ldh, np, zq ? nullptr : sat);
   G2_LAUNCHED();
   return 0;
 }
