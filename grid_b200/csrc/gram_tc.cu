@@ -15,7 +15,8 @@
 // (tile, K split).  Each CTA stages its own 128 query rows and 128 of the 256 reference rows per k-block; the
 // leader issues M=256 N=256 K=16 MMAs; each CTA's TMEM holds its 128 x 256 half of the accumulator (two stages:
 // chunk c+1 accumulates while chunk c drains).
-//   warp 0      TMA producer (both CTAs; transaction bytes land on the LEADER's full barrier) + TMEM allocator
+//   warp 0      TMA producer (both CTAs; transaction bytes land on the LEADER's full barrier, on which only the
+//               leader arrives) + TMEM allocator
 //               + L2 pacing (below)
 //   warp 1      MMA issuer (leader CTA only); commits are multicast to both CTAs' barriers
 //   warps 4-11  epilogue: lane quarter = warp%4, column half = (warp-4)/4, 128 int32 accumulators per thread
@@ -111,8 +112,12 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
   return r;
 }
+// Remote arrive WITHOUT a cluster-scope release fence.  The explicit .release.cluster form compiles to ERRBAR +
+// SYNCS.ARRIVE and cost the epilogue warps (and, when the peer's producer still used it, every k-block) a full
+// memory barrier; what this arrive publishes is only "my tcgen05.ld's are complete" (tcgen05.wait::ld +
+// tcgen05.fence::before_thread_sync precede it), not data written to memory.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // one k-block (c2) x 128 rows starting at c1 x all 64 bins of the block
 __device__ __forceinline__ void tma_load_pair(uint32_t dst, const CUtensorMap* map, uint32_t leader_bar, int row, int kb) {
@@ -246,7 +251,7 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(full0 + 8 * s, 2);   // leader's expect_tx arrive + the peer's remote arrive
+      mbar_init(full0 + 8 * s, 1);   // the leader's expect_tx arrive; both CTAs' TMA bytes complete_tx on the leader
       mbar_init(empty0 + 8 * s, 1);  // one multicast commit
     }
     for (int a = 0; a < ACC_STAGES; ++a) {
@@ -289,8 +294,11 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         if (lane == 0) {
           mbar_wait(empty0 + 8 * stage, phase ^ 1);
           const uint32_t leader_full = map_to_cta(full0 + 8 * stage, 0);
-          if (rank == 0) mbar_expect_tx(full0 + 8 * stage, 2 * STAGE_BYTES);  // bytes of both CTAs
-          else mbar_arrive_cluster(leader_full);
+          // Only the leader arrives (expecting the bytes of both CTAs).  The peer's bytes may land before that
+          // arrive -- the transaction count just goes negative for a moment; the phase cannot complete early
+          // because the leader's arrival is still pending, and it cannot be a phase late because the peer only
+          // refills a slot after the multicast `empty` commit that follows the previous phase's completion.
+          if (rank == 0) mbar_expect_tx(full0 + 8 * stage, 2 * STAGE_BYTES);
           const uint32_t sa = base + stage * STAGE_BYTES;
           tma_load_pair(sa, &map_q, leader_full, qrow, kb);
           tma_load_pair(sa + A_BYTES, &map_r, leader_full, rrow, kb);
