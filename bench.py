@@ -108,22 +108,56 @@ def run_reference(a):
 
 # ------------------------------------------------------------------------------------------------ clocks
 class ClockSampler:
+    """SM clock and throttle reasons sampled DURING the timed region (NVML every ~10 ms; nvidia-smi as a fallback)."""
+
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index):
-        self.index, self.rows, self._stop = index, [], threading.Event()
+        self.index, self.sm, self.max_sm, self.reasons, self._stop = index, [], None, set(), threading.Event()
         self.thread = threading.Thread(target=self._run, daemon=True)
+        self.source = "nvml"
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            # NVML enumerates physical devices; honour CUDA_VISIBLE_DEVICES when it is a plain index list
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+            phys = int(vis.split(",")[index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else index
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_sm = pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv, self.source = None, "nvidia-smi"
 
     def _run(self):
+        nv = self.nv
         while not self._stop.is_set():
             try:
+                if nv is not None:
+                    self.sm.append(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM))
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle)
+                    for nm, bit in (("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown),
+                                    ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
+                                    ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown),
+                                    ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap)):
+                        if r & bit:
+                            self.reasons.add(nm)
+                    self._stop.wait(0.01)
+                    continue
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
                                       "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([x.strip() for x in out.strip().split(",")])
+                row = [x.strip() for x in out.strip().split(",")]
+                if row and row[0].isdigit():
+                    self.sm.append(int(row[0]))
+                    self.max_sm = int(row[1]) if len(row) > 1 and row[1].isdigit() else self.max_sm
+                    for i, nm in enumerate(self.NAMES):
+                        if len(row) > 2 + i and row[2 + i].lower().startswith("active"):
+                            self.reasons.add(nm)
             except Exception:
                 pass
-            self._stop.wait(0.2)
+            self._stop.wait(0.05)
 
     def __enter__(self):
         self.thread.start()
@@ -134,12 +168,9 @@ class ClockSampler:
         self.thread.join(timeout=6)
 
     def summary(self):
-        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
-        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [nm for i, nm in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+        sm = sorted(self.sm)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_sm,
+                "reasons": [nm for nm in self.NAMES if nm in self.reasons], "samples": len(sm), "source": self.source}
 
 
 # ------------------------------------------------------------------------------------------------ our arm
@@ -156,6 +187,7 @@ def run_ours(a):
     dev = torch.device("cuda", local)
     group = None
     if world > 1:
+        os.environ["NCCL_DEBUG"] = os.environ.get("GRIDB200_NCCL_DEBUG", "WARN")  # keep NCCL's banner off stdout
         dist.init_process_group("nccl", device_id=dev)
         group = dist.group.WORLD
     lib = _lib.load()

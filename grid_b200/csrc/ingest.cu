@@ -1,8 +1,210 @@
-// placeholder until the device text parser lands
+// Device ingest of one sample's decompressed mosdepth text (`chrom\tstart\tend\tdepth\n` per line) into one row
+// of the packed fp32 depth matrix, with the line filters of normalize_mosdepth.py:262-285 / :321-352.
+//
+//   k_ingest_scan   : every thread owns 16 text bytes; a thread parses each line that STARTS inside its chunk
+//                     (lines are ~30 bytes, so usually none or one).  A kept line claims its bin with
+//                     atomicMax(winner[col], (line offset + 1) << 24 | hundredths): when a file repeats a bin the
+//                     LAST line wins, as the reference's dict assignment does (:285), independent of scheduling.
+//   k_ingest_finish : winner -> depth_row[col] = hundredths / 100 (correctly rounded fp32; 0.0 = absent).
+//
+// Anything the strict grammar below does not cover (signs, exponents, more than two decimals, irregular or
+// unaligned bins, |depth| >= 41943.04) is COUNTED in stats[1] and skipped; the host then re-parses that file
+// itself, so exotic inputs keep the reference's exact behaviour (Python int()/float() semantics).
 #include "common.cuh"
-extern "C" size_t gridb200_ingest_ws_bytes(int64_t nbytes) { return (size_t)(nbytes > 0 ? nbytes : 0) * 8 + 65536; }
-extern "C" int gridb200_ingest_text(const char*, int64_t, const char*, int32_t, int64_t, int64_t, const uint32_t*, int64_t,
-                                    int64_t, int64_t, float*, int64_t*, void*, size_t, void*) {
-  g2::set_error("device ingest not built");
-  return GRIDB200_ENODEV;
+
+namespace g2 {
+
+struct IngestParams {
+  char prefix[32];
+  int prefix_len;
+  int has_win;
+  long long win_lo, win_hi;
+  const uint32_t* mask;
+  long long mask_kb;
+  long long bin0, b;
+};
+
+enum { ST_KEPT = 0, ST_IRREGULAR = 1, ST_LINES = 2, ST_MASKED = 3, ST_FOREIGN = 4 };
+
+__device__ __forceinline__ bool is_digit(int c) { return c >= '0' && c <= '9'; }
+__device__ __forceinline__ bool is_eol(int c) { return c == '\n' || c < 0; }  // c < 0: end of text
+// what Python's str.strip() removes at the end of a line (besides the newline itself)
+__device__ __forceinline__ bool is_trail_ws(int c) { return c == '\r' || c == ' ' || c == '\v' || c == '\f'; }
+
+struct Cursor {
+  const char* text;
+  long long n, i;
+  __device__ __forceinline__ int peek() const { return i < n ? (int)(unsigned char)text[i] : -1; }
+  __device__ __forceinline__ void next() { ++i; }
+};
+
+// unsigned decimal integer followed by a tab (the caller has already established that the tab exists)
+__device__ bool parse_uint_tab(Cursor& c, long long& out) {
+  long long v = 0;
+  int nd = 0;
+  while (is_digit(c.peek())) {
+    v = v * 10 + (c.peek() - '0');
+    if (++nd > 13) return false;
+    c.next();
+  }
+  if (nd == 0 || c.peek() != '\t') return false;
+  c.next();
+  out = v;
+  return true;
+}
+
+__device__ void parse_line(const char* text, long long n, long long start, const IngestParams& P,
+                           unsigned long long* winner, unsigned long long* stats) {
+  Cursor c{text, n, start};
+  for (int t = 0; t < P.prefix_len; ++t) {  // line.startswith(chrom) -- a PREFIX test on the raw line (:264)
+    if (c.peek() != (int)(unsigned char)P.prefix[t]) return;
+    c.next();
+  }
+  // fields = line.strip().split("\t"); fewer than 4 -> `continue`, whatever they contain (:266-268).
+  // `stop` = one past the last character strip() keeps; tabs at or after it do not separate fields.
+  long long stop = start;
+  int tabs_total = 0, tabs = 0;
+  {
+    Cursor q{text, n, start};
+    int ch;
+    while (!is_eol(ch = q.peek())) {
+      if (ch == '\t') ++tabs_total;
+      else if (!is_trail_ws(ch)) stop = q.i + 1, tabs = tabs_total;
+      q.next();
+    }
+  }
+  if (stop == start) return;  // blank line
+  {
+    const int first = (int)(unsigned char)text[start];
+    if (first == '\t' || is_trail_ws(first)) {  // leading whitespace is stripped by the reference: leave it to the host
+      atomicAdd(&stats[ST_IRREGULAR], 1ULL);
+      return;
+    }
+  }
+  atomicAdd(&stats[ST_LINES], 1ULL);
+  if (tabs < 3) return;
+  // rest of field 0
+  bool foreign = false;
+  while (c.peek() != '\t') {
+    foreign = true;  // the chromosome field is longer than the prefix (chr1 also admits chr10)
+    c.next();
+  }
+  c.next();
+  if (foreign && P.prefix_len > 0) atomicAdd(&stats[ST_FOREIGN], 1ULL);
+  long long s = 0, e = 0;
+  if (!parse_uint_tab(c, s) || !parse_uint_tab(c, e)) {
+    atomicAdd(&stats[ST_IRREGULAR], 1ULL);
+    return;
+  }
+  // depth: digits [ '.' digits{0..2} ], ending at a tab (further mosdepth columns) or at the stripped end
+  long long ip = 0;
+  int nd = 0, nf = 0, frac = 0;
+  while (is_digit(c.peek())) {
+    ip = ip * 10 + (c.peek() - '0');
+    if (++nd > 9) break;
+    c.next();
+  }
+  if (c.peek() == '.') {
+    c.next();
+    while (is_digit(c.peek())) {
+      if (nf < 2) frac = frac * 10 + (c.peek() - '0');
+      ++nf;
+      c.next();
+    }
+  }
+  const bool ok = nd > 0 && nd <= 9 && nf <= 2 && (c.peek() == '\t' || c.i >= stop);
+  if (nf == 1) frac *= 10;
+  const long long h = ip * 100 + frac;
+  if (!ok || h >= (1LL << 22)) {
+    atomicAdd(&stats[ST_IRREGULAR], 1ULL);
+    return;
+  }
+  if (h == 0) return;                                          // depth > 0 (:274, :278)
+  if (P.has_win && !(e >= P.win_lo && s <= P.win_hi)) return;  // closed-interval window test (:274-276)
+  const long long len = e - s, rel = s - P.bin0;
+  if (len <= 0 || len > 1000 || rel < 0 || rel % 1000 != 0 || rel / 1000 >= P.b) {
+    atomicAdd(&stats[ST_IRREGULAR], 1ULL);
+    return;
+  }
+  if (P.mask) {  // any masked kb in [s//1000, e//1000] (:281-283)
+    for (long long kb = s / 1000; kb <= e / 1000; ++kb) {
+      if (kb < P.mask_kb && ((P.mask[kb >> 5] >> (kb & 31)) & 1u)) {
+        atomicAdd(&stats[ST_MASKED], 1ULL);
+        return;
+      }
+    }
+  }
+  atomicMax(&winner[rel / 1000], ((unsigned long long)(start + 1) << 24) | (unsigned long long)h);
+  atomicAdd(&stats[ST_KEPT], 1ULL);
+}
+
+__global__ void __launch_bounds__(256) k_ingest_scan(const char* __restrict__ text, long long n, IngestParams P,
+                                                     unsigned long long* __restrict__ winner,
+                                                     unsigned long long* __restrict__ stats) {
+  const long long c0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 16;
+  if (c0 >= n) return;
+  // bit t of `starts` = a line starts at byte c0 + t  (the byte before it is a newline, or it is byte 0)
+  unsigned starts = 0;
+  if ((c0 + 16 <= n) && ((reinterpret_cast<uintptr_t>(text) & 15) == 0)) {
+    const uint4 v = *reinterpret_cast<const uint4*>(text + c0);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int t = 0; t < 15; ++t)
+      if (((w[t >> 2] >> (8 * (t & 3))) & 0xff) == '\n') starts |= 1u << (t + 1);
+  } else {
+    for (int t = 0; t < 15 && c0 + t < n; ++t)
+      if (text[c0 + t] == '\n') starts |= 1u << (t + 1);
+  }
+  if (c0 == 0 || text[c0 - 1] == '\n') starts |= 1u;
+  while (starts) {
+    const int t = __ffs(starts) - 1;
+    starts &= starts - 1;
+    if (c0 + t < n) parse_line(text, n, c0 + t, P, winner, stats);
+  }
+}
+
+__global__ void k_ingest_finish(const unsigned long long* __restrict__ winner, long long b, float* __restrict__ depth_row) {
+  const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= b) return;
+  const unsigned long long w = winner[j];
+  depth_row[j] = w ? __fdiv_rn((float)(unsigned)(w & 0xFFFFFFull), 100.0f) : 0.0f;
+}
+
+}  // namespace g2
+
+extern "C" size_t gridb200_ingest_ws_bytes(int64_t b) { return (size_t)(b > 0 ? b : 0) * 8 + 256; }
+
+extern "C" int gridb200_ingest_text(const char* text, int64_t nbytes, const char* chrom_prefix, int32_t chrom_len,
+                                    int64_t win_lo, int64_t win_hi, const uint32_t* mask_bits, int64_t mask_kb,
+                                    int64_t bin0, int64_t b, float* depth_row, int64_t* stats, void* ws,
+                                    size_t ws_bytes, void* stream) {
+  using namespace g2;
+  G2_REQUIRE(depth_row && stats && b > 0 && nbytes >= 0, GRIDB200_EINVAL, "bad argument");
+  G2_REQUIRE(text || nbytes == 0, GRIDB200_EINVAL, "null text");
+  G2_REQUIRE(chrom_len >= 0 && chrom_len <= 32 && (chrom_len == 0 || chrom_prefix), GRIDB200_EINVAL,
+             "chromosome prefix must be at most 32 bytes");
+  G2_REQUIRE(ws && ws_bytes >= gridb200_ingest_ws_bytes(b), GRIDB200_EINVAL, "workspace too small: need %zu bytes",
+             gridb200_ingest_ws_bytes(b));
+  G2_REQUIRE(bin0 >= 0 && b < (1LL << 31), GRIDB200_EINVAL, "bad bin grid");
+  cudaStream_t st = as_stream(stream);
+  IngestParams P;
+  memset(&P, 0, sizeof(P));
+  for (int t = 0; t < chrom_len; ++t) P.prefix[t] = chrom_prefix[t];
+  P.prefix_len = chrom_len;
+  P.has_win = win_lo >= 0;
+  P.win_lo = win_lo, P.win_hi = win_hi;
+  P.mask = mask_bits, P.mask_kb = mask_bits ? mask_kb : 0;
+  P.bin0 = bin0, P.b = b;
+  unsigned long long* winner = static_cast<unsigned long long*>(ws);
+  G2_CUDA(cudaMemsetAsync(winner, 0, (size_t)b * 8, st));
+  G2_CUDA(cudaMemsetAsync(stats, 0, 8 * sizeof(int64_t), st));
+  if (nbytes > 0) {
+    const long long chunks = (nbytes + 15) / 16;
+    k_ingest_scan<<<(unsigned)((chunks + 255) / 256), 256, 0, st>>>(text, nbytes, P, winner,
+                                                                   reinterpret_cast<unsigned long long*>(stats));
+    G2_LAUNCHED();
+  }
+  k_ingest_finish<<<(unsigned)((b + 255) / 256), 256, 0, st>>>(winner, b, depth_row);
+  G2_LAUNCHED();
+  return 0;
 }

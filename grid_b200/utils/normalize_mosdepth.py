@@ -57,6 +57,103 @@ def pack_depth_matrix(individuals: dict, mosdepth_dir, chrom, start, end, exclud
     return ids, bins, depth
 
 
+def _inflate(path) -> bytes | None:
+    try:
+        with gzip.open(path, "rb") as fh:
+            return fh.read()
+    except Exception:
+        return None
+
+
+def _last_bin_start(text: bytes) -> int:
+    """Start coordinate of the last parseable line (to size the bin grid when no window is configured)."""
+    for line in reversed(text[-4096:].split(b"\n")):
+        f = line.split(b"\t")
+        if len(f) >= 4 and f[1].isdigit():
+            return int(f[1])
+    return -1
+
+
+def pack_depth_matrix_device(individuals: dict, mosdepth_dir, chrom, start, end, excluded, threads: int = 1,
+                             console=None):
+    """Device ingest (gridb200_ingest_text): the host only inflates; parsing, filtering and packing run on the GPU.
+
+    Applies when the bins form the regular 1000-bp grid `mosdepth --by 1000` writes (mosdepth.py:193-225).  Returns
+    None when they do not (or a file needs Python's int()/float() semantics everywhere) -- the caller then packs
+    on the host with pack_depth_matrix; individual irregular files are re-parsed on the host into their row.
+    Result: (ids, bins[(start, end)], depth tensor [N, ld] on the GPU).
+    """
+    import torch
+
+    from .. import _lib
+    from .._lib import call, ptr
+
+    ids = sorted(individuals)
+    want = norm_chrom(chrom).encode() if chrom else b""
+    if len(want) > 32:
+        return None
+    paths = [find_bed_gz_for_individual(sid, mosdepth_dir) for sid in ids]
+    with ThreadPoolExecutor(max_workers=max(1, threads)) as ex:
+        texts = list(ex.map(lambda p: _inflate(p) if p.exists() else None, paths))
+    if start is not None and end is not None:
+        bin0 = max(0, -(-(start - 1000) // 1000)) * 1000       # first 1000-aligned bin whose end reaches `start`
+        last = (end // 1000) * 1000
+    else:
+        bin0, last = 0, max([_last_bin_start(t) for t in texts if t] or [-1])
+    if last < bin0:
+        return None
+    b = (last - bin0) // 1000 + 1
+    ld = (b + 3) // 4 * 4
+    dev = torch.device("cuda")
+    depth = torch.zeros((len(ids), ld), dtype=torch.float32, device=dev)
+    stats = torch.zeros((len(ids), 8), dtype=torch.int64, device=dev)
+    ws = torch.empty(_lib.load().gridb200_ingest_ws_bytes(b), dtype=torch.uint8, device=dev)
+    # the mask is looked up by the LINE's chromosome (:281-283); one bitset serves when every kept line carries
+    # exactly `chrom` (checked below through stats[4]) -- genome-wide masks go through the host packer
+    mask_bits, mask_kb = None, 0
+    if excluded:
+        if not chrom:
+            return None
+        kbs = excluded.get(norm_chrom(chrom), set())
+        if kbs:
+            mask_kb = max(kbs) + 1
+            bits = np.zeros((mask_kb + 31) // 32, dtype=np.uint32)
+            for kb in kbs:
+                bits[kb >> 5] |= np.uint32(1 << (kb & 31))
+            mask_bits = torch.from_numpy(bits).to(dev)
+    st = torch.cuda.current_stream().cuda_stream
+    keep_alive = []
+    with progress_bar(console, total=len(ids), description="Extracting per-sample regions...") as (progress, task):
+        for i, text in enumerate(texts):
+            if text:
+                t = torch.frombuffer(bytearray(text), dtype=torch.uint8).to(dev, non_blocking=False)
+                keep_alive.append(t)
+                call("gridb200_ingest_text", ptr(t), len(text), want, len(want),
+                     start if start is not None and end is not None else -1, end if end is not None else -1,
+                     ptr(mask_bits), mask_kb, bin0, b, depth.data_ptr() + i * ld * 4, stats.data_ptr() + i * 64,
+                     ptr(ws), ws.numel(), st)
+                if len(keep_alive) > 4:
+                    torch.cuda.current_stream().synchronize()
+                    keep_alive.clear()
+            progress.update(task, advance=1)
+    hs = stats.cpu().numpy()
+    redo = np.nonzero((hs[:, 1] > 0) | ((hs[:, 4] > 0) & bool(excluded)))[0]
+    for i in redo.tolist():  # exotic file: the reference's own parsing rules, on the host, into the same row
+        try:
+            s_, e_, h_ = gio.parse_regions_text(texts[i], chrom, start, end, excluded)
+        except Exception:
+            s_ = e_ = h_ = np.zeros(0, dtype=np.int64)  # the reference drops a file it cannot parse (:286-287)
+        rel = s_ - bin0
+        if len(s_) and (np.any(rel % 1000) or np.any(rel < 0) or np.any(rel // 1000 >= b) or np.any(e_ - s_ > 1000)
+                        or np.any(e_ <= s_)):
+            return None  # bins off the regular grid: only the host packer can represent them
+        row = np.zeros(ld, dtype=np.float32)
+        row[rel // 1000] = h_ / 100.0  # later duplicates overwrite: last wins
+        depth[i] = torch.from_numpy(row).to(dev)
+    bins = np.stack([bin0 + 1000 * np.arange(b, dtype=np.int64), bin0 + 1000 * np.arange(1, b + 1, dtype=np.int64)], axis=1)
+    return ids, bins, depth
+
+
 def normalize_mosdepth(config, console):
     """Same contract as the reference's normalize_mosdepth(config, console) (normalize_mosdepth.py:23-145)."""
     try:
@@ -90,13 +187,20 @@ def normalize_mosdepth(config, console):
 
     from .. import engine
 
-    ids, bins, depth = pack_depth_matrix(individuals, mosdepth_dir, chrom, start, end, excluded, threads, console)
+    packed = None
+    if config.get("gpu", {}).get("device_ingest", True):  # additive key; default = parse on the GPU
+        packed = pack_depth_matrix_device(individuals, mosdepth_dir, chrom, start, end, excluded, threads, console)
+    if packed is None:
+        ids, bins, host_depth = pack_depth_matrix(individuals, mosdepth_dir, chrom, start, end, excluded, threads, console)
+        depth = torch.from_numpy(host_depth).cuda()
+    else:
+        ids, bins, depth = packed
     b = len(bins)
     if b == 0:
         log(console, "No valid samples with regions found.", style="danger")
         sys.exit(1)
     p = engine.Params(min_depth=min_depth, max_depth=max_depth, top_frac=top_frac)
-    res = engine.normalize(torch.from_numpy(depth).cuda(), b, p, want_zq=True, want_zh=False)
+    res = engine.normalize(depth, b, p, want_zq=True, want_zh=False)
     rows = np.nonzero(res.extra["rowcnt"].cpu().numpy() > 0)[0]  # filter_empty_samples (:576-600)
     if len(rows) < len(ids):
         log(console, f"Removed {len(ids) - len(rows)} samples with 0 regions", style="warning")

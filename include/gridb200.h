@@ -177,14 +177,19 @@ GRIDB200_API int gridb200_synth_depth(uint64_t seed, int64_t n, int64_t b, int64
 
 /* ------------------------------------------------------------------ ingest (mosdepth text) --------------- */
 
-/* Parse one sample's decompressed `chrom\tstart\tend\tdepth\n` text on the device and scatter the depths
- * into row `row` of the packed matrix (the line filters of normalize_mosdepth.py:262-285/:321-352):
- * chromosome PREFIX match (chrom_len = 0 matches all), >= 4 tab fields, depth > 0, bin touching the closed
- * window [win_lo, win_hi] (win_lo < 0: no window), not masked (mask_bits: bit kb set = masked, may be null).
- * Column = (start - bin0) / 1000 for bins of exactly 1000 bp aligned to bin0; other lines are counted in
- * stats[1] (irregular) and skipped.  stats (device, 4 x int64): [0]=kept [1]=irregular [2]=lines [3]=masked.
- * ws: 8 bytes per text byte / 16 + 64 KiB. */
-GRIDB200_API size_t gridb200_ingest_ws_bytes(int64_t nbytes);
+/* Parse one sample's decompressed `chrom\tstart\tend\tdepth\n` text on the device and write row `depth_row`
+ * [b] of the packed matrix (the line filters of normalize_mosdepth.py:262-285/:321-352): chromosome PREFIX match
+ * (chrom_len = 0 matches all), >= 4 tab fields, depth > 0, bin touching the closed window [win_lo, win_hi]
+ * (win_lo < 0: no window), no masked kb in [start/1000, end/1000] (mask_bits: bit kb set = masked, mask_kb bits,
+ * may be null).  Column = (start - bin0) / 1000 for bins with start aligned to bin0 and 0 < end - start <= 1000;
+ * a bin repeated in the file keeps its LAST depth (:285).  Bins never seen are written as 0.0f (absent).
+ * stats (device, 8 x int64): [0]=kept lines [1]=irregular lines (outside the strict grammar digits[.dd] /
+ * unaligned / out of range: skipped here -- the caller re-parses such a file on the host to keep the
+ * reference's Python int()/float() semantics) [2]=lines matching the prefix [3]=masked lines [4]=lines whose
+ * chromosome field is longer than the prefix (the reference's startswith quirk: with a mask the caller must
+ * check these, because the mask is looked up by the line's own chromosome).
+ * ws: gridb200_ingest_ws_bytes(b). */
+GRIDB200_API size_t gridb200_ingest_ws_bytes(int64_t b);
 GRIDB200_API int gridb200_ingest_text(const char* text, int64_t nbytes, const char* chrom_prefix, int32_t chrom_len,
                          int64_t win_lo, int64_t win_hi, const uint32_t* mask_bits, int64_t mask_kb,
                          int64_t bin0, int64_t b, float* depth_row, int64_t* stats,

@@ -265,3 +265,85 @@ def test_errors_surface_as_exceptions(eng):
     with pytest.raises(GridB200Error):
         eng.knn(torch.zeros((1, 4, 64), dtype=torch.float16, device="cuda"), 64, torch.zeros(4, dtype=torch.int64, device="cuda"),
                 2, 5000)
+
+
+def _ingest(eng, text: bytes, chrom, lo, hi, mask: dict, bin0: int, b: int):
+    """One gridb200_ingest_text call -> (row of hundredths as int64, stats)."""
+    from grid_b200._lib import call, load, ptr
+
+    want = (chrom if chrom.startswith("chr") else "chr" + chrom).encode() if chrom else b""
+    t = torch.frombuffer(bytearray(text), dtype=torch.uint8).cuda() if text else torch.zeros(1, dtype=torch.uint8).cuda()
+    row = torch.full((b,), -1.0, dtype=torch.float32, device="cuda")
+    stats = torch.zeros(8, dtype=torch.int64, device="cuda")
+    ws = torch.empty(load().gridb200_ingest_ws_bytes(b), dtype=torch.uint8, device="cuda")
+    bits, nkb = None, 0
+    kbs = mask.get(want.decode(), set()) if mask else set()
+    if kbs:
+        nkb = max(kbs) + 1
+        arr = np.zeros((nkb + 31) // 32, dtype=np.uint32)
+        for kb in kbs:
+            arr[kb >> 5] |= np.uint32(1 << (kb & 31))
+        bits = torch.from_numpy(arr).cuda()
+    call("gridb200_ingest_text", ptr(t), len(text), want, len(want), lo if lo is not None else -1,
+         hi if hi is not None else -1, ptr(bits), nkb, bin0, b, ptr(row), ptr(stats), ptr(ws), ws.numel(),
+         torch.cuda.current_stream().cuda_stream)
+    return np.rint(row.cpu().numpy().astype(np.float64) * 100).astype(np.int64), stats.cpu().numpy()
+
+
+def test_device_ingest_matches_the_reference_line_filters(eng):
+    """The device text parser against the host restatement of normalize_mosdepth.py:262-285 on hand-written lines
+    (the reference's own known answers: test_normalize_extra.py:28-115) and on a generated file."""
+    from grid_b200 import io as gio
+
+    lines = ["chr6\t1000\t2000\t25.50", "chr6\t2000\t3000\t0.00", "chr60\t4000\t5000\t7.25", "chr5\t1000\t2000\t9.00",
+             "chr6\t9000\t10000\t31.10", "chr6\t3000\t4000\t12.34", "short\tline", "chr6\t3000\t4000\t13.37", "",
+             "chr6\t5000\t6000\t8", "chr6\t6000\t7000\t8.5\textra\tcols", "chr6\t7000\t7500\t41943.03\r",
+             "chr6\t8000\t9000\t", "chr6\t10000\t11000"]
+    text = "\n".join(lines).encode()                                           # no trailing newline
+    b = 12
+    for chrom, lo, hi, mask in (("chr6", 1000, 4000, {}), ("6", 1000, 4000, {"chr6": {3}}), (None, None, None, {}),
+                                ("chr6", None, None, {"chr6": {1, 2, 9}}), ("chr6", 6500, 6500, {})):
+        s, e, h = gio.parse_regions_text(text, chrom, lo, hi, mask)
+        want = np.zeros(b, dtype=np.int64)
+        want[s // 1000] = h                                                    # later duplicates overwrite
+        got, st = _ingest(eng, text, chrom, lo, hi, mask, 0, b)
+        np.testing.assert_array_equal(got, want)
+        assert st[1] == 0 and st[0] == len(s)                                  # nothing irregular; kept lines agree
+    # with chr6 as prefix the chr60 line is admitted (startswith) and reported as foreign
+    assert _ingest(eng, text, "chr6", None, None, {}, 0, b)[1][4] == 1
+    # lines outside the strict grammar are counted, never guessed
+    for bad in ("chr6\t1000\t2000\t1e1", "chr6\t1000\t2000\t2.345", "chr6\t1000\t2500x\t3.00", "chr6\t1500\t2500\t3.00",
+                "chr6\t1000\t3000\t3.00", "chr6\t99000\t100000\t3.00", "chr6\t1000\t2000\t-3.00", "chr6\t1000\t2000\t41943.04"):
+        got, st = _ingest(eng, (bad + "\nchr6\t0\t1000\t1.00\n").encode(), "chr6", None, None, {}, 0, b)
+        assert st[1] == 1 and got[0] == 100 and got[1:].sum() == 0, bad
+    got, st = _ingest(eng, b"", "chr6", None, None, {}, 0, b)
+    assert got.sum() == 0 and st.sum() == 0
+    # a generated sample file, whole-chromosome, vs the host parser
+    n_bins = 5000
+    hund = synth.depth_hundredths(77, 1, n_bins)[0]
+    body = "".join(f"chr1\t{1000 * j}\t{1000 * (j + 1)}\t{hund[j] // 100}.{hund[j] % 100:02d}\n" for j in range(n_bins))
+    got, st = _ingest(eng, body.encode(), "chr1", None, None, {}, 0, n_bins)
+    np.testing.assert_array_equal(got, hund)
+    assert st[0] == (hund > 0).sum() and st[2] == n_bins
+
+
+def test_device_and_host_packers_agree(tmp_path, eng):
+    """pack_depth_matrix_device (GPU parse) and pack_depth_matrix (host parse) build the same matrix."""
+    from grid_b200 import io as gio
+    from grid_b200.utils import normalize_mosdepth as nm
+
+    cfg = synth.write_cohort_files(tmp_path, 5, 12, 300)
+    samples = [ln.strip() for ln in open(cfg["samples_file"]) if ln.strip()]
+    wd = cfg["mosdepth"]["work_dir"]
+    ind = gio.map_mosdepth_files_to_samples(wd, samples)
+    for chrom, lo, hi in ((cfg.get("chrom"), cfg.get("start_bp"), cfg.get("end_bp")), (cfg.get("chrom"), None, None)):
+        ids_h, bins_h, dep_h = nm.pack_depth_matrix(ind, wd, chrom, lo, hi, {}, 2, None)
+        ids_d, bins_d, dep_d = nm.pack_depth_matrix_device(ind, wd, chrom, lo, hi, {}, 2, None)
+        assert ids_h == ids_d
+        dd = dep_d.cpu().numpy()
+        col = {(int(s), int(e)): j for j, (s, e) in enumerate(bins_d)}
+        seen = np.zeros(dd.shape[1], dtype=bool)
+        for j, (s, e) in enumerate(bins_h):
+            np.testing.assert_array_equal(dd[:, col[(int(s), int(e))]], dep_h[:, j])
+            seen[col[(int(s), int(e))]] = True
+        assert (dd[:, ~seen] == 0).all()                                       # grid bins nobody has stay absent
