@@ -234,51 +234,74 @@ def zh_rowmajor(zh: torch.Tensor) -> torch.Tensor:
     return zh.permute(1, 0, 2).reshape(zh.shape[1], zh.shape[0] * 64)
 
 
+def knn_init(nq: int, k: int, dev):
+    """Empty running k-best lists (ascending by (d2, global index)) for nq query rows."""
+    best_d2 = torch.empty((nq, k), dtype=torch.int64, device=dev)
+    best_idx = torch.empty((nq, k), dtype=torch.int32, device=dev)
+    call("gridb200_topk_init", ptr(best_d2), ptr(best_idx), nq, k, _stream())
+    return best_d2, best_idx
+
+
+def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torch.Tensor, norms_r: torch.Tensor,
+              r_gid0: int, kdim: int, vmax: int, best_d2: torch.Tensor, best_idx: torch.Tensor, impl: int = 0,
+              group=None, max_block_bytes: int = 2 << 30) -> None:
+    """Merge the reference rows of ``zh_r`` (global ids r_gid0..) into the running lists of the query rows of
+    ``zh_q`` (global ids q_gid0..).  Operands are k-blocked [kdim/64, rows, 64]; the N x N distances only ever
+    exist as query-block x reference-shard Gram tiles (<= max_block_bytes)."""
+    for t in (zh_q, zh_r):
+        assert t.dim() == 3 and t.shape[2] == 64 and t.is_contiguous() and t.shape[0] * 64 == kdim, "zh is [kdim/64, n, 64]"
+    nq_all, nr = zh_q.shape[1], zh_r.shape[1]
+    k = best_d2.shape[1]
+    dev, st = zh_q.device, _stream()
+    if impl == 0 and vmax > 511:
+        impl = 1  # |v| > 511: a 64-wide fp32 chunk is no longer exact; the integer SIMT kernel takes over (still GPU)
+    ldd = (nr + 1) // 2 * 2
+    qb = max(1, min(nq_all, max_block_bytes // (8 * ldd)))
+    rchunk = 8192 - k
+    for q0 in range(0, nq_all, qb):
+        nq = min(qb, nq_all - q0)
+        dot = torch.empty((nq, ldd), dtype=torch.int64, device=dev)
+        with _mark("gram"):
+            call("gridb200_gram", zh_q.data_ptr() + q0 * 64 * 2, nq, nq_all, ptr(zh_r), nr, nr, kdim, vmax, ptr(dot), ldd,
+                 0, impl, st)
+        _all_reduce(dot, group)
+        with _mark("topk"):
+            for r0 in range(0, nr, rchunk):
+                n_r = min(rchunk, nr - r0)
+                call("gridb200_topk_merge", dot.data_ptr() + r0 * 8, ldd, nq, n_r, norms_q.data_ptr() + q0 * 8,
+                     norms_r.data_ptr() + r0 * 8, q_gid0 + q0, r_gid0 + r0, k, best_d2.data_ptr() + q0 * k * 8,
+                     best_idx.data_ptr() + q0 * k * 4, st)
+
+
 def knn(zh: torch.Tensor, kdim: int, norms: torch.Tensor, k: int, vmax: int, impl: int = 0, group=None,
         max_block_bytes: int = 2 << 30):
     """Exact k nearest neighbours of every row among all rows (self excluded): (idx[n,k] int32, d2[n,k] int64).
 
     zh is the k-blocked operand [kdim/64, n, 64] written by gridb200_transform / gridb200_knn_prepare.
     d2 is in units of 1e-4 (hundredths squared).  Rows with fewer than k candidates are padded with -1.
-    Bin-sharded multi-GPU: each rank contributes the Gram partial of its bins; partials are all-reduced.
+    Bin-sharded multi-GPU (``group``): each rank contributes the Gram partial of its bins; partials are all-reduced.
     """
     assert zh.dim() == 3 and zh.shape[2] == 64 and zh.is_contiguous() and zh.shape[0] * 64 == kdim, "zh is [kdim/64, n, 64]"
     n = zh.shape[1]
-    dev, st = zh.device, _stream()
-    if impl == 0 and vmax > 511:
-        impl = 1  # |v| > 511: a 64-wide fp32 chunk is no longer exact; the integer SIMT kernel takes over (still GPU)
     k = max(1, min(k, n - 1)) if n > 1 else 1
-    best_d2 = torch.empty((n, k), dtype=torch.int64, device=dev)
-    best_idx = torch.empty((n, k), dtype=torch.int32, device=dev)
-    call("gridb200_topk_init", ptr(best_d2), ptr(best_idx), n, k, st)
-    ldd = (n + 1) // 2 * 2
-    qb = max(1, min(n, max_block_bytes // (8 * ldd)))
-    rchunk = 8192 - k
-    for q0 in range(0, n, qb):
-        nq = min(qb, n - q0)
-        dot = torch.empty((nq, ldd), dtype=torch.int64, device=dev)
-        with _mark("gram"):
-            call("gridb200_gram", zh.data_ptr() + q0 * 64 * 2, nq, n, ptr(zh), n, n, kdim, vmax, ptr(dot), ldd, 0,
-                 impl, st)
-        _all_reduce(dot, group)
-        with _mark("topk"):
-            for r0 in range(0, n, rchunk):
-                nr = min(rchunk, n - r0)
-                call("gridb200_topk_merge", dot.data_ptr() + r0 * 8, ldd, nq, nr, norms.data_ptr() + q0 * 8,
-                     norms.data_ptr() + r0 * 8, q0, r0, k, best_d2.data_ptr() + q0 * k * 8,
-                     best_idx.data_ptr() + q0 * k * 4, st)
+    best_d2, best_idx = knn_init(n, k, zh.device)
+    knn_block(zh, norms, 0, zh, norms, 0, kdim, vmax, best_d2, best_idx, impl=impl, group=group,
+              max_block_bytes=max_block_bytes)
     return best_idx, best_d2
 
 
-def dipcn(counts: torch.Tensor, has_count: torch.Tensor, scale_q: torch.Tensor, nbr_idx: torch.Tensor, n_nbr: int):
-    """Step 6 on device arrays: counts[n,g] int32, has_count[n] uint8, scale_q[n] f64, nbr_idx[n,k] int32 -> out[n,g] f64."""
+def dipcn(counts: torch.Tensor, has_count: torch.Tensor, scale_q: torch.Tensor, nbr_idx: torch.Tensor, n_nbr: int,
+          q_gid0: int = 0):
+    """Step 6 on device arrays: counts[n_all,g] int32, has_count[n_all] uint8, scale_q[n_all] f64 for the WHOLE cohort,
+    nbr_idx[nq,k] int32 (global ids) for query rows q_gid0.. -> out[nq,g] f64."""
     n, g = counts.shape
     dev = counts.device
-    out = torch.empty((n, g), dtype=torch.float64, device=dev)
+    nq = nbr_idx.shape[0]
+    out = torch.empty((nq, g), dtype=torch.float64, device=dev)
     t_ws = torch.empty(n * g, dtype=torch.float64, device=dev)
     with _mark("dipcn"):
         call("gridb200_dipcn", ptr(counts), n, g, counts.stride(0), ptr(has_count), ptr(scale_q), ptr(nbr_idx),
-             nbr_idx.shape[0], nbr_idx.shape[1], 0, int(n_nbr), ptr(out), g, ptr(t_ws), _stream())
+             nq, nbr_idx.shape[1], int(q_gid0), int(n_nbr), ptr(out), g, ptr(t_ws), _stream())
     return out
 
 

@@ -1,0 +1,176 @@
+"""Row-sharded multi-GPU schedule: every rank owns a contiguous block of SAMPLES (all bins) and the reference
+shards travel around a ring (rank r -> r+1) while the Gram/top-k kernels work on the shard that has arrived.
+
+This is the schedule for cohorts whose N x N Gram partials no longer fit (BASELINE configs 3/4); for N << bins
+(configs 1/2) the bin-sharded path in engine.py moves far fewer bytes (DESIGN.md "Multi-GPU").
+
+What crosses the ring / the collectives (torch.distributed; NCCL over NVLink on GPUs, gloo in the CPU tests):
+  * per-bin raw sums and counts, per-bin normalised sums: all-reduce (B x 8..12 bytes each)
+  * the clipped operand shards zh[kdim/64, n_r, 64] (fp16): W-1 ring hops, double-buffered so that hop t+1 is in
+    flight while hop t is being multiplied; every rank keeps its own running k-best lists -> no merge collective
+  * row norms, %.2f scales, read counts: all-gather (N x a few bytes)
+
+The ring driver (`ring_knn`) is device-agnostic: the per-hop work is a callable, so the CPU tests drive the very
+same schedule over gloo with a numpy block kernel.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+
+def shard_rows(n_total: int, world: int) -> tuple[list[int], list[int]]:
+    """Balanced contiguous row blocks: (counts, offsets) per rank; the first n_total % world ranks get one more."""
+    base, extra = divmod(n_total, world)
+    counts = [base + (1 if r < extra else 0) for r in range(world)]
+    offsets = [sum(counts[:r]) for r in range(world)]
+    return counts, offsets
+
+
+def ring_source(rank: int, step: int, world: int) -> int:
+    """Rank whose shard is resident on `rank` at hop `step` (hop 0 = its own)."""
+    return (rank - step) % world
+
+
+def ring_knn(shard: torch.Tensor, shard_rows_max: int, counts: list[int], offsets: list[int], group, block_fn,
+             flat_per_row: int) -> None:
+    """Drive the ring: call block_fn(step, src_rank, ref_shard_view, n_ref, r_gid0) for every hop.
+
+    shard          this rank's reference shard, a contiguous tensor whose storage is `counts[rank] * flat_per_row`
+                   elements (any layout the block kernel understands -- it is only ever moved, never indexed here)
+    shard_rows_max max(counts): the two ring buffers are sized for the largest shard
+    block_fn       consumes the shard resident at this hop; must not keep a reference past the following hop
+    """
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    cur = shard.reshape(-1)
+    if world == 1:
+        block_fn(0, rank, cur, counts[rank], offsets[rank])
+        return
+    bufs = [torch.empty(shard_rows_max * flat_per_row, dtype=shard.dtype, device=shard.device) for _ in range(2)]
+    nxt_rank, prv_rank = dist.get_global_rank(group, (rank + 1) % world), dist.get_global_rank(group, (rank - 1) % world)
+    for step in range(world):
+        src = ring_source(rank, step, world)
+        works = []
+        if step + 1 < world:
+            # pass the resident shard on and receive the next one into the other buffer WHILE this hop computes;
+            # the collective library orders the transfer after everything already queued on the current stream,
+            # i.e. after the previous hop's kernels have finished with the buffer being overwritten
+            incoming = ring_source(rank, step + 1, world)
+            recv_view = bufs[(step + 1) % 2][: counts[incoming] * flat_per_row]
+            send_view = cur[: counts[src] * flat_per_row]
+            ops = [dist.P2POp(dist.isend, send_view, nxt_rank, group), dist.P2POp(dist.irecv, recv_view, prv_rank, group)]
+            works = dist.batch_isend_irecv(ops)
+        block_fn(step, src, cur[: counts[src] * flat_per_row], counts[src], offsets[src])
+        for w in works:
+            w.wait()
+        if step + 1 < world:
+            cur = bufs[(step + 1) % 2]
+
+
+def _all_reduce(t, group):
+    dist.all_reduce(t, group=group)
+
+
+def _all_gather_rows(t: torch.Tensor, counts: list[int], group) -> torch.Tensor:
+    """Concatenate per-rank row blocks of unequal length (dim 0) on every rank."""
+    world = dist.get_world_size(group)
+    mx = max(counts)
+    pad = torch.zeros((mx,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+    pad[: t.shape[0]] = t
+    out = torch.empty((world * mx,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+    dist.all_gather_into_tensor(out, pad, group=group)
+    return torch.cat([out[r * mx: r * mx + counts[r]] for r in range(world)])
+
+
+def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, group, impl: int = 0):
+    """normalize -> kNN -> dipCN for the row block this rank holds (depth [n_local, ld], counts_local [n_local, G]).
+
+    Returns (NormResult for the local rows, idx [n_local, k] GLOBAL sample ids, d2 [n_local, k], dipcn [n_local, G]).
+    Same arithmetic and the same kernels as engine.run_chain; only the exchange steps differ.
+    """
+    from . import engine as E
+    from ._lib import call, load, ptr
+
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    n, ld = E.check_depth(depth, b)
+    dev, st = depth.device, E._stream()
+    i64, f64 = dict(dtype=torch.int64, device=dev), dict(dtype=torch.float64, device=dev)
+    nloc = torch.zeros(world, **i64)
+    nloc[rank] = n
+    _all_reduce(nloc, group)
+    counts = [int(x) for x in nloc.tolist()]
+    offsets = [sum(counts[:r]) for r in range(world)]
+    n_total = sum(counts)
+
+    # ---- step 4: per-bin statistics are summed over ranks, everything per-sample is local ------------------
+    colsum, colcnt = torch.empty(b, **i64), torch.empty(b, dtype=torch.int32, device=dev)
+    valid = torch.empty(b, dtype=torch.uint8, device=dev)
+    with E._mark("col_raw"):
+        call("gridb200_col_raw_stats", ptr(depth), n, b, ld, ptr(colsum), ptr(colcnt), st)
+    _all_reduce(colsum, group)
+    _all_reduce(colcnt, group)
+    call("gridb200_depth_filter", ptr(colsum), ptr(colcnt), b, float(p.min_depth), float(p.max_depth), ptr(valid), st)
+    rowsum, rowcnt = torch.empty(n, **i64), torch.empty(n, dtype=torch.int32, device=dev)
+    with E._mark("row_stats"):
+        call("gridb200_row_stats", ptr(depth), n, b, ld, ptr(valid), ptr(rowsum), ptr(rowcnt), st)
+    raw_mean, scale_q, row_factor = torch.empty(n, **f64), torch.empty(n, **f64), torch.empty(n, **f64)
+    call("gridb200_row_scales", ptr(rowsum), ptr(rowcnt), n, ptr(raw_mean), ptr(scale_q), ptr(row_factor), st)
+    sd, sd2 = torch.empty(b, **f64), torch.empty(b, **f64)
+    ws = E._ws(load().gridb200_col_norm_stats_ws_bytes(n, b), dev)
+    with E._mark("col_norm"):
+        call("gridb200_col_norm_stats", ptr(depth), n, b, ld, ptr(valid), ptr(row_factor), ptr(sd), ptr(sd2), ptr(ws),
+             ws.numel(), st)
+    _all_reduce(sd, group)
+    _all_reduce(sd2, group)
+    n_eff_t = (rowcnt > 0).sum().to(torch.int64).reshape(1)
+    _all_reduce(n_eff_t, group)
+    n_eff = int(n_eff_t.item())
+    mu, s2, ratio = torch.empty(b, **f64), torch.empty(b, **f64), torch.empty(b, **f64)
+    call("gridb200_col_finalize", ptr(sd), ptr(sd2), ptr(colcnt), ptr(valid), b, n_eff, ptr(mu), ptr(s2), ptr(ratio), st)
+    sel_pos = torch.empty(b, dtype=torch.int32, device=dev)
+    keep = torch.empty(b, dtype=torch.uint8, device=dev)
+    info, info2 = torch.empty(4, **f64), torch.empty(2, **f64)
+    ws2 = E._ws(load().gridb200_select_ws_bytes(b), dev)
+    with E._mark("select"):
+        call("gridb200_select", ptr(ratio), b, float(p.top_frac), ptr(sel_pos), ptr(info), ptr(ws2), ws2.numel(), st)
+        call("gridb200_knn_col_filter", ptr(ratio), ptr(sel_pos), b, float(p.frac_r), float(p.sigma2_max), ptr(keep),
+             ptr(info), ptr(info2), ptr(ws2), ws2.numel(), st)
+    host = torch.cat([info, info2]).cpu()
+    zscale, rw, r_use = float(host[0]), int(host[3]), int(host[4])
+    if rw < 0:
+        raise IndexError("list index out of range")
+    if rw == 0:
+        raise ValueError("no bins selected")
+    res = E.NormResult(n=n, b=b, colsum=colsum, colcnt=colcnt, valid=valid, raw_mean=raw_mean, scale_q=scale_q,
+                       row_factor=row_factor, mu=mu, s2=s2, ratio=ratio, sel_pos=sel_pos, keep=keep, zscale=zscale,
+                       rw=rw, rw_local=rw, r_use=r_use)
+    res.extra.update(n_eff=n_eff, rowcnt=rowcnt, row_counts=counts, row_offsets=offsets)
+    kdim = (rw + 63) // 64 * 64
+    zh = torch.empty((kdim // 64, n, 64), dtype=torch.float16, device=dev)
+    if kdim > rw:
+        zh[-1, :, rw % 64:] = 0
+    norms = torch.zeros(n, **i64)
+    sat = torch.zeros(1, **i64)
+    with E._mark("transform"):
+        call("gridb200_transform", ptr(depth), n, b, ld, ptr(row_factor), ptr(mu), ptr(sel_pos), ptr(keep), ptr(info),
+             p.zclip, None, 0, ptr(zh), n, ptr(norms), ptr(sat), st)
+    res.zh, res.kdim, res.norms = zh, kdim, norms
+
+    # ---- step 5: ring of reference shards ------------------------------------------------------------------
+    norms_all = _all_gather_rows(norms, counts, group)
+    k = max(1, min(p.num_neighbors, n_total - 1)) if n_total > 1 else 1
+    best_d2, best_idx = E.knn_init(n, k, dev)
+
+    def block(step, src, flat, n_ref, r_gid0):
+        ref = zh if step == 0 else flat.view(kdim // 64, n_ref, 64)  # hop 0 is the symmetric (same-operand) case
+        E.knn_block(zh, norms, offsets[rank], ref, norms_all[r_gid0:r_gid0 + n_ref], r_gid0, kdim, p.zclip, best_d2,
+                    best_idx, impl=impl)
+
+    ring_knn(zh, max(counts), counts, offsets, group, block, flat_per_row=kdim)
+
+    # ---- step 6: scaled counts are tiny -> all-gather, then a local gather-reduce ----------------------------
+    counts_all = _all_gather_rows(counts_local.contiguous(), counts, group)
+    scale_all = _all_gather_rows(scale_q, counts, group)
+    has = torch.ones(n_total, dtype=torch.uint8, device=dev)
+    cn = E.dipcn(counts_all, has, scale_all, best_idx, p.n_nbr, q_gid0=offsets[rank])
+    return res, best_idx, best_d2, cn

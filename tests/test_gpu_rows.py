@@ -1,0 +1,78 @@
+"""Row-sharded (ring) chain on GPUs against the oracle: one rank (every kernel and collective call of the path, no
+hop) on any box; two and more ranks when the box has the GPUs (NCCL)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+import torch.distributed as dist  # noqa: E402
+import torch.multiprocessing as mp  # noqa: E402
+
+from grid_b200 import synth  # noqa: E402
+from oracle import grid_oracle as O  # noqa: E402
+
+DIPCN_REL = 1e-5
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, seed, n, b, params, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), NCCL_DEBUG="WARN")
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from grid_b200 import engine, ring
+
+        h = synth.depth_hundredths(seed, n, b)
+        counts = synth.read_counts(seed, n, [42599, 1000])
+        want = O.chain_arrays(h / 100.0, counts, **params)
+        cnt, off = ring.shard_rows(n, world)
+        lo, hi = off[rank], off[rank] + cnt[rank]
+        depth = engine.synth_depth(seed, cnt[rank], b, row0=lo)                  # this rank's samples, all bins
+        res, idx, d2, cn = ring.run_chain_rows(depth, b, torch.from_numpy(counts[lo:hi]).cuda(), engine.Params(**params),
+                                               dist.group.WORLD)
+        np.testing.assert_array_equal(idx.cpu().numpy(), want["nbr_idx"][lo:hi])  # global ids, (d2, index) order
+        np.testing.assert_array_equal(d2.cpu().numpy(), want["nbr_d2"][lo:hi])
+        np.testing.assert_allclose(cn.cpu().numpy(), want["dipcn"][lo:hi], rtol=DIPCN_REL)
+        np.testing.assert_array_equal(res.scale_q.cpu().numpy(), want["scale_q"][lo:hi])
+        assert res.rw == len(want["sel"]) and res.r_use == want["r_use"]
+        out.put((rank, "ok"))
+    except Exception as exc:
+        out.put((rank, f"{type(exc).__name__}: {str(exc)[:400]}"))
+    finally:
+        dist.destroy_process_group()
+
+
+def _run(world, seed, n, b, params):
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, seed, n, b, params, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(out.get(timeout=300) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert res == {r: "ok" for r in range(world)}
+
+
+def test_rows_chain_single_rank():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    _run(1, 31, 130, 3000, dict(num_neighbors=20, n_nbr=8))
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_rows_chain_ring(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    # uneven shards (n % world != 0), k larger than a shard, several 256-row tiles per shard at world = 2
+    _run(world, 32, 601, 4000, dict(num_neighbors=350, n_nbr=300))

@@ -1,0 +1,89 @@
+"""The row-sharded ring schedule on CPU: world_size 2 and 3 over gloo, with a numpy block kernel standing in for the
+CUDA Gram/top-k kernels (which need a GPU).  What is under test is the host logic of grid_b200/ring.py: shard
+layout, which shard is resident at which hop, global row offsets, double-buffered send/recv, uneven shards."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+import torch.distributed as dist  # noqa: E402
+import torch.multiprocessing as mp  # noqa: E402
+
+from grid_b200 import ring  # noqa: E402
+
+
+def test_shard_rows_and_ring_source():
+    assert ring.shard_rows(10, 3) == ([4, 3, 3], [0, 4, 7])
+    assert ring.shard_rows(3202, 8)[0] == [401, 401] + [400] * 6 and sum(ring.shard_rows(3202, 8)[0]) == 3202
+    assert ring.shard_rows(2, 4) == ([1, 1, 0, 0], [0, 1, 2, 2])
+    for world in (1, 2, 5, 8):
+        for rank in range(world):
+            seen = [ring.ring_source(rank, t, world) for t in range(world)]
+            assert seen[0] == rank and sorted(seen) == list(range(world))       # every shard visits every rank once
+            # what rank receives at hop t+1 is what rank-1 held at hop t
+            assert all(ring.ring_source(rank, t + 1, world) == ring.ring_source((rank - 1) % world, t, world)
+                       for t in range(world - 1))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, n_total, kdim, k, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(7)
+        full = rng.integers(-200, 201, size=(n_total, kdim)).astype(np.int64)     # every rank can rebuild the cohort
+        counts, offsets = ring.shard_rows(n_total, world)
+        mine = full[offsets[rank]:offsets[rank] + counts[rank]]
+        shard = torch.from_numpy(mine.astype(np.float32).copy())
+        best = [[] for _ in range(counts[rank])]
+        hops = []
+
+        def block(step, src, flat, n_ref, r_gid0):
+            hops.append((step, src, n_ref, r_gid0))
+            ref = flat.view(n_ref, kdim).numpy().astype(np.int64)
+            np.testing.assert_array_equal(ref, full[r_gid0:r_gid0 + n_ref])       # the right shard arrived intact
+            d2 = ((mine[:, None, :] - ref[None, :, :]) ** 2).sum(axis=2)
+            for i in range(counts[rank]):
+                cand = best[i] + [(int(d2[i, j]), r_gid0 + j) for j in range(n_ref) if r_gid0 + j != offsets[rank] + i]
+                best[i] = sorted(cand)[:k]
+
+        ring.ring_knn(shard, max(counts), counts, offsets, dist.group.WORLD, block, flat_per_row=kdim)
+        assert [h[0] for h in hops] == list(range(world))
+        assert sorted(h[1] for h in hops) == list(range(world))
+        # the union over hops equals the global brute-force answer for this rank's rows
+        for i in range(counts[rank]):
+            g = offsets[rank] + i
+            dd = ((full[g][None, :] - full) ** 2).sum(axis=1)
+            want = sorted((int(dd[j]), j) for j in range(n_total) if j != g)[:k]
+            assert best[i] == want
+        # unequal row blocks gather in rank order
+        t = torch.arange(counts[rank], dtype=torch.int64).reshape(-1, 1) + 100 * rank
+        got = ring._all_gather_rows(t, counts, dist.group.WORLD)
+        want = torch.cat([torch.arange(c, dtype=torch.int64).reshape(-1, 1) + 100 * r for r, c in enumerate(counts)])
+        assert torch.equal(got, want)
+        out.put((rank, "ok"))
+    except Exception as exc:  # surface the failure in the parent
+        out.put((rank, f"{type(exc).__name__}: {exc}"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_total", [(2, 9), (3, 10)])
+def test_ring_over_gloo_matches_global_knn(world, n_total):
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n_total, 48, 4, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(out.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert res == {r: "ok" for r in range(world)}
