@@ -44,6 +44,10 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--gram-impl", type=int, default=0, help="debug: 1 = SIMT cross-check kernel")
     ap.add_argument("--norm-only", action="store_true", help="debug: time step 4 only (not a valid bench line)")
+    ap.add_argument("--sharding", default="bins", choices=["bins", "rows"],
+                    help="multi-GPU partition: 'bins' (default; all samples x a bin slice per rank, N x N partials "
+                         "all-reduced) or 'rows' (a sample block per rank, reference shards ring-passed; the schedule "
+                         "for cohorts whose N x N partials do not fit)")
     return ap.parse_args()
 
 
@@ -198,8 +202,17 @@ def run_ours(a):
     lo, hi = min(a.bins, rank * per), min(a.bins, (rank + 1) * per)
     b_local = hi - lo
     p = engine.Params(num_neighbors=a.k, n_nbr=a.n_nbr)
-    depth = engine.synth_depth(SEED, a.samples, b_local, 0, lo, device=dev)
-    counts = torch.from_numpy(synth.read_counts(SEED, a.samples, [LPA_LEN])).to(dev)
+    rows = a.sharding == "rows" and world > 1
+    if rows:
+        from grid_b200 import ring
+
+        rcnt, roff = ring.shard_rows(a.samples, world)
+        b_local = a.bins
+        depth = engine.synth_depth(SEED, rcnt[rank], a.bins, roff[rank], 0, device=dev)
+        counts = torch.from_numpy(synth.read_counts(SEED, a.samples, [LPA_LEN])[roff[rank]:roff[rank] + rcnt[rank]]).to(dev)
+    else:
+        depth = engine.synth_depth(SEED, a.samples, b_local, 0, lo, device=dev)
+        counts = torch.from_numpy(synth.read_counts(SEED, a.samples, [LPA_LEN])).to(dev)
 
     def barrier():
         if group is not None:
@@ -211,6 +224,8 @@ def run_ours(a):
             r = engine.normalize(depth, b_local, p, want_zq=False, want_zh=True, group=group)
             z = torch.zeros((a.samples, 1), dtype=torch.int32, device=dev)
             return r, z, z, z.double()
+        if rows:
+            return ring.run_chain_rows(depth, b_local, counts, p, group, impl=a.gram_impl)
         return engine.run_chain(depth, b_local, counts, p, impl=a.gram_impl, group=group)
 
     for _ in range(a.warmup):
@@ -241,13 +256,13 @@ def run_ours(a):
         try:
             host = torch.empty(depth.shape, dtype=torch.float32, pin_memory=True)
             host.copy_(depth)
-            outs = [torch.empty((a.samples, idx.shape[1]), dtype=torch.int32, pin_memory=True),
-                    torch.empty((a.samples, 1), dtype=torch.float64, pin_memory=True)]
+            outs = [torch.empty((idx.shape[0], idx.shape[1]), dtype=torch.int32, pin_memory=True),
+                    torch.empty((cn.shape[0], 1), dtype=torch.float64, pin_memory=True)]
 
             def e2e_step():
                 depth.copy_(host, non_blocking=True)
                 r, i, d, c = step()
-                if rank == 0:
+                if rank == 0 or rows:  # bin-sharded ranks all hold the same lists; row-sharded ranks hold their own rows
                     outs[0].copy_(i, non_blocking=True)
                     outs[1].copy_(c, non_blocking=True)
 
@@ -288,11 +303,14 @@ def run_ours(a):
         # mirrors them), so the flops it needs are 2*K*(elements of those tiles), not 2*K*N^2.  `achieved` counts
         # only what the tensor pipe has to do; `full_matrix_equivalent` is the SURVEY figure 2*N*N*K over the same time.
         sym = os.environ.get("GRIDB200_GRAM_NOSYM") != "1" and a.gram_impl == 0
-        edges = list(range(0, a.samples, 256)) + [a.samples]
+        nq0 = rcnt[0] if rows else a.samples  # rank 0's query rows
+        edges = list(range(0, nq0, 256)) + [nq0]
         sizes = [edges[i + 1] - edges[i] for i in range(len(edges) - 1)]
         elems = sum(sizes[i] * sizes[j] for i in range(len(sizes)) for j in range(i if sym else 0, len(sizes)))
+        if rows:  # hop 0 is the symmetric own-shard block; the other hops are full rectangular blocks
+            elems += nq0 * (a.samples - nq0)
         flops = 2.0 * elems * res.rw_local  # this rank's launch
-        full_flops = 2.0 * a.samples * a.samples * res.rw_local
+        full_flops = 2.0 * nq0 * a.samples * res.rw_local
         roof = None
         if gram_ms:
             ach = flops / (gram_ms * 1e-3) / 1e12
@@ -302,7 +320,7 @@ def run_ours(a):
                     "algorithmic": (f"2*Rw_local*(elements of the {'upper-triangle ' if sym else ''}256x256 tiles, clipped to N) = "
                                     f"2*{res.rw_local}*{elems} flop per launch"),
                     "full_matrix_equivalent_tflops": full_flops / (gram_ms * 1e-3) / 1e12, "symmetric": sym}
-        cells = a.samples * b_local
+        cells = (rcnt[0] if rows else a.samples) * b_local
         norm_ms = sum(stages.get(s, {}).get("ms", 0.0) for s in ("col_raw", "row_stats", "col_norm", "transform"))
         stage_roof = {}
         for s, byts in (("col_raw", 4), ("row_stats", 4), ("col_norm", 4), ("transform", 6)):
@@ -313,7 +331,7 @@ def run_ours(a):
             "metric": METRIC, "value": a.samples / (ms / 1e3), "unit": "samples/s", "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64 (normalise) + f16 x f16 -> exact int64 (kNN)", "data": "synthetic",
-            "config": {"workload": workload_name(a), "sharding": f"bins x{world}", "l2": "inputs_exceed_l2 (depth matrix "
+            "config": {"workload": workload_name(a), "sharding": f"{'rows (ring)' if rows else 'bins'} x{world}", "l2": "inputs_exceed_l2 (depth matrix "
                        f"{cells * 4 / 1e9:.1f} GB per GPU)", "selected_bins": res.rw, "gram_impl": a.gram_impl, "norm_only_debug": a.norm_only},
             "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches), "roofline": roof,
             "stages": stages, "normalize_roofline": {"algorithmic_bytes_per_cell": 16, "ms": norm_ms,

@@ -19,6 +19,9 @@ SIGNATURES = {
     "gridb200_version": (C.c_char_p, []),
     "gridb200_launch_count": (_u64, []),
     "gridb200_col_raw_stats": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp]),
+    "gridb200_col_row_raw_stats": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
+    "gridb200_row_stats_fused_ws_bytes": (_sz, [_i64]),
+    "gridb200_row_stats_fused": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gridb200_depth_filter": (C.c_int, [_vp, _vp, _i64, _f64, _f64, _vp, _vp]),
     "gridb200_row_stats": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
     "gridb200_row_scales": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp, _vp]),

@@ -23,19 +23,27 @@ static int64_t pick_row_slab(int64_t n, int64_t col_blocks, int64_t min_rows) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// K1: colsum[j] = sum_i h_ij, colcnt[j] = #{h_ij > 0}
+// K1: colsum[j] = sum_i h_ij, colcnt[j] = #{h_ij > 0}; with kRows also the per-sample totals over ALL bins
+// (rowsum_all[i] = sum_j h_ij, rowcnt_all[i] = #{h_ij > 0}), which let step K3 skip its full pass over the matrix
+// when few bins fail the depth filter (see k_row_fix).
 // ---------------------------------------------------------------------------------------------------------
+template <bool kRows>
 __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ depth, int64_t n, int64_t b,
                                                       int64_t ld, int64_t rows_per_slab,
                                                       unsigned long long* __restrict__ colsum,
-                                                      int* __restrict__ colcnt) {
+                                                      int* __restrict__ colcnt,
+                                                      unsigned long long* __restrict__ rowsum_all,
+                                                      int* __restrict__ rowcnt_all) {
   const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
-  if (j0 >= b) return;
+  const bool live = j0 < b;  // dead threads of the last block stay for the warp collectives (they add zeros)
+  if (!kRows && !live) return;
+  const bool lane0 = (threadIdx.x & 31) == 0;
   const int64_t r0 = (int64_t)blockIdx.y * rows_per_slab;
   const int64_t r1 = min(n, r0 + rows_per_slab);
   unsigned long long s[4] = {0, 0, 0, 0};
   int c[4] = {0, 0, 0, 0};
-  const float* p = depth + r0 * ld + j0;
+  const float* p = depth + r0 * ld + (live ? j0 : 0);
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int64_t base = r0; base < r1; base += 512) {  // uint32 partials cannot overflow within 512 rows
     const int64_t lim = (r1 < base + 512 ? r1 : base + 512);
     unsigned ps[4] = {0, 0, 0, 0};
@@ -43,27 +51,46 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ 
     for (; i + 8 <= lim; i += 8) {
       float4 v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = ld_stream(reinterpret_cast<const float4*>(p + u * ld));
+      for (int u = 0; u < 8; ++u) v[u] = live ? ld_stream(reinterpret_cast<const float4*>(p + u * ld)) : zero4;
       p += 8 * ld;
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
         const int h0 = depth_hundredths(v[u].x), h1 = depth_hundredths(v[u].y);
         const int h2 = depth_hundredths(v[u].z), h3 = depth_hundredths(v[u].w);
         ps[0] += h0; ps[1] += h1; ps[2] += h2; ps[3] += h3;
-        c[0] += h0 > 0; c[1] += h1 > 0; c[2] += h2 > 0; c[3] += h3 > 0;
+        const int k0 = h0 > 0, k1 = h1 > 0, k2 = h2 > 0, k3 = h3 > 0;
+        c[0] += k0; c[1] += k1; c[2] += k2; c[3] += k3;
+        if (kRows) {  // 128 bins x h < 2^22 fit 32 bits
+          const unsigned rs = __reduce_add_sync(0xffffffffu, (unsigned)(h0 + h1) + (unsigned)(h2 + h3));
+          const int rc = __reduce_add_sync(0xffffffffu, (k0 + k1) + (k2 + k3));
+          if (lane0 && rc) {
+            atomicAdd(&rowsum_all[i + u], (unsigned long long)rs);
+            atomicAdd(&rowcnt_all[i + u], rc);
+          }
+        }
       }
     }
     for (; i < lim; ++i) {
-      const float4 v = ld_stream(reinterpret_cast<const float4*>(p));
+      const float4 v = live ? ld_stream(reinterpret_cast<const float4*>(p)) : zero4;
       p += ld;
       const int h0 = depth_hundredths(v.x), h1 = depth_hundredths(v.y);
       const int h2 = depth_hundredths(v.z), h3 = depth_hundredths(v.w);
       ps[0] += h0; ps[1] += h1; ps[2] += h2; ps[3] += h3;
-      c[0] += h0 > 0; c[1] += h1 > 0; c[2] += h2 > 0; c[3] += h3 > 0;
+      const int k0 = h0 > 0, k1 = h1 > 0, k2 = h2 > 0, k3 = h3 > 0;
+      c[0] += k0; c[1] += k1; c[2] += k2; c[3] += k3;
+      if (kRows) {
+        const unsigned rs = __reduce_add_sync(0xffffffffu, (unsigned)(h0 + h1) + (unsigned)(h2 + h3));
+        const int rc = __reduce_add_sync(0xffffffffu, (k0 + k1) + (k2 + k3));
+        if (lane0 && rc) {
+          atomicAdd(&rowsum_all[i], (unsigned long long)rs);
+          atomicAdd(&rowcnt_all[i], rc);
+        }
+      }
     }
 #pragma unroll
     for (int q = 0; q < 4; ++q) s[q] += ps[q];
   }
+  if (!live) return;
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
     if (j0 + q < b) {
@@ -100,7 +127,8 @@ constexpr int kRowChunk = kThreads * 4 * kRowUnroll;  // 16384 bins per block
 __global__ void __launch_bounds__(kThreads) k_row_stats(const float* __restrict__ depth, int64_t b, int64_t ld,
                                                         const uint8_t* __restrict__ valid,
                                                         unsigned long long* __restrict__ rowsum,
-                                                        int* __restrict__ rowcnt) {
+                                                        int* __restrict__ rowcnt, const int* __restrict__ skip_if) {
+  if (skip_if && skip_if[0]) return;  // the per-sample totals are being derived by k_row_fix instead
   const int64_t row = blockIdx.y;
   const int64_t c0 = (int64_t)blockIdx.x * kRowChunk;
   const float* p = depth + row * ld;
@@ -154,6 +182,63 @@ __global__ void __launch_bounds__(kThreads) k_row_stats(const float* __restrict_
       atomicAdd(&rowsum[row], ts);
       atomicAdd(&rowcnt[row], tc);
     }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// K3': per-sample sums over the VALID bins from the totals over all bins that K1 produced:
+//   rowsum = rowsum_all - sum over bins that have data but failed the depth filter ("bad" bins).
+// Reading single columns costs a 32-byte sector per 4-byte cell, so this beats the full pass K3 only while the
+// bad bins are fewer than ~1/8 of all bins; k_bad_list decides ON THE DEVICE (no host round trip): it writes
+// mode[0] = 1 (fix-up) or 0 (full pass); k_row_stats and k_row_fix both read it and one of them returns at once.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void k_bad_list(const uint8_t* __restrict__ valid, const int* __restrict__ colcnt, int64_t b,
+                           int* __restrict__ bad, int* __restrict__ nbad) {
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool is_bad = j < b && !valid[j] && colcnt[j] > 0;
+  const unsigned m = __ballot_sync(0xffffffffu, is_bad);
+  if (!m) return;
+  int base = 0;
+  if ((threadIdx.x & 31) == 0) base = atomicAdd(nbad, __popc(m));
+  base = __shfl_sync(0xffffffffu, base, 0);
+  if (is_bad) bad[base + __popc(m & ((1u << (threadIdx.x & 31)) - 1))] = (int)j;  // order is irrelevant: exact sums
+}
+
+__global__ void k_row_mode(const int* __restrict__ nbad, int64_t b, int* __restrict__ mode) {
+  mode[0] = ((int64_t)nbad[0] * 8 <= b) ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(kThreads) k_row_fix(const float* __restrict__ depth, int64_t ld,
+                                                      const int* __restrict__ bad, const int* __restrict__ nbad,
+                                                      const int* __restrict__ mode,
+                                                      const unsigned long long* __restrict__ rowsum_all,
+                                                      const int* __restrict__ rowcnt_all,
+                                                      unsigned long long* __restrict__ rowsum,
+                                                      int* __restrict__ rowcnt) {
+  if (!mode[0]) return;
+  const int64_t row = blockIdx.x;
+  const int nb = nbad[0];
+  const float* p = depth + row * ld;
+  unsigned long long s = 0;
+  int c = 0;
+  for (int t = threadIdx.x; t < nb; t += kThreads) {
+    const int h = depth_hundredths(p[bad[t]]);
+    s += (unsigned)h;
+    c += h > 0;
+  }
+  s = (unsigned long long)warp_sum((long long)s);
+  c = warp_sum(c);
+  __shared__ unsigned long long ss[kThreads / 32];
+  __shared__ int sc[kThreads / 32];
+  if ((threadIdx.x & 31) == 0) ss[threadIdx.x >> 5] = s, sc[threadIdx.x >> 5] = c;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long ts = 0;
+    int tc = 0;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) ts += ss[w], tc += sc[w];
+    rowsum[row] = rowsum_all[row] - ts;
+    rowcnt[row] = rowcnt_all[row] - tc;
   }
 }
 
@@ -342,8 +427,91 @@ __device__ __noinline__ int quantise_slow(double w, double a100, unsigned long l
   return double_to_int_exact(q);
 }
 
+__device__ __forceinline__ void sts_u16(uint32_t addr, int v) {
+  asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((unsigned short)v) : "memory");
+}
+
+// Fast path of one cell: z in fp64, rounded half-even through the magic-number add (no conversion pipe).
+// Returns the hundredths code (garbage when `rare` comes back set: exactly on .5, or beyond the int16 range).
+__device__ __forceinline__ int quantise_fast(int h, double f, double negmu, double a100, bool& rare, bool& neg) {
+  const double w = fma(u32_to_double(h), f, negmu);
+  const double t = w * a100;
+  const double tm = t + kRoundMagic;  // low word = round-half-even(t) as int32
+  const double d = t - (tm - kRoundMagic);
+  rare |= (fabs(d) == 0.5) | ((__double2hiint(t) & 0x7fffffff) >= 0x40DFFF00);
+  neg = __double2hiint(t) < 0;
+  return __double2loint(tm);
+}
+
+// One batch of kRows rows for this thread's 4 bins.  kRows is a compile-time constant for the full batches (no row
+// guards in the unrolled body); the ragged last batch of a slab takes the generic instantiation with nr < kTB.
+template <bool kZq, bool kZh, bool kFull>
+__device__ __forceinline__ void transform_batch(const float4 (&v)[kTB], int nr, const double* __restrict__ sf,
+                                                const double (&negmu)[4], const double (&a100)[4], const int (&zc)[4],
+                                                const uint32_t (&aq)[4], const uint32_t (&ah)[4],
+                                                unsigned* __restrict__ part, bool lane0, const float* __restrict__ colp,
+                                                int64_t ld, unsigned long long* __restrict__ sat) {
+  unsigned rare_rows = 0;
+#pragma unroll
+  for (int u = 0; u < kTB; ++u) {
+    if (!kFull && u >= nr) break;
+    const double f = sf[u];
+    const float vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+    bool rare = false;
+    int vsq = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int h = depth_hundredths(vv[q]);
+      bool neg;
+      int z = quantise_fast(h, f, negmu[q], a100[q], rare, neg);
+      if (kZq) {
+        int code = (z == 0 && neg) ? -32767 : z;  // prints as "-0.00"
+        if (h == 0) code = -32768;                // absent cell (a row without valid bins has no present cell either)
+        sts_u16(aq[q] + u * (kStageRow * 2), code);
+      }
+      if (kZh) {
+        const int c = h != 0 ? max(-zc[q], min(zc[q], z)) : 0;
+        sts_u16(ah[q] + u * (kStageRow * 2), (int)__half_as_ushort(__int2half_rn(c)));
+        vsq += c * c;
+      }
+    }
+    if (rare) rare_rows |= 1u << u;
+    if (kZh) {
+      const int tot = __reduce_add_sync(0xffffffffu, vsq);  // <= 128 * 2048^2 = 2^29
+      if (lane0) part[u] = (unsigned)tot;
+    }
+  }
+  // Rare rows (a value exactly on k+0.5, or outside the int16 code range): redo this thread's 4 cells of that row
+  // from the (cache-resident) source with the exact slow quantiser and patch the staged values and the norm.
+  while (rare_rows) {
+    const int u = __ffs(rare_rows) - 1;
+    rare_rows &= rare_rows - 1;
+    const double f = sf[u];
+    const float4 x = *reinterpret_cast<const float4*>(colp + (int64_t)u * ld);
+    const float vv[4] = {x.x, x.y, x.z, x.w};
+    int delta = 0;
+#pragma unroll 1
+    for (int q = 0; q < 4; ++q) {
+      const int h = depth_hundredths(vv[q]);
+      if (h == 0 || !(f == f) || a100[q] == 0.0) continue;  // absent cell / unselected bin: nothing was kept
+      bool r2 = false, neg;
+      const int zf = quantise_fast(h, f, negmu[q], a100[q], r2, neg);
+      if (!r2) continue;
+      const double w = fma(u32_to_double(h), f, negmu[q]);
+      const int z = quantise_slow(w, a100[q], sat);
+      if (kZq) sts_u16(aq[q] + u * (kStageRow * 2), (z == 0 && w * a100[q] < 0.0) ? -32767 : z);
+      if (kZh) {
+        const int c_old = max(-zc[q], min(zc[q], zf)), c = max(-zc[q], min(zc[q], z));
+        sts_u16(ah[q] + u * (kStageRow * 2), (int)__half_as_ushort(__int2half_rn(c)));
+        delta += c * c - c_old * c_old;
+      }
+    }
+    if (kZh && delta) atomicAdd(&part[u], (unsigned)delta);  // after the warp's own store to part[u] (same warp: ordered)
+  }
+}
+
 template <bool kZq, bool kZh>
-__global__ void __launch_bounds__(kThreads, 3) k_transform(const float* __restrict__ depth, int64_t n, int64_t b,
+__global__ void __launch_bounds__(kThreads, 2) k_transform(const float* __restrict__ depth, int64_t n, int64_t b,
                                                            int64_t ld, const double* __restrict__ row_factor,
                                                            const double* __restrict__ mu,
                                                            const int32_t* __restrict__ sel_pos,
@@ -372,7 +540,7 @@ __global__ void __launch_bounds__(kThreads, 3) k_transform(const float* __restri
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
     pos[q] = (j0 + q < b) ? sel_pos[j0 + q] : -1;
-    negmu[q] = 0.0, a100[q] = 0.0, zc[q] = 0;
+    negmu[q] = 0.0, a100[q] = 0.0, zc[q] = 0;  // unselected bins run with t = 0 into the dump slots
     if (pos[q] >= 0) {
       lo = min(lo, pos[q]), hi = max(hi, pos[q]);
       const double m = mu[j0 + q];
@@ -392,13 +560,17 @@ __global__ void __launch_bounds__(kThreads, 3) k_transform(const float* __restri
   const int p0 = s_lo, len = s_hi - s_lo + 1;  // this block's contiguous output range
   if (s_hi < 0) return;                        // no selected bin in these 1024 columns (block-uniform)
   const int shift = p0 & 7;
-  int off[4];
+  uint32_t aq[4], ah[4];  // shared-memory byte addresses of this thread's 4 staging slots in row 0 of buffer 0
 #pragma unroll
-  for (int q = 0; q < 4; ++q) off[q] = pos[q] >= 0 ? pos[q] - p0 + shift : kDump - q;
+  for (int q = 0; q < 4; ++q) {
+    const int off = pos[q] >= 0 ? pos[q] - p0 + shift : kDump - q;
+    aq[q] = (uint32_t)__cvta_generic_to_shared(s_zq) + 2 * off;
+    ah[q] = (uint32_t)__cvta_generic_to_shared(s_zh) + 2 * off;
+  }
   const float* colp = depth + (j0 < b ? j0 : 0) + r0 * ld;
   const int warp = threadIdx.x >> 5;
-  // the dump slots never reach global memory, but the 32-bit hi-word test below must not see NaN garbage there:
-  // unselected bins run with negmu = a100 = 0, i.e. t = 0 (or NaN for an empty row, which compares false)
+  const bool lane0 = (threadIdx.x & 31) == 0;
+  constexpr uint32_t kBufBytes = kTB * kStageRow * 2;
 
   float4 v[kTB];
   if (any) {
@@ -409,68 +581,32 @@ __global__ void __launch_bounds__(kThreads, 3) k_transform(const float* __restri
   int buf = 0;
   for (int rb = 0; rb < nrow; rb += kTB, buf ^= 1) {
     const int nr = min(kTB, nrow - rb);
-    int16_t* const bq = s_zq + (kZq ? buf * kTB * kStageRow : 0);
-    __half* const bh = s_zh + (kZh ? buf * kTB * kStageRow : 0);
     if (any) {
-#pragma unroll
-      for (int u = 0; u < kTB; ++u) {
-        int vsq = 0;
-        if (u < nr) {
-          const double f = s_f[rb + u];
-          const float vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
-          int zi[4];
-          bool rare = false;
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int h = depth_hundredths(vv[q]);
-            const double w = fma(u32_to_double(h), f, negmu[q]);
-            const double t = w * a100[q];
-            const double tm = t + kRoundMagic;       // low word = round-half-even(t) as int32
-            const double d = t - (tm - kRoundMagic);
-            zi[q] = __double2loint(tm);
-            // exactly on .5 after rounding, or beyond the int16 code range: settle in the slow path
-            rare |= (fabs(d) == 0.5) | ((__double2hiint(t) & 0x7fffffff) >= 0x40DFFF00);
-            if (kZq && zi[q] == 0 && __double2hiint(t) < 0) zi[q] = -32767;  // prints as "-0.00"
-            if (h == 0) zi[q] = -32768;  // absent cell (a row without valid bins has no present cell either)
-          }
-          if (rare) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-              const int h = depth_hundredths(vv[q]);
-              if (h > 0 && f == f && off[q] < kDump - 3) {
-                const double w = fma(u32_to_double(h), f, negmu[q]);
-                const int z = quantise_slow(w, a100[q], sat);
-                zi[q] = (kZq && z == 0 && w * a100[q] < 0.0) ? -32767 : z;
-              }
-            }
-          }
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            if (kZq) bq[u * kStageRow + off[q]] = (int16_t)zi[q];
-            if (kZh) {
-              const int c = zi[q] > -32767 ? max(-zc[q], min(zc[q], zi[q])) : 0;
-              bh[u * kStageRow + off[q]] = __int2half_rn(c);
-              vsq += c * c;
-            }
-          }
-        }
-        if (kZh && u < nr) {
-          const int tot = __reduce_add_sync(0xffffffffu, vsq);  // <= 128 * 2048^2 = 2^29
-          if ((threadIdx.x & 31) == 0) s_part[warp * kTransformSlab + rb + u] = (unsigned)tot;
-        }
-      }
+      unsigned* part = s_part + (kZh ? warp * kTransformSlab + rb : 0);
+      const float* src = colp + (int64_t)rb * ld;
+      if (nr == kTB) transform_batch<kZq, kZh, true>(v, nr, s_f + rb, negmu, a100, zc, aq, ah, part, lane0, src, ld, sat);
+      else transform_batch<kZq, kZh, false>(v, nr, s_f + rb, negmu, a100, zc, aq, ah, part, lane0, src, ld, sat);
       // next batch: in flight during the barrier and the copy-out
       const int rn = rb + kTB;
+      if (rn + kTB <= nrow) {
 #pragma unroll
-      for (int u = 0; u < kTB; ++u)
-        if (rn + u < nrow) v[u] = ld_stream(reinterpret_cast<const float4*>(colp + (int64_t)(rn + u) * ld));
+        for (int u = 0; u < kTB; ++u) v[u] = ld_stream(reinterpret_cast<const float4*>(colp + (int64_t)(rn + u) * ld));
+      } else {
+#pragma unroll
+        for (int u = 0; u < kTB; ++u)
+          if (rn + u < nrow) v[u] = ld_stream(reinterpret_cast<const float4*>(colp + (int64_t)(rn + u) * ld));
+      }
     } else if (kZh) {
       for (int u = 0; u < nr; ++u)
-        if ((threadIdx.x & 31) == 0) s_part[warp * kTransformSlab + rb + u] = 0;
+        if (lane0) s_part[warp * kTransformSlab + rb + u] = 0;
     }
     __syncthreads();
-    if (kZq) copy_out_rows<int16_t, false>(bq, zq, ldq, r0 + rb, nr, p0, len);
-    if (kZh) copy_out_rows<__half, true>(bh, zh, ldh, r0 + rb, nr, p0, len);
+    if (kZq) copy_out_rows<int16_t, false>(s_zq + (buf ? kTB * kStageRow : 0), zq, ldq, r0 + rb, nr, p0, len);
+    if (kZh) copy_out_rows<__half, true>(s_zh + (buf ? kTB * kStageRow : 0), zh, ldh, r0 + rb, nr, p0, len);
+    // the other staging buffer next time
+    const uint32_t flip = buf ? (0u - kBufBytes) : kBufBytes;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) aq[q] += kZq ? flip : 0u, ah[q] += kZh ? flip : 0u;
   }
   if (kZh) {
     __syncthreads();
@@ -538,8 +674,65 @@ extern "C" int gridb200_col_raw_stats(const float* depth, int64_t n, int64_t b, 
     G2_CUDA(cudaMemsetAsync(colsum, 0, b * sizeof(int64_t), st));
     G2_CUDA(cudaMemsetAsync(colcnt, 0, b * sizeof(int32_t), st));
   }
-  k_col_raw<<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(
-      depth, n, b, ld, rows, reinterpret_cast<unsigned long long*>(colsum), colcnt);
+  k_col_raw<false><<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(
+      depth, n, b, ld, rows, reinterpret_cast<unsigned long long*>(colsum), colcnt, nullptr, nullptr);
+  G2_LAUNCHED();
+  return 0;
+}
+
+extern "C" int gridb200_col_row_raw_stats(const float* depth, int64_t n, int64_t b, int64_t ld, int64_t* colsum,
+                                          int32_t* colcnt, int64_t* rowsum_all, int32_t* rowcnt_all, void* stream) {
+  if (int e = check_matrix(depth, n, b, ld)) return e;
+  G2_REQUIRE(colsum && colcnt && rowsum_all && rowcnt_all, GRIDB200_EINVAL, "null output");
+  cudaStream_t st = as_stream(stream);
+  const int64_t cb = (b + kColsPerBlock - 1) / kColsPerBlock;
+  const int64_t rows = pick_row_slab(n, cb, 64);
+  const int64_t slabs = (n + rows - 1) / rows;
+  G2_REQUIRE(slabs <= 65535, GRIDB200_EINVAL, "too many row slabs");
+  if (slabs > 1) {
+    G2_CUDA(cudaMemsetAsync(colsum, 0, b * sizeof(int64_t), st));
+    G2_CUDA(cudaMemsetAsync(colcnt, 0, b * sizeof(int32_t), st));
+  }
+  G2_CUDA(cudaMemsetAsync(rowsum_all, 0, n * sizeof(int64_t), st));
+  G2_CUDA(cudaMemsetAsync(rowcnt_all, 0, n * sizeof(int32_t), st));
+  k_col_raw<true><<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(
+      depth, n, b, ld, rows, reinterpret_cast<unsigned long long*>(colsum), colcnt,
+      reinterpret_cast<unsigned long long*>(rowsum_all), rowcnt_all);
+  G2_LAUNCHED();
+  return 0;
+}
+
+extern "C" size_t gridb200_row_stats_fused_ws_bytes(int64_t b) { return (size_t)(b > 0 ? b : 0) * 4 + 256; }
+
+extern "C" int gridb200_row_stats_fused(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                                        const int32_t* colcnt, const int64_t* rowsum_all, const int32_t* rowcnt_all,
+                                        int64_t* rowsum, int32_t* rowcnt, void* ws, size_t ws_bytes, void* stream) {
+  if (int e = check_matrix(depth, n, b, ld)) return e;
+  G2_REQUIRE(valid && colcnt && rowsum_all && rowcnt_all && rowsum && rowcnt, GRIDB200_EINVAL, "null argument");
+  G2_REQUIRE((reinterpret_cast<uintptr_t>(valid) & 3) == 0, GRIDB200_EINVAL, "valid flags must be 4-byte aligned");
+  G2_REQUIRE(ws && ws_bytes >= gridb200_row_stats_fused_ws_bytes(b), GRIDB200_EINVAL,
+             "workspace too small: need %zu bytes", gridb200_row_stats_fused_ws_bytes(b));
+  G2_REQUIRE(b < (1LL << 31) && n <= 0x7fffffff, GRIDB200_EINVAL, "matrix too large");
+  cudaStream_t st = as_stream(stream);
+  int* flags = static_cast<int*>(ws);  // [0] = number of bad bins, [1] = mode
+  int* bad = flags + 64;
+  G2_CUDA(cudaMemsetAsync(flags, 0, 256, st));
+  G2_CUDA(cudaMemsetAsync(rowsum, 0, n * sizeof(int64_t), st));
+  G2_CUDA(cudaMemsetAsync(rowcnt, 0, n * sizeof(int32_t), st));
+  k_bad_list<<<(unsigned)((b + 255) / 256), 256, 0, st>>>(valid, colcnt, b, bad, flags);
+  G2_LAUNCHED();
+  k_row_mode<<<1, 1, 0, st>>>(flags, b, flags + 1);
+  G2_LAUNCHED();
+  const int64_t chunks = (b + kRowChunk - 1) / kRowChunk;
+  for (int64_t r0 = 0; r0 < n; r0 += 65535) {  // gridDim.y limit
+    const int64_t rows = std::min<int64_t>(65535, n - r0);
+    k_row_stats<<<dim3((unsigned)chunks, (unsigned)rows), kThreads, 0, st>>>(
+        depth + r0 * ld, b, ld, valid, reinterpret_cast<unsigned long long*>(rowsum) + r0, rowcnt + r0, flags + 1);
+    G2_LAUNCHED();
+  }
+  k_row_fix<<<(unsigned)n, kThreads, 0, st>>>(depth, ld, bad, flags, flags + 1,
+                                              reinterpret_cast<const unsigned long long*>(rowsum_all), rowcnt_all,
+                                              reinterpret_cast<unsigned long long*>(rowsum), rowcnt);
   G2_LAUNCHED();
   return 0;
 }
@@ -565,7 +758,7 @@ extern "C" int gridb200_row_stats(const float* depth, int64_t n, int64_t b, int6
   for (int64_t r0 = 0; r0 < n; r0 += 65535) {  // gridDim.y limit
     const int64_t rows = std::min<int64_t>(65535, n - r0);
     k_row_stats<<<dim3((unsigned)chunks, (unsigned)rows), kThreads, 0, st>>>(
-        depth + r0 * ld, b, ld, valid, reinterpret_cast<unsigned long long*>(rowsum) + r0, rowcnt + r0);
+        depth + r0 * ld, b, ld, valid, reinterpret_cast<unsigned long long*>(rowsum) + r0, rowcnt + r0, nullptr);
     G2_LAUNCHED();
   }
   return 0;

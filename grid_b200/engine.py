@@ -125,13 +125,19 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
     f64 = dict(dtype=torch.float64, device=dev)
     colsum, colcnt = torch.empty(b, **i64), torch.empty(b, dtype=torch.int32, device=dev)
     valid = torch.empty(b, dtype=torch.uint8, device=dev)
+    # one pass yields the per-bin sums AND the per-sample totals over all bins; the per-sample sums over the VALID
+    # bins then only need the few bins that failed the depth filter (gridb200_row_stats_fused decides on the device)
+    rowsum_all, rowcnt_all = torch.empty(n, **i64), torch.empty(n, dtype=torch.int32, device=dev)
     with _mark("col_raw"):
-        call("gridb200_col_raw_stats", ptr(depth), n, b, ld, ptr(colsum), ptr(colcnt), st)
+        call("gridb200_col_row_raw_stats", ptr(depth), n, b, ld, ptr(colsum), ptr(colcnt), ptr(rowsum_all),
+             ptr(rowcnt_all), st)
     call("gridb200_depth_filter", ptr(colsum), ptr(colcnt), b, float(p.min_depth), float(p.max_depth), ptr(valid), st)
 
     rowsum, rowcnt = torch.empty(n, **i64), torch.empty(n, dtype=torch.int32, device=dev)
+    ws0 = _ws(_lib.load().gridb200_row_stats_fused_ws_bytes(b), dev)
     with _mark("row_stats"):
-        call("gridb200_row_stats", ptr(depth), n, b, ld, ptr(valid), ptr(rowsum), ptr(rowcnt), st)
+        call("gridb200_row_stats_fused", ptr(depth), n, b, ld, ptr(valid), ptr(colcnt), ptr(rowsum_all), ptr(rowcnt_all),
+             ptr(rowsum), ptr(rowcnt), ptr(ws0), ws0.numel(), st)
     _all_reduce(rowsum, group)
     _all_reduce(rowcnt, group)
     raw_mean, scale_q, row_factor = torch.empty(n, **f64), torch.empty(n, **f64), torch.empty(n, **f64)

@@ -105,14 +105,18 @@ def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, g
     # ---- step 4: per-bin statistics are summed over ranks, everything per-sample is local ------------------
     colsum, colcnt = torch.empty(b, **i64), torch.empty(b, dtype=torch.int32, device=dev)
     valid = torch.empty(b, dtype=torch.uint8, device=dev)
+    rowsum_all, rowcnt_all = torch.empty(n, **i64), torch.empty(n, dtype=torch.int32, device=dev)
     with E._mark("col_raw"):
-        call("gridb200_col_raw_stats", ptr(depth), n, b, ld, ptr(colsum), ptr(colcnt), st)
+        call("gridb200_col_row_raw_stats", ptr(depth), n, b, ld, ptr(colsum), ptr(colcnt), ptr(rowsum_all),
+             ptr(rowcnt_all), st)
     _all_reduce(colsum, group)
     _all_reduce(colcnt, group)
     call("gridb200_depth_filter", ptr(colsum), ptr(colcnt), b, float(p.min_depth), float(p.max_depth), ptr(valid), st)
     rowsum, rowcnt = torch.empty(n, **i64), torch.empty(n, dtype=torch.int32, device=dev)
+    ws0 = E._ws(load().gridb200_row_stats_fused_ws_bytes(b), dev)
     with E._mark("row_stats"):
-        call("gridb200_row_stats", ptr(depth), n, b, ld, ptr(valid), ptr(rowsum), ptr(rowcnt), st)
+        call("gridb200_row_stats_fused", ptr(depth), n, b, ld, ptr(valid), ptr(colcnt), ptr(rowsum_all), ptr(rowcnt_all),
+             ptr(rowsum), ptr(rowcnt), ptr(ws0), ws0.numel(), st)
     raw_mean, scale_q, row_factor = torch.empty(n, **f64), torch.empty(n, **f64), torch.empty(n, **f64)
     call("gridb200_row_scales", ptr(rowsum), ptr(rowcnt), n, ptr(raw_mean), ptr(scale_q), ptr(row_factor), st)
     sd, sd2 = torch.empty(b, **f64), torch.empty(b, **f64)

@@ -59,6 +59,12 @@ GRIDB200_API uint64_t gridb200_launch_count(void);
 GRIDB200_API int gridb200_col_raw_stats(const float* depth, int64_t n, int64_t b, int64_t ld,
                            int64_t* colsum, int32_t* colcnt, void* stream);
 
+/* gridb200_col_raw_stats plus, from the same pass over the matrix, the per-sample totals over ALL bins
+ * (rowsum_all[i] = sum_j round(100*depth[i,j]), rowcnt_all[i] = #present); feeds gridb200_row_stats_fused. */
+GRIDB200_API int gridb200_col_row_raw_stats(const float* depth, int64_t n, int64_t b, int64_t ld,
+                               int64_t* colsum, int32_t* colcnt, int64_t* rowsum_all, int32_t* rowcnt_all,
+                               void* stream);
+
 /* valid[j] = 1 iff colcnt>0 and min_depth <= colsum/(100*colcnt) <= max_depth (normalize_mosdepth.py:81-83). */
 GRIDB200_API int gridb200_depth_filter(const int64_t* colsum, const int32_t* colcnt, int64_t b,
                           double min_depth, double max_depth, uint8_t* valid, void* stream);
@@ -68,6 +74,15 @@ GRIDB200_API int gridb200_depth_filter(const int64_t* colsum, const int32_t* col
  * Column-sharded multi-GPU: all-reduce(sum) both outputs afterwards. */
 GRIDB200_API int gridb200_row_stats(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
                        int64_t* rowsum, int32_t* rowcnt, void* stream);
+
+/* Same result as gridb200_row_stats, derived from the totals of gridb200_col_row_raw_stats: the bins that have
+ * data but failed the depth filter are subtracted column by column.  When those bins are more than 1/8 of all
+ * bins (a strided column read costs a 32-byte sector per cell) the full pass runs instead; the choice is made
+ * on the device, without a host round trip.  ws: gridb200_row_stats_fused_ws_bytes(b). */
+GRIDB200_API size_t gridb200_row_stats_fused_ws_bytes(int64_t b);
+GRIDB200_API int gridb200_row_stats_fused(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                             const int32_t* colcnt, const int64_t* rowsum_all, const int32_t* rowcnt_all,
+                             int64_t* rowsum, int32_t* rowcnt, void* ws, size_t ws_bytes, void* stream);
 
 /* raw_mean[i] = rowsum/(100*rowcnt) (the "scale" column, NaN for an empty row); scale_q[i] = that value
  * after the %.2f text hand-off (normalize_mosdepth.py:552-554 -> find_neighbors.py:111); row_factor[i] =

@@ -347,3 +347,44 @@ def test_device_and_host_packers_agree(tmp_path, eng):
             np.testing.assert_array_equal(dd[:, col[(int(s), int(e))]], dep_h[:, j])
             seen[col[(int(s), int(e))]] = True
         assert (dd[:, ~seen] == 0).all()                                       # grid bins nobody has stay absent
+
+
+@pytest.mark.parametrize("bad_frac", [0.0, 0.02, 0.125, 0.2, 1.0])
+def test_fused_row_stats_equal_the_full_pass(bad_frac, eng):
+    """Per-sample sums over the valid bins derived from the all-bin totals (few failing bins: column fix-up; many:
+    the full pass, chosen on the device) must equal gridb200_row_stats exactly, whatever the share of failing bins."""
+    from grid_b200._lib import call, load, ptr
+
+    n, b = 70, 4099
+    h = synth.depth_hundredths(3, n, b)
+    h[5] = 0                                                                   # a sample with no data at all
+    h[:, 100:140] = 0                                                          # bins nobody has (not "bad": nothing to subtract)
+    ld = (b + 3) // 4 * 4
+    dd = np.zeros((n, ld), dtype=np.float32)
+    dd[:, :b] = h / 100.0
+    depth = torch.from_numpy(dd).cuda()
+    rng = np.random.default_rng(int(bad_frac * 1000))
+    valid_np = (rng.random(b) >= bad_frac).astype(np.uint8)
+    valid = torch.from_numpy(valid_np).cuda()
+    st = torch.cuda.current_stream().cuda_stream
+    i64 = dict(dtype=torch.int64, device="cuda")
+    i32 = dict(dtype=torch.int32, device="cuda")
+    colsum, colcnt = torch.empty(b, **i64), torch.empty(b, **i32)
+    rs_all, rc_all = torch.empty(n, **i64), torch.empty(n, **i32)
+    call("gridb200_col_row_raw_stats", ptr(depth), n, b, ld, ptr(colsum), ptr(colcnt), ptr(rs_all), ptr(rc_all), st)
+    np.testing.assert_array_equal(colsum.cpu().numpy(), h.sum(axis=0))
+    np.testing.assert_array_equal(colcnt.cpu().numpy(), (h > 0).sum(axis=0))
+    np.testing.assert_array_equal(rs_all.cpu().numpy(), h.sum(axis=1))
+    np.testing.assert_array_equal(rc_all.cpu().numpy(), (h > 0).sum(axis=1))
+    want_s, want_c = torch.empty(n, **i64), torch.empty(n, **i32)
+    call("gridb200_row_stats", ptr(depth), n, b, ld, ptr(valid), ptr(want_s), ptr(want_c), st)
+    got_s, got_c = torch.full((n,), -1, **i64), torch.full((n,), -1, **i32)
+    ws = torch.empty(load().gridb200_row_stats_fused_ws_bytes(b), dtype=torch.uint8, device="cuda")
+    call("gridb200_row_stats_fused", ptr(depth), n, b, ld, ptr(valid), ptr(colcnt), ptr(rs_all), ptr(rc_all), ptr(got_s),
+         ptr(got_c), ptr(ws), ws.numel(), st)
+    np.testing.assert_array_equal(got_s.cpu().numpy(), want_s.cpu().numpy())
+    np.testing.assert_array_equal(got_c.cpu().numpy(), want_c.cpu().numpy())
+    np.testing.assert_array_equal(want_s.cpu().numpy(), (h * valid_np[None, :]).sum(axis=1))
+    mode = int(ws.view(torch.int32)[1].item())
+    n_bad = int(((valid_np == 0) & ((h > 0).sum(axis=0) > 0)).sum())
+    assert mode == (1 if n_bad * 8 <= b else 0)
