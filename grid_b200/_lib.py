@@ -60,10 +60,13 @@ def load() -> C.CDLL:
     """Load the library once; raises if it has not been built (python grid_b200/csrc/build.py)."""
     global _lib
     if _lib is None:
-        if not LIB_PATH.exists():
-            raise ImportError(f"{LIB_PATH} is missing: build it with `python grid_b200/csrc/build.py` "
+        import os
+
+        path = Path(os.environ.get("GRIDB200_LIB", LIB_PATH))  # A/B runs of two builds of the SAME library
+        if not path.exists():
+            raise ImportError(f"{path} is missing: build it with `python grid_b200/csrc/build.py` "
                               "(there is no CPU fallback)")
-        lib = C.CDLL(str(LIB_PATH))
+        lib = C.CDLL(str(path))
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(lib, name)
             fn.restype, fn.argtypes = res, args

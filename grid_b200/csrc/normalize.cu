@@ -393,19 +393,22 @@ __device__ __forceinline__ void copy_out_rows(const T* __restrict__ stage, T* __
                                               int64_t row0, int nrows, int p0, int len) {
   const int shift = p0 & 7;
   const int nchunk = (shift + len + 7) >> 3;
-  for (int w = threadIdx.x; w < nchunk * kTB; w += kThreads) {
-    const int r = w / nchunk, q = w - r * nchunk;  // consecutive threads -> consecutive chunks of one row
-    if (r >= nrows) break;
-    const int e0 = 8 * q - shift;  // first element of this chunk relative to p0
-    const T* src = stage + r * kStageRow + 8 * q;
-    const int64_t pe = (int64_t)(p0 - shift) + 8 * q;  // first element of the chunk in the output row
-    T* dst = kBlocked ? out + ((pe >> 6) * ld_out + row0 + r) * 64 + (pe & 63) : out + (row0 + r) * ld_out + pe;
-    if (e0 >= 0 && e0 + 8 <= len) {
-      *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
-    } else {
+  const int lane = threadIdx.x & 31;
+  // one warp per staged row (kTB == warps per block): 32 consecutive 16-byte chunks = 512 contiguous bytes per store
+  for (int r = threadIdx.x >> 5; r < nrows; r += kThreads / 32) {
+    const T* src = stage + r * kStageRow + 8 * lane;
+    const int64_t pe0 = (int64_t)(p0 - shift) + 8 * lane;  // first output element of this lane's first chunk
+    T* dst = kBlocked ? out + ((pe0 >> 6) * ld_out + row0 + r) * 64 + (pe0 & 63) : out + (row0 + r) * ld_out + pe0;
+    const int64_t step = kBlocked ? 4 * ld_out * 64 : 256;  // 32 chunks = 256 elements = 4 k-blocks further on
+    for (int q = lane; q < nchunk; q += 32, src += 256, dst += step) {
+      const int e0 = 8 * q - shift;  // first element of this chunk relative to p0
+      if (e0 >= 0 && e0 + 8 <= len) {
+        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+      } else {
 #pragma unroll
-      for (int e = 0; e < 8; ++e)
-        if (e0 + e >= 0 && e0 + e < len) dst[e] = src[e];
+        for (int e = 0; e < 8; ++e)
+          if (e0 + e >= 0 && e0 + e < len) dst[e] = src[e];
+      }
     }
   }
 }
