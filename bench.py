@@ -311,12 +311,24 @@ def run_ours(a):
             elems += nq0 * (a.samples - nq0)
         flops = 2.0 * elems * res.rw_local  # this rank's launch
         full_flops = 2.0 * nq0 * a.samples * res.rw_local
+        # dram__bytes_read.sum + dram__bytes_write.sum of the Gram kernel from the committed `ncu --set full` capture of
+        # this same workload (profiles/*_ncu_full_summary.json, written by tools/ncu_summary.py); single-GPU launch
+        traffic, traffic_note = None, None
+        try:
+            caps = sorted((ROOT / "profiles").glob("*_ncu_full_summary.json"))
+            for k in json.loads(caps[-1].read_text()) if caps and world == 1 else []:
+                if "k_gram_tc_pair" in k["kernel"]:
+                    traffic = (k["dram_read"]["value"] + k["dram_write"]["value"]) * 1e9
+                    traffic_note = (f"bytes per launch from {caps[-1].name}; the operand itself is "
+                                    f"{a.samples * res.kdim * 2 / 1e9:.1f} GB (read once per wave of tiles), dot matrix 0.08 GB")
+        except Exception:
+            traffic = None
         roof = None
         if gram_ms:
             ach = flops / (gram_ms * 1e-3) / 1e12
             roof = {"bound": "tensor", "kernel": "k_gram_tc_pair (fp16 tcgen05 cta_group::2, fp32 TMEM chunks drained to int64)",
                     "achieved": ach, "peak": tensor_peak, "unit": "TFLOP/s", "frac": ach / tensor_peak,
-                    "traffic": None, "peak_source": which, "launch_ms": gram_ms,
+                    "traffic": traffic, "traffic_note": traffic_note, "peak_source": which, "launch_ms": gram_ms,
                     "algorithmic": (f"2*Rw_local*(elements of the {'upper-triangle ' if sym else ''}256x256 tiles, clipped to N) = "
                                     f"2*{res.rw_local}*{elems} flop per launch"),
                     "full_matrix_equivalent_tflops": full_flops / (gram_ms * 1e-3) / 1e12, "symmetric": sym}

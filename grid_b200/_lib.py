@@ -35,6 +35,7 @@ SIGNATURES = {
                                      _vp, _vp, _vp]),
     "gridb200_knn_prepare": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _i32, _vp, _i64, _vp, _vp]),
     "gridb200_gram": (C.c_int, [_vp, _i64, _i64, _vp, _i64, _i64, _i64, _i32, _vp, _i64, C.c_int, C.c_int, _vp]),
+    "gridb200_gram_set_max_pairs": (C.c_int, [C.c_int]),
     "gridb200_topk_init": (C.c_int, [_vp, _vp, _i64, _i32, _vp]),
     "gridb200_topk_merge": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _i32, _vp, _vp, _vp]),
     "gridb200_dipcn": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _i64, _i32, _i64, _i32, _vp, _i64, _vp, _vp]),

@@ -457,6 +457,16 @@ static int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t nkb
 }  // namespace tc
 }  // namespace g2
 
+// Upper bound on the CTA pairs the Gram kernel occupies (0 = all SMs).  The kernel is persistent with a static
+// item partition, so every pair must be co-resident: a caller that overlaps it with another kernel (the ring
+// schedule overlaps it with NCCL's send/recv kernel) leaves that kernel its SMs through this knob.
+static std::atomic<int> g_max_pairs{0};
+extern "C" int gridb200_gram_set_max_pairs(int pairs) {
+  G2_REQUIRE(pairs >= 0, GRIDB200_EINVAL, "pairs must be >= 0");
+  g_max_pairs.store(pairs);
+  return 0;
+}
+
 int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, int64_t nr, int64_t slabr,
                      int64_t kdim, int32_t vmax, int64_t* dot, int64_t ldd, int accumulate, void* stream) {
   using namespace g2;
@@ -491,7 +501,8 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
     e = getenv("GRIDB200_GRAM_NOPACE");
     no_pace = (e && e[0] == '1') ? 1 : 0;
   }
-  const int workers = std::min(sms / 2, MAX_PAIRS);
+  int workers = std::min(sms / 2, MAX_PAIRS);
+  if (const int cap = g_max_pairs.load()) workers = std::max(1, std::min(workers, cap));
   Work w;
   w.nq = nq, w.nr = nr, w.ldd = ldd;
   w.symmetric = (!no_sym && zq == zr && nq == nr && slabq == slabr) ? 1 : 0;
@@ -520,7 +531,12 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
     const int64_t wave_rows = w.symmetric ? nq
                                           : std::min<int64_t>(nq, (int64_t)w.group_m * TM) +
                                                 std::min<int64_t>(nr, (int64_t)(workers / w.group_m + 1) * TN);
-    int64_t win = (32LL << 20) / (wave_rows * BK * 2);
+    static int64_t win_mb = 0;  // GRIDB200_GRAM_WINDOW_MB: operand bytes the pairs of one wave may be spread over
+    if (!win_mb) {
+      const char* e = getenv("GRIDB200_GRAM_WINDOW_MB");
+      win_mb = (e && atoi(e) > 0) ? atoi(e) : 32;
+    }
+    int64_t win = (win_mb << 20) / (wave_rows * BK * 2);
     win = std::max<int64_t>(2 * PACE, std::min<int64_t>(win, 16 * PACE)) / PACE * PACE;
     w.window = no_pace ? 0 : (int)win;
   }

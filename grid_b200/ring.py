@@ -170,7 +170,18 @@ def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, g
         E.knn_block(zh, norms, offsets[rank], ref, norms_all[r_gid0:r_gid0 + n_ref], r_gid0, kdim, p.zclip, best_d2,
                     best_idx, impl=impl)
 
-    ring_knn(zh, max(counts), counts, offsets, group, block, flat_per_row=kdim)
+    # the persistent Gram kernel must not fight NCCL's send/recv kernel for SMs (a pair that cannot be co-resident
+    # runs its whole static share after everybody else): leave it GRIDB200_RING_COMM_SMS SMs (default 16; NCCL's CTA
+    # count can be bounded with NCCL_MAX_CTAS) while transfers are in flight
+    import os
+
+    comm_sms = int(os.environ.get("GRIDB200_RING_COMM_SMS", "16")) if world > 1 else 0
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    call("gridb200_gram_set_max_pairs", max(1, (sms - comm_sms) // 2) if comm_sms else 0)
+    try:
+        ring_knn(zh, max(counts), counts, offsets, group, block, flat_per_row=kdim)
+    finally:
+        call("gridb200_gram_set_max_pairs", 0)
 
     # ---- step 6: scaled counts are tiny -> all-gather, then a local gather-reduce ----------------------------
     counts_all = _all_gather_rows(counts_local.contiguous(), counts, group)

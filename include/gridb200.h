@@ -162,6 +162,11 @@ GRIDB200_API int gridb200_gram(const void* zq_f16, int64_t nq, int64_t slabq, co
                   int64_t kdim, int32_t vmax, int64_t* dot, int64_t ldd, int accumulate, int impl,
                   void* stream);
 
+/* Cap the number of CTA pairs (2 SMs each) the tensor-core Gram kernel occupies; 0 = all SMs (default).  The kernel
+ * is persistent with a static work partition, so a caller that overlaps it with another kernel (the row-sharded ring
+ * overlaps it with NCCL's send/recv kernel) must leave that kernel its SMs.  Process-wide. */
+GRIDB200_API int gridb200_gram_set_max_pairs(int pairs);
+
 /* d2[i,j] = normq[i] + normr[j] - 2*dot[i,j]; the row's own sample (q_gid0+i == r_gid0+j) is skipped
  * (find_neighbors.py:218-219); merge into the running k-best lists, ascending by (d2, global index) -- the
  * order sklearn's heap + sort yields when no two candidates tie, lower index first among exact ties.
