@@ -55,17 +55,20 @@ constexpr int CHECK_EVERY = 16;             // chunks between int32 overflow che
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
 constexpr int PACE = 16;                    // k-block steps between pacing checks
 constexpr long long PACE_TIMEOUT = 400000;  // cycles a producer will wait for the slowest pair (~0.2 ms)
-constexpr int MAX_PAIRS = 128;
+constexpr int MAX_PAIRS = 128;              // static schedule: CTA pairs of one launch
+constexpr int PACE_SLOTS = 192;             // progress table entries (static: pair id; dynamic: the leader's %smid)
+constexpr int CLC_SLOTS = 2;                // work-stealing responses in flight per pair
+constexpr int CLC_CONSUMERS = 2 * (1 + EPI_WARPS) + 2;  // both producers + all epilogue warps + MMA lane + scheduler
 
 // kind::f16 instruction descriptor: D=f32 (bit 4), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24
 constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
 
-// progress table of the pacing scheme: (launch epoch << 32) | k-block step, one entry per CTA pair
-__device__ unsigned long long g_pace[MAX_PAIRS];
+// progress table of the pacing scheme: (launch epoch << 32) | k-block offset inside the current item
+__device__ unsigned long long g_pace[PACE_SLOTS];
 
 struct Work {
   int tiles_m, tiles_n, ntiles, ksplits, kb_total, kb_per_split, ck, group_m;
-  int symmetric, window;
+  int symmetric, window, pace_slots;
   unsigned epoch;
   int64_t nq, nr, ldd;
 };
@@ -118,6 +121,39 @@ __device__ __forceinline__ uint32_t map_to_cta(uint32_t addr, uint32_t rank) {
 // tcgen05.fence::before_thread_sync precede it), not data written to memory.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
   asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx_cluster(uint32_t cluster_addr, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_addr), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ uint32_t sm_id() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(r));
+  return r;
+}
+// Cluster launch control (work stealing in hardware): ask the grid scheduler to cancel one cluster of this grid
+// that has not started yet.  The 16-byte answer is written to `resp` in EVERY CTA of the asking cluster and
+// completes 16 transaction bytes on the mbarrier at `bar` in each of them.
+__device__ __forceinline__ void clc_try_cancel(uint32_t resp, uint32_t bar) {
+  asm volatile(
+      "clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.multicast::cluster::all.b128 [%0], [%1];" ::"r"(resp),
+      "r"(bar)
+      : "memory");
+}
+// answer -> work item (the cancelled cluster's index), or -1 when nothing was left to cancel
+__device__ __forceinline__ int clc_decode(uint32_t resp) {
+  uint32_t ok, x;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b128 r;\n\t.reg .b32 y, z;\n\t"
+      "ld.shared.b128 r, [%2];\n\t"
+      "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p, r;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "mov.u32 %1, 0;\n\t"
+      "@p clusterlaunchcontrol.query_cancel.get_first_ctaid.v4.b32.b128 {%1, y, z, _}, r;\n\t}"
+      : "=r"(ok), "=r"(x)
+      : "r"(resp)
+      : "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // our generic-proxy read precedes the next answer
+  return ok ? (int)(x >> 1) : -1;
 }
 // one k-block (c2) x 128 rows starting at c1 x all 64 bins of the block
 __device__ __forceinline__ void tma_load_pair(uint32_t dst, const CUtensorMap* map, uint32_t leader_bar, int row, int kb) {
@@ -208,34 +244,59 @@ __device__ __forceinline__ void decode_item(const Work& w, int item, int& ks, in
   tn = r / gsize;
 }
 
-// Whole warp 0.  Publish this pair's step, then hold the producer until the slowest pair is within `window` steps.
-__device__ __forceinline__ void pace(const Work& w, int pair_id, int npairs, uint32_t rank, int lane, unsigned step,
-                                     bool& enabled) {
+// Whole warp 0.  Publish this pair's offset inside its item, then hold the producer until every pair of its cohort
+// is within `window` k-blocks.  Items all have the same K length and the item order is K-split major, so pairs at
+// the same offset stream the same bins.  A pair further behind than 4 windows is out of phase (it joined late: the
+// dynamic schedule starts clusters whenever SMs become free) and is not waited for.
+__device__ __forceinline__ void pace(const Work& w, int slot, uint32_t rank, int lane, unsigned off, bool& enabled) {
   if (rank == 0 && lane == 0)
-    *reinterpret_cast<volatile unsigned long long*>(&g_pace[pair_id]) = ((unsigned long long)w.epoch << 32) | step;
-  if (!enabled || step < (unsigned)w.window) return;
-  const unsigned need = step - (unsigned)w.window;
+    *reinterpret_cast<volatile unsigned long long*>(&g_pace[slot]) = ((unsigned long long)w.epoch << 32) | off;
+  if (!enabled || off < (unsigned)w.window) return;
+  const unsigned need = off - (unsigned)w.window;
+  const unsigned behind = off > 4u * (unsigned)w.window ? off - 4u * (unsigned)w.window : 0u;
   const long long t0 = clock64();
   for (;;) {
     unsigned m = 0xffffffffu;
-    for (int p = lane; p < npairs; p += 32) {
+    for (int p = lane; p < w.pace_slots; p += 32) {
       const unsigned long long v = *reinterpret_cast<volatile unsigned long long*>(&g_pace[p]);
-      const unsigned e = (unsigned)(v >> 32);
-      // an older epoch = that pair has not started in this launch; a newer one = a later launch owns the table
-      const unsigned s = e == w.epoch ? (unsigned)v : (e < w.epoch ? 0u : 0xffffffffu);
-      m = min(m, s);
+      // another epoch = no pair of this launch on that slot (yet, or any more): nothing to wait for
+      const unsigned s = (unsigned)(v >> 32) == w.epoch ? (unsigned)v : 0xffffffffu;
+      if (s >= behind) m = min(m, s);
     }
     m = __reduce_min_sync(0xffffffffu, m);
     if (m >= need) return;
-    if (clock64() - t0 > PACE_TIMEOUT) {  // warp-uniform enough: every lane sees a similar clock; decide by lane 0
-      enabled = false;
-    }
+    if (clock64() - t0 > PACE_TIMEOUT) enabled = false;  // decided by lane 0 below
     enabled = __shfl_sync(0xffffffffu, (int)enabled, 0) != 0;
     if (!enabled) return;
     __nanosleep(200);
   }
 }
 
+// The item after `item` for one role of a pair.
+//   static  : round robin over the pairs of the launch.
+//   dynamic : the next answer of the cluster-launch-control ring (filled by the leader's scheduler warp).  Every
+//             consumer of an answer arrives on the LEADER's `empty` barrier of that slot; kWarp = a whole warp
+//             reads the answer and lane 0 arrives for it.
+struct Cursor {
+  int slot = 0;
+  uint32_t phase = 0;
+};
+template <bool kDynamic, bool kWarp>
+__device__ __forceinline__ int next_item(int item, int npairs, int nitems, uint32_t clc_full0, uint32_t clc_empty0,
+                                         uint32_t clc_resp0, Cursor& c, int lane) {
+  if (!kDynamic) {
+    item += npairs;
+    return item < nitems ? item : -1;
+  }
+  mbar_wait(clc_full0 + 8 * c.slot, c.phase);
+  const int nxt = clc_decode(clc_resp0 + 16 * c.slot);
+  if (kWarp) __syncwarp();
+  if (!kWarp || lane == 0) mbar_arrive_cluster(map_to_cta(clc_empty0 + 8 * c.slot, 0));
+  if (++c.slot == CLC_SLOTS) c.slot = 0, c.phase ^= 1;
+  return nxt;
+}
+
+template <bool kDynamic>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_r, const Work w,
                long long* __restrict__ dot) {
@@ -244,8 +305,12 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
   const uint32_t bars = base + STAGES * STAGE_BYTES;
   const uint32_t full0 = bars, empty0 = bars + 8 * STAGES, tfull0 = bars + 16 * STAGES, tempty0 = tfull0 + 8 * ACC_STAGES;
   const uint32_t tmem_slot = tempty0 + 8 * ACC_STAGES;
+  const uint32_t clc_full0 = tmem_slot + 8, clc_empty0 = clc_full0 + 8 * CLC_SLOTS, sched_go = clc_empty0 + 8 * CLC_SLOTS;
+  const uint32_t clc_resp0 = bars + 192;  // 16-byte aligned (bars is 1024-aligned)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_ctarank();
+  // static: this pair takes items pair_id, pair_id + npairs, ...; dynamic: one cluster was launched per item, a
+  // running pair starts with its own and then cancels not-yet-started clusters and does their items itself
   const int pair_id = blockIdx.x >> 1, npairs = gridDim.x >> 1;
   const int nitems = w.ntiles * w.ksplits;
 
@@ -258,6 +323,11 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
       mbar_init(tfull0 + 8 * a, 1);                // one multicast commit
       mbar_init(tempty0 + 8 * a, 2 * EPI_WARPS);   // every epilogue warp of both CTAs (leader's copy is used)
     }
+    for (int c = 0; c < CLC_SLOTS; ++c) {
+      mbar_init(clc_full0 + 8 * c, 1);               // the scheduler's expect_tx arrive (+ 16 answer bytes)
+      mbar_init(clc_empty0 + 8 * c, CLC_CONSUMERS);  // leader's copy is used
+    }
+    mbar_init(sched_go, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 0) {
@@ -279,16 +349,19 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
     }
     int stage = 0;
     uint32_t phase = 0;
-    unsigned step = 0;
     bool pacing = w.window > 0 && npairs > 1;
-    for (int item = pair_id; item < nitems; item += npairs) {
+    const int pace_slot = kDynamic ? (int)sm_id() : pair_id;  // one CTA per SM: the leader's SM names the pair
+    Cursor cur;
+    for (int item = pair_id; item >= 0 && item < nitems;
+         item = next_item<kDynamic, true>(item, npairs, nitems, clc_full0, clc_empty0, clc_resp0, cur, lane)) {
+      if (kDynamic && rank == 0 && lane == 0) mbar_arrive_cluster(map_to_cta(sched_go, 0));  // fetch the item after this
       int ks, tm, tn;
       decode_item(w, item, ks, tm, tn);
       const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
       const int qrow = tm * TM + (int)rank * CTA_ROWS, rrow = tn * TN + (int)rank * CTA_ROWS;
-      for (int kb = kb0; kb < kb1; ++kb, ++step) {
-        if (step % PACE == 0) {
-          pace(w, pair_id, npairs, rank, lane, step, pacing);
+      for (int kb = kb0; kb < kb1; ++kb) {
+        if ((kb - kb0) % PACE == 0) {
+          pace(w, pace_slot, rank, lane, (unsigned)(kb - kb0), pacing);
           __syncwarp();
         }
         if (lane == 0) {
@@ -307,13 +380,15 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
       }
     }
     if (rank == 0 && lane == 0)  // finished: never hold anybody back
-      *reinterpret_cast<volatile unsigned long long*>(&g_pace[pair_id]) = ((unsigned long long)w.epoch << 32) | 0xffffffffu;
+      *reinterpret_cast<volatile unsigned long long*>(&g_pace[pace_slot]) = ((unsigned long long)w.epoch << 32) | 0xffffffffu;
   } else if (warp == 1) {
     // ===================================== MMA issuer (leader only) =========================
     if (rank == 0 && lane == 0) {
       int stage = 0, acc = 0;
       uint32_t phase = 0, acc_phase = 0;
-      for (int item = pair_id; item < nitems; item += npairs) {
+      Cursor cur;
+      for (int item = pair_id; item >= 0 && item < nitems;
+           item = next_item<kDynamic, false>(item, npairs, nitems, clc_full0, clc_empty0, clc_resp0, cur, 0)) {
         int ks, tm, tn;
         decode_item(w, item, ks, tm, tn);
         const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
@@ -338,6 +413,21 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
         }
       }
     }
+  } else if (warp == 2) {
+    // ===================================== work-stealing scheduler (leader only, dynamic) ===
+    if (kDynamic && rank == 0 && lane == 0) {
+      Cursor cur;
+      uint32_t go_phase = 0;
+      for (;;) {
+        mbar_wait(sched_go, go_phase);  // the producer has started an item: steal the one after it, no further ahead
+        go_phase ^= 1;
+        mbar_wait(clc_empty0 + 8 * cur.slot, cur.phase ^ 1);  // every role of both CTAs has read the old answer
+        mbar_expect_tx(clc_full0 + 8 * cur.slot, 16);
+        mbar_expect_tx_cluster(map_to_cta(clc_full0 + 8 * cur.slot, 1), 16);
+        clc_try_cancel(clc_resp0 + 16 * cur.slot, clc_full0 + 8 * cur.slot);
+        if (next_item<true, false>(0, 0, 0, clc_full0, clc_empty0, clc_resp0, cur, 0) < 0) break;
+      }
+    }
   } else if (warp >= EPI_WARP0) {
     // ===================================== epilogue (both CTAs) =============================
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS_EPI));
@@ -347,7 +437,9 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
     for (int i = 0; i < EPI_COLS; ++i) acc32[i] = 0;
     int acc = 0, since_check = 0;
     uint32_t acc_phase = 0;
-    for (int item = pair_id; item < nitems; item += npairs) {
+    Cursor cur;
+    for (int item = pair_id; item >= 0 && item < nitems;
+         item = next_item<kDynamic, true>(item, npairs, nitems, clc_full0, clc_empty0, clc_resp0, cur, lane)) {
       int ks, tm, tn;
       decode_item(w, item, ks, tm, tn);
       const int kb0 = ks * w.kb_per_split, kb1 = min(w.kb_total, kb0 + w.kb_per_split);
@@ -457,9 +549,10 @@ static int make_map(CUtensorMap* map, const void* ptr, int64_t rows, int64_t nkb
 }  // namespace tc
 }  // namespace g2
 
-// Upper bound on the CTA pairs the Gram kernel occupies (0 = all SMs).  The kernel is persistent with a static
-// item partition, so every pair must be co-resident: a caller that overlaps it with another kernel (the ring
-// schedule overlaps it with NCCL's send/recv kernel) leaves that kernel its SMs through this knob.
+// Upper bound on the CTA pairs the Gram kernel occupies (0 = no bound, the default).  A bound selects the static
+// schedule: a persistent grid of that many pairs with a round-robin item partition, which needs every pair to be
+// co-resident.  Without a bound the kernel uses cluster launch control (one cluster per item, running clusters
+// cancel and absorb the ones that have not started), which adapts to whatever SMs other kernels leave free.
 static std::atomic<int> g_max_pairs{0};
 extern "C" int gridb200_gram_set_max_pairs(int pairs) {
   G2_REQUIRE(pairs >= 0, GRIDB200_EINVAL, "pairs must be >= 0");
@@ -486,7 +579,9 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
     G2_CUDA(cudaGetDeviceProperties(&prop, dev));
     G2_REQUIRE(prop.major == 10, GRIDB200_ENODEV, "tcgen05 path needs an sm_100 device (found sm_%d%d)", prop.major,
                prop.minor);
-    G2_CUDA(cudaFuncSetAttribute(k_gram_tc_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    G2_CUDA(cudaFuncSetAttribute(k_gram_tc_pair<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    G2_CUDA(cudaFuncSetAttribute(k_gram_tc_pair<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    G2_REQUIRE(prop.multiProcessorCount <= PACE_SLOTS, GRIDB200_ENODEV, "more SMs than pacing slots");
     sms = prop.multiProcessorCount;
   }
   const int64_t nkb = kdim / BK;
@@ -494,15 +589,19 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
   if (int e = make_map(&mq, zq, nq, nkb, slabq)) return e;
   if (int e = make_map(&mr, zr, nr, nkb, slabr)) return e;
 
-  static int no_sym = -1, no_pace = -1;  // debugging switches
+  static int no_sym = -1, no_pace = -1, static_sched = 0;  // debugging switches
   if (no_sym < 0) {
+    const char* sch = getenv("GRIDB200_GRAM_SCHED");  // "static": round-robin item partition instead of work stealing
+    static_sched = (sch && sch[0] == 's') ? 1 : 0;
     const char* e = getenv("GRIDB200_GRAM_NOSYM");
     no_sym = (e && e[0] == '1') ? 1 : 0;
     e = getenv("GRIDB200_GRAM_NOPACE");
     no_pace = (e && e[0] == '1') ? 1 : 0;
   }
   int workers = std::min(sms / 2, MAX_PAIRS);
-  if (const int cap = g_max_pairs.load()) workers = std::max(1, std::min(workers, cap));
+  const int cap = g_max_pairs.load();
+  if (cap) workers = std::max(1, std::min(workers, cap));
+  const bool dynamic = !static_sched && !cap;
   Work w;
   w.nq = nq, w.nr = nr, w.ldd = ldd;
   w.symmetric = (!no_sym && zq == zr && nq == nr && slabq == slabr) ? 1 : 0;
@@ -511,7 +610,12 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
   w.ntiles = w.symmetric ? w.tiles_m * (w.tiles_m + 1) / 2 : w.tiles_m * w.tiles_n;
   w.kb_total = (int)nkb;
   w.ck = (int)std::min<int64_t>(ck, w.kb_total);
-  w.group_m = 4;
+  static int group_m_env = -1;  // GRIDB200_GRAM_GROUP_M: tile rows per band of the general (non-symmetric) walk
+  if (group_m_env < 0) {
+    const char* e = getenv("GRIDB200_GRAM_GROUP_M");
+    group_m_env = (e && atoi(e) > 0) ? atoi(e) : 0;
+  }
+  w.group_m = group_m_env ? group_m_env : 4;
   // K splits: best wave efficiency over the workers, each split at least 4 chunks long
   const int chunks = (w.kb_total + w.ck - 1) / w.ck;
   int best_s = 1;
@@ -544,8 +648,13 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
   w.epoch = epoch.fetch_add(1) + 1;
   if (!accumulate) G2_CUDA(cudaMemset2DAsync(dot, ldd * sizeof(int64_t), 0, nr * sizeof(int64_t), nq, st));
   const long long items = (long long)w.ntiles * w.ksplits;
+  G2_REQUIRE(items < (1LL << 30), GRIDB200_EINVAL, "too many work items");
   const int nwork = (int)std::min<long long>(items, workers);
-  k_gram_tc_pair<<<2 * nwork, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, reinterpret_cast<long long*>(dot));
+  w.pace_slots = dynamic ? sms : nwork;
+  if (dynamic)  // one cluster per item; the clusters that get SMs cancel the rest and take their items over
+    k_gram_tc_pair<true><<<2 * (unsigned)items, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, reinterpret_cast<long long*>(dot));
+  else
+    k_gram_tc_pair<false><<<2 * nwork, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, reinterpret_cast<long long*>(dot));
   G2_LAUNCHED();
   if (w.symmetric && w.tiles_m > 1) {
     const unsigned nb = (unsigned)((nq + 31) / 32);

@@ -170,12 +170,12 @@ def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, g
         E.knn_block(zh, norms, offsets[rank], ref, norms_all[r_gid0:r_gid0 + n_ref], r_gid0, kdim, p.zclip, best_d2,
                     best_idx, impl=impl)
 
-    # the persistent Gram kernel must not fight NCCL's send/recv kernel for SMs (a pair that cannot be co-resident
-    # runs its whole static share after everybody else): leave it GRIDB200_RING_COMM_SMS SMs (default 16; NCCL's CTA
-    # count can be bounded with NCCL_MAX_CTAS) while transfers are in flight
+    # The Gram kernel shares the GPU with NCCL's send/recv kernel while a transfer is in flight.  Its default
+    # schedule (cluster launch control) adapts to the SMs it gets.  GRIDB200_RING_COMM_SMS=<n> instead selects the
+    # static schedule on all but n SMs (A/B aid).
     import os
 
-    comm_sms = int(os.environ.get("GRIDB200_RING_COMM_SMS", "16")) if world > 1 else 0
+    comm_sms = int(os.environ.get("GRIDB200_RING_COMM_SMS", "0")) if world > 1 else 0
     sms = torch.cuda.get_device_properties(dev).multi_processor_count
     call("gridb200_gram_set_max_pairs", max(1, (sms - comm_sms) // 2) if comm_sms else 0)
     try:
