@@ -297,9 +297,11 @@ def knn(zh: torch.Tensor, kdim: int, norms: torch.Tensor, k: int, vmax: int, imp
 
 
 def dipcn(counts: torch.Tensor, has_count: torch.Tensor, scale_q: torch.Tensor, nbr_idx: torch.Tensor, n_nbr: int,
-          q_gid0: int = 0):
+          q_gid0: int = 0, rule: str = "pipeline"):
     """Step 6 on device arrays: counts[n_all,g] int32, has_count[n_all] uint8, scale_q[n_all] f64 for the WHOLE cohort,
-    nbr_idx[nq,k] int32 (global ids) for query rows q_gid0.. -> out[nq,g] f64."""
+    nbr_idx[nq,k] int32 (global ids) for query rows q_gid0.. -> out[nq,g] f64.
+    rule: "pipeline" = compute_dipcn.py:62-88; "exon" = compute_dipcn_dir/compute_diploid_cn.py:8-63."""
+    rule_id = {"pipeline": 0, "exon": 1}[rule]
     n, g = counts.shape
     dev = counts.device
     nq = nbr_idx.shape[0]
@@ -307,7 +309,7 @@ def dipcn(counts: torch.Tensor, has_count: torch.Tensor, scale_q: torch.Tensor, 
     t_ws = torch.empty(n * g, dtype=torch.float64, device=dev)
     with _mark("dipcn"):
         call("gridb200_dipcn", ptr(counts), n, g, counts.stride(0), ptr(has_count), ptr(scale_q), ptr(nbr_idx),
-             nq, nbr_idx.shape[1], int(q_gid0), int(n_nbr), ptr(out), g, ptr(t_ws), _stream())
+             nq, nbr_idx.shape[1], int(q_gid0), int(n_nbr), rule_id, ptr(out), g, ptr(t_ws), _stream())
     return out
 
 

@@ -179,13 +179,21 @@ GRIDB200_API int gridb200_topk_merge(const int64_t* dot, int64_t ldd, int64_t nq
 
 /* ------------------------------------------------------------------ step 6: compute_dipcn ---------------- */
 
-/* out[i,g] = (counts[q0+i,g]/scale[q0+i]) / mean_{first n_nbr neighbours j with has_count[j]} counts[j,g]/scale[j]
- * (compute_dipcn.py:62-88); NaN where the reference omits the sample (no count / no contributing neighbour).
- * counts [n_all, g] int32 (read counts are integers and stay so), scale_q [n_all] = the %.2f-rounded scales,
- * nbr_idx [nq,k] global indices (-1 = empty slot).  t_ws: n_all*g doubles of scratch. */
+/* out[i,g] = (counts[q0+i,g]/scale[q0+i]) / mean over contributing neighbours j of counts[j,g]/scale[j]; NaN where
+ * the reference omits the sample.  counts [n_all, g] int32 (read counts are integers and stay so), scale_q [n_all] =
+ * the %.2f-rounded scales, nbr_idx [nq,k] global indices (-1 = empty slot).  t_ws: n_all*g doubles of scratch.
+ * rule = which of the reference's two skip rules applies:
+ *   GRIDB200_DIPCN_PIPELINE  compute_dipcn.py:62-88 (what `grid wgs` runs): the first n_nbr neighbours THAT HAVE a
+ *                            count contribute (absent ones do not use up the budget); query omitted without a count
+ *                            or without a contributor.
+ *   GRIDB200_DIPCN_EXON      compute_dipcn_dir/compute_diploid_cn.py:8-63: the list is cut to n_nbr entries first;
+ *                            per region only neighbours with count > 0 and scale > 0 contribute; query omitted on a
+ *                            zero count, a non-positive scale or no contributor. */
+#define GRIDB200_DIPCN_PIPELINE 0
+#define GRIDB200_DIPCN_EXON 1
 GRIDB200_API int gridb200_dipcn(const int32_t* counts, int64_t n_all, int64_t g, int64_t ldc, const uint8_t* has_count,
                    const double* scale_q, const int32_t* nbr_idx, int64_t nq, int32_t k, int64_t q_gid0,
-                   int32_t n_nbr, double* out, int64_t ldo, double* t_ws, void* stream);
+                   int32_t n_nbr, int32_t rule, double* out, int64_t ldo, double* t_ws, void* stream);
 
 /* ------------------------------------------------------------------ synthetic cohorts (bench / tests) ---- */
 

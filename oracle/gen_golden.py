@@ -12,6 +12,8 @@ what is committed is what the REFERENCE produced:
                   num_neighbors > N-1 (truncation), one sample without a read count
   arrays.npz      normalize_matrix / select_high_variance_regions / filter_regions_by_variance /
                   find_neighbors_sklearn outputs on in-memory arrays (incl. NaN cells)
+  exon.npz        compute_diploid_cn_for_exon on a 40-sample cohort with zero counts, samples without counts and
+                  non-positive scales, all four exon types (python oracle/gen_golden.py exon regenerates only this)
   manifest.json   shapes, seeds, sha256 of every generated input file
 """
 
@@ -134,13 +136,43 @@ def array_case(manifest):
     manifest["arrays"] = {"depth": "synth.depth_hundredths(3,64,300)/100 with NaNs (rng 11)", "k": 20}
 
 
+def exon_case():
+    from grid.utils.compute_dipcn_dir.compute_diploid_cn import compute_diploid_cn_for_exon
+
+    rng = np.random.default_rng(5)
+    n, k = 40, 12
+    keys = ("1B_KIV3", "1B_KIV2", "1B_tied", "1A")
+    raw = rng.integers(0, 400, size=(n, 4))
+    raw[rng.random((n, 4)) < 0.15] = 0
+    has = rng.random(n) > 0.15
+    scales = np.round(rng.uniform(0.6, 1.6, n), 2)
+    scales[3], scales[17] = 0.0, -1.0
+    idx = np.stack([rng.permutation(np.delete(np.arange(n), i))[:k] for i in range(n)]).astype(np.int32)
+    ids = synth.sample_ids(n)
+    counts = {ids[i]: dict(zip(keys, (int(v) for v in raw[i]))) for i in range(n) if has[i]}
+    nbrs = {ids[i]: (float(scales[i]), [(ids[j], float(scales[j]), 0.5) for j in idx[i]]) for i in range(n)}
+    types = ("1B_KIV3", "1B_notKIV3", "1B", "1A")
+    res = {}
+    for nn in (5, 200):
+        out = np.full((n, 4), np.nan)
+        for c, t in enumerate(types):
+            for sid, v in compute_diploid_cn_for_exon(counts, nbrs, t, n_neighbors=nn).items():
+                out[ids.index(sid), c] = v
+        res[f"out_n{nn}"] = out
+    np.savez_compressed(GOLD / "exon.npz", raw=raw, has=has, scales=scales, idx=idx, **res)
+
+
 def main():
     GOLD.mkdir(parents=True, exist_ok=True)
+    if sys.argv[1:] == ["exon"]:
+        exon_case()
+        return
     manifest = {"reference": "caterer-z-t/GRiD @ /root/reference", "sklearn": __import__("sklearn").__version__,
                 "numpy": np.__version__}
     file_case("c1_lpa", cfg_c1, manifest)
     file_case("masked", cfg_masked, manifest)
     array_case(manifest)
+    exon_case()
     (GOLD / "manifest.json").write_text(json.dumps(manifest, indent=1, sort_keys=True) + "\n")
     print("golden written to", GOLD)
 

@@ -447,6 +447,73 @@ def dipcn_arrays(counts, has_count, scales, nbr_idx, n_nbr: int) -> np.ndarray:
     return out
 
 
+def exon_count(counts_dict: dict, exon_type: str) -> int:
+    """Count of one exon type from the four stored keys (compute_dipcn_dir/get_exon_count.py:7-44)."""
+    g = counts_dict.get
+    if exon_type == "1B_KIV3":
+        return g("1B_KIV3", 0)
+    if exon_type == "1B_notKIV3":
+        return g("1B_KIV2", 0) + g("1B_tied", 0)
+    if exon_type == "1B":
+        return g("1B_KIV3", 0) + g("1B_KIV2", 0) + g("1B_tied", 0)
+    if exon_type == "1A":
+        return g("1A", 0)
+    raise ValueError(f"Unknown exon type: {exon_type}")
+
+
+EXON_TYPES = ("1B_KIV3", "1B_notKIV3", "1B", "1A")
+
+
+def dipcn_exon(counts: dict, neighbors: dict, exon_type: str, n_neighbors: int = 200) -> dict:
+    """The exon variant of dipCN (compute_dipcn_dir/compute_diploid_cn.py:8-63).  Differs from :func:`dipcn`:
+    the neighbour list is cut to its first n entries BEFORE anything is skipped (a neighbour without counts uses up
+    a slot); zero counts and non-positive scales do not contribute; a sample with a zero count, a non-positive
+    scale or no contributor is omitted.  neighbors[id] = (scale, [(nbr_id, nbr_scale, distance), ...])."""
+    out = {}
+    for sid, (s_scale, lst) in neighbors.items():
+        if sid not in counts:
+            continue
+        c = exon_count(counts[sid], exon_type)
+        if c == 0:
+            continue
+        tot, num = 0.0, 0
+        for nid, ns, _d in lst[:n_neighbors]:
+            if nid not in counts:
+                continue
+            nc = exon_count(counts[nid], exon_type)
+            if nc > 0 and ns > 0:
+                tot += nc / ns
+                num += 1
+        if num > 0 and s_scale > 0:
+            mean = tot / num
+            if mean > 0:
+                out[sid] = (c / s_scale) / mean
+    return out
+
+
+def dipcn_arrays_exon(counts, has_count, scales, nbr_idx, n_nbr: int) -> np.ndarray:
+    """Array form of :func:`dipcn_exon` for G count columns at once (same argument layout as dipcn_arrays)."""
+    counts = np.asarray(counts)
+    scales = np.asarray(scales, dtype=np.float64)
+    n, g = counts.shape
+    out = np.full((n, g), np.nan)
+    for i in range(n):
+        if not has_count[i]:
+            continue
+        js = [j for j in nbr_idx[i][:n_nbr] if j >= 0 and has_count[j]]
+        for c in range(g):
+            if counts[i, c] == 0:
+                continue
+            tot, num = 0.0, 0
+            for j in js:
+                if counts[j, c] > 0 and scales[j] > 0:
+                    tot += float(counts[j, c]) / float(scales[j])
+                    num += 1
+            if num > 0 and scales[i] > 0 and tot / num > 0:
+                out[i, c] = (float(counts[i, c]) / float(scales[i])) / (tot / num)
+    return out
+
+
 def compute_diploid_genotypes(config: dict) -> Path:
     """File-level step 6 (compute_dipcn.py:10-101); output written the way DataFrame.to_csv does (repr floats)."""
     import pandas as pd

@@ -388,3 +388,33 @@ def test_fused_row_stats_equal_the_full_pass(bad_frac, eng):
     mode = int(ws.view(torch.int32)[1].item())
     n_bad = int(((valid_np == 0) & ((h > 0).sum(axis=0) > 0)).sum())
     assert mode == (1 if n_bad * 8 <= b else 0)
+
+
+@pytest.mark.parametrize("nn", [5, 200])
+def test_dipcn_exon_rule_matches_the_reference_golden(nn, golden, eng):  # compute_dipcn_dir/compute_diploid_cn.py:8-63
+    g = np.load(golden / "exon.npz")
+    raw = g["raw"]
+    cols = np.stack([raw[:, 0], raw[:, 1] + raw[:, 2], raw[:, 0] + raw[:, 1] + raw[:, 2], raw[:, 3]], axis=1)
+    got = eng.dipcn(torch.from_numpy(cols.astype(np.int32)).cuda(), torch.from_numpy(g["has"].astype(np.uint8)).cuda(),
+                    torch.from_numpy(g["scales"]).cuda(), torch.from_numpy(g["idx"]).cuda(), nn, rule="exon").cpu().numpy()
+    want = g[f"out_n{nn}"]
+    np.testing.assert_array_equal(np.isnan(got), np.isnan(want))
+    np.testing.assert_allclose(got[~np.isnan(want)], want[~np.isnan(want)], rtol=1e-14)
+
+
+def test_dipcn_batch_over_regions_both_rules(eng):
+    """C5 shape in small: G = 734 regions at once; absent counts, zero counts, -1 padded lists, query offset."""
+    rng = np.random.default_rng(8)
+    n, g, k, q0, nq = 300, 734, 64, 37, 120
+    counts = rng.integers(0, 3000, (n, g)).astype(np.int32)
+    counts[rng.random((n, g)) < 0.05] = 0
+    has = (rng.random(n) > 0.1).astype(np.uint8)
+    scales = np.round(rng.uniform(0.5, 2.0, n), 2)
+    idx = np.stack([rng.permutation(np.delete(np.arange(n), i))[:k] for i in range(n)]).astype(np.int32)
+    idx[rng.random(idx.shape) < 0.03] = -1
+    for rule, fn in (("pipeline", O.dipcn_arrays), ("exon", O.dipcn_arrays_exon)):
+        want = fn(counts, has, scales, idx, 40)[q0:q0 + nq]
+        got = eng.dipcn(torch.from_numpy(counts).cuda(), torch.from_numpy(has).cuda(), torch.from_numpy(scales).cuda(),
+                        torch.from_numpy(idx[q0:q0 + nq]).cuda(), 40, q_gid0=q0, rule=rule).cpu().numpy()
+        np.testing.assert_array_equal(np.isnan(got), np.isnan(want))
+        np.testing.assert_allclose(got[~np.isnan(want)], want[~np.isnan(want)], rtol=1e-13)
