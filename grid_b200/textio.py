@@ -1,0 +1,171 @@
+"""Step-4 hand-off file at device speed: same bytes after gunzip as grid_b200.io /
+the reference (normalize_mosdepth.py:502-554, find_neighbors.py:81-124), but the N x Rw cells are formatted and
+parsed by CUDA kernels (csrc/textio.cu) and gzip runs as independent members on a thread pool (a concatenation of
+gzip members is a gzip file; `gzip.open`, which the reference reads with, handles it).
+
+The host keeps what is small: ids, scales, the two header lines, line boundaries (memchr).
+"""
+
+from __future__ import annotations
+
+import gzip
+import zlib
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+
+from . import io as gio
+
+MEMBER_BYTES = 8 << 20   # uncompressed text per gzip member (rows are never split)
+BATCH_BYTES = 256 << 20  # device/pinned text buffer per formatting or parsing batch
+
+
+def _deflate_member(parts) -> bytes:
+    co = zlib.compressobj(6, zlib.DEFLATED, 31)  # wbits 31 = gzip container
+    out = [co.compress(p) for p in parts]
+    out.append(co.flush())
+    return b"".join(out)
+
+
+def write_normalized_output(path, ids, zq, rw: int, mu_sel: np.ndarray, ratio_sel: np.ndarray, raw_means: np.ndarray,
+                            threads: int = 8) -> None:
+    """Step-4 file from the DEVICE matrix zq[N, ldq] (int16 codes, torch CUDA tensor), N = len(ids) rows."""
+    import torch
+
+    from ._lib import call, load, ptr
+
+    n = len(ids)
+    assert zq.is_cuda and zq.dtype == torch.int16 and zq.shape[0] >= n
+    st = torch.cuda.current_stream().cuda_stream
+    head = (f"{n}\t{rw}\t" + "\t".join(gio.fixed(v, 3) for v in mu_sel) + "\n"
+            + f"{n}\t{rw}\t" + "\t".join(gio.fixed(v, 3) for v in ratio_sel) + "\n").encode()
+    pool = ThreadPoolExecutor(max_workers=max(1, int(threads)))
+    with open(path, "wb") as out:
+        if rw == 0 or n == 0:  # nothing for the device to do: rows are "id\tscale\t\n" (join of no fields)
+            body = "".join(f"{sid}\t{raw_means[i]:.2f}\t\n" for i, sid in enumerate(ids)).encode()
+            out.write(_deflate_member([head, body]))
+            return
+        per = int(max(1, min(65535, BATCH_BYTES // (8 * rw))))
+        ws = torch.empty(load().gridb200_format_z_ws_bytes(per, rw), dtype=torch.uint8, device=zq.device)
+        row_off = torch.empty(per + 1, dtype=torch.int64, device=zq.device)
+        text = torch.empty(per * rw * 8, dtype=torch.uint8, device=zq.device)
+        host = torch.empty(per * rw * 8, dtype=torch.uint8, pin_memory=True)
+        pending = [head]
+        pending_bytes = len(head)
+        jobs = []
+        for r0 in range(0, n, per):
+            cnt = min(per, n - r0)
+            base = zq[r0:r0 + cnt]
+            call("gridb200_format_z_measure", ptr(base), cnt, rw, zq.stride(0), ptr(row_off), ptr(ws), ws.numel(), st)
+            call("gridb200_format_z_write", ptr(base), cnt, rw, zq.stride(0), ptr(row_off), ptr(ws), ptr(text),
+                 text.numel(), st)
+            off = row_off[: cnt + 1].cpu().numpy()  # synchronises the stream
+            total = int(off[-1])
+            host[:total].copy_(text[:total])
+            blob = host[:total].numpy().tobytes()  # detach from the pinned buffer: workers outlive this batch
+            view = memoryview(blob)
+            for i in range(cnt):
+                pre = f"{ids[r0 + i]}\t{raw_means[r0 + i]:.2f}\t".encode()
+                pending += [pre, view[off[i]:off[i + 1]]]
+                pending_bytes += len(pre) + int(off[i + 1] - off[i])
+                if pending_bytes >= MEMBER_BYTES:
+                    jobs.append(pool.submit(_deflate_member, pending))
+                    pending, pending_bytes = [], 0
+            while len(jobs) > 4 * max(1, int(threads)):  # bound the text held in flight
+                out.write(jobs.pop(0).result())
+        if pending:
+            jobs.append(pool.submit(_deflate_member, pending))
+        for j in jobs:
+            out.write(j.result())
+    pool.shutdown()
+
+
+class _Fallback(Exception):
+    pass
+
+
+def read_normalized_data(path, device="cuda"):
+    """Step-4 file -> (ids, ratios[Rw] float64, zq[N, ldq] int16 DEVICE tensor, scales[N] float64).
+    Files outside the writer's grammar are re-read by grid_b200.io.read_normalized_data (Python float() semantics)."""
+    import torch
+
+    try:
+        return _read_device(path, torch.device(device))
+    except _Fallback:
+        ids, ratios, zq, scales = gio.read_normalized_data(path)
+        ld = (zq.shape[1] + 7) // 8 * 8
+        t = torch.full((len(ids), max(ld, 8)), gio.ZQ_NA, dtype=torch.int16, device=device)
+        if zq.size:
+            t[:, : zq.shape[1]] = torch.from_numpy(zq).to(device)
+        return ids, ratios, t, scales
+
+
+def _read_device(path, dev):
+    import torch
+
+    from ._lib import call, load, ptr
+
+    st = torch.cuda.current_stream().cuda_stream
+    ids, scales = [], []
+    with gzip.open(path, "rb") as fh:
+        h1 = fh.readline()
+        h2 = fh.readline()
+        try:
+            n_hdr, rw = int(h1.split(b"\t", 2)[0]), int(h1.split(b"\t", 2)[1])
+        except (ValueError, IndexError):
+            raise _Fallback()
+        toks = h2.strip().split(b"\t")[2:]
+        ratios = np.array([float("nan") if t in (b"NA", b"nan") else float(t) for t in toks])
+        if len(ratios) != rw or rw == 0 or n_hdr <= 0:
+            raise _Fallback()
+        ld = (rw + 7) // 8 * 8
+        zq = torch.full((n_hdr, ld), gio.ZQ_NA, dtype=torch.int16, device=dev)
+        stats = torch.zeros(4, dtype=torch.int64, device=dev)
+        bad = torch.zeros(4, dtype=torch.int64, device=dev)
+        carry = b""
+        row = 0
+        while True:
+            block = fh.read(BATCH_BYTES)
+            buf = carry + block
+            if not buf:
+                break
+            end = len(buf) if not block else buf.rfind(b"\n") + 1
+            if end == 0:  # no complete line yet
+                carry = buf
+                continue
+            carry = buf[end:]
+            offs = [0]
+            pos = 0
+            while pos < end:
+                nl = buf.find(b"\n", pos, end)
+                nxt = end if nl < 0 else nl + 1
+                t1 = buf.find(b"\t", pos, nxt)
+                t2 = buf.find(b"\t", t1 + 1, nxt) if t1 >= 0 else -1
+                if t2 < 0:
+                    raise _Fallback()
+                try:
+                    scales.append(float(buf[t1 + 1:t2]))
+                except ValueError:
+                    raise _Fallback()
+                ids.append(buf[pos:t1].decode())
+                offs.append(nxt)
+                pos = nxt
+            cnt = len(offs) - 1
+            if row + cnt > n_hdr:
+                raise _Fallback()
+            t_text = torch.frombuffer(bytearray(buf[:end]), dtype=torch.uint8).to(dev)
+            t_off = torch.tensor(offs, dtype=torch.int64, device=dev)
+            max_line = int(np.diff(np.asarray(offs)).max())
+            for r0 in range(0, cnt, 65535):
+                c = min(65535, cnt - r0)
+                ws = torch.empty(load().gridb200_parse_z_ws_bytes(c, max_line), dtype=torch.uint8, device=dev)
+                call("gridb200_parse_z_rows", ptr(t_text), t_off.data_ptr() + 8 * r0, c, max_line, 2, rw,
+                     zq.data_ptr() + (row + r0) * ld * 2, ld, ptr(stats), ptr(ws), ws.numel(), st)
+                bad += stats
+            row += cnt
+            if not block:
+                break
+        b = bad.cpu().numpy()
+        if b[1] or b[2] or b[0] != row * rw:
+            raise _Fallback()
+    return ids, ratios, zq[:row], np.array(scales)

@@ -38,9 +38,15 @@ def find_neighbors(config, console):
     from .. import _lib, engine
     from .._lib import call, ptr
 
-    ids, ratios, zq, scales = read_normalized_data(input_file)
-    n, rw = zq.shape
     dev = torch.device("cuda")
+    if config.get("gpu", {}).get("device_text", True):  # additive key; default = parse the cells on the GPU
+        from .. import textio
+
+        ids, ratios, tzq, scales = textio.read_normalized_data(input_file, dev)
+    else:
+        ids, ratios, zq, scales = read_normalized_data(input_file)
+        tzq = torch.from_numpy(np.ascontiguousarray(zq)).to(dev)
+    n, rw = len(ids), len(ratios)
     p = engine.Params(zmax=zmax, sigma2_max=sigma2_max, frac_r=frac_r, num_neighbors=n_neighbors)
     with progress_bar(console, total=n, description="Finding neighbors...") as (progress, task):
         if rw == 0 or n < 2:
@@ -63,7 +69,6 @@ def find_neighbors(config, console):
             extreme = int(np.sum(ratios > sigma2_max))
             if extreme and console:
                 log(console, f"Removed {extreme} / {rw} regions with sigma2ratio > {sigma2_max}", style="warning")
-            tzq = torch.from_numpy(np.ascontiguousarray(zq)).to(dev)
             zh, kdim, norms = engine.prepare_from_zq(tzq, rw, keep, p.zclip)
             tidx, td2 = engine.knn(zh, kdim, norms, n_neighbors, p.zclip)
             idx, d2 = tidx.cpu().numpy(), td2.cpu().numpy()

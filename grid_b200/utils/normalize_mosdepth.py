@@ -208,9 +208,17 @@ def normalize_mosdepth(config, console):
         log(console, "No valid samples with regions found.", style="danger")
         sys.exit(1)
     sel = np.nonzero(res.sel_pos.cpu().numpy() >= 0)[0]
-    zq = res.zq.cpu().numpy()[rows][:, : res.rw] if res.zq is not None else np.zeros((len(rows), 0), dtype=np.int16)
-    gio.write_normalized_output(output_path, [ids[i] for i in rows], zq, res.mu.cpu().numpy()[sel],
-                                res.ratio.cpu().numpy()[sel], res.raw_mean.cpu().numpy()[rows])
+    mu_sel, ratio_sel = res.mu.cpu().numpy()[sel], res.ratio.cpu().numpy()[sel]
+    raw_means = res.raw_mean.cpu().numpy()[rows]
+    kept_ids = [ids[i] for i in rows]
+    if config.get("gpu", {}).get("device_text", True) and res.zq is not None:  # additive key; default = format on the GPU
+        from .. import textio
+
+        zq_dev = res.zq if len(rows) == len(ids) else res.zq[torch.from_numpy(rows).to(res.zq.device)]
+        textio.write_normalized_output(output_path, kept_ids, zq_dev, res.rw, mu_sel, ratio_sel, raw_means, threads=threads)
+    else:
+        zq = res.zq.cpu().numpy()[rows][:, : res.rw] if res.zq is not None else np.zeros((len(rows), 0), dtype=np.int16)
+        gio.write_normalized_output(output_path, kept_ids, zq, mu_sel, ratio_sel, raw_means)
     log(console, f"Mosdepth normalization complete. Results written to {output_path}", style="success")
 
     if remove_intermediate:  # mosdepth.remove_intermediate_files(dir, console, include_region_bed_gz=True), mosdepth.py:300-326

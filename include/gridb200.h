@@ -223,6 +223,34 @@ GRIDB200_API int gridb200_ingest_text(const char* text, int64_t nbytes, const ch
                          int64_t bin0, int64_t b, float* depth_row, int64_t* stats,
                          void* ws, size_t ws_bytes, void* stream);
 
+/* ------------------------------------------------------------------ step-4 hand-off text --- */
+
+/* The N x Rw body of the step-4 file, on the device.  Codes are the int16 hundredths gridb200_transform writes
+ * (-32768 = "NA", -32767 = "-0.00").  Replaces the per-cell f-string of write_normalized_output
+ * (normalize_mosdepth.py:548-552) and the per-token float() of read_normalized_data (find_neighbors.py:107-121).
+ *
+ * gridb200_format_z_measure: row_off[0..rows] (device) = byte offset of every row's text in the batch; row i is
+ *   "z\tz\t...z\n" (the host writes "id\tscale\t" in front).  rows <= 65535 per call.
+ * gridb200_format_z_write:   fills text[0 .. row_off[rows]) (text_cap >= that; 8 bytes per cell always suffice).
+ *   `ws` must be the workspace the measure call filled.  ws: gridb200_format_z_ws_bytes(rows, rw). */
+GRIDB200_API size_t gridb200_format_z_ws_bytes(int64_t rows, int64_t rw);
+GRIDB200_API int gridb200_format_z_measure(const int16_t* zq, int64_t rows, int64_t rw, int64_t ldq, int64_t* row_off,
+                              void* ws, size_t ws_bytes, void* stream);
+GRIDB200_API int gridb200_format_z_write(const int16_t* zq, int64_t rows, int64_t rw, int64_t ldq,
+                            const int64_t* row_off, const void* ws, char* text, int64_t text_cap, void* stream);
+
+/* Inverse: line i of the batch is text[line_off[i], line_off[i+1]) including its newline (line_off: device,
+ * rows+1 entries; the host finds line ends with memchr while it inflates).  Fields skip_fields.. of every line are
+ * decoded into zq[i, 0..rw).  Accepted cell grammar: NA | nan | [-]d{1,3}.dd with |value| <= 327.66 ("-0.00" reads
+ * back as 0, as float() does).  stats[0] = cells decoded, stats[1] = tokens outside the grammar, stats[2] = lines
+ * whose field count is not skip_fields + rw: when either is non-zero the caller must re-read the file on the host
+ * (the reference's float() accepts more spellings than the writer produces).
+ * ws: gridb200_parse_z_ws_bytes(rows, max_line_bytes), max_line_bytes >= the longest line. */
+GRIDB200_API size_t gridb200_parse_z_ws_bytes(int64_t rows, int64_t max_line_bytes);
+GRIDB200_API int gridb200_parse_z_rows(const char* text, const int64_t* line_off, int64_t rows, int64_t max_line_bytes,
+                          int32_t skip_fields, int64_t rw, int16_t* zq, int64_t ldq, int64_t* stats,
+                          void* ws, size_t ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -418,3 +418,110 @@ def test_dipcn_batch_over_regions_both_rules(eng):
                         torch.from_numpy(idx[q0:q0 + nq]).cuda(), 40, q_gid0=q0, rule=rule).cpu().numpy()
         np.testing.assert_array_equal(np.isnan(got), np.isnan(want))
         np.testing.assert_allclose(got[~np.isnan(want)], want[~np.isnan(want)], rtol=1e-13)
+
+
+# ---- step-4 hand-off text on the device (csrc/textio.cu) ------------------------------------------------------
+def _codes(rng, n, rw):
+    c = rng.integers(-450, 451, size=(n, rw)).astype(np.int16)
+    special = rng.random((n, rw))
+    c[special < 0.05] = -32768          # NA
+    c[(special >= 0.05) & (special < 0.07)] = -32767   # -0.00
+    c[(special >= 0.07) & (special < 0.09)] = rng.choice(np.array([32766, -32766, 999, 1000, -1000, 9999, 10000, -10000, 0, 5, -5], dtype=np.int16),
+                                                         size=int(((special >= 0.07) & (special < 0.09)).sum()))
+    return c
+
+
+def _host_text(codes):
+    from grid_b200 import io as gio
+
+    tab = gio._z_table()
+    return "".join("\t".join(tab[int(v) + 32768] for v in row) + "\n" for row in codes).encode()
+
+
+@pytest.mark.parametrize("n,rw,ld", [(1, 1, 8), (3, 7, 8), (5, 2048, 2048), (4, 2049, 2056), (7, 6001, 6003), (300, 38, 40)])
+def test_device_formatter_and_parser_match_the_host_writer(n, rw, ld, eng):
+    from grid_b200._lib import call, load, ptr
+
+    rng = np.random.default_rng(n * 1000 + rw)
+    codes = _codes(rng, n, rw)
+    zq = torch.full((n, ld), 12345, dtype=torch.int16, device="cuda")
+    zq[:, :rw] = torch.from_numpy(codes).cuda()
+    st = torch.cuda.current_stream().cuda_stream
+    ws = torch.empty(load().gridb200_format_z_ws_bytes(n, rw), dtype=torch.uint8, device="cuda")
+    row_off = torch.empty(n + 1, dtype=torch.int64, device="cuda")
+    call("gridb200_format_z_measure", ptr(zq), n, rw, ld, ptr(row_off), ptr(ws), ws.numel(), st)
+    off = row_off.cpu().numpy()
+    want = _host_text(codes)
+    assert int(off[-1]) == len(want)
+    text = torch.zeros(int(off[-1]) + 64, dtype=torch.uint8, device="cuda")
+    call("gridb200_format_z_write", ptr(zq), n, rw, ld, ptr(row_off), ptr(ws), text.data_ptr() + 3, int(off[-1]), st)  # odd phase
+    got = bytes(text[3:3 + int(off[-1])].cpu().numpy())
+    assert got == want
+    assert int(text[3 + int(off[-1]):].sum()) == 0 and int(text[:3].sum()) == 0  # nothing written outside
+    # ...and back: every line gets an "id\tscale\t" prefix of a different length, as in the file
+    lines = want.split(b"\n")[:-1]
+    full = b"".join(f"S{i:0{1 + i % 5}d}\t1.{i % 100:02d}\t".encode() + ln + b"\n" for i, ln in enumerate(lines))
+    offs = np.concatenate([[0], np.cumsum([len(f"S{i:0{1 + i % 5}d}\t1.{i % 100:02d}\t") + len(ln) + 1 for i, ln in enumerate(lines)])])
+    t_text = torch.frombuffer(bytearray(full), dtype=torch.uint8).cuda()
+    t_off = torch.from_numpy(offs.astype(np.int64)).cuda()
+    back = torch.full((n, ld), -32768, dtype=torch.int16, device="cuda")
+    stats = torch.zeros(4, dtype=torch.int64, device="cuda")
+    max_line = int(np.diff(offs).max())
+    ws2 = torch.empty(load().gridb200_parse_z_ws_bytes(n, max_line), dtype=torch.uint8, device="cuda")
+    call("gridb200_parse_z_rows", ptr(t_text), ptr(t_off), n, max_line, 2, rw, ptr(back), ld, ptr(stats), ptr(ws2), ws2.numel(), st)
+    s = stats.cpu().numpy()
+    assert (s[0], s[1], s[2]) == (n * rw, 0, 0)
+    expect = codes.copy()
+    expect[expect == -32767] = 0  # "-0.00" reads back as zero
+    np.testing.assert_array_equal(back[:, :rw].cpu().numpy(), expect)
+
+
+def test_device_parser_flags_what_it_does_not_understand(eng):
+    from grid_b200._lib import call, load, ptr
+
+    good = b"A\t1.00\t0.10\tNA\tnan\t-3.25\n"
+    cases = {b"A\t1.00\t0.1\tNA\tnan\t-3.25\n": (1, 0), b"A\t1.00\t1e-1\tNA\tnan\t-3.25\n": (1, 0),
+             b"A\t1.00\t0.10\tNA\tnan\n": (0, 1), b"A\t1.00\t0.10\tNA\tnan\t-3.25\t7.00\n": (0, 1),
+             b"A\t1.00\t0.10\tNaN\tnan\t-3.25\n": (1, 0), b"A\t1.00\t500.00\tNA\tnan\t-3.25\n": (1, 0), good: (0, 0)}
+    st = torch.cuda.current_stream().cuda_stream
+    for text, (bad_tok, bad_row) in cases.items():
+        t = torch.frombuffer(bytearray(text), dtype=torch.uint8).cuda()
+        off = torch.tensor([0, len(text)], dtype=torch.int64, device="cuda")
+        zq = torch.full((1, 8), -32768, dtype=torch.int16, device="cuda")
+        stats = torch.zeros(4, dtype=torch.int64, device="cuda")
+        ws = torch.empty(load().gridb200_parse_z_ws_bytes(1, len(text)), dtype=torch.uint8, device="cuda")
+        call("gridb200_parse_z_rows", ptr(t), ptr(off), 1, len(text), 2, 4, ptr(zq), 8, ptr(stats), ptr(ws), ws.numel(), st)
+        s = stats.cpu().numpy()
+        assert (int(s[1]), int(s[2])) == (bad_tok, bad_row), text
+    assert zq[0, :4].cpu().tolist() == [10, -32768, -32768, -325]
+
+
+def test_device_text_file_round_trip_and_fallback(tmp_path, eng):
+    from grid_b200 import io as gio, textio
+
+    rng = np.random.default_rng(4)
+    n, rw = 37, 4500
+    codes = _codes(rng, n, rw)
+    ids = synth.sample_ids(n)
+    mu, ratio, raw = rng.uniform(0.5, 2, rw), rng.uniform(50, 300, rw), rng.uniform(20, 40, n)
+    ratio[3] = np.nan
+    zq = torch.from_numpy(codes).cuda()
+    old_member = textio.MEMBER_BYTES
+    textio.MEMBER_BYTES = 100_000  # several gzip members
+    try:
+        textio.write_normalized_output(tmp_path / "dev.tsv.gz", ids, zq, rw, mu, ratio, raw, threads=4)
+    finally:
+        textio.MEMBER_BYTES = old_member
+    gio.write_normalized_output(tmp_path / "host.tsv.gz", ids, codes, mu, ratio, raw)
+    assert gzip.open(tmp_path / "dev.tsv.gz", "rb").read() == gzip.open(tmp_path / "host.tsv.gz", "rb").read()
+    ids2, ratios2, zq2, scales2 = textio.read_normalized_data(tmp_path / "host.tsv.gz")
+    h_ids, h_ratios, h_zq, h_scales = gio.read_normalized_data(tmp_path / "host.tsv.gz")
+    assert ids2 == h_ids
+    np.testing.assert_array_equal(ratios2, h_ratios)
+    np.testing.assert_array_equal(scales2, h_scales)
+    np.testing.assert_array_equal(zq2[:, :rw].cpu().numpy(), h_zq)
+    # a file the strict grammar rejects (one-decimal value) goes through the host reader and still arrives
+    with gzip.open(tmp_path / "odd.tsv.gz", "wt") as f:
+        f.write("2\t3\t1.000\t1.000\t1.000\n2\t3\t100.000\t100.000\tNA\nA\t30.00\t0.5\tNA\t-1.25\nB\t31.00\t0.25\t0.00\t2.00\n")
+    ids3, _, zq3, _ = textio.read_normalized_data(tmp_path / "odd.tsv.gz")
+    assert ids3 == ["A", "B"] and zq3[:, :3].cpu().tolist() == [[50, -32768, -125], [25, 0, 200]]
