@@ -20,15 +20,115 @@ MEMBER_BYTES = 8 << 20   # uncompressed text per gzip member (rows are never spl
 BATCH_BYTES = 256 << 20  # device/pinned text buffer per formatting or parsing batch
 
 
-def _deflate_member(parts) -> bytes:
-    co = zlib.compressobj(6, zlib.DEFLATED, 31)  # wbits 31 = gzip container
-    out = [co.compress(p) for p in parts]
+GZIP_LEVEL = 3           # hand-off files are intermediates: favour speed (any level inflates to the same bytes)
+_EXTRA_ID = b"GB"        # gzip extra subfield: u32 = bytes of this whole member (header + deflate + trailer)
+_HDR_LEN = 10 + 2 + 4 + 4  # fixed header, XLEN, subfield header, subfield payload
+
+
+def _deflate_member(parts, level: int | None = None) -> bytes:
+    """One self-contained gzip member whose header says how long the member is (the idea of BGZF), so that a reader
+    can hop from member to member and inflate them in parallel.  Any gzip reader just skips the extra field."""
+    co = zlib.compressobj(GZIP_LEVEL if level is None else level, zlib.DEFLATED, -15)  # raw deflate
+    crc, size, out = 0, 0, []
+    for p in parts:
+        crc = zlib.crc32(p, crc)
+        size += len(p)
+        out.append(co.compress(p))
     out.append(co.flush())
-    return b"".join(out)
+    body = b"".join(out)
+    total = _HDR_LEN + len(body) + 8
+    head = b"\x1f\x8b\x08\x04" + b"\x00\x00\x00\x00" + b"\x00\xff" + (8).to_bytes(2, "little") \
+        + _EXTRA_ID + (4).to_bytes(2, "little") + total.to_bytes(4, "little")
+    return head + body + (crc & 0xFFFFFFFF).to_bytes(4, "little") + (size & 0xFFFFFFFF).to_bytes(4, "little")
+
+
+def _split_members(raw: bytes):
+    """[(start, end)] of the members of a file written by _deflate_member, or None if any member lacks the size field."""
+    spans, pos, n = [], 0, len(raw)
+    while pos < n:
+        if n - pos < _HDR_LEN or raw[pos:pos + 4] != b"\x1f\x8b\x08\x04" or raw[pos + 12:pos + 14] != _EXTRA_ID \
+                or raw[pos + 10:pos + 12] != b"\x08\x00":
+            return None
+        total = int.from_bytes(raw[pos + 16:pos + 20], "little")
+        if total < _HDR_LEN + 8 or pos + total > n:
+            return None
+        spans.append((pos, pos + total))
+        pos += total
+    return spans
+
+
+def _inflate_member(raw, span) -> bytes:
+    a, b = span
+    data = zlib.decompress(raw[a + _HDR_LEN:b - 8], -15)
+    if zlib.crc32(data) != int.from_bytes(raw[b - 8:b - 4], "little"):
+        raise OSError("CRC check failed in a gzip member")
+    return data
+
+
+class _MemberStream:
+    """File-like view (readline / read) of a multi-member file whose members are inflated `threads` at a time."""
+
+    def __init__(self, raw: bytes, spans, threads: int):
+        self.raw, self.spans, self.next = raw, spans, 0
+        self.pool = ThreadPoolExecutor(max_workers=max(1, int(threads)))
+        self.ahead = []
+        self.buf = b""
+        self.depth = 2 * max(1, int(threads))
+
+    def _fill(self) -> bool:
+        while self.next < len(self.spans) and len(self.ahead) < self.depth:
+            self.ahead.append(self.pool.submit(_inflate_member, self.raw, self.spans[self.next]))
+            self.next += 1
+        if not self.ahead:
+            return False
+        self.buf += self.ahead.pop(0).result()
+        return True
+
+    def readline(self) -> bytes:
+        while True:
+            nl = self.buf.find(b"\n")
+            if nl >= 0:
+                line, self.buf = self.buf[:nl + 1], self.buf[nl + 1:]
+                return line
+            if not self._fill():
+                line, self.buf = self.buf, b""
+                return line
+
+    def read(self, size: int) -> bytes:
+        parts, got = [self.buf], len(self.buf)
+        self.buf = b""
+        while got < size and (self.ahead or self.next < len(self.spans)):
+            self._fill()
+            parts.append(self.buf)
+            got += len(self.buf)
+            self.buf = b""
+        return b"".join(parts)
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.pool.shutdown(wait=False, cancel_futures=True)
+
+
+def _open_text(path, threads: int):
+    """Parallel member reader for our own files, plain streaming gzip for anybody else's (the reference's)."""
+    with open(path, "rb") as f:
+        probe = f.read(_HDR_LEN)
+        if len(probe) == _HDR_LEN and probe[:4] == b"\x1f\x8b\x08\x04" and probe[12:14] == _EXTRA_ID:
+            raw = probe + f.read()
+            spans = _split_members(raw)
+            if spans is not None:
+                return _MemberStream(raw, spans, threads)
+    return gzip.open(path, "rb")
+
+
+def _fixed3_line(values) -> str:
+    return "\t".join(["NA" if v != v else "%.3f" % v for v in np.asarray(values, dtype=np.float64).tolist()])
 
 
 def write_normalized_output(path, ids, zq, rw: int, mu_sel: np.ndarray, ratio_sel: np.ndarray, raw_means: np.ndarray,
-                            threads: int = 8) -> None:
+                            threads: int = 8, level: int | None = None) -> None:
     """Step-4 file from the DEVICE matrix zq[N, ldq] (int16 codes, torch CUDA tensor), N = len(ids) rows."""
     import torch
 
@@ -37,13 +137,12 @@ def write_normalized_output(path, ids, zq, rw: int, mu_sel: np.ndarray, ratio_se
     n = len(ids)
     assert zq.is_cuda and zq.dtype == torch.int16 and zq.shape[0] >= n
     st = torch.cuda.current_stream().cuda_stream
-    head = (f"{n}\t{rw}\t" + "\t".join(gio.fixed(v, 3) for v in mu_sel) + "\n"
-            + f"{n}\t{rw}\t" + "\t".join(gio.fixed(v, 3) for v in ratio_sel) + "\n").encode()
+    head = (f"{n}\t{rw}\t" + _fixed3_line(mu_sel) + "\n" + f"{n}\t{rw}\t" + _fixed3_line(ratio_sel) + "\n").encode()
     pool = ThreadPoolExecutor(max_workers=max(1, int(threads)))
     with open(path, "wb") as out:
         if rw == 0 or n == 0:  # nothing for the device to do: rows are "id\tscale\t\n" (join of no fields)
             body = "".join(f"{sid}\t{raw_means[i]:.2f}\t\n" for i, sid in enumerate(ids)).encode()
-            out.write(_deflate_member([head, body]))
+            out.write(_deflate_member([head, body], level))
             return
         per = int(max(1, min(65535, BATCH_BYTES // (8 * rw))))
         ws = torch.empty(load().gridb200_format_z_ws_bytes(per, rw), dtype=torch.uint8, device=zq.device)
@@ -69,12 +168,12 @@ def write_normalized_output(path, ids, zq, rw: int, mu_sel: np.ndarray, ratio_se
                 pending += [pre, view[off[i]:off[i + 1]]]
                 pending_bytes += len(pre) + int(off[i + 1] - off[i])
                 if pending_bytes >= MEMBER_BYTES:
-                    jobs.append(pool.submit(_deflate_member, pending))
+                    jobs.append(pool.submit(_deflate_member, pending, level))
                     pending, pending_bytes = [], 0
             while len(jobs) > 4 * max(1, int(threads)):  # bound the text held in flight
                 out.write(jobs.pop(0).result())
         if pending:
-            jobs.append(pool.submit(_deflate_member, pending))
+            jobs.append(pool.submit(_deflate_member, pending, level))
         for j in jobs:
             out.write(j.result())
     pool.shutdown()
@@ -84,13 +183,13 @@ class _Fallback(Exception):
     pass
 
 
-def read_normalized_data(path, device="cuda"):
+def read_normalized_data(path, device="cuda", threads: int = 8):
     """Step-4 file -> (ids, ratios[Rw] float64, zq[N, ldq] int16 DEVICE tensor, scales[N] float64).
     Files outside the writer's grammar are re-read by grid_b200.io.read_normalized_data (Python float() semantics)."""
     import torch
 
     try:
-        return _read_device(path, torch.device(device))
+        return _read_device(path, torch.device(device), threads)
     except _Fallback:
         ids, ratios, zq, scales = gio.read_normalized_data(path)
         ld = (zq.shape[1] + 7) // 8 * 8
@@ -100,14 +199,14 @@ def read_normalized_data(path, device="cuda"):
         return ids, ratios, t, scales
 
 
-def _read_device(path, dev):
+def _read_device(path, dev, threads):
     import torch
 
     from ._lib import call, load, ptr
 
     st = torch.cuda.current_stream().cuda_stream
     ids, scales = [], []
-    with gzip.open(path, "rb") as fh:
+    with _open_text(path, threads) as fh:
         h1 = fh.readline()
         h2 = fh.readline()
         try:

@@ -42,7 +42,7 @@ def find_neighbors(config, console):
     if config.get("gpu", {}).get("device_text", True):  # additive key; default = parse the cells on the GPU
         from .. import textio
 
-        ids, ratios, tzq, scales = textio.read_normalized_data(input_file, dev)
+        ids, ratios, tzq, scales = textio.read_normalized_data(input_file, dev, threads=config.get("threads", 1))
     else:
         ids, ratios, zq, scales = read_normalized_data(input_file)
         tzq = torch.from_numpy(np.ascontiguousarray(zq)).to(dev)

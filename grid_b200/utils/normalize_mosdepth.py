@@ -215,7 +215,8 @@ def normalize_mosdepth(config, console):
         from .. import textio
 
         zq_dev = res.zq if len(rows) == len(ids) else res.zq[torch.from_numpy(rows).to(res.zq.device)]
-        textio.write_normalized_output(output_path, kept_ids, zq_dev, res.rw, mu_sel, ratio_sel, raw_means, threads=threads)
+        textio.write_normalized_output(output_path, kept_ids, zq_dev, res.rw, mu_sel, ratio_sel, raw_means, threads=threads,
+                                       level=config.get("gpu", {}).get("gzip_level"))
     else:
         zq = res.zq.cpu().numpy()[rows][:, : res.rw] if res.zq is not None else np.zeros((len(rows), 0), dtype=np.int16)
         gio.write_normalized_output(output_path, kept_ids, zq, mu_sel, ratio_sel, raw_means)

@@ -103,3 +103,45 @@ def test_product_never_imports_the_oracle():
 
     for f in pathlib.Path(gio.__file__).parent.rglob("*.py"):
         assert "oracle" not in f.read_text().replace("the oracle", ""), f
+
+
+def test_gzip_members_with_size_field_interoperate(tmp_path):
+    """Files written by grid_b200.textio are ordinary gzip (any reader inflates them) whose members can also be
+    located without inflating; files from other writers fall back to streaming."""
+    import gzip
+    import random
+
+    from grid_b200 import textio as T
+
+    rnd = random.Random(3)
+    chunks = [("".join(rnd.choice("0123456789.\t-") for _ in range(rnd.randrange(1, 50000))) + "\n").encode() for _ in range(9)]
+    raw = b"".join(T._deflate_member([c[: len(c) // 2], c[len(c) // 2:]], level) for c, level in zip(chunks, [1, 3, 6, 9, None, 0, 2, 4, 5]))
+    p = tmp_path / "m.gz"
+    p.write_bytes(raw)
+    assert gzip.open(p, "rb").read() == b"".join(chunks)
+    spans = T._split_members(raw)
+    assert len(spans) == 9 and spans[0][0] == 0 and spans[-1][1] == len(raw)
+    with T._open_text(p, 3) as f:
+        assert isinstance(f, T._MemberStream)
+        assert f.readline() == chunks[0]
+        rest = b""
+        while True:
+            blk = f.read(70000)
+            if not blk:
+                break
+            rest += blk
+        assert rest == b"".join(chunks[1:])
+    # a corrupted member is caught by its CRC
+    bad = bytearray(raw)
+    bad[spans[4][0] + T._HDR_LEN + 5] ^= 0x55
+    (tmp_path / "bad.gz").write_bytes(bytes(bad))
+    with pytest.raises(Exception):
+        with T._open_text(tmp_path / "bad.gz", 2) as f:
+            while f.read(1 << 20):
+                pass
+    # somebody else's gzip: streaming reader
+    q = tmp_path / "plain.gz"
+    q.write_bytes(gzip.compress(b"a\tb\n"))
+    with T._open_text(q, 2) as f:
+        assert not isinstance(f, T._MemberStream) and f.readline() == b"a\tb\n"
+    assert T._fixed3_line([1.0, float("nan"), 2.0005, -0.0004]) == "1.000\tNA\t2.001\t-0.000"
