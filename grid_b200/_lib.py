@@ -43,6 +43,8 @@ SIGNATURES = {
     "gridb200_ingest_ws_bytes": (_sz, [_i64]),
     "gridb200_ingest_text": (C.c_int, [_vp, _i64, C.c_char_p, _i32, _i64, _i64, _vp, _i64, _i64, _i64, _vp, _vp, _vp,
                                        _sz, _vp]),
+    "gridb200_depth_pack_u16": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp]),
+    "gridb200_depth_unpack_u16": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _i64, _i64, _vp]),
     "gridb200_format_z_ws_bytes": (_sz, [_i64, _i64]),
     "gridb200_format_z_measure": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _sz, _vp]),
     "gridb200_format_z_write": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _i64, _vp]),

@@ -208,3 +208,95 @@ extern "C" int gridb200_ingest_text(const char* text, int64_t nbytes, const char
   G2_LAUNCHED();
   return 0;
 }
+
+// ---- packed host format: uint16 hundredths --------------------------------------------------------------
+// mosdepth depths are two-decimal numbers, so a cell is an integer number of hundredths; below 655.35 it fits
+// 16 bits.  The host keeps (and PCIe carries) 2 bytes per cell instead of 4; 0xFFFF marks a cell whose value is in
+// the escape list (cell index, fp32 value).  Unpacking reproduces the fp32 matrix bit for bit:
+// h / 100 correctly rounded, the same conversion k_ingest_finish applies.
+namespace g2 {
+
+__global__ void __launch_bounds__(256) k_pack_u16(const float* __restrict__ depth, int64_t n, int64_t b, int64_t ld,
+                                                  uint16_t* __restrict__ out, int64_t ldo, int64_t row0_global,
+                                                  int64_t* __restrict__ esc_cell, float* __restrict__ esc_val,
+                                                  int64_t esc_cap, unsigned long long* __restrict__ esc_count) {
+  const int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  const int64_t i = blockIdx.y;
+  if (j >= b) return;
+  const float* p = depth + i * ld + j;
+  uint16_t* o = out + i * ldo + j;
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    if (j + t >= b) break;
+    const float x = p[t];
+    const int h = depth_hundredths(x);
+    uint16_t code = (uint16_t)h;
+    if (h >= 65535 || !(x < 41943.04f)) {  // does not fit (or is beyond what depth_hundredths recovers exactly)
+      code = 0xFFFF;
+      const unsigned long long slot = atomicAdd(esc_count, 1ULL);
+      if ((int64_t)slot < esc_cap) esc_cell[slot] = (row0_global + i) * b + (j + t), esc_val[slot] = x;
+    }
+    o[t] = code;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_unpack_u16(const uint16_t* __restrict__ src, int64_t n, int64_t b, int64_t lds,
+                                                    float* __restrict__ depth, int64_t ld) {
+  const int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  const int64_t i = blockIdx.y;
+  if (j >= b) return;
+  const uint16_t* s = src + i * lds + j;
+  float* d = depth + i * ld + j;
+  if (j + 8 <= b && ((reinterpret_cast<uintptr_t>(s) & 15) == 0) && ((reinterpret_cast<uintptr_t>(d) & 15) == 0)) {
+    const uint4 v = *reinterpret_cast<const uint4*>(s);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    float f[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) f[t] = __fdiv_rn((float)((w[t >> 1] >> (16 * (t & 1))) & 0xFFFFu), 100.0f);
+    reinterpret_cast<float4*>(d)[0] = make_float4(f[0], f[1], f[2], f[3]);
+    reinterpret_cast<float4*>(d)[1] = make_float4(f[4], f[5], f[6], f[7]);
+  } else {
+    for (int t = 0; t < 8 && j + t < b; ++t) d[t] = __fdiv_rn((float)s[t], 100.0f);
+  }
+}
+
+// depth[cell / b - row0][cell % b] = value for the escape cells that fall into rows [row0, row0 + n)
+__global__ void k_patch_depth(const int64_t* __restrict__ cell, const float* __restrict__ val, int64_t count, int64_t b,
+                              int64_t row0, int64_t n, float* __restrict__ depth, int64_t ld) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= count) return;
+  const int64_t r = cell[e] / b - row0, c = cell[e] % b;
+  if (r >= 0 && r < n) depth[r * ld + c] = val[e];
+}
+
+}  // namespace g2
+
+extern "C" int gridb200_depth_pack_u16(const float* depth, int64_t n, int64_t b, int64_t ld, uint16_t* out, int64_t ldo,
+                                       int64_t row0, int64_t* esc_cell, float* esc_val, int64_t esc_cap,
+                                       int64_t* esc_count, void* stream) {
+  using namespace g2;
+  G2_REQUIRE(depth && out && esc_count && n > 0 && b > 0 && ld >= b && ldo >= b && n <= 65535, GRIDB200_EINVAL,
+             "bad argument (rows per call <= 65535)");
+  G2_REQUIRE(esc_cap == 0 || (esc_cell && esc_val), GRIDB200_EINVAL, "escape arrays missing");
+  k_pack_u16<<<dim3((unsigned)((b + 1023) / 1024), (unsigned)n), 256, 0, as_stream(stream)>>>(
+      depth, n, b, ld, out, ldo, row0, esc_cell, esc_val, esc_cap, reinterpret_cast<unsigned long long*>(esc_count));
+  G2_LAUNCHED();
+  return 0;
+}
+
+extern "C" int gridb200_depth_unpack_u16(const uint16_t* src, int64_t n, int64_t b, int64_t lds, float* depth,
+                                         int64_t ld, const int64_t* esc_cell, const float* esc_val, int64_t esc_count,
+                                         int64_t row0, void* stream) {
+  using namespace g2;
+  G2_REQUIRE(src && depth && n > 0 && b > 0 && lds >= b && ld >= b && n <= 65535, GRIDB200_EINVAL,
+             "bad argument (rows per call <= 65535)");
+  G2_REQUIRE(esc_count == 0 || (esc_cell && esc_val), GRIDB200_EINVAL, "escape arrays missing");
+  cudaStream_t st = as_stream(stream);
+  k_unpack_u16<<<dim3((unsigned)((b + 2047) / 2048), (unsigned)n), 256, 0, st>>>(src, n, b, lds, depth, ld);
+  G2_LAUNCHED();
+  if (esc_count > 0) {
+    k_patch_depth<<<(unsigned)((esc_count + 255) / 256), 256, 0, st>>>(esc_cell, esc_val, esc_count, b, row0, n, depth, ld);
+    G2_LAUNCHED();
+  }
+  return 0;
+}

@@ -223,6 +223,19 @@ GRIDB200_API int gridb200_ingest_text(const char* text, int64_t nbytes, const ch
                          int64_t bin0, int64_t b, float* depth_row, int64_t* stats,
                          void* ws, size_t ws_bytes, void* stream);
 
+/* Packed host format of the depth matrix: uint16 hundredths (0 = absent), 2 bytes per cell over PCIe instead of 4.
+ * A cell that does not fit (depth >= 655.35) holds 0xFFFF and its value travels in an escape list
+ * (esc_cell = global_row * b + bin, esc_val = the fp32 depth).  pack: device fp32 rows [row0, row0+n) -> codes;
+ * *esc_count (device, caller-zeroed, accumulates across calls) may exceed esc_cap -- then re-run with larger arrays.
+ * unpack: codes -> the fp32 matrix the other entry points take, bit-identical to ingesting the text
+ * (h / 100 correctly rounded), then escape cells of these rows are overwritten.  n <= 65535 rows per call. */
+GRIDB200_API int gridb200_depth_pack_u16(const float* depth, int64_t n, int64_t b, int64_t ld, uint16_t* out, int64_t ldo,
+                            int64_t row0, int64_t* esc_cell, float* esc_val, int64_t esc_cap, int64_t* esc_count,
+                            void* stream);
+GRIDB200_API int gridb200_depth_unpack_u16(const uint16_t* src, int64_t n, int64_t b, int64_t lds, float* depth,
+                              int64_t ld, const int64_t* esc_cell, const float* esc_val, int64_t esc_count,
+                              int64_t row0, void* stream);
+
 /* ------------------------------------------------------------------ step-4 hand-off text --- */
 
 /* The N x Rw body of the step-4 file, on the device.  Codes are the int16 hundredths gridb200_transform writes

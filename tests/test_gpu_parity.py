@@ -525,3 +525,28 @@ def test_device_text_file_round_trip_and_fallback(tmp_path, eng):
         f.write("2\t3\t1.000\t1.000\t1.000\n2\t3\t100.000\t100.000\tNA\nA\t30.00\t0.5\tNA\t-1.25\nB\t31.00\t0.25\t0.00\t2.00\n")
     ids3, _, zq3, _ = textio.read_normalized_data(tmp_path / "odd.tsv.gz")
     assert ids3 == ["A", "B"] and zq3[:, :3].cpu().tolist() == [[50, -32768, -125], [25, 0, 200]]
+
+
+def test_packed_host_format_round_trips_bit_for_bit(eng):
+    """uint16 hundredths + escape list -> the same fp32 matrix (incl. values that do not fit 16 bits, odd widths)."""
+    n, b = 300, 4099
+    depth = eng.synth_depth(11, n, b)
+    ld = depth.stride(0)
+    depth[5, 17] = 655.35      # first value that needs an escape
+    depth[5, 18] = 655.34      # last that does not
+    depth[299, 4098] = 12345.67
+    depth[0, 0] = 41943.03
+    depth[7, 9] = 50000.0      # beyond the exact-hundredths range: carried verbatim
+    want = depth.clone()
+    packed = eng.pack_depth(depth, b, chunk_rows=64)
+    assert packed.esc_cell.numel() == 4 and packed.codes.dtype == torch.uint16
+    assert sorted(packed.esc_cell.tolist()) == sorted([5 * b + 17, 299 * b + 4098, 0, 7 * b + 9])
+    out = torch.full_like(depth, -1.0)
+    eng.upload_packed(packed, out, chunk_rows=77)
+    torch.cuda.synchronize()
+    assert torch.equal(out[:, :b].view(torch.int32), want[:, :b].view(torch.int32))
+    # and a second upload into the same buffers (staging reuse) after changing the source
+    packed.codes[3, 4] = 1234
+    eng.upload_packed(packed, out, chunk_rows=77)
+    torch.cuda.synchronize()
+    assert float(out[3, 4]) == np.float32(12.34)
