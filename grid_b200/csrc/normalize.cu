@@ -123,14 +123,20 @@ __global__ void k_depth_filter(const long long* __restrict__ colsum, const int* 
 // ---------------------------------------------------------------------------------------------------------
 constexpr int kRowUnroll = 16;
 constexpr int kRowChunk = kThreads * 4 * kRowUnroll;  // 16384 bins per block
+constexpr int64_t kRowGridY = 32;                     // rows are strided over this many blocks per bin chunk
 
 __global__ void __launch_bounds__(kThreads) k_row_stats(const float* __restrict__ depth, int64_t b, int64_t ld,
                                                         const uint8_t* __restrict__ valid,
                                                         unsigned long long* __restrict__ rowsum,
-                                                        int* __restrict__ rowcnt, const int* __restrict__ skip_if) {
+                                                        int* __restrict__ rowcnt, const int* __restrict__ skip_if,
+                                                        int64_t nrows) {
   if (skip_if && skip_if[0]) return;  // the per-sample totals are being derived by k_row_fix instead
-  const int64_t row = blockIdx.y;
+  // rows are strided over gridDim.y so that the launch that finds skip_if set costs a few thousand empty blocks,
+  // not one per (chunk, row)
   const int64_t c0 = (int64_t)blockIdx.x * kRowChunk;
+  __shared__ unsigned long long ss[kThreads / 32];
+  __shared__ int sc[kThreads / 32];
+  for (int64_t row = blockIdx.y; row < nrows; row += gridDim.y) {
   const float* p = depth + row * ld;
   float4 v[kRowUnroll];
   uint32_t m[kRowUnroll];
@@ -163,8 +169,6 @@ __global__ void __launch_bounds__(kThreads) k_row_stats(const float* __restrict_
   }
   s = (unsigned long long)warp_sum((long long)s);
   c = warp_sum(c);
-  __shared__ unsigned long long ss[kThreads / 32];
-  __shared__ int sc[kThreads / 32];
   if ((threadIdx.x & 31) == 0) {
     ss[threadIdx.x >> 5] = s;
     sc[threadIdx.x >> 5] = c;
@@ -182,6 +186,8 @@ __global__ void __launch_bounds__(kThreads) k_row_stats(const float* __restrict_
       atomicAdd(&rowsum[row], ts);
       atomicAdd(&rowcnt[row], tc);
     }
+  }
+  __syncthreads();  // ss / sc are reused by the next row
   }
 }
 
@@ -729,8 +735,8 @@ extern "C" int gridb200_row_stats_fused(const float* depth, int64_t n, int64_t b
   const int64_t chunks = (b + kRowChunk - 1) / kRowChunk;
   for (int64_t r0 = 0; r0 < n; r0 += 65535) {  // gridDim.y limit
     const int64_t rows = std::min<int64_t>(65535, n - r0);
-    k_row_stats<<<dim3((unsigned)chunks, (unsigned)rows), kThreads, 0, st>>>(
-        depth + r0 * ld, b, ld, valid, reinterpret_cast<unsigned long long*>(rowsum) + r0, rowcnt + r0, flags + 1);
+    k_row_stats<<<dim3((unsigned)chunks, (unsigned)std::min<int64_t>(rows, kRowGridY)), kThreads, 0, st>>>(
+        depth + r0 * ld, b, ld, valid, reinterpret_cast<unsigned long long*>(rowsum) + r0, rowcnt + r0, flags + 1, rows);
     G2_LAUNCHED();
   }
   k_row_fix<<<(unsigned)n, kThreads, 0, st>>>(depth, ld, bad, flags, flags + 1,
@@ -760,8 +766,8 @@ extern "C" int gridb200_row_stats(const float* depth, int64_t n, int64_t b, int6
   const int64_t chunks = (b + kRowChunk - 1) / kRowChunk;
   for (int64_t r0 = 0; r0 < n; r0 += 65535) {  // gridDim.y limit
     const int64_t rows = std::min<int64_t>(65535, n - r0);
-    k_row_stats<<<dim3((unsigned)chunks, (unsigned)rows), kThreads, 0, st>>>(
-        depth + r0 * ld, b, ld, valid, reinterpret_cast<unsigned long long*>(rowsum) + r0, rowcnt + r0, nullptr);
+    k_row_stats<<<dim3((unsigned)chunks, (unsigned)std::min<int64_t>(rows, kRowGridY)), kThreads, 0, st>>>(
+        depth + r0 * ld, b, ld, valid, reinterpret_cast<unsigned long long*>(rowsum) + r0, rowcnt + r0, nullptr, rows);
     G2_LAUNCHED();
   }
   return 0;

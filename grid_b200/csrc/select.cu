@@ -82,6 +82,13 @@ __global__ void __launch_bounds__(kSelThreads) k_sel_pass(const double* __restri
   const int shift = 56 - 8 * pass;
   unsigned long long pre[3];
   for (int t = 0; t < 3; ++t) pre[t] = st->prefix[t];
+  // targets whose prefixes still agree share one histogram: alias[t] = the first target with t's prefix.  (The
+  // ratios of one cohort share sign, exponent and often several mantissa bytes, and the two median ranks agree to
+  // the last byte almost always -- counting once instead of three times is most of this kernel's time.)
+  int alias[3] = {0, 1, 2};
+  for (int t = 1; t < nt; ++t)
+    for (int u = t - 1; u >= 0; --u)
+      if (pass == 0 || (pre[u] >> (shift + 8)) == (pre[t] >> (shift + 8))) alias[t] = alias[u];
   const int64_t stride = (int64_t)gridDim.x * kSelThreads;
   const int64_t nround = ((n + stride - 1) / stride) * stride;  // keep warps converged for match_any
   for (int64_t i = (int64_t)blockIdx.x * kSelThreads + threadIdx.x; i < nround; i += stride) {
@@ -90,6 +97,7 @@ __global__ void __launch_bounds__(kSelThreads) k_sel_pass(const double* __restri
     const unsigned long long key = key_of(v);
     const unsigned digit = (unsigned)(key >> shift) & 0xffu;
     for (int t = 0; t < nt; ++t) {
+      if (alias[t] != t) continue;
       const bool hit = cand && (pass == 0 || (key >> (shift + 8)) == (pre[t] >> (shift + 8)));
       const unsigned ballot = __ballot_sync(0xffffffffu, hit);
       if (!ballot) continue;
@@ -105,8 +113,8 @@ __global__ void __launch_bounds__(kSelThreads) k_sel_pass(const double* __restri
   __syncthreads();
   unsigned* hist = hist_all + (size_t)pass * 3 * 256;
   for (int t = threadIdx.x; t < 3 * 256; t += kSelThreads) {
-    const unsigned c = (&sh[0][0])[t];
-    if (c) atomicAdd(&hist[t], c);
+    const unsigned c = sh[alias[t >> 8]][t & 255];  // an aliased target receives a copy of its leader's counts
+    if (c && (t >> 8) < nt) atomicAdd(&hist[t], c);
   }
   __threadfence();
   __syncthreads();
@@ -114,10 +122,14 @@ __global__ void __launch_bounds__(kSelThreads) k_sel_pass(const double* __restri
   __syncthreads();
   if (!s_last) return;
   __threadfence();
+  // the complete histograms, fetched by the whole block (a single thread walking 255 dependent L2 loads cost
+  // ~50 us per pass -- more than the counting itself)
+  for (int t = threadIdx.x; t < 3 * 256; t += kSelThreads) (&sh[0][0])[t] = __ldcg(&hist[t]);
+  __syncthreads();
   if (threadIdx.x < nt) {
     const int t = threadIdx.x;
     unsigned long long r = st->rank[t];
-    const volatile unsigned* h = hist + t * 256;
+    const unsigned* h = sh[t];
     int d = 0;
     for (; d < 255; ++d) {
       const unsigned c = h[d];

@@ -264,19 +264,50 @@ def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torc
     ldd = (nr + 1) // 2 * 2
     qb = max(1, min(nq_all, max_block_bytes // (8 * ldd)))
     rchunk = 8192 - k
+    world, rank = 1, 0
+    if group is not None:
+        import torch.distributed as dist
+
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
     for q0 in range(0, nq_all, qb):
         nq = min(qb, nq_all - q0)
-        dot = torch.empty((nq, ldd), dtype=torch.int64, device=dev)
+        m = -(-nq // world)  # query rows per rank after the reduce-scatter
+        dot = torch.empty((m * world, ldd), dtype=torch.int64, device=dev)
+        if m * world > nq:
+            dot[nq:].zero_()
         with _mark("gram"):
             call("gridb200_gram", zh_q.data_ptr() + q0 * 64 * 2, nq, nq_all, ptr(zh_r), nr, nr, kdim, vmax, ptr(dot), ldd,
                  0, impl, st)
-        _all_reduce(dot, group)
+        if world > 1:
+            # bin-sharded: every rank holds a partial of the whole block.  Reduce-scatter it by query rows, merge the
+            # k-best lists of MY rows only, then all-gather the (small) lists -- instead of all-reducing the block and
+            # repeating the whole merge on every rank.
+            mine = torch.empty((m, ldd), dtype=torch.int64, device=dev)
+            dist.reduce_scatter_tensor(mine, dot, group=group)
+            r_lo = min(nq, rank * m)
+            n_mine = min(nq, r_lo + m) - r_lo
+        else:
+            mine, r_lo, n_mine = dot, 0, nq
         with _mark("topk"):
             for r0 in range(0, nr, rchunk):
+                if n_mine <= 0:
+                    break
                 n_r = min(rchunk, nr - r0)
-                call("gridb200_topk_merge", dot.data_ptr() + r0 * 8, ldd, nq, n_r, norms_q.data_ptr() + q0 * 8,
-                     norms_r.data_ptr() + r0 * 8, q_gid0 + q0, r_gid0 + r0, k, best_d2.data_ptr() + q0 * k * 8,
-                     best_idx.data_ptr() + q0 * k * 4, st)
+                call("gridb200_topk_merge", mine.data_ptr() + r0 * 8, ldd, n_mine, n_r,
+                     norms_q.data_ptr() + (q0 + r_lo) * 8, norms_r.data_ptr() + r0 * 8, q_gid0 + q0 + r_lo, r_gid0 + r0, k,
+                     best_d2.data_ptr() + (q0 + r_lo) * k * 8, best_idx.data_ptr() + (q0 + r_lo) * k * 4, st)
+        if world > 1:
+            part_d2 = torch.zeros((m, k), dtype=torch.int64, device=dev)
+            part_idx = torch.zeros((m, k), dtype=torch.int32, device=dev)
+            if n_mine > 0:
+                part_d2[:n_mine] = best_d2[q0 + r_lo:q0 + r_lo + n_mine]
+                part_idx[:n_mine] = best_idx[q0 + r_lo:q0 + r_lo + n_mine]
+            all_d2 = torch.empty((m * world, k), dtype=torch.int64, device=dev)
+            all_idx = torch.empty((m * world, k), dtype=torch.int32, device=dev)
+            dist.all_gather_into_tensor(all_d2, part_d2, group=group)
+            dist.all_gather_into_tensor(all_idx, part_idx, group=group)
+            best_d2[q0:q0 + nq] = all_d2[:nq]
+            best_idx[q0:q0 + nq] = all_idx[:nq]
 
 
 def knn(zh: torch.Tensor, kdim: int, norms: torch.Tensor, k: int, vmax: int, impl: int = 0, group=None,

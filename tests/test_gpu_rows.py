@@ -24,6 +24,32 @@ def _free_port():
         return s.getsockname()[1]
 
 
+def _worker_bins(rank, world, port, seed, n, b, params, out):
+    """Bin-sharded chain: every rank holds all samples x a bin slice; Gram partials are reduce-scattered."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), NCCL_DEBUG="WARN")
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from grid_b200 import engine
+
+        h = synth.depth_hundredths(seed, n, b)
+        counts = synth.read_counts(seed, n, [42599, 1000])
+        want = O.chain_arrays(h / 100.0, counts, **params)
+        per = -(-(-(-b // world)) // 64) * 64
+        lo, hi = min(b, rank * per), min(b, (rank + 1) * per)
+        depth = engine.synth_depth(seed, n, hi - lo, 0, lo)                      # all samples, this rank's bins
+        res, idx, d2, cn = engine.run_chain(depth, hi - lo, torch.from_numpy(counts).cuda(), engine.Params(**params),
+                                            group=dist.group.WORLD)
+        np.testing.assert_array_equal(idx.cpu().numpy(), want["nbr_idx"])
+        np.testing.assert_array_equal(d2.cpu().numpy(), want["nbr_d2"])
+        np.testing.assert_allclose(cn.cpu().numpy(), want["dipcn"], rtol=DIPCN_REL)
+        out.put((rank, "ok"))
+    except Exception as exc:
+        out.put((rank, f"{type(exc).__name__}: {str(exc)[:400]}"))
+    finally:
+        dist.destroy_process_group()
+
+
 def _worker(rank, world, port, seed, n, b, params, out):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), NCCL_DEBUG="WARN")
     torch.cuda.set_device(rank)
@@ -51,11 +77,11 @@ def _worker(rank, world, port, seed, n, b, params, out):
         dist.destroy_process_group()
 
 
-def _run(world, seed, n, b, params):
+def _run(world, seed, n, b, params, worker=None):
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, seed, n, b, params, out)) for r in range(world)]
+    procs = [ctx.Process(target=worker or _worker, args=(r, world, port, seed, n, b, params, out)) for r in range(world)]
     for p in procs:
         p.start()
     res = dict(out.get(timeout=300) for _ in procs)
@@ -76,3 +102,11 @@ def test_rows_chain_ring(world):
         pytest.skip(f"needs {world} GPUs")
     # uneven shards (n % world != 0), k larger than a shard, several 256-row tiles per shard at world = 2
     _run(world, 32, 601, 4000, dict(num_neighbors=350, n_nbr=300))
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_bins_chain_reduce_scatter(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    # n not divisible by world (padded reduce-scatter rows), k > rows per rank
+    _run(world, 33, 601, 4000, dict(num_neighbors=350, n_nbr=300), worker=_worker_bins)
