@@ -408,12 +408,18 @@ __device__ __forceinline__ void copy_out_rows(const T* __restrict__ stage, T* __
     const int64_t step = kBlocked ? 4 * ld_out * 64 : 256;  // 32 chunks = 256 elements = 4 k-blocks further on
     for (int q = lane; q < nchunk; q += 32, src += 256, dst += step) {
       const int e0 = 8 * q - shift;  // first element of this chunk relative to p0
-      if (e0 >= 0 && e0 + 8 <= len) {
-        *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
-      } else {
-#pragma unroll
-        for (int e = 0; e < 8; ++e)
-          if (e0 + e >= 0 && e0 + e < len) dst[e] = src[e];
+      if (e0 >= 0 && e0 + 8 <= len) *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(src);
+    }
+    // the (at most two) ragged chunks of the row: lanes 0-7 take the elements of the first chunk, lanes 8-15 those
+    // of the last one -- one 2-byte store per lane instead of one lane walking eight guarded stores
+    if (lane < 16) {
+      const int q = lane < 8 ? 0 : nchunk - 1;
+      const int e = 8 * q - shift + (lane & 7);  // element relative to p0
+      const bool ragged = (8 * q - shift < 0) || (8 * q - shift + 8 > len);
+      if (ragged && e >= 0 && e < len && (lane < 8 || nchunk > 1)) {
+        const int64_t pe = (int64_t)p0 + e;
+        T* d = kBlocked ? out + ((pe >> 6) * ld_out + row0 + r) * 64 + (pe & 63) : out + (row0 + r) * ld_out + pe;
+        *d = stage[r * kStageRow + shift + e];
       }
     }
   }
@@ -499,7 +505,7 @@ __device__ __forceinline__ void transform_batch(const float4 (&v)[kTB], int nr, 
     const float4 x = *reinterpret_cast<const float4*>(colp + (int64_t)u * ld);
     const float vv[4] = {x.x, x.y, x.z, x.w};
     int delta = 0;
-#pragma unroll 1
+#pragma unroll
     for (int q = 0; q < 4; ++q) {
       const int h = depth_hundredths(vv[q]);
       if (h == 0 || !(f == f) || a100[q] == 0.0) continue;  // absent cell / unselected bin: nothing was kept
