@@ -34,8 +34,13 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ 
                                                       int* __restrict__ colcnt,
                                                       unsigned long long* __restrict__ rowsum_all,
                                                       int* __restrict__ rowcnt_all) {
+  // per-sample partials of this block's 1024 bins for one chunk of 512 rows: the warps add into shared memory and the
+  // block sends ONE global atomic per row and chunk (a global atomic per warp and row -- 1.5e8 of them on 3202
+  // addresses at config 2 -- was what held this pass at 0.75 of HBM speed)
+  __shared__ unsigned s_lo[kRows ? 512 : 1], s_hi[kRows ? 512 : 1];  // 64-bit sums as two words (native 32-bit atomics)
+  __shared__ int s_rc[kRows ? 512 : 1];
   const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
-  const bool live = j0 < b;  // dead threads of the last block stay for the warp collectives (they add zeros)
+  const bool live = j0 < b;  // dead threads of the last block stay for the collectives and barriers (they add zeros)
   if (!kRows && !live) return;
   const bool lane0 = (threadIdx.x & 31) == 0;
   const int64_t r0 = (int64_t)blockIdx.y * rows_per_slab;
@@ -46,6 +51,10 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ 
   const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
   for (int64_t base = r0; base < r1; base += 512) {  // uint32 partials cannot overflow within 512 rows
     const int64_t lim = (r1 < base + 512 ? r1 : base + 512);
+    if (kRows) {
+      for (int t = threadIdx.x; t < 512; t += kThreads) s_lo[t] = 0, s_hi[t] = 0, s_rc[t] = 0;
+      __syncthreads();
+    }
     unsigned ps[4] = {0, 0, 0, 0};
     int64_t i = base;
     for (; i + 8 <= lim; i += 8) {
@@ -64,8 +73,8 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ 
           const unsigned rs = __reduce_add_sync(0xffffffffu, (unsigned)(h0 + h1) + (unsigned)(h2 + h3));
           const int rc = __reduce_add_sync(0xffffffffu, (k0 + k1) + (k2 + k3));
           if (lane0 && rc) {
-            atomicAdd(&rowsum_all[i + u], (unsigned long long)rs);
-            atomicAdd(&rowcnt_all[i + u], rc);
+            if (atomicAdd(&s_lo[i + u - base], rs) + rs < rs) atomicAdd(&s_hi[i + u - base], 1u);  // carry
+            atomicAdd(&s_rc[i + u - base], rc);
           }
         }
       }
@@ -82,13 +91,23 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ 
         const unsigned rs = __reduce_add_sync(0xffffffffu, (unsigned)(h0 + h1) + (unsigned)(h2 + h3));
         const int rc = __reduce_add_sync(0xffffffffu, (k0 + k1) + (k2 + k3));
         if (lane0 && rc) {
-          atomicAdd(&rowsum_all[i], (unsigned long long)rs);
-          atomicAdd(&rowcnt_all[i], rc);
+          if (atomicAdd(&s_lo[i - base], rs) + rs < rs) atomicAdd(&s_hi[i - base], 1u);  // carry
+          atomicAdd(&s_rc[i - base], rc);
         }
       }
     }
 #pragma unroll
     for (int q = 0; q < 4; ++q) s[q] += ps[q];
+    if (kRows) {
+      __syncthreads();
+      for (int t = threadIdx.x; t < (int)(lim - base); t += kThreads) {
+        if (s_rc[t]) {
+          atomicAdd(&rowsum_all[base + t], ((unsigned long long)s_hi[t] << 32) | s_lo[t]);
+          atomicAdd(&rowcnt_all[base + t], s_rc[t]);
+        }
+      }
+      __syncthreads();
+    }
   }
   if (!live) return;
 #pragma unroll
