@@ -30,7 +30,13 @@ def compute_diploid_genotypes(config, console) -> None:
 
     from .. import engine
 
+    from .. import handoff
+
     reads = gio.load_read_counts(read_counts_file)
+    cached = handoff.take(neighbors_file) if handoff.enabled(config) else None
+    if cached is not None:  # step 5 of this process wrote that very file: ids, %.2f scales and index lists as arrays
+        _from_arrays(cached["ids"], cached["scales"], cached["idx"], reads, n_nbr, output_file, console)
+        return
     ids, scales, lists = load_neighbors(neighbors_file)
     # universe of samples = file rows plus any neighbour id that only appears inside a list
     pos = {}
@@ -82,5 +88,39 @@ def compute_diploid_genotypes(config, console) -> None:
     if missing:
         log(console, f"Warning: {len(missing)} neighbor IDs not found in read counts "
                      f"(showing up to 5: {list(missing)[:5]})", style="warning")
+    gio.write_dipcn(output_file, rows)
+    log(console, f"Saved {len(rows)} samples → {output_file}", style="success")
+
+
+def _from_arrays(ids, scales, idx, reads, n_nbr, output_file, console) -> None:
+    """Step 6 when the neighbour lists are already index arrays (unique ids, every neighbour is a row of the file)."""
+    import torch
+
+    from .. import engine
+
+    n = len(ids)
+    counts = np.zeros((n, 1), dtype=np.int32)
+    has = np.zeros(n, dtype=np.uint8)
+    pos = {sid: i for i, sid in enumerate(ids)}
+    for sid, v in reads.items():
+        i = pos.get(sid)
+        if i is not None:
+            if v != int(v) or not (0 <= v < 2**31):
+                raise ValueError(f"read count of {sid} is not a non-negative 32-bit integer: {v}")
+            counts[i, 0] = int(v)
+            has[i] = 1
+    with progress_bar(console, total=n, description="Computing dipCN...") as (progress, task):
+        dev = torch.device("cuda")
+        t_idx = idx if isinstance(idx, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(idx))
+        out = engine.dipcn(torch.from_numpy(counts).to(dev), torch.from_numpy(has).to(dev),
+                           torch.from_numpy(np.asarray(scales, dtype=np.float64)).to(dev), t_idx.to(dev).contiguous(),
+                           n_nbr).cpu().numpy()[:, 0]
+        progress.advance(task, n)
+    rows = [(sid, float(out[i])) for i, sid in enumerate(ids) if not np.isnan(out[i])]
+    missing_idx = np.unique(idx[idx >= 0]) if not isinstance(idx, torch.Tensor) else torch.unique(idx[idx >= 0]).cpu().numpy()
+    missing = [ids[j] for j in missing_idx.tolist() if not has[j]]
+    if missing:
+        log(console, f"Warning: {len(missing)} neighbor IDs not found in read counts "
+                     f"(showing up to 5: {missing[:5]})", style="warning")
     gio.write_dipcn(output_file, rows)
     log(console, f"Saved {len(rows)} samples → {output_file}", style="success")

@@ -39,7 +39,12 @@ def find_neighbors(config, console):
     from .._lib import call, ptr
 
     dev = torch.device("cuda")
-    if config.get("gpu", {}).get("device_text", True):  # additive key; default = parse the cells on the GPU
+    from .. import handoff
+
+    cached = handoff.take(input_file) if handoff.enabled(config) else None
+    if cached is not None:  # this process wrote that very file a moment ago: the arrays are still on the GPU
+        ids, ratios, tzq, scales = cached["ids"], cached["ratios"], cached["zq"], cached["scales"]
+    elif config.get("gpu", {}).get("device_text", True):  # additive key; default = parse the cells on the GPU
         from .. import textio
 
         ids, ratios, tzq, scales = textio.read_normalized_data(input_file, dev, threads=config.get("threads", 1))
@@ -74,4 +79,7 @@ def find_neighbors(config, console):
             idx, d2 = tidx.cpu().numpy(), td2.cpu().numpy()
         progress.advance(task, n)
     save_neighbors(output_file, ids, scales, idx, d2, r_use)
+    if handoff.enabled(config) and len(set(ids)) == len(ids) and idx.shape[1] > 0:
+        handoff.put(output_file, ids=list(ids), scales=np.array([float("%.2f" % v) for v in np.asarray(scales).tolist()]),
+                    idx=idx)
     log(console, f"Saved neighbors to {output_file}", style="success")

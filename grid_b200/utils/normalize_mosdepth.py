@@ -220,6 +220,14 @@ def normalize_mosdepth(config, console):
     else:
         zq = res.zq.cpu().numpy()[rows][:, : res.rw] if res.zq is not None else np.zeros((len(rows), 0), dtype=np.int16)
         gio.write_normalized_output(output_path, kept_ids, zq, mu_sel, ratio_sel, raw_means)
+    from .. import handoff
+
+    if handoff.enabled(config) and res.zq is not None and len(rows) == len(ids):
+        # what read_normalized_data would hand step 5: ids, the %.3f ratios, the codes ("-0.00" reads as 0), %.2f scales
+        res.zq.masked_fill_(res.zq == gio.ZQ_NEG_ZERO, 0)
+        handoff.put(output_path, ids=kept_ids, zq=res.zq, rw=res.rw,
+                    ratios=np.array([float("nan") if v != v else float("%.3f" % v) for v in ratio_sel.tolist()]),
+                    scales=np.array([float("%.2f" % v) for v in raw_means.tolist()]))
     log(console, f"Mosdepth normalization complete. Results written to {output_path}", style="success")
 
     if remove_intermediate:  # mosdepth.remove_intermediate_files(dir, console, include_region_bed_gz=True), mosdepth.py:300-326

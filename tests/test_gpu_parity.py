@@ -42,10 +42,22 @@ def _run_steps(cfg):
     return od / "norm.tsv.gz", od / "nbrs.zMax2.0.tsv.gz", od / "dipcn.tsv"
 
 
+@pytest.mark.parametrize("handoff", [True, False])
 @pytest.mark.parametrize("case", sorted(CASES))
-def test_file_chain_matches_reference_golden(case, tmp_path, golden, eng):
-    """BASELINE config 1 (N=100, LPA window) and the masked/truncated edge case, through the three step functions."""
-    norm, nbrs, dip = _run_steps(CASES[case](tmp_path))
+def test_file_chain_matches_reference_golden(case, handoff, tmp_path, golden, eng, monkeypatch):
+    """BASELINE config 1 (N=100, LPA window) and the masked/truncated edge case, through the three step functions --
+    once with the in-process device hand-off between the steps, once with every step parsing the previous file."""
+    from grid_b200 import handoff as H, io as gio, textio
+
+    cfg = CASES[case](tmp_path)
+    cfg["gpu"] = {"device_handoff": handoff}
+    H.clear()
+    if handoff:  # prove the files are NOT parsed again: both readers are out of order
+        def boom(*a, **k):
+            raise AssertionError("a hand-off file was parsed although this process had just written it")
+        monkeypatch.setattr(textio, "read_normalized_data", boom)
+        monkeypatch.setattr("grid_b200.utils.compute_dipcn.load_neighbors", boom)
+    norm, nbrs, dip = _run_steps(cfg)
     assert_norm_files_equal(norm, golden / case / "norm.tsv")
     assert_neighbor_files_equal(nbrs, golden / case / "nbrs.zMax2.0.tsv")
     assert_dipcn_files_equal(dip, golden / case / "dipcn.tsv", rel=DIPCN_REL)
@@ -550,3 +562,25 @@ def test_packed_host_format_round_trips_bit_for_bit(eng):
     eng.upload_packed(packed, out, chunk_rows=77)
     torch.cuda.synchronize()
     assert float(out[3, 4]) == np.float32(12.34)
+
+
+def test_handoff_is_dropped_when_the_file_changes(tmp_path, eng):
+    """A step-4 file rewritten by somebody else (here: the oracle) between the steps must be parsed, not trusted."""
+    from grid_b200 import handoff as H
+    from grid_b200.utils.find_neighbors import find_neighbors
+    from grid_b200.utils.normalize_mosdepth import normalize_mosdepth
+
+    cfg = synth.write_cohort_files(tmp_path, 5, 30, 90)
+    H.clear()
+    normalize_mosdepth(cfg, None)
+    norm = Path(cfg["output_dir"]) / "norm.tsv.gz"
+    assert H._CACHE, "step 4 should have left a hand-off entry"
+    # another cohort's step-4 output lands on the same path
+    cfg2 = synth.write_cohort_files(tmp_path / "other", 6, 30, 90)
+    O.normalize_mosdepth(cfg2)
+    norm.write_bytes((Path(cfg2["output_dir"]) / "norm.tsv.gz").read_bytes())
+    find_neighbors(cfg, None)
+    got = gzip.open(Path(cfg["output_dir"]) / "nbrs.zMax2.0.tsv.gz", "rt").read()
+    O.find_neighbors(cfg2)
+    (tmp_path / "got.tsv").write_text(got)
+    assert_neighbor_files_equal(tmp_path / "got.tsv", Path(cfg2["output_dir"]) / "nbrs.zMax2.0.tsv.gz")

@@ -145,3 +145,30 @@ def test_gzip_members_with_size_field_interoperate(tmp_path):
     with T._open_text(q, 2) as f:
         assert not isinstance(f, T._MemberStream) and f.readline() == b"a\tb\n"
     assert T._fixed3_line([1.0, float("nan"), 2.0005, -0.0004]) == "1.000\tNA\t2.001\t-0.000"
+
+
+def test_handoff_entries_are_tied_to_the_file(tmp_path):
+    import os
+    import time
+
+    from grid_b200 import handoff as H
+
+    H.clear()
+    p = tmp_path / "a.gz"
+    p.write_bytes(b"one")
+    H.put(p, x=1)
+    assert H.take(p) == {"x": 1} and H.take(p) is None          # consumed
+    H.put(p, x=2)
+    time.sleep(0.01)
+    p.write_bytes(b"two")                                        # same size, new mtime
+    os.utime(p, ns=(time.time_ns(), time.time_ns()))
+    assert H.take(p) is None
+    H.put(p, x=3)
+    p.unlink()
+    assert H.take(p) is None
+    q = tmp_path / "b.gz"
+    q.write_bytes(b"q")
+    (tmp_path / "link.gz").symlink_to(q)
+    H.put(tmp_path / "link.gz", x=4)
+    assert H.take(q) == {"x": 4}                                 # keyed by real path
+    assert H.enabled({}) and H.enabled({"gpu": None}) and not H.enabled({"gpu": {"device_handoff": False}})
