@@ -173,3 +173,64 @@ def write_cohort_files(root, seed: int, n: int, r: int, window=None, region_name
         "compute_haploid_genotypes": {"run": False},
         "index": {"run": False},
     }
+
+
+# ---- step 7 inputs (hi_inference): a dipCN table plus IBS (computeIBSpbwt) or IBD (iLASH) haplotype neighbours ----
+def write_hi_inputs(root, seed: int, n: int, method: str = "ibs", weighted: bool = False, n_iters: int = 100,
+                    max_neighbors: int = 10, min_neighbors: int = 1) -> dict:
+    """Synthetic step-7 cohort under `root`; returns the config.  Deliberately untidy: haplotypes with no neighbours or
+    more than max_neighbors, ids missing from the dipCN table, malformed rows, self-neighbours, duplicate edges."""
+    import gzip
+    from pathlib import Path
+
+    root = Path(root)
+    out = root / "out"
+    out.mkdir(parents=True, exist_ok=True)
+    rng = np.random.default_rng(seed)
+    ids = sample_ids(n)
+    irr = np.round(rng.normal(20.0, 4.0, n).clip(2.0, None), 6)
+    with open(out / "dipcn.tsv", "w") as fh:
+        fh.write("Sample\tNorm_Reads\n")
+        for sid, v in zip(ids, irr):
+            fh.write(f"{sid}\t{float(v)!r}\n")
+    cfg = {"output_dir": str(out), "output_file_type": "tsv", "start_bp": 160_605_062, "end_bp": 160_647_661,
+           "compute_diploid_genotypes": {"output_file_prefix": "dipcn"},
+           "compute_haploid_genotypes": {"output_file_prefix": "hap", "method": method, "n_iters": n_iters,
+                                         "max_neighbors": max_neighbors, "min_neighbors": min_neighbors}}
+    hc = cfg["compute_haploid_genotypes"]
+    if method == "ibs":
+        path = root / "ibs.txt.gz"
+        with gzip.open(path, "wt") as fh:
+            fh.write("ID\thap\tnbrInd\tcMlen\tcMedge\tIDnbr\thapNbr\n")
+            for i in range(n):
+                for h in (1, 2):
+                    cnt = int(rng.integers(0, max_neighbors + 5)) if rng.random() > 0.06 else 0
+                    for t in range(cnt):
+                        j = int(rng.integers(0, n))
+                        nid = ids[j] if rng.random() > 0.03 else f"X{j:07d}"
+                        hn = int(rng.integers(1, 3)) if rng.random() > 0.02 else 3
+                        fh.write(f"{ids[i]}\t{h}\t{t}\t{rng.uniform(0.5, 9):.3f}\t{rng.uniform(0, 1):.3f}\t{nid}\t{hn}\n")
+                if rng.random() < 0.02:
+                    fh.write(f"{ids[i]}\t1\tbroken\n\n")
+        hc["ibs_output"] = str(path)
+    else:
+        path = root / "ilash.match.gz"
+        lo, hi = cfg["start_bp"], cfg["end_bp"]
+        with gzip.open(path, "wt") as fh:
+            for _ in range(n * max_neighbors):
+                i, j = int(rng.integers(0, n)), int(rng.integers(0, n))
+                f1 = ids[i] if rng.random() > 0.02 else f"X{i:07d}"
+                h1, h2 = int(rng.integers(0, 2)), int(rng.integers(0, 2))
+                centre = int(rng.integers(lo - 6_000_000, hi + 6_000_000))
+                half = int(rng.integers(50_000, 3_000_000))
+                length = float(np.round(rng.uniform(0.2, 6.0), 2 if rng.random() > 0.3 else 1))  # ties in length too
+                match = float(np.round(rng.uniform(0.6, 1.0), 3))
+                sep = "\t" if rng.random() > 0.1 else " "
+                row = [f1, f"{f1}_{h1}", ids[j], f"{ids[j]}_{h2}", "6", centre - half, centre + half, centre - half + 7,
+                       centre + half - 7, length, match]
+                fh.write(sep.join(str(x) for x in row) + "\n")
+                if rng.random() < 0.01:
+                    fh.write("short\trow\n")
+        hc["ibd_output"] = str(path)
+        hc["weighted"] = weighted
+    return cfg

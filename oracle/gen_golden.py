@@ -14,6 +14,7 @@ what is committed is what the REFERENCE produced:
                   find_neighbors_sklearn outputs on in-memory arrays (incl. NaN cells)
   exon.npz        compute_diploid_cn_for_exon on a 40-sample cohort with zero counts, samples without counts and
                   non-positive scales, all four exon types (python oracle/gen_golden.py exon regenerates only this)
+  hi/<case>.tsv   step 7 (hi_inference) outputs for IBS, IBD and weighted IBD neighbour files (gen_golden.py hi)
   manifest.json   shapes, seeds, sha256 of every generated input file
 """
 
@@ -162,10 +163,29 @@ def exon_case():
     np.savez_compressed(GOLD / "exon.npz", raw=raw, has=has, scales=scales, idx=idx, **res)
 
 
+from gen_golden_cases import HI_CASES  # noqa: E402
+
+
+def hi_case():
+    """Step 7 through the reference's hi_inference(config, console): tests/golden/hi/<case>.tsv (inputs are regenerated
+    from grid_b200.synth.write_hi_inputs at test time)."""
+    from grid.utils import hi_inference as ref_hi
+
+    (GOLD / "hi").mkdir(parents=True, exist_ok=True)
+    for name, kw in HI_CASES.items():
+        with tempfile.TemporaryDirectory() as tmp:
+            cfg = synth.write_hi_inputs(tmp, **kw)
+            ref_hi.hi_inference(cfg, None)
+            shutil.copy(Path(cfg["output_dir"]) / "hap.tsv", GOLD / "hi" / f"{name}.tsv")
+
+
 def main():
     GOLD.mkdir(parents=True, exist_ok=True)
     if sys.argv[1:] == ["exon"]:
         exon_case()
+        return
+    if sys.argv[1:] == ["hi"]:
+        hi_case()
         return
     manifest = {"reference": "caterer-z-t/GRiD @ /root/reference", "sklearn": __import__("sklearn").__version__,
                 "numpy": np.__version__}
@@ -173,6 +193,7 @@ def main():
     file_case("masked", cfg_masked, manifest)
     array_case(manifest)
     exon_case()
+    hi_case()
     (GOLD / "manifest.json").write_text(json.dumps(manifest, indent=1, sort_keys=True) + "\n")
     print("golden written to", GOLD)
 
