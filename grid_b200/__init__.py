@@ -7,11 +7,12 @@ STEP_TARGETS = {
     "grid.utils.normalize_mosdepth": ("normalize_mosdepth", "grid_b200.utils.normalize_mosdepth"),
     "grid.utils.find_neighbors": ("find_neighbors", "grid_b200.utils.find_neighbors"),
     "grid.utils.compute_dipcn": ("compute_diploid_genotypes", "grid_b200.utils.compute_dipcn"),
+    "grid.utils.hi_inference": ("hi_inference", "grid_b200.utils.hi_inference"),  # step 7, the path's consumer
 }
 
 
 def install() -> None:
-    """Rebind the three step functions on the reference's modules so `grid wgs config.yaml` runs them on the GPU.
+    """Rebind the step functions on the reference's modules so `grid wgs config.yaml` runs them on the GPU.
 
     grid/pipeline.py:66-93 imports each step lazily (`from .utils.X import f`) at call time, so replacing the
     attribute on the already-imported module is enough -- the mechanism the reference's own tests use to patch

@@ -264,6 +264,25 @@ GRIDB200_API int gridb200_parse_z_rows(const char* text, const int64_t* line_off
                           int32_t skip_fields, int64_t rw, int16_t* zq, int64_t ldq, int64_t* stats,
                           void* ws, size_t ws_bytes, void* stream);
 
+/* ------------------------------------------------------------------ step 7: hi_inference --- */
+
+/* Iterative haplotype phasing of hi_inference.py:179-233, in the reference's in-place (Gauss-Seidel) order.
+ * Haplotype h of sample i is index 2i+h.  Neighbours in CSR form: entries nbr_ptr[x] .. nbr_ptr[x+1] of nbr_hap
+ * (haplotype indices) / nbr_w (weights) belong to haplotype x, in the reference's list order.
+ * hap[2n] in/out: NaN for samples that do not take part, IRR/2 for the others on entry.
+ * order / level_ptr_host: the level schedule -- order[level_ptr[l] .. level_ptr[l+1]) are the samples of level l, where
+ *   level(i) = 1 + max level over neighbour samples j < i that take part (0 if none); level_ptr_host is a HOST
+ *   array of n_levels+1 entries (the call launches one kernel per level and sweep).
+ * old_ws: 2n doubles of device scratch.  Results equal the reference's doubles bit for bit. */
+GRIDB200_API int gridb200_hi_phase(const double* irr, int64_t n, const int64_t* nbr_ptr, const int32_t* nbr_hap,
+                      const double* nbr_w, const int32_t* order, const int64_t* level_ptr_host, int32_t n_levels,
+                      int32_t n_iters, double* hap, double* old_ws, void* stream);
+
+/* imp[2i+h] = weighted mean of the phased neighbours of haplotype 2i+h after the last sweep, mean_irr/2 when it
+ * has none (hi_inference.py:236-256). */
+GRIDB200_API int gridb200_hi_impute(const int64_t* nbr_ptr, const int32_t* nbr_hap, const double* nbr_w,
+                       const double* hap, int64_t n, double mean_irr, double* imp, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -73,7 +73,7 @@ def test_install_rebinds_reference_steps(monkeypatch):
     utils = types.ModuleType("grid.utils")
     mods = {"grid": pkg, "grid.utils": utils}
     for name, fn in (("normalize_mosdepth", "normalize_mosdepth"), ("find_neighbors", "find_neighbors"),
-                     ("compute_dipcn", "compute_diploid_genotypes")):
+                     ("compute_dipcn", "compute_diploid_genotypes"), ("hi_inference", "hi_inference")):
         m = types.ModuleType(f"grid.utils.{name}")
         setattr(m, fn, lambda config, console: "reference")
         setattr(utils, name, m)
@@ -83,8 +83,9 @@ def test_install_rebinds_reference_steps(monkeypatch):
     import grid_b200
 
     grid_b200.install()
-    from grid_b200.utils import compute_dipcn, find_neighbors, normalize_mosdepth
+    from grid_b200.utils import compute_dipcn, find_neighbors, hi_inference, normalize_mosdepth
 
+    assert mods["grid.utils.hi_inference"].hi_inference is hi_inference.hi_inference
     assert mods["grid.utils.normalize_mosdepth"].normalize_mosdepth is normalize_mosdepth.normalize_mosdepth
     assert mods["grid.utils.find_neighbors"].find_neighbors is find_neighbors.find_neighbors
     assert mods["grid.utils.compute_dipcn"].compute_diploid_genotypes is compute_dipcn.compute_diploid_genotypes
