@@ -69,6 +69,9 @@ def find_neighbors(config, console):
             call("gridb200_knn_col_filter", ptr(t_ratio), ptr(sel), rw, float(frac_r), float(sigma2_max), ptr(keep),
                  ptr(info), ptr(info2), ptr(ws), ws.numel(), torch.cuda.current_stream().cuda_stream)
             r_use = int(info2[0].item())
+            if r_use == 0:  # the reference hands sklearn an N x 0 matrix here, which raises (find_neighbors.py:207-213)
+                raise ValueError(f"Found array with 0 feature(s) (shape=({n}, 0)) while a minimum of 1 is required "
+                                 "by NearestNeighbors.")
             if not np.isfinite(ratios).any():
                 log(console, "Warning: no finite variance ratios — keeping all regions", style="warning")
             extreme = int(np.sum(ratios > sigma2_max))

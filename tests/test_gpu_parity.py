@@ -584,3 +584,50 @@ def test_handoff_is_dropped_when_the_file_changes(tmp_path, eng):
     O.find_neighbors(cfg2)
     (tmp_path / "got.tsv").write_text(got)
     assert_neighbor_files_equal(tmp_path / "got.tsv", Path(cfg2["output_dir"]) / "nbrs.zMax2.0.tsv.gz")
+
+
+def _tiny_step4(path, ids, scales, ratios, rows):
+    """A step-4 file written by hand (what any writer, including the reference, may produce)."""
+    n, rw = len(ids), len(ratios)
+    fmt3 = lambda v: "NA" if v != v else f"{v:.3f}"  # noqa: E731
+    with gzip.open(path, "wt") as f:
+        f.write(f"{n}\t{rw}\t" + "\t".join("1.000" for _ in ratios) + "\n")
+        f.write(f"{n}\t{rw}\t" + "\t".join(fmt3(v) for v in ratios) + "\n")
+        for sid, sc, row in zip(ids, scales, rows):
+            f.write(f"{sid}\t{sc:.2f}\t" + "\t".join("NA" if v != v else f"{v:.2f}" for v in row) + "\n")
+
+
+@pytest.mark.parametrize("name,ids,ratios,rows,knobs", [
+    ("squared_distance_3_4_5", ["A", "B"], [100.0, 100.0], [[0.0, 0.0], [3.0, 4.0]], {}),   # test_neighbors.py:69-74
+    ("single_sample", ["A"], [100.0, 120.0], [[0.5, -0.5]], {}),
+    ("k_beyond_n", ["A", "B", "C"], [100.0, 90.0, 80.0], [[0.1, 0.2, 0.3], [0.1, 0.2, 0.4], [1.5, -1.5, 0.0]], {"num_neighbors": 500}),
+    ("na_cells_and_clip", ["A", "B", "C"], [100.0, 90.0], [[float("nan"), 5.0], [-7.25, float("nan")], [0.0, 1.99]], {}),
+    ("all_ratios_nan_keeps_all", ["A", "B", "C"], [float("nan")] * 3, [[0.1, 0.2, 0.3], [0.3, 0.2, 0.1], [0.0, 0.0, 0.0]], {}),
+    ("sigma2_max_drops_every_region", ["A", "B", "C"], [2000.0, 3000.0], [[0.1, 0.2], [0.3, 0.2], [0.0, 0.1]], {"sigma2_max": 1000.0}),
+    ("frac_r_half", ["A", "B", "C", "D"], [10.0, 40.0, 30.0, 20.0], [[0.1, 1.0, 0.3, -0.4], [0.3, -1.0, 0.1, 0.4], [0.0, 0.5, 0.0, 0.0], [1.0, 1.0, 1.0, 1.0]], {"frac_r": 0.5}),
+    ("exact_ties", ["A", "B", "C", "D"], [100.0], [[0.0], [1.0], [-1.0], [1.0]], {}),
+])
+def test_find_neighbors_edge_cases_match_the_oracle(name, ids, ratios, rows, knobs, tmp_path, eng):
+    """Hand-written step-4 files through our step 5 and through the oracle's: the neighbour files must agree
+    (helpers.assert_neighbor_files_equal allows reordering only inside exact distance ties)."""
+    from grid_b200.utils.find_neighbors import find_neighbors
+
+    od = tmp_path / "out"
+    od.mkdir()
+    cfg = {"output_dir": str(od), "output_file_type": "tsv",
+           "mosdepth": {"normalize": {"output_file_prefix": "norm"},
+                        "neighbors": {"output_file_prefix": "nbrs", "zmax": 2.0, "num_neighbors": 2, **knobs}}}
+    _tiny_step4(od / "norm.tsv.gz", ids, [30.0 + i for i in range(len(ids))], ratios, rows)
+    if name == "sigma2_max_drops_every_region":  # N x 0 matrix: scikit-learn refuses it, and so do we
+        with pytest.raises(ValueError, match="0 feature"):
+            O.find_neighbors(cfg)
+        with pytest.raises(ValueError, match="0 feature"):
+            find_neighbors(cfg, None)
+        return
+    find_neighbors(cfg, None)
+    mine = od / "mine.tsv"
+    mine.write_text(gzip.open(od / "nbrs.zMax2.0.tsv.gz", "rt").read())
+    O.find_neighbors(cfg)
+    assert_neighbor_files_equal(mine, od / "nbrs.zMax2.0.tsv.gz")
+    if name == "squared_distance_3_4_5":  # clipped at zmax = 2: (0,0)-(2,2) -> 8 / (2 * 2 regions) = 2.00
+        assert mine.read_text().splitlines()[0].split("\t")[4] == "2.00"
