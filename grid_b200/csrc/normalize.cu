@@ -286,6 +286,99 @@ __global__ void k_row_scales(const long long* __restrict__ rowsum, const int* __
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// K3'': per-sample means that sit EXACTLY on a %.2f tie.
+//
+// The reference prints np.nanmean(row) with %.2f.  k_row_scales computes the mean from exact integer sums, which is
+// the correctly rounded value; numpy's is a pairwise floating-point sum and may be an ulp or two off.  The two print
+// the same two decimals unless the exact mean is k + 0.005 -- then the ulp decides, and that is not rare for small
+// windows (probability 1/count for an even count of bins: percent level at BASELINE config 1).  The distance of an
+// exact mean to the nearest tie is 0 or at least 1/(2*count), far beyond the summation noise, so ONLY exact ties
+// need numpy's own value: for those rows one thread replays numpy's pairwise summation (loops_utils.h.src,
+// DOUBLE_pairwise_sum: blocks of <= 128 with 8 strided accumulators, halves split at a multiple of 8) over the
+// row's valid bins in column order, NaN cells as 0.0, exactly as nansum does.
+// ---------------------------------------------------------------------------------------------------------
+struct RowCursor {
+  const float* row;
+  const uint8_t* valid;
+  int64_t j;
+  __device__ double next() {  // value of the next valid bin: depth as the double the reference parsed, absent -> 0.0
+    while (!valid[j]) ++j;
+    const int h = depth_hundredths(row[j++]);
+    return h ? __ddiv_rn((double)h, 100.0) : 0.0;
+  }
+};
+
+__device__ double numpy_pairwise_leaf(RowCursor& c, int64_t n) {  // n <= 128
+  if (n < 8) {
+    double res = 0.0;
+    for (int64_t i = 0; i < n; ++i) res = __dadd_rn(res, c.next());
+    return res;
+  }
+  double r[8];
+  for (int k = 0; k < 8; ++k) r[k] = c.next();
+  int64_t i = 8;
+  for (; i < n - (n % 8); i += 8)
+    for (int k = 0; k < 8; ++k) r[k] = __dadd_rn(r[k], c.next());
+  double res = __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])),
+                         __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
+  for (; i < n; ++i) res = __dadd_rn(res, c.next());
+  return res;
+}
+
+// sum(n) = n <= 128 ? leaf(n) : sum(n2) + sum(n - n2), n2 = n/2 rounded down to a multiple of 8; the elements are
+// consumed strictly in order, so the recursion runs over an explicit stack (depth <= log2(n))
+__device__ double numpy_pairwise_sum(RowCursor& c, int64_t n) {
+  struct Frame {
+    int64_t n;
+    double left;
+    int phase;
+  };
+  Frame st[40];
+  int sp = 0;
+  st[0] = Frame{n, 0.0, 0};
+  double ret = 0.0;
+  while (sp >= 0) {
+    Frame& f = st[sp];
+    if (f.n <= 128) {
+      ret = numpy_pairwise_leaf(c, f.n);
+      --sp;
+      continue;
+    }
+    int64_t n2 = f.n / 2;
+    n2 -= n2 % 8;
+    if (f.phase == 0) {
+      f.phase = 1;
+      st[++sp] = Frame{n2, 0.0, 0};
+    } else if (f.phase == 1) {
+      f.left = ret;
+      f.phase = 2;
+      const int64_t rest = f.n - n2;
+      st[++sp] = Frame{rest, 0.0, 0};
+    } else {
+      ret = __dadd_rn(f.left, ret);
+      --sp;
+    }
+  }
+  return ret;
+}
+
+__global__ void k_row_mean_ties(const float* __restrict__ depth, int64_t n, int64_t b, int64_t ld,
+                                const uint8_t* __restrict__ valid, const long long* __restrict__ rowsum,
+                                const int* __restrict__ rowcnt, double* __restrict__ raw_mean,
+                                double* __restrict__ scale_q) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const long long cnt = rowcnt[i], s = rowsum[i];
+  if (cnt <= 0 || s <= 0 || (2 * s) % (2 * cnt) != cnt) return;  // mean in hundredths = s / cnt is not k + 1/2
+  int64_t nvalid = 0;
+  for (int64_t j = 0; j < b; ++j) nvalid += valid[j] != 0;
+  RowCursor c{depth + i * ld, valid, 0};
+  const double m = __ddiv_rn(__dadd_rn(0.0, numpy_pairwise_sum(c, nvalid)), (double)cnt);
+  if (raw_mean) raw_mean[i] = m;
+  if (scale_q) scale_q[i] = printf_round(m, 100.0) / 100.0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // K4: sd[j] = sum_i (y_ij - 1), sd2[j] = sum_i (y_ij - 1)^2 over present cells (shifted-data variance).
 // Deterministic: with several row slabs each slab writes its own partial, reduced in slab order afterwards.
 // ---------------------------------------------------------------------------------------------------------
@@ -803,6 +896,17 @@ extern "C" int gridb200_row_scales(const int64_t* rowsum, const int32_t* rowcnt,
   G2_REQUIRE(rowsum && rowcnt && n > 0, GRIDB200_EINVAL, "bad argument");
   k_row_scales<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(
       reinterpret_cast<const long long*>(rowsum), rowcnt, n, raw_mean, scale_q, row_factor);
+  G2_LAUNCHED();
+  return 0;
+}
+
+extern "C" int gridb200_row_means_exact(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                                        const int64_t* rowsum, const int32_t* rowcnt, double* raw_mean,
+                                        double* scale_q, void* stream) {
+  if (int e = check_matrix(depth, n, b, ld)) return e;
+  G2_REQUIRE(valid && rowsum && rowcnt, GRIDB200_EINVAL, "null argument");
+  k_row_mean_ties<<<(unsigned)((n + 63) / 64), 64, 0, as_stream(stream)>>>(
+      depth, n, b, ld, valid, reinterpret_cast<const long long*>(rowsum), rowcnt, raw_mean, scale_q);
   G2_LAUNCHED();
   return 0;
 }

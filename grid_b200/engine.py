@@ -142,6 +142,10 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
     _all_reduce(rowcnt, group)
     raw_mean, scale_q, row_factor = torch.empty(n, **f64), torch.empty(n, **f64), torch.empty(n, **f64)
     call("gridb200_row_scales", ptr(rowsum), ptr(rowcnt), n, ptr(raw_mean), ptr(scale_q), ptr(row_factor), st)
+    if group is None:  # exact %.2f ties take numpy's own mean (needs whole rows: not available when bins are sharded,
+        #                where rows are millions of bins long and an exact tie has probability ~1/bins)
+        call("gridb200_row_means_exact", ptr(depth), n, b, ld, ptr(valid), ptr(rowsum), ptr(rowcnt), ptr(raw_mean),
+             ptr(scale_q), st)
 
     sd, sd2 = torch.empty(b, **f64), torch.empty(b, **f64)
     ws = _ws(_lib.load().gridb200_col_norm_stats_ws_bytes(n, b), dev)

@@ -119,6 +119,8 @@ def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, g
              ptr(rowsum), ptr(rowcnt), ptr(ws0), ws0.numel(), st)
     raw_mean, scale_q, row_factor = torch.empty(n, **f64), torch.empty(n, **f64), torch.empty(n, **f64)
     call("gridb200_row_scales", ptr(rowsum), ptr(rowcnt), n, ptr(raw_mean), ptr(scale_q), ptr(row_factor), st)
+    call("gridb200_row_means_exact", ptr(depth), n, b, ld, ptr(valid), ptr(rowsum), ptr(rowcnt), ptr(raw_mean),
+         ptr(scale_q), st)  # rows are whole on their rank here
     sd, sd2 = torch.empty(b, **f64), torch.empty(b, **f64)
     ws = E._ws(load().gridb200_col_norm_stats_ws_bytes(n, b), dev)
     with E._mark("col_norm"):

@@ -91,6 +91,14 @@ GRIDB200_API int gridb200_row_stats_fused(const float* depth, int64_t n, int64_t
 GRIDB200_API int gridb200_row_scales(const int64_t* rowsum, const int32_t* rowcnt, int64_t n,
                         double* raw_mean, double* scale_q, double* row_factor, void* stream);
 
+/* After gridb200_row_scales: rows whose exact mean lies exactly on a %.2f tie (k + 0.005) get numpy's own value --
+ * np.nanmean's pairwise floating-point sum over the row's valid bins, replayed operation by operation -- because there
+ * the last ulp decides which way the reference's "%.2f" goes (normalize_mosdepth.py:120, :548).  No other row can
+ * differ: a non-tie mean is at least 1/(2*count) hundredths from a tie.  Needs the whole row (all bins) on this GPU. */
+GRIDB200_API int gridb200_row_means_exact(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                             const int64_t* rowsum, const int32_t* rowcnt, double* raw_mean, double* scale_q,
+                             void* stream);
+
 /* Per-bin sums of the row-normalised matrix y = depth/rowmean, shifted by 1: sd[j] = sum_i (y-1),
  * sd2[j] = sum_i (y-1)^2 over present cells of valid bins (normalize_mosdepth.py:445-446 in one pass).
  * ws: gridb200_col_norm_stats_ws_bytes(n,b).  Row-sharded multi-GPU: all-reduce(sum) sd and sd2. */

@@ -584,7 +584,7 @@ def chain_arrays(depth: np.ndarray, counts: np.ndarray, min_depth=20, max_depth=
     mat = d[:, valid]
     have = ~np.all(np.isnan(mat), axis=1)
     rows = np.nonzero(have)[0]
-    mat = mat[rows]
+    mat = np.ascontiguousarray(mat[rows])  # the reference fills a fresh C-order matrix (:404): nanmean over a row is pairwise
     raw_means = np.nanmean(mat, axis=1)
     z, ratio, mu, s2 = normalize_matrix(mat)
     sel = select_high_variance(ratio, top_frac)

@@ -631,3 +631,99 @@ def test_find_neighbors_edge_cases_match_the_oracle(name, ids, ratios, rows, kno
     assert_neighbor_files_equal(mine, od / "nbrs.zMax2.0.tsv.gz")
     if name == "squared_distance_3_4_5":  # clipped at zmax = 2: (0,0)-(2,2) -> 8 / (2 * 2 regions) = 2.00
         assert mine.read_text().splitlines()[0].split("\t")[4] == "2.00"
+
+
+def _mutate_step4_inputs(cfg, name):
+    """Config / input variations of step 4 that the goldens do not cover."""
+    work = Path(cfg["mosdepth"]["work_dir"])
+    n = cfg["mosdepth"]["normalize"]
+    if name == "genome_wide":            # chrom = None: no prefix test, no window
+        cfg.update(chrom=None, start_bp=None, end_bp=None)
+    elif name == "chrom_without_prefix":  # "1" is compared as "chr1" (norm_chrom)
+        cfg.update(chrom="1")
+    elif name == "sub_window":           # closed-interval overlap test on both ends
+        cfg.update(start_bp=20_500, end_bp=60_000)
+    elif name == "tight_depth_filter":
+        n.update(min_depth=33, max_depth=36)
+    elif name == "top_frac_half":
+        n.update(top_frac=0.5)
+    elif name == "top_frac_zero":        # threshold = smallest ratio, strict '>' drops exactly the minimum
+        n.update(top_frac=0.0)
+    elif name == "empty_and_short_files":
+        files = sorted(work.glob("*.regions.bed.gz"))
+        with gzip.open(files[3], "wt") as f:   # a sample without any line: removed from the output
+            f.write("")
+        with gzip.open(files[5], "wt") as f:   # only bins that the depth filter rejects, plus malformed lines
+            f.write("chr1\t1000\t2000\t0.01\nshort\tline\nchr1\t2000\t3000\t0.00\n")
+    elif name == "duplicate_bin_last_wins":
+        f0 = sorted(work.glob("*.regions.bed.gz"))[0]
+        text = gzip.open(f0, "rt").read()
+        with gzip.open(f0, "wt") as f:
+            f.write(text + "chr1\t7000\t8000\t41.25\n")
+    elif name == "mask_whole_stretch":
+        Path(n["repeat_mask_file"]).write_text("chr1\t30000\t45999\n1\t70000\t70001\n")
+    return cfg
+
+
+@pytest.mark.parametrize("name", ["genome_wide", "chrom_without_prefix", "sub_window", "tight_depth_filter", "top_frac_half",
+                                  "top_frac_zero", "empty_and_short_files", "duplicate_bin_last_wins", "mask_whole_stretch"])
+@pytest.mark.parametrize("device_ingest", [True, False])
+def test_normalize_mosdepth_variations_match_the_oracle(name, device_ingest, tmp_path, eng):
+    from grid_b200.utils.normalize_mosdepth import normalize_mosdepth
+
+    cfg = _mutate_step4_inputs(synth.write_cohort_files(tmp_path, 17, 36, 110), name)
+    cfg["gpu"] = {"device_ingest": device_ingest, "device_handoff": False}
+    normalize_mosdepth(cfg, None)
+    out = Path(cfg["output_dir"]) / "norm.tsv.gz"
+    mine = tmp_path / "mine.tsv"
+    mine.write_text(gzip.open(out, "rt").read())
+    out.unlink()
+    assert O.normalize_mosdepth(cfg) is not None
+    assert_norm_files_equal(mine, out)
+
+
+@pytest.mark.parametrize("b", [6, 43, 130, 1000, 4100, 70001])
+def test_sample_means_on_exact_two_decimal_ties_take_numpys_value(b, eng):
+    """np.nanmean is a pairwise floating-point sum; when the exact mean is k + 0.005 its last ulp decides what "%.2f"
+    prints (normalize_mosdepth.py:120, :548).  Rows built to sit exactly on such ties must print as numpy's do."""
+    from grid_b200._lib import call, ptr
+
+    rng = np.random.default_rng(b)
+    n = 64
+    h = rng.integers(1500, 6000, size=(n, b)).astype(np.int64)
+    h[rng.random((n, b)) < 0.02] = 0                       # absent cells (NaN in the reference's matrix)
+    valid = (rng.random(b) < 0.8).astype(np.uint8)
+    valid[:2] = 1
+    ties = 0
+    for i in range(n):                                     # nudge one valid, present cell so that 2*sum == cnt (mod 2*cnt)
+        cols = np.nonzero(valid & (h[i] > 0))[0]
+        cnt = len(cols)
+        if cnt % 2 or i % 4 == 3:                          # odd counts cannot tie; leave every fourth row alone
+            continue
+        s = int(h[i, cols].sum())
+        delta = (cnt // 2 - s) % cnt
+        h[i, cols[0]] += delta
+        ties += 1
+    assert ties > 10
+    x = np.where(h > 0, h / 100.0, np.nan)
+    # the reference's matrix is a fresh C-order array (normalize_mosdepth.py:404): row sums are numpy's PAIRWISE sums
+    want_mean = np.nanmean(np.ascontiguousarray(x[:, valid.astype(bool)]), axis=1)
+    want_q = np.array([float("%.2f" % v) for v in want_mean])
+    ld = (b + 3) // 4 * 4
+    depth = torch.zeros((n, ld), dtype=torch.float32, device="cuda")
+    depth[:, :b] = torch.from_numpy((h / 100.0).astype(np.float32)).cuda()
+    vmask = valid.astype(bool)
+    rowsum = torch.from_numpy(np.where(vmask, h, 0).sum(axis=1)).cuda()
+    rowcnt = torch.from_numpy(((h > 0) & vmask).sum(axis=1).astype(np.int32)).cuda()
+    raw, q, f = (torch.empty(n, dtype=torch.float64, device="cuda") for _ in range(3))
+    st = torch.cuda.current_stream().cuda_stream
+    tvalid = torch.from_numpy(valid).cuda()
+    call("gridb200_row_scales", ptr(rowsum), ptr(rowcnt), n, ptr(raw), ptr(q), ptr(f), st)
+    before = q.cpu().numpy().copy()
+    call("gridb200_row_means_exact", ptr(depth), n, b, ld, ptr(tvalid), ptr(rowsum), ptr(rowcnt), ptr(raw), ptr(q), st)
+    np.testing.assert_array_equal(q.cpu().numpy(), want_q)
+    # rows on a tie now carry numpy's double itself; and the exercise is not vacuous: some ties did print differently
+    tie_rows = np.array([(2 * int(s)) % (2 * int(c)) == int(c) for s, c in zip(rowsum.cpu().tolist(), rowcnt.cpu().tolist())])
+    np.testing.assert_array_equal(raw.cpu().numpy()[tie_rows], want_mean[tie_rows])
+    if b >= 130:
+        assert (before != want_q).any()
