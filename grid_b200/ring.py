@@ -82,8 +82,13 @@ def _all_gather_rows(t: torch.Tensor, counts: list[int], group) -> torch.Tensor:
     return torch.cat([out[r * mx: r * mx + counts[r]] for r in range(world)])
 
 
-def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, group, impl: int = 0):
+def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, group, impl: int = 0,
+                   release_depth: bool = False):
     """normalize -> kNN -> dipCN for the row block this rank holds (depth [n_local, ld], counts_local [n_local, G]).
+
+    release_depth: free the depth matrix's device memory as soon as step 4 has consumed it (the caller's tensor is left
+    with empty storage).  The fp32 matrix is twice the size of the fp16 operand, and the ring needs room for two
+    incoming shards: at BASELINE config 3 (6 250 samples x 2.9e6 bins per rank) that is 72 GB handed back in time.
 
     Returns (NormResult for the local rows, idx [n_local, k] GLOBAL sample ids, d2 [n_local, k], dipcn [n_local, G]).
     Same arithmetic and the same kernels as engine.run_chain; only the exchange steps differ.
@@ -161,6 +166,10 @@ def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, g
         call("gridb200_transform", ptr(depth), n, b, ld, ptr(row_factor), ptr(mu), ptr(sel_pos), ptr(keep), ptr(info),
              p.zclip, None, 0, ptr(zh), n, ptr(norms), ptr(sat), st)
     res.zh, res.kdim, res.norms = zh, kdim, norms
+    if release_depth:
+        torch.cuda.current_stream(dev).synchronize()
+        depth.untyped_storage().resize_(0)
+        del depth
 
     # ---- step 5: ring of reference shards ------------------------------------------------------------------
     norms_all = _all_gather_rows(norms, counts, group)
