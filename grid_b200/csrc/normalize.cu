@@ -27,6 +27,16 @@ static int64_t pick_row_slab(int64_t n, int64_t col_blocks, int64_t min_rows) {
 // (rowsum_all[i] = sum_j h_ij, rowcnt_all[i] = #{h_ij > 0}), which let step K3 skip its full pass over the matrix
 // when few bins fail the depth filter (see k_row_fix).
 // ---------------------------------------------------------------------------------------------------------
+// One warp's partial of one row into the block's shared accumulators.  rs < 2^29 (128 bins x h < 2^22): its low 16
+// bits and the rest go to separate words, so eight warps cannot overflow either and no carry has to be read back --
+// three fire-and-forget shared-memory reductions (written as asm: the compiler turns an atomicAdd inside a divergent
+// branch into a dozen instructions of warp aggregation).
+__device__ __forceinline__ void row_partial(unsigned* lo, unsigned* hi, int* cnt, unsigned rs, int rc) {
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(lo)), "r"(rs & 0xFFFFu) : "memory");
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(hi)), "r"(rs >> 16) : "memory");
+  asm volatile("red.shared.add.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(cnt)), "r"((unsigned)rc) : "memory");
+}
+
 template <bool kRows>
 __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ depth, int64_t n, int64_t b,
                                                       int64_t ld, int64_t rows_per_slab,
@@ -37,7 +47,7 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ 
   // per-sample partials of this block's 1024 bins for one chunk of 512 rows: the warps add into shared memory and the
   // block sends ONE global atomic per row and chunk (a global atomic per warp and row -- 1.5e8 of them on 3202
   // addresses at config 2 -- was what held this pass at 0.75 of HBM speed)
-  __shared__ unsigned s_lo[kRows ? 512 : 1], s_hi[kRows ? 512 : 1];  // 64-bit sums as two words (native 32-bit atomics)
+  __shared__ unsigned s_lo[kRows ? 512 : 1], s_hi[kRows ? 512 : 1];  // sums split at bit 16: plain 32-bit reductions
   __shared__ int s_rc[kRows ? 512 : 1];
   const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
   const bool live = j0 < b;  // dead threads of the last block stay for the collectives and barriers (they add zeros)
@@ -72,10 +82,7 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ 
         if (kRows) {  // 128 bins x h < 2^22 fit 32 bits
           const unsigned rs = __reduce_add_sync(0xffffffffu, (unsigned)(h0 + h1) + (unsigned)(h2 + h3));
           const int rc = __reduce_add_sync(0xffffffffu, (k0 + k1) + (k2 + k3));
-          if (lane0 && rc) {
-            if (atomicAdd(&s_lo[i + u - base], rs) + rs < rs) atomicAdd(&s_hi[i + u - base], 1u);  // carry
-            atomicAdd(&s_rc[i + u - base], rc);
-          }
+          if (lane0 && rc) row_partial(&s_lo[i + u - base], &s_hi[i + u - base], &s_rc[i + u - base], rs, rc);
         }
       }
     }
@@ -90,10 +97,7 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ 
       if (kRows) {
         const unsigned rs = __reduce_add_sync(0xffffffffu, (unsigned)(h0 + h1) + (unsigned)(h2 + h3));
         const int rc = __reduce_add_sync(0xffffffffu, (k0 + k1) + (k2 + k3));
-        if (lane0 && rc) {
-          if (atomicAdd(&s_lo[i - base], rs) + rs < rs) atomicAdd(&s_hi[i - base], 1u);  // carry
-          atomicAdd(&s_rc[i - base], rc);
-        }
+        if (lane0 && rc) row_partial(&s_lo[i - base], &s_hi[i - base], &s_rc[i - base], rs, rc);
       }
     }
 #pragma unroll
@@ -102,7 +106,7 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ 
       __syncthreads();
       for (int t = threadIdx.x; t < (int)(lim - base); t += kThreads) {
         if (s_rc[t]) {
-          atomicAdd(&rowsum_all[base + t], ((unsigned long long)s_hi[t] << 32) | s_lo[t]);
+          atomicAdd(&rowsum_all[base + t], ((unsigned long long)s_hi[t] << 16) + s_lo[t]);
           atomicAdd(&rowcnt_all[base + t], s_rc[t]);
         }
       }
