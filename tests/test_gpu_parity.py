@@ -97,12 +97,24 @@ def _array_case(seed, n, b, holes=0.0, **kw):
     return (h / 100.0).astype(np.float32), h / 100.0, counts
 
 
+def _random_cases(count):
+    """Seeded sweep over shapes and knobs (incl. zmax 6.0 -> |v| up to 600 > 511: the integer SIMT Gram takes over)."""
+    rng = np.random.default_rng(2025)
+    out = []
+    for t in range(count):
+        out.append((100 + t, int(rng.integers(20, 300)), int(rng.integers(64, 6000)), float(rng.choice([0.0, 0.02, 0.3])),
+                    dict(zmax=float(rng.choice([1.0, 2.0, 3.0, 5.0, 6.0])), top_frac=float(rng.choice([0.05, 0.1, 0.3])),
+                         num_neighbors=int(rng.choice([3, 50])), n_nbr=int(rng.choice([2, 30])),
+                         min_depth=float(rng.choice([20, 28])), max_depth=float(rng.choice([100, 45])))))
+    return out
+
+
 @pytest.mark.parametrize("seed,n,b,holes,params", [
     (1, 64, 300, 0.01, dict(num_neighbors=20, n_nbr=8)),
     (2, 257, 2100, 0.0, dict(num_neighbors=500, n_nbr=300)),          # k > N-1
     (3, 130, 5000, 0.05, dict(min_depth=30, max_depth=40, top_frac=0.5, num_neighbors=40, n_nbr=10, zmax=1.5)),
     (4, 33, 1030, 0.0, dict(top_frac=0.0, frac_r=0.5, sigma2_max=0.9, num_neighbors=5, n_nbr=5)),
-])
+] + _random_cases(12))
 def test_array_chain_matches_oracle(seed, n, b, holes, params, eng):
     depth, decimals, counts = _array_case(seed, n, b, holes)
     want = O.chain_arrays(decimals, counts, **params)
