@@ -93,13 +93,39 @@ def pack_depth_matrix_device(individuals: dict, mosdepth_dir, chrom, start, end,
     if len(want) > 32:
         return None
     paths = [find_bed_gz_for_individual(sid, mosdepth_dir) for sid in ids]
-    with ThreadPoolExecutor(max_workers=max(1, threads)) as ex:
-        texts = list(ex.map(lambda p: _inflate(p) if p.exists() else None, paths))
+    cached: dict[int, bytes | None] = {}  # texts inflated ahead of the stream (to size the grid): used once, then dropped
+
+    def inflate(i):
+        if i in cached:
+            return cached.pop(i)
+        return _inflate(paths[i]) if paths[i].exists() else None
+
+    def stream():
+        """(i, text) in sample order, at most 2 * threads files inflated ahead: host memory stays bounded however
+        large the cohort is (config 2 is 3 202 files of ~90 MB of text each)."""
+        ahead = max(2, 2 * int(threads))
+        with ThreadPoolExecutor(max_workers=max(1, int(threads))) as ex:
+            futs, nxt = [], 0
+            for i in range(len(paths)):
+                while nxt < len(paths) and len(futs) < ahead:
+                    futs.append(ex.submit(inflate, nxt))
+                    nxt += 1
+                yield i, futs.pop(0).result()
+
     if start is not None and end is not None:
         bin0 = max(0, -(-(start - 1000) // 1000)) * 1000       # first 1000-aligned bin whose end reaches `start`
         last = (end // 1000) * 1000
     else:
-        bin0, last = 0, max([_last_bin_start(t) for t in texts if t] or [-1])
+        # no window: the grid ends where the files end.  Every sample of a cohort is binned over the same reference,
+        # so the first few files tell; a later file that reaches further sends the cohort to the host packer (below).
+        bin0, last = 0, -1
+        for i in range(len(paths)):
+            if len(cached) >= 4:
+                break
+            if paths[i].exists():
+                cached[i] = _inflate(paths[i])
+                if cached[i]:
+                    last = max(last, _last_bin_start(cached[i]))
     if last < bin0:
         return None
     b = (last - bin0) // 1000 + 1
@@ -124,8 +150,10 @@ def pack_depth_matrix_device(individuals: dict, mosdepth_dir, chrom, start, end,
     st = torch.cuda.current_stream().cuda_stream
     keep_alive = []
     with progress_bar(console, total=len(ids), description="Extracting per-sample regions...") as (progress, task):
-        for i, text in enumerate(texts):
+        for i, text in stream():
             if text:
+                if _last_bin_start(text) > last and not (start is not None and end is not None):
+                    return None  # this file reaches beyond the grid sized from the first ones
                 t = torch.frombuffer(bytearray(text), dtype=torch.uint8).to(dev, non_blocking=False)
                 keep_alive.append(t)
                 call("gridb200_ingest_text", ptr(t), len(text), want, len(want),
@@ -140,7 +168,7 @@ def pack_depth_matrix_device(individuals: dict, mosdepth_dir, chrom, start, end,
     redo = np.nonzero((hs[:, 1] > 0) | ((hs[:, 4] > 0) & bool(excluded)))[0]
     for i in redo.tolist():  # exotic file: the reference's own parsing rules, on the host, into the same row
         try:
-            s_, e_, h_ = gio.parse_regions_text(texts[i], chrom, start, end, excluded)
+            s_, e_, h_ = gio.parse_regions_text(_inflate(paths[i]), chrom, start, end, excluded)
         except Exception:
             s_ = e_ = h_ = np.zeros(0, dtype=np.int64)  # the reference drops a file it cannot parse (:286-287)
         rel = s_ - bin0
