@@ -234,3 +234,80 @@ def write_hi_inputs(root, seed: int, n: int, method: str = "ibs", weighted: bool
         hc["ibd_output"] = str(path)
         hc["weighted"] = weighted
     return cfg
+
+
+# ---- step-3 inputs: genome-style regions files for compute_region_coverage, read records for count_reads ----
+REGION_QUERIES = [
+    ("lpa", "chr6", LPA[1], LPA[2]),                       # both ends cut a bin
+    ("inside_one_bin", "chr6", 160_610_100, 160_610_900),
+    ("bin_aligned", "chr6", 160_606_000, 160_640_000),
+    ("wide", "chr6", 160_500_000, 160_800_000),            # wider than the file's chr6 lines
+    ("beyond", "chr6", 170_000_000, 170_100_000),          # no overlap -> 0
+    ("other_chrom", "chr60", 160_600_000, 160_650_000),    # exact name test: chr6 lines must not count
+    ("absent_chrom", "chrX", 0, 1_000_000),
+]
+
+
+def write_region_files(root, seed: int, n: int, flank_kb: int = 20, by: int = 1000) -> list:
+    """n genome-style `{id}_LPA.regions.bed.gz` files under root: chr5 lines, chr6 bins of `by` bp from flank_kb before
+    the LPA window to flank_kb after it (0.1 % of them 0.00, a duplicated bin, one line with extra columns), chr60
+    lines.  Returns the paths in sample order."""
+    root = Path(root)
+    root.mkdir(parents=True, exist_ok=True)
+    lo = (LPA[1] // 1000 - flank_kb) * 1000
+    hi = (LPA[2] // 1000 + 1 + flank_kb) * 1000
+    starts = np.arange(lo, hi, by, dtype=np.int64)
+    h = depth_hundredths(seed, n, starts.size)
+    paths = []
+    for i, sid in enumerate(sample_ids(n)):
+        p = root / f"{sid}_LPA.regions.bed.gz"
+        with gzip.open(p, "wt", compresslevel=1) as fh:
+            for j in range(3):
+                fh.write(f"chr5\t{lo + j * by}\t{lo + (j + 1) * by}\t{31 + j}.25\n")
+            for j, s in enumerate(starts):
+                extra = "\tgene7" if j == 5 else ""
+                fh.write(f"chr6\t{s}\t{s + by}\t{h[i, j] // 100}.{h[i, j] % 100:02d}{extra}\n")
+            fh.write(f"chr6\t{starts[7]}\t{starts[7] + by}\t{h[i, 7] // 100}.{h[i, 7] % 100:02d}\n")  # repeated bin: counted twice
+            for j in range(4):
+                fh.write(f"chr60\t{LPA[1] - 500 + j * by}\t{LPA[1] - 500 + (j + 1) * by}\t{12 + j}.50\n")
+        paths.append(p)
+    return paths
+
+
+READ_FLAG_PALETTE = np.array([83, 99, 147, 163, 83, 99, 147, 163, 83 | 0x400, 99 | 0x100, 65, 4, 0, 67 | 0x800, 163 | 0x400,
+                              97], dtype=np.uint16)
+READ_REGIONS = [  # (tid, start, end): overlapping, nested, identical, empty, other reference
+    (6, LPA[1], LPA[2]), (6, LPA[1] + 10_000, LPA[1] + 20_000), (6, LPA[1], LPA[2]), (6, LPA[1] - 3_000, LPA[1] + 100),
+    (6, LPA[2] - 1, LPA[2] + 2_000), (6, LPA[1] + 500, LPA[1] + 500), (5, LPA[1], LPA[2]), (6, 0, 1_000),
+    (7, LPA[1] + 7, LPA[1] + 30_007),
+]
+
+
+def read_columns(seed: int, ns: int, mean_reads: int = 4000):
+    """Columnar read records for ns samples: (flag u16, mapq u8, tid i32, next_tid i32, pos i32), sample_off[ns+1].
+    Positions fall around the LPA window on references 5..7 (mostly 6) with reads exactly on region boundaries;
+    every fourth sample is short and sample 2 has no reads at all."""
+    key = stream_key(seed, 9)
+    s_idx = np.arange(ns, dtype=np.uint64)
+    per = (mean_reads * (0.5 + uniform(hash2(key, s_idx, 0)))).astype(np.int64)
+    per[3::4] //= 16
+    if ns > 2:
+        per[2] = 0
+    sample_off = np.concatenate([[0], np.cumsum(per)]).astype(np.int64)
+    n = int(sample_off[-1])
+    r = np.arange(n, dtype=np.uint64)
+    hf, hp = hash2(key, r, 1), hash2(key, r, 2)
+    flag = READ_FLAG_PALETTE[(hf & np.uint64(15)).astype(np.int64)]
+    mapq = ((hf >> np.uint64(8)) % np.uint64(61)).astype(np.uint8)
+    mapq[(hf >> np.uint64(20)) % np.uint64(9) == 0] = 0
+    sel = (hf >> np.uint64(32)) % np.uint64(20)
+    tid = np.where(sel == 0, 5, np.where(sel == 1, 7, 6)).astype(np.int32)
+    next_tid = np.where((hf >> np.uint64(40)) % np.uint64(10) == 0, tid + 1, tid).astype(np.int32)
+    span = LPA[2] - LPA[1] + 10_000
+    pos = (LPA[1] - 5_000 + (hp % np.uint64(span)).astype(np.int64)).astype(np.int64)
+    edge = (hp >> np.uint64(40)) % np.uint64(50)
+    for code, val in ((0, LPA[1]), (1, LPA[1] - 1), (2, LPA[2] - 1), (3, LPA[2]), (4, LPA[1] + 10_000), (5, LPA[1] + 19_999)):
+        pos[edge == code] = val
+    unplaced = (hp >> np.uint64(50)) % np.uint64(97) == 0
+    tid[unplaced], next_tid[unplaced], pos[unplaced] = -1, -1, -1
+    return (flag, mapq, tid, next_tid, pos.astype(np.int32)), sample_off

@@ -291,6 +291,38 @@ GRIDB200_API int gridb200_hi_phase(const double* irr, int64_t n, const int64_t* 
 GRIDB200_API int gridb200_hi_impute(const int64_t* nbr_ptr, const int32_t* nbr_hap, const double* nbr_w,
                        const double* hap, int64_t n, double mean_irr, double* imp, void* stream);
 
+/* ------------------------------------------------------------------ the path's producers */
+
+/* Overlap-weighted depth of the region [start, end) on `chrom` for a BATCH of samples: the body of
+ * compute_region_coverage (mosdepth.py:264-297) without its float arithmetic.  `text` is the concatenation of the
+ * samples' decompressed `chrom\tstart\tend\tdepth\n` files, EACH ENDING IN A NEWLINE; file f is
+ * text[file_off[f], file_off[f+1]) (file_off: device, nfiles+1 entries).  Chromosome test: exact equality (:290).
+ * out (device, [nfiles][4] int64, overwritten): [0] = sum over overlapping lines of hundredths(depth) * overlap_bp,
+ * [1] = sum of overlap_bp, [2] = number of overlapping lines, [3] = lines outside the strict grammar
+ * (digits \t digits \t digits[.dd]; blank lines; leading blanks; < 4 fields) on ANY chromosome -- the reference
+ * converts every line before it looks at the chromosome, so the caller replays such a file with Python semantics.
+ * The caller turns [0], [1], [2] into int(round(100 * (region_cov / covered_bp))): exact quotient, except within
+ * the rounding noise of the reference's sequential fp64 sum around a .5 tie (grid_b200/utils/mosdepth.py). */
+GRIDB200_API int gridb200_region_coverage(const char* text, int64_t nbytes, const int64_t* file_off, int32_t nfiles,
+                             const char* chrom, int32_t chrom_len, int64_t start, int64_t end,
+                             int64_t* out, void* stream);
+
+/* The read filter of count_reads_in_region (count_reads.py:95-105) over columnar read records, for a batch of
+ * samples and G regions at once.  Read r of sample s: sample_off[s] <= r < sample_off[s+1] (device, ns+1 entries).
+ * A read is counted when flag_bits has bit `flag` set (65536 bits = 2048 words: the exact-value test
+ * `read.flag in proper_flags`), mapq >= min_mapq, tid == next_tid, flag & 0x400 == 0 (duplicate), flag & 0x100 == 0
+ * (secondary), and start_g <= pos < end_g on the region's reference.
+ * Regions arrive as a sorted table of distinct boundary keys, bounds[nb] with key = (tid << 32) | position, and per
+ * region the indices lo_g / hi_g of its start / end key in that table (hi_g <= lo_g: empty region, count 0).
+ * counts (device, [ns][g_regions] int64, overwritten).  Columns must be 16-byte aligned.
+ * ws: gridb200_count_reads_ws_bytes(ns, nb).  15 bytes per read of compulsory traffic. */
+GRIDB200_API size_t gridb200_count_reads_ws_bytes(int32_t ns, int32_t nb);
+GRIDB200_API int gridb200_count_reads(const uint16_t* flag, const uint8_t* mapq, const int32_t* tid, const int32_t* next_tid,
+                         const int32_t* pos, int64_t n_reads, const int64_t* sample_off, int32_t ns,
+                         const uint32_t* flag_bits, int32_t min_mapq, const int64_t* bounds, int32_t nb,
+                         const int32_t* lo, const int32_t* hi, int32_t g_regions, int64_t* counts,
+                         void* ws, size_t ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

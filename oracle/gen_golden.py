@@ -14,6 +14,8 @@ what is committed is what the REFERENCE produced:
                   find_neighbors_sklearn outputs on in-memory arrays (incl. NaN cells)
   exon.npz        compute_diploid_cn_for_exon on a 40-sample cohort with zero counts, samples without counts and
                   non-positive scales, all four exon types (python oracle/gen_golden.py exon regenerates only this)
+  step3.json      compute_region_coverage (mosdepth.py:264) and count_reads_in_region (count_reads.py:82, pysam replaced
+                  by an in-memory reader) on the seeded step-3 inputs (gen_golden.py step3)
   hi/<case>.tsv   step 7 (hi_inference) outputs for IBS, IBD and weighted IBD neighbour files (gen_golden.py hi)
   manifest.json   shapes, seeds, sha256 of every generated input file
 """
@@ -179,8 +181,67 @@ def hi_case():
             shutil.copy(Path(cfg["output_dir"]) / "hap.tsv", GOLD / "hi" / f"{name}.tsv")
 
 
+from gen_golden_cases import STEP3_COVERAGE, STEP3_READS  # noqa: E402
+
+
+class _FakeRead:
+    """What count_reads_in_region touches on a pysam.AlignedSegment (count_reads.py:95-105)."""
+    __slots__ = ("flag", "mapq", "reference_id", "next_reference_id", "reference_start")
+
+    def __init__(self, flag, mapq, tid, ntid, pos):
+        self.flag, self.mapq, self.reference_id, self.next_reference_id, self.reference_start = flag, mapq, tid, ntid, pos
+
+    is_duplicate = property(lambda self: bool(self.flag & 0x400))
+    is_secondary = property(lambda self: bool(self.flag & 0x100))
+
+
+def _fake_alignment_file(samples, read_len=150):
+    """Stand-in for pysam.AlignmentFile over in-memory columns; fetch() honours htslib's contract: the reads on that
+    reference whose alignment [pos, pos + len) overlaps [start, end)."""
+    class Fake:
+        def __init__(self, path, mode=None, reference_filename=None):
+            self.cols = samples[path]
+
+        def __enter__(self):
+            return self
+
+        def __exit__(self, *a):
+            return False
+
+        def fetch(self, chrom, start, end):
+            flag, mapq, tid, ntid, pos = self.cols
+            t = int(chrom[3:])
+            for i in np.flatnonzero((tid == t) & (pos < end) & (pos + read_len > start)):
+                yield _FakeRead(int(flag[i]), int(mapq[i]), int(tid[i]), int(ntid[i]), int(pos[i]))
+    return Fake
+
+
+def step3_case():
+    """compute_region_coverage and count_reads_in_region of the unmodified reference on the seeded step-3 inputs:
+    tests/golden/step3.json."""
+    from grid.utils import count_reads as ref_cr
+    from grid.utils import mosdepth as ref_md
+
+    res = {"coverage": {}, "reads": {}}
+    for name, kw in STEP3_COVERAGE.items():
+        with tempfile.TemporaryDirectory() as tmp:
+            paths = synth.write_region_files(tmp, **kw)
+            res["coverage"][name] = {q[0]: [ref_md.compute_region_coverage(p, q[1], q[2], q[3]) for p in paths]
+                                     for q in synth.REGION_QUERIES}
+    for name, kw in STEP3_READS.items():
+        cols, off = synth.read_columns(kw["seed"], kw["ns"], kw["mean_reads"])
+        samples = {f"s{s}": tuple(c[off[s]:off[s + 1]] for c in cols) for s in range(kw["ns"])}
+        with patch.object(ref_cr.pysam, "AlignmentFile", _fake_alignment_file(samples)):
+            res["reads"][name] = [[ref_cr.count_reads_in_region(f"s{s}", "ref.fa", f"chr{t}", lo, hi, kw["flags"], kw["min_mapq"])
+                                   for (t, lo, hi) in synth.READ_REGIONS] for s in range(kw["ns"])]
+    (GOLD / "step3.json").write_text(json.dumps(res, indent=1, sort_keys=True) + "\n")
+
+
 def main():
     GOLD.mkdir(parents=True, exist_ok=True)
+    if sys.argv[1:] == ["step3"]:
+        step3_case()
+        return
     if sys.argv[1:] == ["exon"]:
         exon_case()
         return
@@ -194,6 +255,7 @@ def main():
     array_case(manifest)
     exon_case()
     hi_case()
+    step3_case()
     (GOLD / "manifest.json").write_text(json.dumps(manifest, indent=1, sort_keys=True) + "\n")
     print("golden written to", GOLD)
 
