@@ -53,6 +53,12 @@ SIGNATURES = {
     "gridb200_format_z_write": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _i64, _vp]),
     "gridb200_parse_z_ws_bytes": (_sz, [_i64, _i64]),
     "gridb200_parse_z_rows": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _i64, _vp, _i64, _vp, _vp, _sz, _vp]),
+    "gridb200_format_nbrs_ws_bytes": (_sz, [_i64]),
+    "gridb200_format_nbrs_measure": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _i32, _i64, _i64, _i64, _vp, _vp, _sz, _vp]),
+    "gridb200_format_nbrs_write": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _i64, _i32, _i64, _i64, _i64, _vp, _vp, _i64, _vp]),
+    "gridb200_hash_tokens": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
+    "gridb200_parse_nbrs_rows": (C.c_int, [_vp, _vp, _i64, _i64, _vp, _vp, _vp, _vp, _i64, _i32, _vp, _i64, _vp, _vp, _vp,
+                                           _sz, _vp]),
     "gridb200_region_coverage": (C.c_int, [_vp, _i64, _vp, _i32, C.c_char_p, _i32, _i64, _i64, _vp, _vp]),
     "gridb200_count_reads_ws_bytes": (_sz, [_i32, _i32]),
     "gridb200_count_reads": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _i32,

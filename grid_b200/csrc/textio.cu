@@ -276,6 +276,121 @@ __global__ void k_parse_check_rows(const int64_t* __restrict__ row_tabs, int64_t
   if (r < rows && row_tabs[r] != want_tabs) atomicAdd(&stats[PS_BAD_ROWS], 1ULL);
 }
 
+
+// ---- step-5 file, reading side (load_neighbors, compute_dipcn.py:105-152) ------------------------------------------------
+// A line is  id \t scale ( \t nbr_id \t nbr_scale \t dist )*.  In a file step 5 wrote, every "nbr_id\tnbr_scale" is byte for
+// byte the "id\tscale" head of some line, so neighbours are resolved to row indices by hashing that token and comparing
+// the bytes; a token that is nobody's head, a line whose field count is not 2 + 3m, or more entries than the caller
+// allowed are counted and the host re-reads the file with the reference's rules.
+enum { PN_ENTRIES = 0, PN_UNRESOLVED = 1, PN_BAD_ROWS = 2 };
+
+__device__ __forceinline__ unsigned long long tok_hash_step(unsigned long long h, int c) {
+  return (h ^ (unsigned long long)c) * 0x100000001B3ULL;  // FNV-1a
+}
+__device__ __forceinline__ long long tok_hash_finish(unsigned long long h) {
+  h ^= h >> 30, h *= 0xBF58476D1CE4E5B9ULL, h ^= h >> 27, h *= 0x94D049BB133111EBULL, h ^= h >> 31;
+  return (long long)h;
+}
+
+__global__ void k_tok_hash(const char* __restrict__ tok, const int64_t* __restrict__ tok_off, int64_t n,
+                           long long* __restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  unsigned long long h = 0xCBF29CE484222325ULL;
+  for (int64_t p = tok_off[i]; p < tok_off[i + 1]; ++p) h = tok_hash_step(h, (unsigned char)tok[p]);
+  out[i] = tok_hash_finish(h);
+}
+
+struct NbrTable {
+  const char* tok;
+  const int64_t* tok_off;
+  const long long* hash_sorted;  // ascending (signed)
+  const int32_t* hash_row;       // row whose head has hash_sorted[i]
+  int64_t n;
+};
+
+// the entry token starting at p: "id \t scale" up to (not including) the second tab, the newline or the end of the line
+__device__ __forceinline__ int resolve_entry(const char* __restrict__ text, int64_t p, int64_t end, const NbrTable& T) {
+  unsigned long long h = 0xCBF29CE484222325ULL;
+  int tabs = 0;
+  int64_t q = p;
+  for (; q < end; ++q) {
+    const int c = (unsigned char)text[q];
+    if (c == '\n' || (c == '\t' && ++tabs == 2)) break;
+    h = tok_hash_step(h, c);
+  }
+  if (tabs < 1) return -1;  // an id without a scale
+  const long long key = tok_hash_finish(h);
+  int64_t lo = 0, hi = T.n;
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (T.hash_sorted[mid] < key) lo = mid + 1;
+    else hi = mid;
+  }
+  if (lo >= T.n || T.hash_sorted[lo] != key) return -1;
+  const int row = T.hash_row[lo];
+  const int64_t t0 = T.tok_off[row], tl = T.tok_off[row + 1] - t0;
+  if (tl != q - p) return -1;
+  for (int64_t t = 0; t < tl; ++t)
+    if (T.tok[t0 + t] != text[p + t]) return -1;
+  return row;
+}
+
+__global__ void __launch_bounds__(THREADS) k_parse_nbr_entries(const char* __restrict__ text,
+                                                               const int64_t* __restrict__ line_off, int nchunks,
+                                                               const uint32_t* __restrict__ chunk_tabs, NbrTable T,
+                                                               int32_t k_cap, int32_t* __restrict__ idx, int64_t ld,
+                                                               unsigned long long* __restrict__ stats) {
+  const int64_t r = blockIdx.y;
+  const int64_t ls = line_off[r], le = line_off[r + 1];
+  const int64_t p0 = ls + (int64_t)blockIdx.x * CHUNK_BYTES + threadIdx.x * BYTES;
+  unsigned starts = 0;
+  int tabs = 0;
+  if (p0 < le) {
+    int prev = p0 == ls ? '\t' : (int)(unsigned char)text[p0 - 1];
+#pragma unroll
+    for (int i = 0; i < BYTES; ++i) {
+      const int c = p0 + i < le ? (int)(unsigned char)text[p0 + i] : '\n';
+      if (prev == '\t' && p0 + i < le) starts |= 1u << i;
+      tabs += (c == '\t' && p0 + i < le) ? 1 : 0;
+      prev = c;
+    }
+  }
+  int total;
+  const int before = block_excl_scan(tabs, &total);
+  if (!starts) return;
+  int field = (int)chunk_tabs[r * nchunks + blockIdx.x] + before;
+  unsigned long long good = 0, bad = 0;
+  for (int i = 0; i < BYTES; ++i) {
+    if (p0 + i >= le) break;
+    if ((starts & (1u << i)) && field >= 2 && (field - 2) % 3 == 0) {
+      const int e = (field - 2) / 3;
+      const int row = e < k_cap ? resolve_entry(text, p0 + i, le, T) : -1;
+      if (row >= 0) idx[r * ld + e] = row, ++good;
+      else ++bad;
+    }
+    if (text[p0 + i] == '\t') ++field;
+  }
+  if (good) atomicAdd(&stats[PN_ENTRIES], good);
+  if (bad) atomicAdd(&stats[PN_UNRESOLVED], bad);
+}
+
+// a row must have 2 + 3m fields; its entry count goes to n_entries
+__global__ void k_parse_nbr_check_rows(const int64_t* __restrict__ row_tabs, int64_t rows, int32_t k_cap,
+                                       int32_t* __restrict__ n_entries, unsigned long long* __restrict__ stats) {
+  const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  const int64_t fields = row_tabs[r] + 1;
+  const bool ok = fields >= 2 && (fields - 2) % 3 == 0 && (fields - 2) / 3 <= k_cap;
+  n_entries[r] = ok ? (int32_t)((fields - 2) / 3) : -1;
+  if (!ok) atomicAdd(&stats[PN_BAD_ROWS], 1ULL);
+}
+
+__global__ void k_fill_i32(int32_t* __restrict__ p, int64_t rows, int64_t cols, int64_t ld, int32_t v) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < rows * cols) p[(i / cols) * ld + i % cols] = v;
+}
+
 }  // namespace textio
 }  // namespace g2
 
@@ -354,6 +469,45 @@ extern "C" int gridb200_parse_z_rows(const char* text, const int64_t* line_off, 
   G2_LAUNCHED();
   k_parse_cells<<<dim3(nch, (unsigned)rows), THREADS, 0, st>>>(text, line_off, nch, chunk, skip_fields, rw, zq, ldq,
                                                               reinterpret_cast<unsigned long long*>(stats));
+  G2_LAUNCHED();
+  return 0;
+}
+
+extern "C" int gridb200_hash_tokens(const char* tok, const int64_t* tok_off, int64_t n, int64_t* hash, void* stream) {
+  G2_REQUIRE(tok && tok_off && hash && n > 0, GRIDB200_EINVAL, "bad argument");
+  k_tok_hash<<<(unsigned)((n + 255) / 256), 256, 0, as_stream(stream)>>>(tok, tok_off, n, reinterpret_cast<long long*>(hash));
+  G2_LAUNCHED();
+  return 0;
+}
+
+extern "C" int gridb200_parse_nbrs_rows(const char* text, const int64_t* line_off, int64_t rows, int64_t max_line_bytes,
+                                        const char* tok, const int64_t* tok_off, const int64_t* hash_sorted,
+                                        const int32_t* hash_row, int64_t n_tok, int32_t k_cap, int32_t* idx, int64_t ld,
+                                        int32_t* n_entries, int64_t* stats, void* ws, size_t ws_bytes, void* stream) {
+  G2_REQUIRE(text && line_off && tok && tok_off && hash_sorted && hash_row && idx && n_entries && stats && ws,
+             GRIDB200_EINVAL, "null pointer");
+  G2_REQUIRE(rows > 0 && rows <= 65535 && n_tok > 0 && n_tok < (1LL << 31) && k_cap > 0 && ld >= k_cap &&
+                 max_line_bytes > 0 && max_line_bytes < (1LL << 31),
+             GRIDB200_EINVAL, "bad shape (rows per call <= 65535)");
+  G2_REQUIRE(ws_bytes >= gridb200_parse_z_ws_bytes(rows, max_line_bytes), GRIDB200_EINVAL,
+             "workspace too small: need %zu bytes", gridb200_parse_z_ws_bytes(rows, max_line_bytes));
+  cudaStream_t st = as_stream(stream);
+  const int nch = parse_chunks(max_line_bytes);
+  uint32_t* chunk = static_cast<uint32_t*>(ws);
+  int64_t* row_tabs = reinterpret_cast<int64_t*>(static_cast<char*>(ws) + (((size_t)rows * nch * 4 + 7) & ~(size_t)7));
+  G2_CUDA(cudaMemsetAsync(stats, 0, 4 * sizeof(int64_t), st));
+  k_fill_i32<<<(unsigned)((rows * k_cap + 255) / 256), 256, 0, st>>>(idx, rows, k_cap, ld, -1);
+  G2_LAUNCHED();
+  k_parse_count<<<dim3(nch, (unsigned)rows), THREADS, 0, st>>>(text, line_off, nch, chunk);
+  G2_LAUNCHED();
+  k_chunk_scan<<<(unsigned)rows, THREADS, 0, st>>>(chunk, nch, row_tabs);
+  G2_LAUNCHED();
+  k_parse_nbr_check_rows<<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(row_tabs, rows, k_cap, n_entries,
+                                                                        reinterpret_cast<unsigned long long*>(stats));
+  G2_LAUNCHED();
+  NbrTable T{tok, tok_off, reinterpret_cast<const long long*>(hash_sorted), hash_row, n_tok};
+  k_parse_nbr_entries<<<dim3(nch, (unsigned)rows), THREADS, 0, st>>>(text, line_off, nch, chunk, T, k_cap, idx, ld,
+                                                                    reinterpret_cast<unsigned long long*>(stats));
   G2_LAUNCHED();
   return 0;
 }

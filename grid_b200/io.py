@@ -11,6 +11,7 @@ Formats (reference file:line, paths under /root/reference/grid/utils/):
 from __future__ import annotations
 
 import gzip
+import math
 import io as _io
 from pathlib import Path
 
@@ -164,8 +165,10 @@ def save_neighbors(path, ids, scales: np.ndarray, nbr_idx: np.ndarray, nbr_d2: n
             for j, d2 in zip(nbr_idx[i].tolist(), nbr_d2[i].tolist()):
                 if j < 0:
                     break
-                # the reference squares sklearn's sqrt again (find_neighbors.py:222) before normalising
-                sq = ((d2 / 1e4) ** 0.5) ** 2
+                # the reference squares sklearn's sqrt again (find_neighbors.py:222) before normalising; sqrt and the
+                # product are the correctly rounded IEEE operations (C sqrt, numpy's square), as on the device
+                s = math.sqrt(d2 / 1e4)
+                sq = s * s
                 parts += [ids[j], sc[j], f"{sq / (2 * r_use):.2f}"]
             out.write("\t".join(parts) + "\n")
 

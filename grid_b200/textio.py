@@ -268,3 +268,152 @@ def _read_device(path, dev, threads):
         if b[1] or b[2] or b[0] != row * rw:
             raise _Fallback()
     return ids, ratios, zq[:row], np.array(scales)
+
+
+# ---- step-5 file (save_neighbors, find_neighbors.py:231-267) --------------------------------------------------------
+def save_neighbors(path, ids, scales, nbr_idx, nbr_d2, r_use: int, threads: int = 8, level: int | None = None) -> None:
+    """The neighbours file from the DEVICE k-best lists (nbr_idx int32 [N, k], nbr_d2 int64 [N, k] exact squared
+    distances in 1e-4 units): same bytes after gunzip as grid_b200.io.save_neighbors.  The host contributes one
+    "id\\tscale" token per sample; every entry is formatted by gridb200_format_nbrs_*; rows are deflated as independent
+    gzip members on a thread pool."""
+    import torch
+
+    from ._lib import call, load, ptr
+
+    n = len(ids)
+    assert nbr_idx.is_cuda and nbr_idx.dtype == torch.int32 and nbr_d2.dtype == torch.int64 and nbr_idx.shape == nbr_d2.shape
+    assert nbr_idx.shape[0] == n and nbr_idx.stride(1) in (0, 1) and nbr_idx.stride(0) == nbr_d2.stride(0)
+    dev = nbr_idx.device
+    st = torch.cuda.current_stream().cuda_stream
+    k = int(nbr_idx.shape[1])
+    with open(path, "wb") as out:
+        if n == 0:
+            out.write(_deflate_member([b""], level))
+            return
+        toks = [f"{sid}\t{v:.2f}".encode() for sid, v in zip(ids, np.asarray(scales, dtype=np.float64).tolist())]
+        tok_off = np.concatenate([[0], np.cumsum([len(t) for t in toks])]).astype(np.int64)
+        t_tok = torch.frombuffer(bytearray(b"".join(toks)), dtype=torch.uint8).to(dev)
+        t_off = torch.from_numpy(tok_off).to(dev)
+        longest = int(np.diff(tok_off).max())
+        row_cap = longest + 1 + k * (2 + longest + 24)  # an entry: two tabs, a token, at most 24 bytes of distance
+        per = int(max(1, min(65535, n, BATCH_BYTES // row_cap)))
+        ws = torch.empty(load().gridb200_format_nbrs_ws_bytes(per), dtype=torch.uint8, device=dev)
+        row_off = torch.empty(per + 1, dtype=torch.int64, device=dev)
+        text = torch.empty(per * row_cap, dtype=torch.uint8, device=dev)
+        host = torch.empty(per * row_cap, dtype=torch.uint8, pin_memory=True)
+        pool = ThreadPoolExecutor(max_workers=max(1, int(threads)))
+        jobs = []
+        ld = nbr_idx.stride(0) if k else 0
+        for r0 in range(0, n, per):
+            cnt = min(per, n - r0)
+            pi = nbr_idx.data_ptr() + 4 * r0 * ld if k else None
+            pd = nbr_d2.data_ptr() + 8 * r0 * ld if k else None
+            call("gridb200_format_nbrs_measure", ptr(t_tok), ptr(t_off), n, pi, pd, cnt, k, ld, r0, int(r_use), ptr(row_off),
+                 ptr(ws), ws.numel(), st)
+            call("gridb200_format_nbrs_write", ptr(t_tok), ptr(t_off), n, pi, pd, cnt, k, ld, r0, int(r_use), ptr(row_off),
+                 ptr(text), text.numel(), st)
+            off = row_off[: cnt + 1].cpu().numpy()  # synchronises the stream
+            total = int(off[-1])
+            host[:total].copy_(text[:total])
+            blob = host[:total].numpy().tobytes()  # detach from the pinned buffer: workers outlive this batch
+            view = memoryview(blob)
+            a = 0
+            while a < cnt:  # members of >= MEMBER_BYTES whole rows
+                b = int(np.searchsorted(off, off[a] + MEMBER_BYTES, side="left"))
+                b = min(max(b, a + 1), cnt)
+                jobs.append(pool.submit(_deflate_member, [view[off[a]:off[b]]], level))
+                a = b
+            while len(jobs) > 4 * max(1, int(threads)):
+                out.write(jobs.pop(0).result())
+        for j in jobs:
+            out.write(j.result())
+        pool.shutdown()
+
+
+def load_neighbors_device(path, device="cuda", threads: int = 8):
+    """Neighbours file -> (ids, scales[N] float64, idx[N, kmax] int32 DEVICE tensor, -1 padded), for files whose every
+    "nbr_id\\tnbr_scale" is the "id\\tscale" head of one of the lines (what step 5 writes) and whose ids are distinct.
+    Raises _Fallback for anything else; the caller then uses grid_b200.io.load_neighbors (the reference's rules)."""
+    import torch
+
+    from ._lib import call, load, ptr
+
+    dev = torch.device(device)
+    st = torch.cuda.current_stream().cuda_stream
+    ids, scales, heads, batches = [], [], [], []
+    kmax = 0
+    with _open_text(path, threads) as fh:
+        carry = b""
+        while True:
+            block = fh.read(BATCH_BYTES)
+            buf = carry + block
+            if not buf:
+                break
+            if b"\r" in buf:
+                raise _Fallback()
+            end = len(buf) if not block else buf.rfind(b"\n") + 1
+            if end == 0:
+                carry = buf
+                continue
+            carry = buf[end:]
+            if not buf[:end].endswith(b"\n"):  # last line of the file without a newline
+                buf, end = buf[:end] + b"\n", end + 1
+            offs, pos = [0], 0
+            while pos < end:
+                nxt = buf.find(b"\n", pos, end) + 1
+                t1 = buf.find(b"\t", pos, nxt)
+                t2 = buf.find(b"\t", t1 + 1, nxt) if t1 >= 0 else -1
+                stop = t2 if t2 >= 0 else nxt - 1
+                if t1 < 0 or t1 == pos:
+                    raise _Fallback()
+                try:
+                    scales.append(float(buf[t1 + 1:stop]))
+                except ValueError:
+                    raise _Fallback()
+                if buf[t1 + 1:stop].strip() != buf[t1 + 1:stop] or buf[pos:t1].strip() != buf[pos:t1]:
+                    raise _Fallback()  # blanks the reference's strip() / float() would remove
+                ids.append(buf[pos:t1].decode())
+                heads.append(buf[pos:stop])
+                fields = buf.count(b"\t", pos, nxt) + 1
+                if (fields - 2) % 3:
+                    raise _Fallback()
+                kmax = max(kmax, (fields - 2) // 3)
+                offs.append(nxt)
+                pos = nxt
+            batches.append((torch.frombuffer(bytearray(buf[:end]), dtype=torch.uint8).to(dev),
+                            torch.tensor(offs, dtype=torch.int64, device=dev), int(np.diff(np.asarray(offs)).max())))
+            if not block:
+                break
+    n = len(ids)
+    if n == 0 or len(set(ids)) != n:
+        raise _Fallback()
+    idx = torch.full((n, max(kmax, 1)), -1, dtype=torch.int32, device=dev)
+    if kmax == 0:
+        return ids, np.array(scales), idx
+    tok_off = np.concatenate([[0], np.cumsum([len(h) for h in heads])]).astype(np.int64)
+    t_tok = torch.frombuffer(bytearray(b"".join(heads)), dtype=torch.uint8).to(dev)
+    t_off = torch.from_numpy(tok_off).to(dev)
+    hashes = torch.empty(n, dtype=torch.int64, device=dev)
+    call("gridb200_hash_tokens", ptr(t_tok), ptr(t_off), n, ptr(hashes), st)
+    hs, order = torch.sort(hashes)
+    if n > 1 and bool((hs[1:] == hs[:-1]).any()):
+        raise _Fallback()
+    hrow = order.to(torch.int32)
+    stats = torch.zeros(4, dtype=torch.int64, device=dev)
+    total = torch.zeros(4, dtype=torch.int64, device=dev)
+    row = 0
+    for t_text, t_lines, max_line in batches:
+        cnt = t_lines.numel() - 1
+        for r0 in range(0, cnt, 65535):
+            c = min(65535, cnt - r0)
+            ws = torch.empty(load().gridb200_parse_z_ws_bytes(c, max_line), dtype=torch.uint8, device=dev)
+            n_ent = torch.empty(c, dtype=torch.int32, device=dev)
+            call("gridb200_parse_nbrs_rows", ptr(t_text), t_lines.data_ptr() + 8 * r0, c, max_line, ptr(t_tok), ptr(t_off),
+                 ptr(hs), ptr(hrow), n, kmax, idx.data_ptr() + 4 * (row + r0) * idx.stride(0), idx.stride(0), ptr(n_ent),
+                 ptr(stats), ptr(ws), ws.numel(), st)
+            total += stats
+        row += cnt
+    b = total.cpu().numpy()
+    if b[1] or b[2]:
+        raise _Fallback()
+    return ids, np.array(scales), idx

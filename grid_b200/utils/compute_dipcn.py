@@ -37,6 +37,16 @@ def compute_diploid_genotypes(config, console) -> None:
     if cached is not None:  # step 5 of this process wrote that very file: ids, %.2f scales and index lists as arrays
         _from_arrays(cached["ids"], cached["scales"], cached["idx"], reads, n_nbr, output_file, console)
         return
+    if config.get("gpu", {}).get("device_text", True):  # additive key; default = resolve the lists on the GPU
+        from .. import textio
+
+        try:
+            d_ids, d_scales, d_idx = textio.load_neighbors_device(neighbors_file, threads=config.get("threads", 1))
+        except textio._Fallback:  # not a file step 5 wrote (foreign ids, odd fields): the reference's rules below
+            pass
+        else:
+            _from_arrays(d_ids, d_scales, d_idx, reads, n_nbr, output_file, console)
+            return
     ids, scales, lists = load_neighbors(neighbors_file)
     # universe of samples = file rows plus any neighbour id that only appears inside a list
     pos = {}

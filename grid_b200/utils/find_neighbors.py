@@ -53,6 +53,7 @@ def find_neighbors(config, console):
         tzq = torch.from_numpy(np.ascontiguousarray(zq)).to(dev)
     n, rw = len(ids), len(ratios)
     p = engine.Params(zmax=zmax, sigma2_max=sigma2_max, frac_r=frac_r, num_neighbors=n_neighbors)
+    tidx = td2 = None
     with progress_bar(console, total=n, description="Finding neighbors...") as (progress, task):
         if rw == 0 or n < 2:
             idx = np.full((n, 0), -1, dtype=np.int32)
@@ -79,9 +80,15 @@ def find_neighbors(config, console):
                 log(console, f"Removed {extreme} / {rw} regions with sigma2ratio > {sigma2_max}", style="warning")
             zh, kdim, norms = engine.prepare_from_zq(tzq, rw, keep, p.zclip)
             tidx, td2 = engine.knn(zh, kdim, norms, n_neighbors, p.zclip)
-            idx, d2 = tidx.cpu().numpy(), td2.cpu().numpy()
+            idx = tidx.cpu().numpy()
         progress.advance(task, n)
-    save_neighbors(output_file, ids, scales, idx, d2, r_use)
+    if tidx is not None and config.get("gpu", {}).get("device_text", True):  # entries formatted on the GPU
+        from .. import textio
+
+        textio.save_neighbors(output_file, ids, scales, tidx, td2, r_use, threads=config.get("threads", 1),
+                              level=config.get("gpu", {}).get("gzip_level"))
+    else:
+        save_neighbors(output_file, ids, scales, idx, d2 if tidx is None else td2.cpu().numpy(), r_use)
     if handoff.enabled(config) and len(set(ids)) == len(ids) and idx.shape[1] > 0:
         handoff.put(output_file, ids=list(ids), scales=np.array([float("%.2f" % v) for v in np.asarray(scales).tolist()]),
                     idx=idx)

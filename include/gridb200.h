@@ -272,6 +272,39 @@ GRIDB200_API int gridb200_parse_z_rows(const char* text, const int64_t* line_off
                           int32_t skip_fields, int64_t rw, int16_t* zq, int64_t ldq, int64_t* stats,
                           void* ws, size_t ws_bytes, void* stream);
 
+/* The body of the step-5 neighbours file (save_neighbors, find_neighbors.py:231-267) from the k-best lists in HBM:
+ * row i = token[row0+i] ( '\t' token[j] '\t' dist )* '\n' over the entries j = idx[i][0..] up to the first negative
+ * index, dist = "%.2f" % (sqrt(d2/1e4)^2 / (2 * r_use)) with d2 the exact integer squared distance in units of 1e-4
+ * (r_use == 0 counts as 1, :256-257).  token[s] = tok[tok_off[s] .. tok_off[s+1]) is the host-made "id\tscale" text of
+ * sample s (n_tok samples; ids are arbitrary strings).  idx / d2 point at the first row of the batch, row stride ld.
+ * measure: row_off[0..rows] (device) = byte offsets of the rows in the batch text; rows <= 65535 per call.
+ * write:   fills text[0 .. row_off[rows]).  ws: gridb200_format_nbrs_ws_bytes(rows). */
+GRIDB200_API size_t gridb200_format_nbrs_ws_bytes(int64_t rows);
+GRIDB200_API int gridb200_format_nbrs_measure(const char* tok, const int64_t* tok_off, int64_t n_tok, const int32_t* idx,
+                                 const int64_t* d2, int64_t rows, int32_t k, int64_t ld, int64_t row0,
+                                 int64_t r_use, int64_t* row_off, void* ws, size_t ws_bytes, void* stream);
+GRIDB200_API int gridb200_format_nbrs_write(const char* tok, const int64_t* tok_off, int64_t n_tok, const int32_t* idx,
+                               const int64_t* d2, int64_t rows, int32_t k, int64_t ld, int64_t row0,
+                               int64_t r_use, const int64_t* row_off, char* text, int64_t text_cap, void* stream);
+
+/* Reading side (load_neighbors, compute_dipcn.py:105-152) for files step 5 wrote: every "nbr_id\tnbr_scale" of such a
+ * file is byte for byte the "id\tscale" head of one of its lines, so neighbours become row indices by hashing that
+ * token and comparing bytes.
+ * gridb200_hash_tokens: hash[s] (int64) of token s = tok[tok_off[s] .. tok_off[s+1]); the caller sorts them (they must
+ *   be distinct) and passes hash_sorted / hash_row (row of each sorted hash).
+ * gridb200_parse_nbrs_rows: line i of the batch is text[line_off[i], line_off[i+1]) including its newline (as for
+ *   gridb200_parse_z_rows).  idx[i][e] (row stride ld) = row index of entry e, -1 beyond the line's entries (columns
+ *   0..k_cap-1 are overwritten); n_entries[i] = number of entries, -1 for a line whose field count is not 2 + 3m or
+ *   exceeds k_cap.  stats (device, 4 x int64): [0] entries resolved, [1] entries whose token is no line's head,
+ *   [2] irregular lines -- when [1] or [2] is non-zero the caller re-reads the file with the reference's rules.
+ *   The distance field is not looked at (the reference ignores it too).  ws: gridb200_parse_z_ws_bytes(rows,
+ *   max_line_bytes). */
+GRIDB200_API int gridb200_hash_tokens(const char* tok, const int64_t* tok_off, int64_t n, int64_t* hash, void* stream);
+GRIDB200_API int gridb200_parse_nbrs_rows(const char* text, const int64_t* line_off, int64_t rows, int64_t max_line_bytes,
+                             const char* tok, const int64_t* tok_off, const int64_t* hash_sorted,
+                             const int32_t* hash_row, int64_t n_tok, int32_t k_cap, int32_t* idx, int64_t ld,
+                             int32_t* n_entries, int64_t* stats, void* ws, size_t ws_bytes, void* stream);
+
 /* ------------------------------------------------------------------ step 7: hi_inference --- */
 
 /* Iterative haplotype phasing of hi_inference.py:179-233, in the reference's in-place (Gauss-Seidel) order.
