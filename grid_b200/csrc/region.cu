@@ -129,10 +129,21 @@ __global__ void __launch_bounds__(256) k_read_hist(ReadCols R, long long n_reads
     const int tt[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
     const int nn[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
     const int pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+    long long key[kReadsPerThread];
 #pragma unroll
-    for (int t = 0; t < kReadsPerThread; ++t)
-      take((fw[t >> 1] >> (16 * (t & 1))) & 0xFFFFu, (int)((mw[t >> 2] >> (8 * (t & 3))) & 0xFFu), tt[t], nn[t], pp[t],
-           r + t);
+    for (int t = 0; t < kReadsPerThread; ++t) {
+      const bool ok = read_passes((fw[t >> 1] >> (16 * (t & 1))) & 0xFFFFu, (int)((mw[t >> 2] >> (8 * (t & 3))) & 0xFFu), tt[t],
+                                  nn[t], flag_bits, min_mapq) && tt[t] >= 0 && pp[t] >= 0;
+      key[t] = ok ? (((long long)tt[t] << 32) | (long long)(unsigned)pp[t]) : -1;  // -1: before every boundary
+    }
+    int e[kReadsPerThread];
+    interval_of_n<kReadsPerThread>(key, bounds, nb, e);
+#pragma unroll
+    for (int t = 0; t < kReadsPerThread; ++t) {
+      if (e[t] == 0 || e[t] == nb) continue;  // outside every region (no region spans the first or the last interval)
+      if (local) atomicAdd(&sh[e[t]], 1u);
+      else atomicAdd(&hist[(long long)sample_of(r + t, sample_off, ns) * ne + e[t]], 1u);
+    }
   } else {
     for (long long q = r; q < r1; ++q) take(R.flag[q], R.mapq[q], R.tid[q], R.next_tid[q], R.pos[q], q);
   }

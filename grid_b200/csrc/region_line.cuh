@@ -114,4 +114,22 @@ G2_HD int interval_of(long long key, const long long* bounds, int nb) {
   return lo;
 }
 
+// interval_of for N keys at once, branch-free and in lockstep (N independent loads per step instead of one dependent
+// chain per key): lo grows by descending powers of two while bounds[lo + step - 1] <= key.
+template <int N>
+G2_HD void interval_of_n(const long long (&key)[N], const long long* bounds, int nb, int (&out)[N]) {
+#pragma unroll
+  for (int t = 0; t < N; ++t) out[t] = 0;
+  int top = 1;
+  while (top * 2 <= nb) top *= 2;
+  for (int step = nb > 0 ? top : 0; step > 0; step >>= 1) {
+#pragma unroll
+    for (int t = 0; t < N; ++t) {
+      const int cand = out[t] + step;
+      const long long b = bounds[(cand <= nb ? cand : nb) - 1];
+      if (cand <= nb && b <= key[t]) out[t] = cand;
+    }
+  }
+}
+
 }  // namespace g2

@@ -26,11 +26,37 @@ extern "C" void rl_count_reads(const uint16_t* flag, const uint8_t* mapq, const 
                                const long long* bounds, int nb, const int32_t* lo, const int32_t* hi, int g,
                                long long* counts) {
   std::vector<uint32_t> hist(nb + 1, 0);
-  for (long long r = 0; r < n; ++r) {
+  long long r = 0;
+  for (; r + 8 <= n; r += 8) {  // the kernel's vector path: eight keys searched in lockstep, rejected reads as key -1
+    long long key[8];
+    int e[8];
+    for (int t = 0; t < 8; ++t) {
+      const bool ok = g2::read_passes(flag[r + t], mapq[r + t], tid[r + t], ntid[r + t], flag_bits, min_mapq) &&
+                      tid[r + t] >= 0 && pos[r + t] >= 0;
+      key[t] = ok ? (((long long)tid[r + t] << 32) | (long long)(unsigned)pos[r + t]) : -1;
+    }
+    g2::interval_of_n<8>(key, bounds, nb, e);
+    for (int t = 0; t < 8; ++t)
+      if (e[t] != 0 && e[t] != nb) ++hist[e[t]];
+  }
+  for (; r < n; ++r) {  // the kernel's tail path
     if (!g2::read_passes(flag[r], mapq[r], tid[r], ntid[r], flag_bits, min_mapq)) continue;
     if (tid[r] < 0 || pos[r] < 0) continue;
     ++hist[g2::interval_of(((long long)tid[r] << 32) | (long long)(unsigned)pos[r], bounds, nb)];
   }
   for (int e = 1; e <= nb; ++e) hist[e] += hist[e - 1];
   for (int k = 0; k < g; ++k) counts[k] = hi[k] > lo[k] ? (long long)(hist[hi[k]] - hist[lo[k]]) : 0;
+}
+
+// interval_of_n against interval_of on arbitrary keys
+extern "C" int rl_interval_check(const long long* keys, long long n, const long long* bounds, int nb) {
+  for (long long r = 0; r + 8 <= n; r += 8) {
+    long long key[8];
+    int e[8];
+    for (int t = 0; t < 8; ++t) key[t] = keys[r + t];
+    g2::interval_of_n<8>(key, bounds, nb, e);
+    for (int t = 0; t < 8; ++t)
+      if (e[t] != g2::interval_of(key[t], bounds, nb)) return 0;
+  }
+  return 1;
 }

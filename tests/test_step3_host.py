@@ -238,6 +238,16 @@ def test_region_table_handles_overlap_nesting_and_empty_regions(hostlib):
     assert want.sum() > 0
 
 
+def test_lockstep_interval_search_equals_the_scalar_one(hostlib):
+    rng = np.random.default_rng(5)
+    hostlib.rl_interval_check.argtypes = [C.c_void_p, C.c_longlong, C.c_void_p, C.c_int]
+    for nb in (0, 1, 2, 3, 7, 8, 9, 1000, 1468, 4095, 4097):
+        bounds = np.unique(rng.integers(0, 1 << 40, nb).astype(np.int64))
+        keys = np.concatenate([rng.integers(-5, 1 << 40, 4000), bounds, bounds - 1, bounds + 1, [-1, 0, (1 << 62)]]).astype(np.int64)
+        keys = np.ascontiguousarray(keys[: len(keys) // 8 * 8])
+        assert hostlib.rl_interval_check(keys.ctypes.data, len(keys), bounds.ctypes.data, len(bounds)) == 1, nb
+
+
 def test_flag_bitmap_is_an_exact_value_test():
     bits = gcr.flag_bitmap([83, 147, None, "99", 70000, -1, True])
     on = [f for f in range(65536) if (bits[f >> 5] >> (f & 31)) & 1]
