@@ -139,6 +139,36 @@ def level_schedule(nbrs: HapNeighbours, takes_part: np.ndarray):
     return order, level_ptr
 
 
+def level_schedule_device(t_ptr, t_hap, takes_part: np.ndarray):
+    """level_schedule on the GPU: relaxation passes (gridb200_hi_level_pass) until nothing moves, then a stable sort
+    by level.  Returns (order int32 DEVICE tensor, level_ptr int64 numpy) -- the same arrays as level_schedule."""
+    import torch
+
+    from .._lib import call, ptr
+
+    dev, n = t_ptr.device, len(takes_part)
+    st = torch.cuda.current_stream().cuda_stream
+    level = torch.from_numpy(np.where(takes_part, 0, -1).astype(np.int32)).to(dev)
+    changed = torch.zeros(1, dtype=torch.int32, device=dev)
+    while n:
+        changed.zero_()
+        for _ in range(8):  # the flag is read once per eight passes; a pass over 5e4 samples takes microseconds
+            call("gridb200_hi_level_pass", ptr(t_ptr), ptr(t_hap), n, ptr(level), ptr(changed), st)
+        if int(changed.item()) == 0:
+            break
+    lv = level.to(torch.int64)
+    act = lv >= 0
+    n_active = int(act.sum().item())
+    if n_active == 0:
+        return torch.zeros(0, dtype=torch.int32, device=dev), np.zeros(1, dtype=np.int64)
+    key = torch.where(act, lv, torch.full_like(lv, 1 << 40))
+    order = torch.sort(key, stable=True).indices[:n_active].to(torch.int32).contiguous()
+    n_levels = int(lv.max().item()) + 1
+    level_ptr = np.zeros(n_levels + 1, dtype=np.int64)
+    level_ptr[1:] = torch.cumsum(torch.bincount(lv[act], minlength=n_levels), 0).cpu().numpy()
+    return order, level_ptr
+
+
 def _run_phasing(IRRs, hap_nbrs, MIN_NBR, N_ITERS, console):
     """(hap_IRRs [2N], mean_IRRs, imputed [2N]) on the GPU; same values as the reference's loop (hi_inference.py:179-256)."""
     import torch
@@ -164,12 +194,11 @@ def _run_phasing(IRRs, hap_nbrs, MIN_NBR, N_ITERS, console):
     if n == 0:
         return hap0, mean_irr, hap0.copy()
     # a NaN IRR never takes part in the sweeps (the reference tests the haplotype value, which is then NaN)
-    order, level_ptr = level_schedule(nbrs, takes_part & ~np.isnan(irr))
     dev = torch.device("cuda")
     st = torch.cuda.current_stream().cuda_stream
-    d = {k: torch.from_numpy(v).to(dev) for k, v in
-         dict(irr=irr, ptr=nbrs.ptr, hap=nbrs.hap, w=nbrs.w, order=order, val=hap0).items()}
-    old = torch.empty_like(d["val"])
+    d = {k: torch.from_numpy(v).to(dev) for k, v in dict(irr=irr, ptr=nbrs.ptr, hap=nbrs.hap, w=nbrs.w, val=hap0).items()}
+    d["order"], level_ptr = level_schedule_device(d["ptr"], d["hap"], takes_part & ~np.isnan(irr))
+    old = torch.empty(2 * n + len(level_ptr) + 1, dtype=torch.float64, device=dev)  # snapshot + the level table
     imp = torch.empty_like(d["val"])
     call("gridb200_hi_phase", ptr(d["irr"]), n, ptr(d["ptr"]), ptr(d["hap"]), ptr(d["w"]), ptr(d["order"]),
          level_ptr.ctypes.data, len(level_ptr) - 1, int(N_ITERS), ptr(d["val"]), ptr(old), st)

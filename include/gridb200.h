@@ -314,10 +314,17 @@ GRIDB200_API int gridb200_parse_nbrs_rows(const char* text, const int64_t* line_
  * order / level_ptr_host: the level schedule -- order[level_ptr[l] .. level_ptr[l+1]) are the samples of level l, where
  *   level(i) = 1 + max level over neighbour samples j < i that take part (0 if none); level_ptr_host is a HOST
  *   array of n_levels+1 entries (the call launches one kernel per level and sweep).
- * old_ws: 2n doubles of device scratch.  Results equal the reference's doubles bit for bit. */
+ * old_ws: device scratch of 2n doubles followed by n_levels + 1 int64 (the level table, for the single cooperative
+ *   launch that runs all sweeps with a grid barrier between levels).  Results equal the reference's doubles bit for bit. */
 GRIDB200_API int gridb200_hi_phase(const double* irr, int64_t n, const int64_t* nbr_ptr, const int32_t* nbr_hap,
                       const double* nbr_w, const int32_t* order, const int64_t* level_ptr_host, int32_t n_levels,
                       int32_t n_iters, double* hap, double* old_ws, void* stream);
+
+/* One in-place relaxation pass of the level schedule: level[i] (>= 0 for samples that take part, -1 otherwise; start
+ * from 0 / -1) becomes 1 + max level over neighbour samples j < i that take part (0 if none); *changed (device) is set to
+ * 1 when any level moved.  Repeat until a pass leaves *changed at 0 (at most depth + 1 passes). */
+GRIDB200_API int gridb200_hi_level_pass(const int64_t* nbr_ptr, const int32_t* nbr_hap, int64_t n, int32_t* level,
+                           int32_t* changed, void* stream);
 
 /* imp[2i+h] = weighted mean of the phased neighbours of haplotype 2i+h after the last sweep, mean_irr/2 when it
  * has none (hi_inference.py:236-256). */

@@ -63,3 +63,36 @@ def test_edge_cases(tmp_path, hi):
         got, mean, _ = hi._run_phasing([8.0, 6.0, float("nan")], lists, 1, iters, None)
         assert all((a == b) or (math.isnan(a) and math.isnan(b)) for a, b in zip(got.tolist(), want))
         assert math.isnan(mean) and math.isnan(wm)
+
+
+def test_device_level_schedule_equals_the_host_schedule(tmp_path, hi):
+    cfg = synth.write_hi_inputs(tmp_path, seed=77, n=6000, method="ibs", n_iters=3)
+    ids, irr, index = hi._read_dip_cn_file(Path(cfg["output_dir"]) / "dipcn.tsv")
+    lists = hi._load_ibs_neighbors(cfg["compute_haploid_genotypes"]["ibs_output"], index, 10)
+    nbrs = hi.HapNeighbours(lists)
+    takes_part = (nbrs.count[0::2] >= 1) & (nbrs.count[1::2] >= 1)
+    takes_part[::11] = False
+    want_order, want_ptr = hi.level_schedule(nbrs, takes_part)
+    order, level_ptr = hi.level_schedule_device(torch.from_numpy(nbrs.ptr).cuda(), torch.from_numpy(nbrs.hap).cuda(), takes_part)
+    assert np.array_equal(level_ptr, want_ptr) and np.array_equal(order.cpu().numpy(), want_order)
+    assert len(level_ptr) > 5
+    # nobody takes part
+    order, level_ptr = hi.level_schedule_device(torch.from_numpy(nbrs.ptr).cuda(), torch.from_numpy(nbrs.hap).cuda(),
+                                                np.zeros_like(takes_part))
+    assert order.numel() == 0 and level_ptr.tolist() == [0]
+
+
+def test_one_cooperative_launch_equals_one_launch_per_level(tmp_path, hi, monkeypatch):
+    cfg = synth.write_hi_inputs(tmp_path, seed=5, n=20000, method="ibs", n_iters=30)
+    ids, irr, index = hi._read_dip_cn_file(Path(cfg["output_dir"]) / "dipcn.tsv")
+    lists = hi._load_ibs_neighbors(cfg["compute_haploid_genotypes"]["ibs_output"], index, 10)
+    from grid_b200 import _lib
+
+    before = _lib.load().gridb200_launch_count()
+    coop = hi._run_phasing(irr, lists, 1, 30, None)
+    mid = _lib.load().gridb200_launch_count()
+    monkeypatch.setenv("GRIDB200_HI_SCHED", "levels")
+    per_level = hi._run_phasing(irr, lists, 1, 30, None)
+    after = _lib.load().gridb200_launch_count()
+    assert np.array_equal(coop[0], per_level[0], equal_nan=True) and np.array_equal(coop[2], per_level[2], equal_nan=True)
+    assert (after - mid) - (mid - before) > 30 * 5     # the per-level path really launched once per level and sweep
