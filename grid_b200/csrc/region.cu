@@ -94,7 +94,7 @@ __device__ __forceinline__ int sample_of(long long r, const long long* __restric
 __global__ void __launch_bounds__(256) k_read_hist(ReadCols R, long long n_reads,
                                                    const long long* __restrict__ sample_off, int ns,
                                                    const uint32_t* __restrict__ flag_bits, int min_mapq,
-                                                   const long long* __restrict__ bounds, int nb,
+                                                   const long long* __restrict__ bounds, int nb, BucketDir D,
                                                    uint32_t* __restrict__ hist) {
   __shared__ uint32_t sh[kSmemIntervals];
   __shared__ int s_first, s_last;
@@ -114,8 +114,9 @@ __global__ void __launch_bounds__(256) k_read_hist(ReadCols R, long long n_reads
   auto take = [&](unsigned flag, int mapq, int tid, int ntid, int pos, long long q) {
     if (!read_passes(flag, mapq, tid, ntid, flag_bits, min_mapq)) return;
     if (tid < 0 || pos < 0) return;  // unplaced: no region contains it
-    const long long key = ((long long)tid << 32) | (long long)(unsigned)pos;
-    const int e = interval_of(key, bounds, nb);
+    const int e = D.first ? interval_by_bucket(tid, pos, bounds, D)
+                          : interval_of(((long long)tid << 32) | (long long)(unsigned)pos, bounds, nb);
+    if (e <= 0 || e >= nb) return;  // no region spans the first or the last interval
     if (local) atomicAdd(&sh[e], 1u);
     else atomicAdd(&hist[(long long)sample_of(q, sample_off, ns) * ne + e], 1u);
   };
@@ -129,21 +130,10 @@ __global__ void __launch_bounds__(256) k_read_hist(ReadCols R, long long n_reads
     const int tt[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
     const int nn[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
     const int pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
-    long long key[kReadsPerThread];
 #pragma unroll
-    for (int t = 0; t < kReadsPerThread; ++t) {
-      const bool ok = read_passes((fw[t >> 1] >> (16 * (t & 1))) & 0xFFFFu, (int)((mw[t >> 2] >> (8 * (t & 3))) & 0xFFu), tt[t],
-                                  nn[t], flag_bits, min_mapq) && tt[t] >= 0 && pp[t] >= 0;
-      key[t] = ok ? (((long long)tt[t] << 32) | (long long)(unsigned)pp[t]) : -1;  // -1: before every boundary
-    }
-    int e[kReadsPerThread];
-    interval_of_n<kReadsPerThread>(key, bounds, nb, e);
-#pragma unroll
-    for (int t = 0; t < kReadsPerThread; ++t) {
-      if (e[t] == 0 || e[t] == nb) continue;  // outside every region (no region spans the first or the last interval)
-      if (local) atomicAdd(&sh[e[t]], 1u);
-      else atomicAdd(&hist[(long long)sample_of(r + t, sample_off, ns) * ne + e[t]], 1u);
-    }
+    for (int t = 0; t < kReadsPerThread; ++t)
+      take((fw[t >> 1] >> (16 * (t & 1))) & 0xFFFFu, (int)((mw[t >> 2] >> (8 * (t & 3))) & 0xFFu), tt[t], nn[t], pp[t],
+           r + t);
   } else {
     for (long long q = r; q < r1; ++q) take(R.flag[q], R.mapq[q], R.tid[q], R.next_tid[q], R.pos[q], q);
   }
@@ -222,7 +212,8 @@ extern "C" size_t gridb200_count_reads_ws_bytes(int32_t ns, int32_t nb) {
 extern "C" int gridb200_count_reads(const uint16_t* flag, const uint8_t* mapq, const int32_t* tid, const int32_t* next_tid,
                                     const int32_t* pos, int64_t n_reads, const int64_t* sample_off, int32_t ns,
                                     const uint32_t* flag_bits, int32_t min_mapq, const int64_t* bounds, int32_t nb,
-                                    const int32_t* lo, const int32_t* hi, int32_t g_regions, int64_t* counts, void* ws,
+                                    const int32_t* lo, const int32_t* hi, int32_t g_regions, const int32_t* bucket_first,
+                                    int32_t bucket_shift, int32_t buckets_per_tid, int32_t n_tid, int64_t* counts, void* ws,
                                     size_t ws_bytes, void* stream) {
   using namespace g2;
   G2_REQUIRE(sample_off && flag_bits && counts && ns > 0 && n_reads >= 0 && g_regions > 0 && nb >= 0, GRIDB200_EINVAL,
@@ -232,6 +223,8 @@ extern "C" int gridb200_count_reads(const uint16_t* flag, const uint8_t* mapq, c
   G2_REQUIRE(((reinterpret_cast<uintptr_t>(flag) | reinterpret_cast<uintptr_t>(mapq) | reinterpret_cast<uintptr_t>(tid) |
                reinterpret_cast<uintptr_t>(next_tid) | reinterpret_cast<uintptr_t>(pos)) & 15) == 0,
              GRIDB200_EINVAL, "read columns must be 16-byte aligned");
+  G2_REQUIRE(!bucket_first || (bucket_shift >= 0 && bucket_shift < 31 && buckets_per_tid > 0 && n_tid > 0), GRIDB200_EINVAL,
+             "bad bucket directory");
   G2_REQUIRE(ws && ws_bytes >= gridb200_count_reads_ws_bytes(ns, nb), GRIDB200_EINVAL,
              "workspace too small: need %zu bytes", gridb200_count_reads_ws_bytes(ns, nb));
   cudaStream_t st = as_stream(stream);
@@ -243,7 +236,8 @@ extern "C" int gridb200_count_reads(const uint16_t* flag, const uint8_t* mapq, c
     G2_REQUIRE(blocks < (1LL << 31), GRIDB200_EINVAL, "too many reads in one call");
     ReadCols R{flag, mapq, tid, next_tid, pos};
     k_read_hist<<<(unsigned)blocks, 256, 0, st>>>(R, n_reads, reinterpret_cast<const long long*>(sample_off), ns, flag_bits,
-                                                 min_mapq, reinterpret_cast<const long long*>(bounds), nb, hist);
+                                                 min_mapq, reinterpret_cast<const long long*>(bounds), nb,
+                                                 BucketDir{bucket_first, bucket_shift, buckets_per_tid, n_tid}, hist);
     G2_LAUNCHED();
   }
   k_region_counts<<<(unsigned)ns, 256, 0, st>>>(hist, ne, lo, hi, g_regions, reinterpret_cast<long long*>(counts));

@@ -114,22 +114,22 @@ G2_HD int interval_of(long long key, const long long* bounds, int nb) {
   return lo;
 }
 
-// interval_of for N keys at once, branch-free and in lockstep (N independent loads per step instead of one dependent
-// chain per key): lo grows by descending powers of two while bounds[lo + step - 1] <= key.
-template <int N>
-G2_HD void interval_of_n(const long long (&key)[N], const long long* bounds, int nb, int (&out)[N]) {
-#pragma unroll
-  for (int t = 0; t < N; ++t) out[t] = 0;
-  int top = 1;
-  while (top * 2 <= nb) top *= 2;
-  for (int step = nb > 0 ? top : 0; step > 0; step >>= 1) {
-#pragma unroll
-    for (int t = 0; t < N; ++t) {
-      const int cand = out[t] + step;
-      const long long b = bounds[(cand <= nb ? cand : nb) - 1];
-      if (cand <= nb && b <= key[t]) out[t] = cand;
-    }
-  }
+// Coarse directory over the boundary table: bucket b = tid * per_tid + (pos >> shift) holds first[b] = number of
+// boundaries below the bucket's first key, so a position's interval is first[b] plus a search among the (usually zero
+// or one) boundaries that fall inside its bucket: one 8-byte load instead of log2(nb) dependent ones.
+// Returns -1 for a position no region can contain (reference beyond the last region's, or beyond the directory).
+struct BucketDir {
+  const int32_t* first;  // n_tid * per_tid + 1 entries
+  int shift, per_tid, n_tid;
+};
+
+G2_HD int interval_by_bucket(int tid, int pos, const long long* bounds, const BucketDir& D) {
+  const int col = pos >> D.shift;
+  if (tid >= D.n_tid || col >= D.per_tid) return -1;
+  const long long b = (long long)tid * D.per_tid + col;
+  const int lo = D.first[b], hi = D.first[b + 1];
+  const long long key = ((long long)tid << 32) | (long long)(unsigned)pos;
+  return lo + interval_of(key, bounds + lo, hi - lo);
 }
 
 }  // namespace g2

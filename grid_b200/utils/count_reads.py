@@ -49,7 +49,28 @@ def region_table(regions):
     return bounds, lo, hi
 
 
-def count_reads_columns(cols, sample_off, regions, proper_flags, min_mapq: int = 1):
+MAX_BUCKETS = 1 << 17  # directory entries (512 KB): small enough to live in L1/L2 next to the read stream
+
+
+def bucket_directory(bounds: np.ndarray):
+    """(first int32[n_tid * per_tid + 1], shift, per_tid, n_tid) over the sorted boundary keys: first[b] = number of keys
+    below the first key of bucket b = tid * per_tid + (pos >> shift).  None when there is no boundary at all."""
+    if bounds.size == 0:
+        return None
+    n_tid = int(bounds[-1] >> 32) + 1
+    max_pos = int((bounds & 0xFFFFFFFF).max())
+    shift = 10
+    while n_tid * ((max_pos >> shift) + 2) > MAX_BUCKETS and shift < 30:
+        shift += 1
+    per_tid = (max_pos >> shift) + 2          # one bucket past the last boundary: every region end lies inside
+    if n_tid * per_tid > (1 << 24):
+        return None                            # absurd reference ids: plain binary search
+    b = np.arange(n_tid * per_tid + 1, dtype=np.int64)
+    starts = ((b // per_tid) << 32) | ((b % per_tid) << shift)
+    return np.searchsorted(bounds, starts, side="left").astype(np.int32), shift, per_tid, n_tid
+
+
+def count_reads_columns(cols, sample_off, regions, proper_flags, min_mapq: int = 1, use_directory: bool = True):
     """counts[ns, G] (int64 tensor on the GPU) for ns samples' reads given as five columns (numpy arrays or CUDA
     tensors: flag u16, mapq u8, tid i32, next_tid i32, pos i32), sample s owning reads sample_off[s]:sample_off[s+1]."""
     import torch
@@ -86,9 +107,11 @@ def count_reads_columns(cols, sample_off, regions, proper_flags, min_mapq: int =
     d = lambda a: torch.from_numpy(a).to(dev)  # noqa: E731
     off_d, bits_d, bounds_d, lo_d, hi_d = d(off), d(flag_bitmap(proper_flags)), d(bounds), d(lo), d(hi)
     ws = torch.empty(lib.gridb200_count_reads_ws_bytes(ns, bounds.size), dtype=torch.uint8, device=dev)
+    directory = bucket_directory(bounds) if use_directory else None
+    first_d, shift, per_tid, n_tid = (d(directory[0]), *directory[1:]) if directory else (None, 0, 0, 0)
     call("gridb200_count_reads", ptr(flag), ptr(mapq), ptr(tid), ptr(ntid), ptr(pos), n, ptr(off_d), ns, ptr(bits_d), mm,
-         ptr(bounds_d), int(bounds.size), ptr(lo_d), ptr(hi_d), g, ptr(counts), ptr(ws), ws.numel(),
-         torch.cuda.current_stream().cuda_stream)
+         ptr(bounds_d), int(bounds.size), ptr(lo_d), ptr(hi_d), g, ptr(first_d), shift, per_tid, n_tid, ptr(counts),
+         ptr(ws), ws.numel(), torch.cuda.current_stream().cuda_stream)
     return counts
 
 

@@ -354,13 +354,18 @@ GRIDB200_API int gridb200_region_coverage(const char* text, int64_t nbytes, cons
  * (secondary), and start_g <= pos < end_g on the region's reference.
  * Regions arrive as a sorted table of distinct boundary keys, bounds[nb] with key = (tid << 32) | position, and per
  * region the indices lo_g / hi_g of its start / end key in that table (hi_g <= lo_g: empty region, count 0).
+ * bucket_first (device, optional): a directory over bounds -- entry tid * buckets_per_tid + (pos >> bucket_shift) =
+ * number of boundary keys below (tid << 32) | ((pos >> bucket_shift) << bucket_shift), n_tid * buckets_per_tid + 1
+ * entries, buckets_per_tid << bucket_shift beyond every region end; a read's interval then costs one load plus a
+ * search among the boundaries of its own bucket.  NULL: plain binary search over bounds.
  * counts (device, [ns][g_regions] int64, overwritten).  Columns must be 16-byte aligned.
  * ws: gridb200_count_reads_ws_bytes(ns, nb).  15 bytes per read of compulsory traffic. */
 GRIDB200_API size_t gridb200_count_reads_ws_bytes(int32_t ns, int32_t nb);
 GRIDB200_API int gridb200_count_reads(const uint16_t* flag, const uint8_t* mapq, const int32_t* tid, const int32_t* next_tid,
                          const int32_t* pos, int64_t n_reads, const int64_t* sample_off, int32_t ns,
                          const uint32_t* flag_bits, int32_t min_mapq, const int64_t* bounds, int32_t nb,
-                         const int32_t* lo, const int32_t* hi, int32_t g_regions, int64_t* counts,
+                         const int32_t* lo, const int32_t* hi, int32_t g_regions, const int32_t* bucket_first,
+                         int32_t bucket_shift, int32_t buckets_per_tid, int32_t n_tid, int64_t* counts,
                          void* ws, size_t ws_bytes, void* stream);
 
 #ifdef __cplusplus

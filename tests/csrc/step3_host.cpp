@@ -24,39 +24,30 @@ extern "C" void rl_region_coverage(const char* text, long long n, const char* ch
 extern "C" void rl_count_reads(const uint16_t* flag, const uint8_t* mapq, const int32_t* tid, const int32_t* ntid,
                                const int32_t* pos, long long n, const uint32_t* flag_bits, int min_mapq,
                                const long long* bounds, int nb, const int32_t* lo, const int32_t* hi, int g,
-                               long long* counts) {
+                               const int32_t* first, int shift, int per_tid, int n_tid, long long* counts) {
   std::vector<uint32_t> hist(nb + 1, 0);
-  long long r = 0;
-  for (; r + 8 <= n; r += 8) {  // the kernel's vector path: eight keys searched in lockstep, rejected reads as key -1
-    long long key[8];
-    int e[8];
-    for (int t = 0; t < 8; ++t) {
-      const bool ok = g2::read_passes(flag[r + t], mapq[r + t], tid[r + t], ntid[r + t], flag_bits, min_mapq) &&
-                      tid[r + t] >= 0 && pos[r + t] >= 0;
-      key[t] = ok ? (((long long)tid[r + t] << 32) | (long long)(unsigned)pos[r + t]) : -1;
-    }
-    g2::interval_of_n<8>(key, bounds, nb, e);
-    for (int t = 0; t < 8; ++t)
-      if (e[t] != 0 && e[t] != nb) ++hist[e[t]];
-  }
-  for (; r < n; ++r) {  // the kernel's tail path
+  const g2::BucketDir D{first, shift, per_tid, n_tid};
+  for (long long r = 0; r < n; ++r) {  // the body of k_read_hist's take()
     if (!g2::read_passes(flag[r], mapq[r], tid[r], ntid[r], flag_bits, min_mapq)) continue;
     if (tid[r] < 0 || pos[r] < 0) continue;
-    ++hist[g2::interval_of(((long long)tid[r] << 32) | (long long)(unsigned)pos[r], bounds, nb)];
+    const int e = D.first ? g2::interval_by_bucket(tid[r], pos[r], bounds, D)
+                          : g2::interval_of(((long long)tid[r] << 32) | (long long)(unsigned)pos[r], bounds, nb);
+    if (e <= 0 || e >= nb) continue;
+    ++hist[e];
   }
   for (int e = 1; e <= nb; ++e) hist[e] += hist[e - 1];
   for (int k = 0; k < g; ++k) counts[k] = hi[k] > lo[k] ? (long long)(hist[hi[k]] - hist[lo[k]]) : 0;
 }
 
-// interval_of_n against interval_of on arbitrary keys
-extern "C" int rl_interval_check(const long long* keys, long long n, const long long* bounds, int nb) {
-  for (long long r = 0; r + 8 <= n; r += 8) {
-    long long key[8];
-    int e[8];
-    for (int t = 0; t < 8; ++t) key[t] = keys[r + t];
-    g2::interval_of_n<8>(key, bounds, nb, e);
-    for (int t = 0; t < 8; ++t)
-      if (e[t] != g2::interval_of(key[t], bounds, nb)) return 0;
+// interval_by_bucket against interval_of on arbitrary positions: equal wherever the directory answers, and it may
+// decline (-1) only beyond every boundary of that reference
+extern "C" int rl_bucket_check(const int32_t* tid, const int32_t* pos, long long n, const long long* bounds, int nb,
+                               const int32_t* first, int shift, int per_tid, int n_tid) {
+  const g2::BucketDir D{first, shift, per_tid, n_tid};
+  for (long long r = 0; r < n; ++r) {
+    const long long key = ((long long)tid[r] << 32) | (long long)(unsigned)pos[r];
+    const int want = g2::interval_of(key, bounds, nb), got = g2::interval_by_bucket(tid[r], pos[r], bounds, D);
+    if (got >= 0 ? got != want : !(want == nb || (want < nb && (bounds[want] >> 32) > tid[r]))) return 0;
   }
   return 1;
 }

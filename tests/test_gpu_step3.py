@@ -178,6 +178,8 @@ def test_read_counts_many_regions_and_ragged_samples(mods):
             a = lo0 + int(rng.integers(0, 55_000))
             regions.append((int(rng.choice([5, 6, 6, 6, 7])), a, a + int(rng.integers(-20, 9_000))))
         got = cr.count_reads_columns(cols, off, regions, [83, 99, 147, 163], 1).cpu().numpy()
+        plain = cr.count_reads_columns(cols, off, regions, [83, 99, 147, 163], 1, use_directory=False).cpu().numpy()
+        assert (got == plain).all()          # bucket directory vs plain binary search over the boundary table
         sub = rng.choice(g, 40, replace=False)
         want = so.count_reads_regions(cols, off, [regions[k] for k in sub], [83, 99, 147, 163], 1)
         assert (got[:, sub] == want).all()

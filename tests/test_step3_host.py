@@ -75,7 +75,8 @@ def hostlib(tmp_path_factory):
     lib = C.CDLL(str(out))
     lib.rl_region_coverage.argtypes = [C.c_char_p, C.c_longlong, C.c_char_p, C.c_int, C.c_longlong, C.c_longlong, C.c_void_p]
     lib.rl_count_reads.argtypes = [C.c_void_p] * 5 + [C.c_longlong, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
-                                                      C.c_void_p, C.c_int, C.c_void_p]
+                                                      C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
+    lib.rl_bucket_check.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int]
     return lib
 
 
@@ -206,14 +207,17 @@ def test_decision_never_contradicts_the_float_evaluation():
 
 
 # ---- read counting ---------------------------------------------------------------------------------------------------
-def host_counts(lib, cols, off, regions, flags, min_mapq):
+def host_counts(lib, cols, off, regions, flags, min_mapq, use_directory=True):
     bounds, lo, hi = gcr.region_table(regions)
     bits = gcr.flag_bitmap(flags)
+    directory = gcr.bucket_directory(bounds) if use_directory else None
+    first, shift, per_tid, n_tid = directory if directory else (None, 0, 0, 0)
     out = np.zeros((len(off) - 1, len(regions)), dtype=np.int64)
     for s in range(len(off) - 1):
         sl = [np.ascontiguousarray(c[off[s]:off[s + 1]]) for c in cols]
         lib.rl_count_reads(*(c.ctypes.data for c in sl), len(sl[0]), bits.ctypes.data, int(min_mapq), bounds.ctypes.data,
-                           len(bounds), lo.ctypes.data, hi.ctypes.data, len(regions), out[s].ctypes.data)
+                           len(bounds), lo.ctypes.data, hi.ctypes.data, len(regions),
+                           first.ctypes.data if first is not None else None, shift, per_tid, n_tid, out[s].ctypes.data)
     return out
 
 
@@ -238,14 +242,28 @@ def test_region_table_handles_overlap_nesting_and_empty_regions(hostlib):
     assert want.sum() > 0
 
 
-def test_lockstep_interval_search_equals_the_scalar_one(hostlib):
+def test_bucket_directory_equals_the_binary_search(hostlib, monkeypatch):
     rng = np.random.default_rng(5)
-    hostlib.rl_interval_check.argtypes = [C.c_void_p, C.c_longlong, C.c_void_p, C.c_int]
-    for nb in (0, 1, 2, 3, 7, 8, 9, 1000, 1468, 4095, 4097):
-        bounds = np.unique(rng.integers(0, 1 << 40, nb).astype(np.int64))
-        keys = np.concatenate([rng.integers(-5, 1 << 40, 4000), bounds, bounds - 1, bounds + 1, [-1, 0, (1 << 62)]]).astype(np.int64)
-        keys = np.ascontiguousarray(keys[: len(keys) // 8 * 8])
-        assert hostlib.rl_interval_check(keys.ctypes.data, len(keys), bounds.ctypes.data, len(bounds)) == 1, nb
+    for nb, max_tid, max_pos, cap in [(1, 0, 1000, 1 << 17), (2, 3, 5000, 1 << 17), (1468, 24, 250_000_000, 1 << 17),
+                                      (4000, 2, 3_000_000, 64), (300, 40, (1 << 31) - 1, 1 << 12)]:
+        monkeypatch.setattr(gcr, "MAX_BUCKETS", cap)
+        keys = (rng.integers(0, max_tid + 1, nb).astype(np.int64) << 32) | rng.integers(0, max_pos + 1, nb).astype(np.int64)
+        bounds = np.unique(keys)
+        first, shift, per_tid, n_tid = gcr.bucket_directory(bounds)
+        assert len(first) == n_tid * per_tid + 1 <= max(cap, n_tid * 2) + 1 and first[-1] <= len(bounds)
+        tid = np.concatenate([rng.integers(0, max_tid + 3, 6000), bounds >> 32, bounds >> 32, bounds >> 32]).astype(np.int32)
+        bp = (bounds & 0xFFFFFFFF)
+        pos = np.concatenate([rng.integers(0, min(max_pos * 2 + 10, (1 << 31) - 1), 6000), bp, np.maximum(bp - 1, 0),
+                              np.minimum(bp + 1, (1 << 31) - 1)]).astype(np.int32)
+        assert hostlib.rl_bucket_check(tid.ctypes.data, pos.ctypes.data, len(tid), bounds.ctypes.data, len(bounds),
+                                       first.ctypes.data, shift, per_tid, n_tid) == 1, (nb, max_tid)
+
+
+def test_counts_with_and_without_the_directory_agree(hostlib):
+    kw = STEP3_READS["mapq1"]
+    cols, off = synth.read_columns(kw["seed"], kw["ns"], kw["mean_reads"])
+    a = host_counts(hostlib, cols, off, synth.READ_REGIONS, kw["flags"], 1, use_directory=False)
+    assert a.tolist() == GOLD["reads"]["mapq1"]
 
 
 def test_flag_bitmap_is_an_exact_value_test():
