@@ -88,31 +88,45 @@ __device__ __forceinline__ int sample_of(long long r, const long long* __restric
   return lo;
 }
 
+// 128-/64-bit streaming loads that do not allocate in L1: the read columns are touched once, and L1 is better spent
+// on the bucket directory and the boundary table (ncu: with plain loads the lookups cost 2.2 GB of L2->SM traffic
+// on top of the 1.5 GB of columns).
+__device__ __forceinline__ uint4 ld_stream_u4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint2 ld_stream_u2(const void* p) {
+  uint2 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+  return r;
+}
+
 // hist[s, e] += reads of sample s that pass the filter and fall into elementary interval e of the region boundaries.
-// A block takes 2048 consecutive reads (one 16-byte load per column and thread where the column's element size
-// allows); when they all belong to one sample -- nearly always -- the histogram is built in shared memory.
+// A block takes kChunks x 2048 consecutive reads (one 16-byte load per column and thread where the column's element
+// size allows); when they all belong to one sample -- nearly always -- the histogram is built in shared memory.
+constexpr int kChunks = 4;
+
 __global__ void __launch_bounds__(256) k_read_hist(ReadCols R, long long n_reads,
                                                    const long long* __restrict__ sample_off, int ns,
-                                                   const uint32_t* __restrict__ flag_bits, int min_mapq,
+                                                   const uint32_t* __restrict__ flag_bits, const FlagSet F, int min_mapq,
                                                    const long long* __restrict__ bounds, int nb, BucketDir D,
                                                    uint32_t* __restrict__ hist) {
   __shared__ uint32_t sh[kSmemIntervals];
   __shared__ int s_first, s_last;
-  const long long r0 = (long long)blockIdx.x * kReadsPerBlock;
-  const long long r1 = r0 + kReadsPerBlock < n_reads ? r0 + kReadsPerBlock : n_reads;
+  const long long r0 = (long long)blockIdx.x * (kReadsPerBlock * kChunks);
+  const long long r1 = r0 + kReadsPerBlock * kChunks < n_reads ? r0 + kReadsPerBlock * kChunks : n_reads;
   const int ne = nb + 1;
-  if (threadIdx.x == 0) {
-    s_first = sample_of(r0, sample_off, ns);
-    s_last = sample_of(r1 - 1, sample_off, ns);
-  }
+  if (threadIdx.x == 0) s_first = sample_of(r0, sample_off, ns);
+  if (threadIdx.x == 32) s_last = sample_of(r1 - 1, sample_off, ns);
   const bool fits = ne <= kSmemIntervals;
   if (fits)
     for (int e = threadIdx.x; e < ne; e += blockDim.x) sh[e] = 0;
   __syncthreads();
   const bool local = fits && s_first == s_last;
-  const long long r = r0 + (long long)threadIdx.x * kReadsPerThread;
   auto take = [&](unsigned flag, int mapq, int tid, int ntid, int pos, long long q) {
-    if (!read_passes(flag, mapq, tid, ntid, flag_bits, min_mapq)) return;
+    // count_reads.py:96-100, then the position test as an interval lookup
+    if (!read_passes(flag, mapq, tid, ntid, F, flag_bits, min_mapq)) return;
     if (tid < 0 || pos < 0) return;  // unplaced: no region contains it
     const int e = D.first ? interval_by_bucket(tid, pos, bounds, D)
                           : interval_of(((long long)tid << 32) | (long long)(unsigned)pos, bounds, nb);
@@ -120,22 +134,27 @@ __global__ void __launch_bounds__(256) k_read_hist(ReadCols R, long long n_reads
     if (local) atomicAdd(&sh[e], 1u);
     else atomicAdd(&hist[(long long)sample_of(q, sample_off, ns) * ne + e], 1u);
   };
-  if (r + kReadsPerThread <= r1) {
-    const uint4 f = *reinterpret_cast<const uint4*>(R.flag + r);
-    const uint2 m = *reinterpret_cast<const uint2*>(R.mapq + r);
-    const uint32_t fw[4] = {f.x, f.y, f.z, f.w}, mw[2] = {m.x, m.y};
-    const int4 t0 = reinterpret_cast<const int4*>(R.tid + r)[0], t1 = reinterpret_cast<const int4*>(R.tid + r)[1];
-    const int4 n0 = reinterpret_cast<const int4*>(R.next_tid + r)[0], n1 = reinterpret_cast<const int4*>(R.next_tid + r)[1];
-    const int4 p0 = reinterpret_cast<const int4*>(R.pos + r)[0], p1 = reinterpret_cast<const int4*>(R.pos + r)[1];
-    const int tt[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
-    const int nn[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
-    const int pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+#pragma unroll 1
+  for (int c = 0; c < kChunks; ++c) {
+    const long long r = r0 + (long long)c * kReadsPerBlock + (long long)threadIdx.x * kReadsPerThread;
+    if (r >= r1) break;
+    if (r + kReadsPerThread <= r1) {
+      const uint4 f = ld_stream_u4(R.flag + r);
+      const uint2 m = ld_stream_u2(R.mapq + r);
+      const uint4 t0 = ld_stream_u4(R.tid + r), t1 = ld_stream_u4(R.tid + r + 4);
+      const uint4 n0 = ld_stream_u4(R.next_tid + r), n1 = ld_stream_u4(R.next_tid + r + 4);
+      const uint4 p0 = ld_stream_u4(R.pos + r), p1 = ld_stream_u4(R.pos + r + 4);
+      const uint32_t fw[4] = {f.x, f.y, f.z, f.w}, mw[2] = {m.x, m.y};
+      const uint32_t tt[8] = {t0.x, t0.y, t0.z, t0.w, t1.x, t1.y, t1.z, t1.w};
+      const uint32_t nn[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
+      const uint32_t pp[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
 #pragma unroll
-    for (int t = 0; t < kReadsPerThread; ++t)
-      take((fw[t >> 1] >> (16 * (t & 1))) & 0xFFFFu, (int)((mw[t >> 2] >> (8 * (t & 3))) & 0xFFu), tt[t], nn[t], pp[t],
-           r + t);
-  } else {
-    for (long long q = r; q < r1; ++q) take(R.flag[q], R.mapq[q], R.tid[q], R.next_tid[q], R.pos[q], q);
+      for (int t = 0; t < kReadsPerThread; ++t)
+        take((fw[t >> 1] >> (16 * (t & 1))) & 0xFFFFu, (int)((mw[t >> 2] >> (8 * (t & 3))) & 0xFFu), (int)tt[t], (int)nn[t],
+             (int)pp[t], r + t);
+    } else {
+      for (long long q = r; q < r1; ++q) take(R.flag[q], R.mapq[q], R.tid[q], R.next_tid[q], R.pos[q], q);
+    }
   }
   if (local) {
     __syncthreads();
@@ -211,7 +230,8 @@ extern "C" size_t gridb200_count_reads_ws_bytes(int32_t ns, int32_t nb) {
 
 extern "C" int gridb200_count_reads(const uint16_t* flag, const uint8_t* mapq, const int32_t* tid, const int32_t* next_tid,
                                     const int32_t* pos, int64_t n_reads, const int64_t* sample_off, int32_t ns,
-                                    const uint32_t* flag_bits, int32_t min_mapq, const int64_t* bounds, int32_t nb,
+                                    const uint32_t* flag_bits, const uint16_t* flag_set_host, int32_t flag_set_n,
+                                    int32_t min_mapq, const int64_t* bounds, int32_t nb,
                                     const int32_t* lo, const int32_t* hi, int32_t g_regions, const int32_t* bucket_first,
                                     int32_t bucket_shift, int32_t buckets_per_tid, int32_t n_tid, int64_t* counts, void* ws,
                                     size_t ws_bytes, void* stream) {
@@ -232,11 +252,20 @@ extern "C" int gridb200_count_reads(const uint16_t* flag, const uint8_t* mapq, c
   const int ne = nb + 1;
   G2_CUDA(cudaMemsetAsync(hist, 0, (size_t)ns * ne * sizeof(uint32_t), st));
   if (n_reads > 0) {
-    const long long blocks = (n_reads + kReadsPerBlock - 1) / kReadsPerBlock;
+    const long long per_block = (long long)kReadsPerBlock * kChunks;
+    const long long blocks = (n_reads + per_block - 1) / per_block;
     G2_REQUIRE(blocks < (1LL << 31), GRIDB200_EINVAL, "too many reads in one call");
     ReadCols R{flag, mapq, tid, next_tid, pos};
+    FlagSet F;
+    memset(&F, 0, sizeof(F));
+    if (flag_set_n >= 0 && flag_set_n <= 8 && (flag_set_n == 0 || flag_set_host)) {
+      for (int t = 0; t < flag_set_n; ++t) F.v[t] = flag_set_host[t];
+      F.n = flag_set_n;
+    } else {
+      F.n = -1;
+    }
     k_read_hist<<<(unsigned)blocks, 256, 0, st>>>(R, n_reads, reinterpret_cast<const long long*>(sample_off), ns, flag_bits,
-                                                 min_mapq, reinterpret_cast<const long long*>(bounds), nb,
+                                                 F, min_mapq, reinterpret_cast<const long long*>(bounds), nb,
                                                  BucketDir{bucket_first, bucket_shift, buckets_per_tid, n_tid}, hist);
     G2_LAUNCHED();
   }
