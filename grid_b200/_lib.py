@@ -62,8 +62,8 @@ SIGNATURES = {
                                            _sz, _vp]),
     "gridb200_region_coverage": (C.c_int, [_vp, _i64, _vp, _i32, C.c_char_p, _i32, _i64, _i64, _vp, _vp]),
     "gridb200_count_reads_ws_bytes": (_sz, [_i32, _i32]),
-    "gridb200_count_reads": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _i32, _vp, _vp, _i32, _i32, _vp, _i32, _vp, _vp,
-                                       _i32, _vp, _i32, _i32, _i32, _vp, _vp, _sz, _vp]),
+    "gridb200_count_reads": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _i64, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _vp, _i32,
+                                       _vp, _i32, _i32, _i32, _vp, _vp, _sz, _vp]),
 }
 
 

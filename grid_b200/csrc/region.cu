@@ -109,7 +109,7 @@ constexpr int kChunks = 4;
 
 __global__ void __launch_bounds__(256) k_read_hist(ReadCols R, long long n_reads,
                                                    const long long* __restrict__ sample_off, int ns,
-                                                   const uint32_t* __restrict__ flag_bits, const FlagSet F, int min_mapq,
+                                                   const uint32_t* __restrict__ flag_bits, int min_mapq,
                                                    const long long* __restrict__ bounds, int nb, BucketDir D,
                                                    uint32_t* __restrict__ hist) {
   __shared__ uint32_t sh[kSmemIntervals];
@@ -126,7 +126,7 @@ __global__ void __launch_bounds__(256) k_read_hist(ReadCols R, long long n_reads
   const bool local = fits && s_first == s_last;
   auto take = [&](unsigned flag, int mapq, int tid, int ntid, int pos, long long q) {
     // count_reads.py:96-100, then the position test as an interval lookup
-    if (!read_passes(flag, mapq, tid, ntid, F, flag_bits, min_mapq)) return;
+    if (!read_passes(flag, mapq, tid, ntid, flag_bits, min_mapq)) return;
     if (tid < 0 || pos < 0) return;  // unplaced: no region contains it
     const int e = D.first ? interval_by_bucket(tid, pos, bounds, D)
                           : interval_of(((long long)tid << 32) | (long long)(unsigned)pos, bounds, nb);
@@ -230,8 +230,7 @@ extern "C" size_t gridb200_count_reads_ws_bytes(int32_t ns, int32_t nb) {
 
 extern "C" int gridb200_count_reads(const uint16_t* flag, const uint8_t* mapq, const int32_t* tid, const int32_t* next_tid,
                                     const int32_t* pos, int64_t n_reads, const int64_t* sample_off, int32_t ns,
-                                    const uint32_t* flag_bits, const uint16_t* flag_set_host, int32_t flag_set_n,
-                                    int32_t min_mapq, const int64_t* bounds, int32_t nb,
+                                    const uint32_t* flag_bits, int32_t min_mapq, const int64_t* bounds, int32_t nb,
                                     const int32_t* lo, const int32_t* hi, int32_t g_regions, const int32_t* bucket_first,
                                     int32_t bucket_shift, int32_t buckets_per_tid, int32_t n_tid, int64_t* counts, void* ws,
                                     size_t ws_bytes, void* stream) {
@@ -256,16 +255,8 @@ extern "C" int gridb200_count_reads(const uint16_t* flag, const uint8_t* mapq, c
     const long long blocks = (n_reads + per_block - 1) / per_block;
     G2_REQUIRE(blocks < (1LL << 31), GRIDB200_EINVAL, "too many reads in one call");
     ReadCols R{flag, mapq, tid, next_tid, pos};
-    FlagSet F;
-    memset(&F, 0, sizeof(F));
-    if (flag_set_n >= 0 && flag_set_n <= 8 && (flag_set_n == 0 || flag_set_host)) {
-      for (int t = 0; t < flag_set_n; ++t) F.v[t] = flag_set_host[t];
-      F.n = flag_set_n;
-    } else {
-      F.n = -1;
-    }
     k_read_hist<<<(unsigned)blocks, 256, 0, st>>>(R, n_reads, reinterpret_cast<const long long*>(sample_off), ns, flag_bits,
-                                                 F, min_mapq, reinterpret_cast<const long long*>(bounds), nb,
+                                                 min_mapq, reinterpret_cast<const long long*>(bounds), nb,
                                                  BucketDir{bucket_first, bucket_shift, buckets_per_tid, n_tid}, hist);
     G2_LAUNCHED();
   }

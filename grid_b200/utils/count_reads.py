@@ -70,8 +70,7 @@ def bucket_directory(bounds: np.ndarray):
     return np.searchsorted(bounds, starts, side="left").astype(np.int32), shift, per_tid, n_tid
 
 
-def count_reads_columns(cols, sample_off, regions, proper_flags, min_mapq: int = 1, use_directory: bool = True,
-                        use_flag_set: bool = True):
+def count_reads_columns(cols, sample_off, regions, proper_flags, min_mapq: int = 1, use_directory: bool = True):
     """counts[ns, G] (int64 tensor on the GPU) for ns samples' reads given as five columns (numpy arrays or CUDA
     tensors: flag u16, mapq u8, tid i32, next_tid i32, pos i32), sample s owning reads sample_off[s]:sample_off[s+1]."""
     import torch
@@ -110,11 +109,7 @@ def count_reads_columns(cols, sample_off, regions, proper_flags, min_mapq: int =
     ws = torch.empty(lib.gridb200_count_reads_ws_bytes(ns, bounds.size), dtype=torch.uint8, device=dev)
     directory = bucket_directory(bounds) if use_directory else None
     first_d, shift, per_tid, n_tid = (d(directory[0]), *directory[1:]) if directory else (None, 0, 0, 0)
-    bits = flag_bitmap(proper_flags)
-    members = np.flatnonzero(np.unpackbits(bits.view(np.uint8), bitorder="little")).astype(np.uint16)
-    small = members if members.size <= 8 and use_flag_set else None
-    call("gridb200_count_reads", ptr(flag), ptr(mapq), ptr(tid), ptr(ntid), ptr(pos), n, ptr(off_d), ns, ptr(bits_d),
-         small.ctypes.data if small is not None and small.size else None, int(small.size) if small is not None else -1, mm,
+    call("gridb200_count_reads", ptr(flag), ptr(mapq), ptr(tid), ptr(ntid), ptr(pos), n, ptr(off_d), ns, ptr(bits_d), mm,
          ptr(bounds_d), int(bounds.size), ptr(lo_d), ptr(hi_d), g, ptr(first_d), shift, per_tid, n_tid, ptr(counts),
          ptr(ws), ws.numel(), torch.cuda.current_stream().cuda_stream)
     return counts

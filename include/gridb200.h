@@ -350,8 +350,7 @@ GRIDB200_API int gridb200_region_coverage(const char* text, int64_t nbytes, cons
 /* The read filter of count_reads_in_region (count_reads.py:95-105) over columnar read records, for a batch of
  * samples and G regions at once.  Read r of sample s: sample_off[s] <= r < sample_off[s+1] (device, ns+1 entries).
  * A read is counted when flag_bits has bit `flag` set (65536 bits = 2048 words: the exact-value test
- * `read.flag in proper_flags`; when the set has at most 8 members the caller may also pass them as flag_set_host
- * [flag_set_n], a HOST array -- they are then compared in registers and the table is not read; flag_set_n < 0: table), mapq >= min_mapq, tid == next_tid, flag & 0x400 == 0 (duplicate), flag & 0x100 == 0
+ * `read.flag in proper_flags` -- 8 KB that stay in L1), mapq >= min_mapq, tid == next_tid, flag & 0x400 == 0 (duplicate), flag & 0x100 == 0
  * (secondary), and start_g <= pos < end_g on the region's reference.
  * Regions arrive as a sorted table of distinct boundary keys, bounds[nb] with key = (tid << 32) | position, and per
  * region the indices lo_g / hi_g of its start / end key in that table (hi_g <= lo_g: empty region, count 0).
@@ -364,8 +363,7 @@ GRIDB200_API int gridb200_region_coverage(const char* text, int64_t nbytes, cons
 GRIDB200_API size_t gridb200_count_reads_ws_bytes(int32_t ns, int32_t nb);
 GRIDB200_API int gridb200_count_reads(const uint16_t* flag, const uint8_t* mapq, const int32_t* tid, const int32_t* next_tid,
                          const int32_t* pos, int64_t n_reads, const int64_t* sample_off, int32_t ns,
-                         const uint32_t* flag_bits, const uint16_t* flag_set_host, int32_t flag_set_n,
-                         int32_t min_mapq, const int64_t* bounds, int32_t nb,
+                         const uint32_t* flag_bits, int32_t min_mapq, const int64_t* bounds, int32_t nb,
                          const int32_t* lo, const int32_t* hi, int32_t g_regions, const int32_t* bucket_first,
                          int32_t bucket_shift, int32_t buckets_per_tid, int32_t n_tid, int64_t* counts,
                          void* ws, size_t ws_bytes, void* stream);

@@ -22,17 +22,13 @@ extern "C" void rl_region_coverage(const char* text, long long n, const char* ch
 }
 
 extern "C" void rl_count_reads(const uint16_t* flag, const uint8_t* mapq, const int32_t* tid, const int32_t* ntid,
-                               const int32_t* pos, long long n, const uint32_t* flag_bits, const uint16_t* flag_set,
-                               int flag_set_n, int min_mapq,
+                               const int32_t* pos, long long n, const uint32_t* flag_bits, int min_mapq,
                                const long long* bounds, int nb, const int32_t* lo, const int32_t* hi, int g,
                                const int32_t* first, int shift, int per_tid, int n_tid, long long* counts) {
   std::vector<uint32_t> hist(nb + 1, 0);
   const g2::BucketDir D{first, shift, per_tid, n_tid};
-  g2::FlagSet F = {};
-  F.n = flag_set_n;
-  for (int t = 0; t < flag_set_n && t < 8; ++t) F.v[t] = flag_set[t];
   for (long long r = 0; r < n; ++r) {  // the body of k_read_hist's take()
-    if (!g2::read_passes(flag[r], mapq[r], tid[r], ntid[r], F, flag_bits, min_mapq)) continue;
+    if (!g2::read_passes(flag[r], mapq[r], tid[r], ntid[r], flag_bits, min_mapq)) continue;
     if (tid[r] < 0 || pos[r] < 0) continue;
     const int e = D.first ? g2::interval_by_bucket(tid[r], pos[r], bounds, D)
                           : g2::interval_of(((long long)tid[r] << 32) | (long long)(unsigned)pos[r], bounds, nb);

@@ -180,9 +180,7 @@ def test_read_counts_many_regions_and_ragged_samples(mods):
         got = cr.count_reads_columns(cols, off, regions, [83, 99, 147, 163], 1).cpu().numpy()
         plain = cr.count_reads_columns(cols, off, regions, [83, 99, 147, 163], 1, use_directory=False).cpu().numpy()
         assert (got == plain).all()          # bucket directory vs plain binary search over the boundary table
-        table = cr.count_reads_columns(cols, off, regions, [83, 99, 147, 163], 1, use_flag_set=False).cpu().numpy()
-        assert (got == table).all()          # flags compared in registers vs the 65536-bit table
-        many = list(range(60, 180))          # more than 8 flags: always the table
+        many = list(range(60, 180))
         assert (cr.count_reads_columns(cols, off, regions[:50], many, 1).cpu().numpy()
                 == so.count_reads_regions(cols, off, regions[:50], many, 1)).all()
         sub = rng.choice(g, 40, replace=False)

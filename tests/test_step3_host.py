@@ -74,9 +74,8 @@ def hostlib(tmp_path_factory):
                    check=True)
     lib = C.CDLL(str(out))
     lib.rl_region_coverage.argtypes = [C.c_char_p, C.c_longlong, C.c_char_p, C.c_int, C.c_longlong, C.c_longlong, C.c_void_p]
-    lib.rl_count_reads.argtypes = [C.c_void_p] * 5 + [C.c_longlong, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
-                                                      C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int,
-                                                      C.c_int, C.c_void_p]
+    lib.rl_count_reads.argtypes = [C.c_void_p] * 5 + [C.c_longlong, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p,
+                                                      C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]
     lib.rl_bucket_check.argtypes = [C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int]
     return lib
 
@@ -208,18 +207,15 @@ def test_decision_never_contradicts_the_float_evaluation():
 
 
 # ---- read counting ---------------------------------------------------------------------------------------------------
-def host_counts(lib, cols, off, regions, flags, min_mapq, use_directory=True, use_flag_set=True):
+def host_counts(lib, cols, off, regions, flags, min_mapq, use_directory=True):
     bounds, lo, hi = gcr.region_table(regions)
     bits = gcr.flag_bitmap(flags)
-    members = np.flatnonzero(np.unpackbits(bits.view(np.uint8), bitorder="little")).astype(np.uint16)
-    fs_n = len(members) if use_flag_set and len(members) <= 8 else -1
     directory = gcr.bucket_directory(bounds) if use_directory else None
     first, shift, per_tid, n_tid = directory if directory else (None, 0, 0, 0)
     out = np.zeros((len(off) - 1, len(regions)), dtype=np.int64)
     for s in range(len(off) - 1):
         sl = [np.ascontiguousarray(c[off[s]:off[s + 1]]) for c in cols]
-        lib.rl_count_reads(*(c.ctypes.data for c in sl), len(sl[0]), bits.ctypes.data, members.ctypes.data, fs_n,
-                           int(min_mapq), bounds.ctypes.data,
+        lib.rl_count_reads(*(c.ctypes.data for c in sl), len(sl[0]), bits.ctypes.data, int(min_mapq), bounds.ctypes.data,
                            len(bounds), lo.ctypes.data, hi.ctypes.data, len(regions),
                            first.ctypes.data if first is not None else None, shift, per_tid, n_tid, out[s].ctypes.data)
     return out
@@ -268,9 +264,7 @@ def test_counts_with_and_without_the_directory_agree(hostlib):
     cols, off = synth.read_columns(kw["seed"], kw["ns"], kw["mean_reads"])
     a = host_counts(hostlib, cols, off, synth.READ_REGIONS, kw["flags"], 1, use_directory=False)
     assert a.tolist() == GOLD["reads"]["mapq1"]
-    b = host_counts(hostlib, cols, off, synth.READ_REGIONS, kw["flags"], 1, use_flag_set=False)   # 65536-bit table
-    assert b.tolist() == GOLD["reads"]["mapq1"]
-    many = list(range(60, 180))                                                                   # > 8 flags: table
+    many = list(range(60, 180))
     c = host_counts(hostlib, cols, off, synth.READ_REGIONS, many, 1)
     assert c.tolist() == so.count_reads_regions(cols, off, synth.READ_REGIONS, many, 1).tolist() and c.sum() > 0
 

@@ -88,12 +88,9 @@ ws = torch.empty(load().gridb200_count_reads_ws_bytes(ns, bounds.size), dtype=to
 out_k = torch.empty((ns, g_regions), dtype=torch.int64, device=dev)
 
 
-flag_arr = np.asarray(flags, dtype=np.uint16)
-
-
-def kernels(directory, flag_set=True):
-    call("gridb200_count_reads", ptr(flag), ptr(mapq), ptr(tid), ptr(ntid), ptr(pos), reads, ptr(t_off), ns, ptr(t_bits),
-         flag_arr.ctypes.data if flag_set else None, len(flags) if flag_set else -1, 1, ptr(t_bounds), int(bounds.size), ptr(t_lo), ptr(t_hi), g_regions, ptr(t_first) if directory else None, shift, per_tid,
+def kernels(directory):
+    call("gridb200_count_reads", ptr(flag), ptr(mapq), ptr(tid), ptr(ntid), ptr(pos), reads, ptr(t_off), ns, ptr(t_bits), 1,
+         ptr(t_bounds), int(bounds.size), ptr(t_lo), ptr(t_hi), g_regions, ptr(t_first) if directory else None, shift, per_tid,
          n_tid, ptr(out_k), ptr(ws), ws.numel(), st)
 
 
@@ -110,8 +107,6 @@ ms = timed(lambda: kernels(True))
 same = bool((out_k == counts).all())
 ms_plain = timed(lambda: kernels(False))
 same = same and bool((out_k == counts).all())
-ms_table = timed(lambda: kernels(True, flag_set=False))
-same = same and bool((out_k == counts).all())
 # check one sample against the oracle, and time the oracle's G passes over it
 s = 5
 sl_cols = [c[sample_off[s]:sample_off[s + 1]].cpu().numpy() for c in (flag.view(torch.int16), mapq, tid, ntid, pos)]
@@ -120,7 +115,7 @@ t0 = time.perf_counter()
 want = so.count_reads_regions(sl_cols, [0, len(sl_cols[0])], regions[:32], flags, 1)
 t_np = time.perf_counter() - t0
 res["count_reads"] = {"workload": f"{reads} reads in {ns} samples x {g_regions} regions, one pass", "ms": round(ms, 3),
-                      "ms_plain_binary_search": round(ms_plain, 3), "ms_flag_table_instead_of_registers": round(ms_table, 3), "ms_python_call_with_table_build": round(ms_call, 3),
+                      "ms_plain_binary_search": round(ms_plain, 3), "ms_python_call_with_table_build": round(ms_call, 3),
                       "directory": {"shift": shift, "buckets": int(first.size), "ms_by_buckets": sweep}, "kernels_agree": same,
                       "reads_per_s": round(reads / ms * 1e3), "GBps_at_15B_per_read": round(15 * reads / ms / 1e6, 1),
                       "frac_hbm": round(15 * reads / ms / 1e6 / hbm, 3), "total_counted": int(counts.sum()),
