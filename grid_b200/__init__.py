@@ -11,6 +11,15 @@ STEP_TARGETS = {
 }
 
 
+# Helpers of the steps before the path, rebound at function level: run_mosdepth_single_cram calls
+# compute_region_coverage (mosdepth.py:185) and process_single_cram calls count_reads_in_region (count_reads.py:137) through
+# their module globals.  Optional: the reference's count_reads module needs pysam to import at all.
+HELPER_TARGETS = {
+    "grid.utils.mosdepth": ("compute_region_coverage", "grid_b200.utils.mosdepth"),
+    "grid.utils.count_reads": ("count_reads_in_region", "grid_b200.utils.count_reads"),
+}
+
+
 def install() -> None:
     """Rebind the step functions on the reference's modules so `grid wgs config.yaml` runs them on the GPU.
 
@@ -25,3 +34,9 @@ def install() -> None:
     _lib.load()  # fail now, loudly, if the CUDA library is not built
     for ref_mod, (fn, mine) in STEP_TARGETS.items():
         setattr(importlib.import_module(ref_mod), fn, getattr(importlib.import_module(mine), fn))
+    for ref_mod, (fn, mine) in HELPER_TARGETS.items():
+        try:
+            target = importlib.import_module(ref_mod)
+        except ImportError:
+            continue
+        setattr(target, fn, getattr(importlib.import_module(mine), fn))

@@ -78,11 +78,19 @@ def test_install_rebinds_reference_steps(monkeypatch):
         setattr(m, fn, lambda config, console: "reference")
         setattr(utils, name, m)
         mods[f"grid.utils.{name}"] = m
+    md = types.ModuleType("grid.utils.mosdepth")           # helper-level target; grid.utils.count_reads is absent here
+    md.compute_region_coverage = lambda *a: "reference"     # (it needs pysam), which install() must tolerate
+    utils.mosdepth = md
+    mods["grid.utils.mosdepth"] = md
     for k, v in mods.items():
         monkeypatch.setitem(sys.modules, k, v)
+    monkeypatch.setitem(sys.modules, "grid.utils.count_reads", None)   # import raises ImportError
     import grid_b200
 
     grid_b200.install()
+    from grid_b200.utils import mosdepth as our_md
+
+    assert md.compute_region_coverage is our_md.compute_region_coverage
     from grid_b200.utils import compute_dipcn, find_neighbors, hi_inference, normalize_mosdepth
 
     assert mods["grid.utils.hi_inference"].hi_inference is hi_inference.hi_inference
