@@ -109,7 +109,7 @@ def run_reference(a):
         "e2e": {"value": val, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -365,13 +365,27 @@ def run_ours(a):
         }
         if world == 1 and not a.no_cpu:
             line["cpu_baseline"] = cpu_baseline(a)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if group is not None:
         dist.destroy_process_group()
 
 
+_RESULT_FD = 1
+
+
+def emit(line: dict) -> None:
+    """The ONE JSON line, on the process's original stdout."""
+    os.write(_RESULT_FD, (json.dumps(line) + "\n").encode())
+
+
 def main():
+    global _RESULT_FD
     a = parse_args()
+    # Libraries write banners to file descriptor 1 (NCCL prints its version there at NCCL_DEBUG=WARN): keep the real
+    # stdout for the result line only and send everything else that lands on fd 1 to stderr.
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     if a.impl == "reference":
         run_reference(a)
     else:
