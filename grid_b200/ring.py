@@ -33,20 +33,22 @@ def ring_source(rank: int, step: int, world: int) -> int:
 
 
 def ring_knn(shard: torch.Tensor, shard_rows_max: int, counts: list[int], offsets: list[int], group, block_fn,
-             flat_per_row: int) -> None:
+             flat_per_row: int, bufs=None) -> None:
     """Drive the ring: call block_fn(step, src_rank, ref_shard_view, n_ref, r_gid0) for every hop.
 
     shard          this rank's reference shard, a contiguous tensor whose storage is `counts[rank] * flat_per_row`
                    elements (any layout the block kernel understands -- it is only ever moved, never indexed here)
     shard_rows_max max(counts): the two ring buffers are sized for the largest shard
     block_fn       consumes the shard resident at this hop; must not keep a reference past the following hop
+    bufs           optional pair of flat receive buffers of at least shard_rows_max * flat_per_row elements
     """
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     cur = shard.reshape(-1)
     if world == 1:
         block_fn(0, rank, cur, counts[rank], offsets[rank])
         return
-    bufs = [torch.empty(shard_rows_max * flat_per_row, dtype=shard.dtype, device=shard.device) for _ in range(2)]
+    if bufs is None:  # (a caller that runs many rings passes its two buffers in, sized for its largest shard)
+        bufs = [torch.empty(shard_rows_max * flat_per_row, dtype=shard.dtype, device=shard.device) for _ in range(2)]
     nxt_rank, prv_rank = dist.get_global_rank(group, (rank + 1) % world), dist.get_global_rank(group, (rank - 1) % world)
     for step in range(world):
         src = ring_source(rank, step, world)
@@ -200,3 +202,221 @@ def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, g
     has = torch.ones(n_total, dtype=torch.uint8, device=dev)
     cn = E.dipcn(counts_all, has, scale_all, best_idx, p.n_nbr, q_gid0=offsets[rank])
     return res, best_idx, best_d2, cn
+
+
+# ---- cohorts larger than aggregate HBM (BASELINE config 4): query blocks x ring rounds -------------------------------
+#
+# With N = 5e5 samples x 2.6e6 selected bins the fp16 operand is 2.6 TB against 8 x 180 GB, so no rank can even hold
+# the operand of its own rows.  Every rank therefore cuts its rows into `rounds` blocks that are REGENERATED from the
+# source (a synthetic generator, or a loader of mosdepth files) whenever they are needed:
+#
+#   for each query block qi of mine (operand resident):              rounds
+#       for each round ri:                                           rounds
+#           transform my block ri (source -> depth -> fp16 operand), send it round the ring;     1 regeneration
+#           on every hop multiply the resident query block with the block that has arrived       W Gram blocks
+#
+# Regeneration costs one source + transform pass per W Gram blocks, the ring moves each block W - 1 times over NVLink
+# while the Gram kernel (10x longer than the transfer at these shapes) runs, and the per-bin statistics of step 4 are
+# accumulated over the blocks in two streaming passes.  Nothing is ever resident but one query block, one reference
+# block, the two ring buffers and one fp32 source block.
+def block_layout(counts: list[int], block_rows: int):
+    """(rounds, per-rank (block counts, block offsets)) -- every rank cuts its rows into the same number of blocks."""
+    rounds = max(1, -(-max(counts) // max(1, int(block_rows))))
+    if min(counts) < rounds:
+        raise ValueError(f"a rank holds fewer rows ({min(counts)}) than there are rounds ({rounds})")
+    return rounds, [shard_rows(c, rounds) for c in counts]
+
+
+def ring_knn_blocked(rounds: int, blocks, rank_offsets: list[int], group, load_query, load_ref, block_fn,
+                     flat_per_row: int, dtype=None, device=None) -> None:
+    """The schedule above, device-agnostic (the CPU tests drive it over gloo with a numpy block kernel).
+
+    blocks[r] = (counts, offsets) of rank r's blocks within its own rows; rank_offsets[r] = its first global row.
+    load_query(qi)                     make query block qi resident
+    load_ref(qi, ri) -> flat tensor    this rank's block ri in ring layout (counts[ri] * flat_per_row elements)
+    block_fn(qi, ri, step, src, flat, n_ref, r_gid0)   as ring_knn's, told which query block and round it serves
+    """
+    world = dist.get_world_size(group)
+    biggest = max(max(b[0]) for b in blocks)
+    bufs = None
+    for qi in range(rounds):
+        load_query(qi)
+        for ri in range(rounds):
+            shard = load_ref(qi, ri)
+            if bufs is None and world > 1:
+                bufs = [torch.empty(biggest * flat_per_row, dtype=shard.dtype, device=shard.device) for _ in range(2)]
+            cnts = [blocks[r][0][ri] for r in range(world)]
+            offs = [rank_offsets[r] + blocks[r][1][ri] for r in range(world)]
+            ring_knn(shard, max(cnts), cnts, offs, group,
+                     lambda step, src, flat, n_ref, r_gid0, qi=qi, ri=ri: block_fn(qi, ri, step, src, flat, n_ref, r_gid0),
+                     flat_per_row, bufs=bufs)
+
+
+def block_operand(res, depth: torch.Tensor, row0: int, p):
+    """(zh [kdim/64, nr, 64] fp16, norms [nr] int64) of the local rows row0.. whose depth block is `depth`, with the
+    cohort statistics held in `res` (a NormResult of run_chain_rows_blocked)."""
+    from . import engine as E
+    from ._lib import call, ptr
+
+    nr, ld = E.check_depth(depth, res.b)
+    dev = depth.device
+    kdim = (res.rw + 63) // 64 * 64
+    zh = torch.empty((kdim // 64, nr, 64), dtype=torch.float16, device=dev)
+    if kdim > res.rw:
+        zh[-1, :, res.rw % 64:] = 0
+    norms = torch.zeros(nr, dtype=torch.int64, device=dev)
+    sat = torch.zeros(1, dtype=torch.int64, device=dev)
+    with E._mark("transform"):
+        call("gridb200_transform", ptr(depth), nr, res.b, ld, ptr(res.row_factor[row0:row0 + nr]), ptr(res.mu),
+             ptr(res.sel_pos), ptr(res.keep), ptr(res.extra["info"]), p.zclip, None, 0, ptr(zh), nr, ptr(norms), ptr(sat),
+             E._stream())
+    return zh, norms
+
+
+def run_chain_rows_blocked(source, n_local: int, b: int, counts_local: torch.Tensor, p, group, block_rows: int,
+                           impl: int = 0):
+    """normalize -> kNN -> dipCN for the n_local rows this rank owns WITHOUT holding them: `source(row0, nrows)` returns
+    the fp32 depth block [nrows, ld] of local rows row0.. (on the device) each time it is asked.
+
+    Same kernels and arithmetic as run_chain_rows; per-bin sums are accumulated block by block (fp64 partials are added
+    in block order, then all-reduced).  Returns (NormResult without operand, idx [n_local, k] global ids, d2, dipcn).
+    """
+    from . import engine as E
+    from ._lib import call, load, ptr
+
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    dev, st = counts_local.device, E._stream()
+    n = int(n_local)
+    i64, f64 = dict(dtype=torch.int64, device=dev), dict(dtype=torch.float64, device=dev)
+    i32 = dict(dtype=torch.int32, device=dev)
+    nloc = torch.zeros(world, **i64)
+    nloc[rank] = n
+    _all_reduce(nloc, group)
+    counts = [int(x) for x in nloc.tolist()]
+    offsets = [sum(counts[:r]) for r in range(world)]
+    n_total = sum(counts)
+    rounds, blocks = block_layout(counts, block_rows)
+    my_cnt, my_off = blocks[rank]
+
+    def fetch(bi):
+        with E._mark("source"):
+            depth = source(my_off[bi], my_cnt[bi])
+        nr, ld = E.check_depth(depth, b)
+        if nr != my_cnt[bi]:
+            raise ValueError(f"source returned {nr} rows for a block of {my_cnt[bi]}")
+        return depth, nr, ld
+
+    # ---- step 4, pass 1: per-bin raw sums (-> depth filter) and per-sample totals --------------------------------
+    colsum, colcnt = torch.zeros(b, **i64), torch.zeros(b, **i32)
+    t_sum, t_cnt = torch.empty(b, **i64), torch.empty(b, **i32)
+    rowsum_all, rowcnt_all = torch.empty(n, **i64), torch.empty(n, **i32)
+    for bi in range(rounds):
+        depth, nr, ld = fetch(bi)
+        r0 = my_off[bi]
+        with E._mark("col_raw"):
+            call("gridb200_col_row_raw_stats", ptr(depth), nr, b, ld, ptr(t_sum), ptr(t_cnt), ptr(rowsum_all[r0:r0 + nr]),
+                 ptr(rowcnt_all[r0:r0 + nr]), st)
+        colsum += t_sum
+        colcnt += t_cnt
+        del depth
+    _all_reduce(colsum, group)
+    _all_reduce(colcnt, group)
+    valid = torch.empty(b, dtype=torch.uint8, device=dev)
+    call("gridb200_depth_filter", ptr(colsum), ptr(colcnt), b, float(p.min_depth), float(p.max_depth), ptr(valid), st)
+
+    # ---- pass 2: per-sample means over the valid bins, per-bin normalised sums ----------------------------------
+    rowsum, rowcnt = torch.empty(n, **i64), torch.empty(n, **i32)
+    raw_mean, scale_q, row_factor = torch.empty(n, **f64), torch.empty(n, **f64), torch.empty(n, **f64)
+    sd, sd2 = torch.zeros(b, **f64), torch.zeros(b, **f64)
+    t_sd, t_sd2 = torch.empty(b, **f64), torch.empty(b, **f64)
+    ws0 = E._ws(load().gridb200_row_stats_fused_ws_bytes(b), dev)
+    for bi in range(rounds):
+        depth, nr, ld = fetch(bi)
+        sl = slice(my_off[bi], my_off[bi] + nr)
+        with E._mark("row_stats"):
+            call("gridb200_row_stats_fused", ptr(depth), nr, b, ld, ptr(valid), ptr(colcnt), ptr(rowsum_all[sl]),
+                 ptr(rowcnt_all[sl]), ptr(rowsum[sl]), ptr(rowcnt[sl]), ptr(ws0), ws0.numel(), st)
+        call("gridb200_row_scales", ptr(rowsum[sl]), ptr(rowcnt[sl]), nr, ptr(raw_mean[sl]), ptr(scale_q[sl]),
+             ptr(row_factor[sl]), st)
+        call("gridb200_row_means_exact", ptr(depth), nr, b, ld, ptr(valid), ptr(rowsum[sl]), ptr(rowcnt[sl]),
+             ptr(raw_mean[sl]), ptr(scale_q[sl]), st)
+        ws = E._ws(load().gridb200_col_norm_stats_ws_bytes(nr, b), dev)
+        with E._mark("col_norm"):
+            call("gridb200_col_norm_stats", ptr(depth), nr, b, ld, ptr(valid), ptr(row_factor[sl]), ptr(t_sd), ptr(t_sd2),
+                 ptr(ws), ws.numel(), st)
+        sd += torch.nan_to_num(t_sd, nan=0.0)      # (bins outside `valid` carry no sum)
+        sd2 += torch.nan_to_num(t_sd2, nan=0.0)
+        del depth
+    _all_reduce(sd, group)
+    _all_reduce(sd2, group)
+    n_eff_t = (rowcnt > 0).sum().to(torch.int64).reshape(1)
+    _all_reduce(n_eff_t, group)
+    n_eff = int(n_eff_t.item())
+    mu, s2, ratio = torch.empty(b, **f64), torch.empty(b, **f64), torch.empty(b, **f64)
+    call("gridb200_col_finalize", ptr(sd), ptr(sd2), ptr(colcnt), ptr(valid), b, n_eff, ptr(mu), ptr(s2), ptr(ratio), st)
+    sel_pos = torch.empty(b, **i32)
+    keep = torch.empty(b, dtype=torch.uint8, device=dev)
+    info, info2 = torch.empty(4, **f64), torch.empty(2, **f64)
+    ws2 = E._ws(load().gridb200_select_ws_bytes(b), dev)
+    with E._mark("select"):
+        call("gridb200_select", ptr(ratio), b, float(p.top_frac), ptr(sel_pos), ptr(info), ptr(ws2), ws2.numel(), st)
+        call("gridb200_knn_col_filter", ptr(ratio), ptr(sel_pos), b, float(p.frac_r), float(p.sigma2_max), ptr(keep),
+             ptr(info), ptr(info2), ptr(ws2), ws2.numel(), st)
+    host = torch.cat([info, info2]).cpu()
+    zscale, rw, r_use = float(host[0]), int(host[3]), int(host[4])
+    if rw < 0:
+        raise IndexError("list index out of range")
+    if rw == 0:
+        raise ValueError("no bins selected")
+    res = E.NormResult(n=n, b=b, colsum=colsum, colcnt=colcnt, valid=valid, raw_mean=raw_mean, scale_q=scale_q,
+                       row_factor=row_factor, mu=mu, s2=s2, ratio=ratio, sel_pos=sel_pos, keep=keep, zscale=zscale,
+                       rw=rw, rw_local=rw, r_use=r_use)
+    res.extra.update(n_eff=n_eff, rowcnt=rowcnt, row_counts=counts, row_offsets=offsets, rounds=rounds, blocks=blocks)
+    res.extra["info"] = info
+    kdim = (rw + 63) // 64 * 64
+
+    def operand(bi):
+        """fp16 k-blocked operand and exact row norms of my block bi, from a fresh copy of its source rows."""
+        depth, nr, ld = fetch(bi)
+        return block_operand(res, depth, my_off[bi], p)
+
+    # ---- step 5: query blocks x rounds x ring hops -----------------------------------------------------------------
+    k = max(1, min(p.num_neighbors, n_total - 1)) if n_total > 1 else 1
+    idx_all, d2_all = torch.empty((n, k), **i32), torch.empty((n, k), **i64)
+    cur = {}
+
+    def flush_query():
+        if cur:
+            sl = slice(my_off[cur["qi"]], my_off[cur["qi"]] + my_cnt[cur["qi"]])
+            idx_all[sl], d2_all[sl] = cur["best_idx"], cur["best_d2"]
+
+    def load_query(qi):
+        flush_query()
+        cur.clear()
+        zq, nq = operand(qi)
+        bd2, bidx = E.knn_init(my_cnt[qi], k, dev)
+        cur.update(qi=qi, zq=zq, nq=nq, best_d2=bd2, best_idx=bidx)
+
+    def load_ref(qi, ri):
+        cur["zr"], nr_ = (cur["zq"], cur["nq"]) if ri == qi else operand(ri)   # my own block: the symmetric Gram case
+        cnts = [blocks[r][0][ri] for r in range(world)]
+        cur["norms_round"] = _all_gather_rows(nr_, cnts, group) if world > 1 else nr_
+        cur["round_off"] = [sum(cnts[:r]) for r in range(world)]
+        return cur["zr"]
+
+    def block_fn(qi, ri, step, src, flat, n_ref, r_gid0):
+        ref = cur["zr"] if step == 0 else flat.view(kdim // 64, n_ref, 64)
+        nr_ = cur["norms_round"][cur["round_off"][src]:cur["round_off"][src] + n_ref]
+        E.knn_block(cur["zq"], cur["nq"], offsets[rank] + my_off[qi], ref, nr_, r_gid0, kdim, p.zclip, cur["best_d2"],
+                    cur["best_idx"], impl=impl)
+
+    ring_knn_blocked(rounds, blocks, offsets, group, load_query, load_ref, block_fn, flat_per_row=kdim)
+    flush_query()
+    cur.clear()
+
+    # ---- step 6 --------------------------------------------------------------------------------------------------------
+    counts_all = _all_gather_rows(counts_local.contiguous(), counts, group)
+    scale_all = _all_gather_rows(scale_q, counts, group)
+    has = torch.ones(n_total, dtype=torch.uint8, device=dev)
+    cn = E.dipcn(counts_all, has, scale_all, idx_all, p.n_nbr, q_gid0=offsets[rank])
+    return res, idx_all, d2_all, cn

@@ -77,6 +77,44 @@ def _worker(rank, world, port, seed, n, b, params, out):
         dist.destroy_process_group()
 
 
+def _worker_blocked(rank, world, port, seed, n, b, params, out):
+    """Out-of-core schedule: no rank ever holds its rows; blocks are regenerated from the synthetic source on demand."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), NCCL_DEBUG="WARN")
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from grid_b200 import engine, ring
+
+        params = dict(params)
+        block_rows = params.pop("block_rows")
+        h = synth.depth_hundredths(seed, n, b)
+        counts = synth.read_counts(seed, n, [42599, 1000])
+        want = O.chain_arrays(h / 100.0, counts, **params)
+        cnt, off = ring.shard_rows(n, world)
+        lo, hi = off[rank], off[rank] + cnt[rank]
+        asked = []
+
+        def source(r0, nr):
+            asked.append((r0, nr))
+            return engine.synth_depth(seed, nr, b, row0=lo + r0)
+
+        res, idx, d2, cn = ring.run_chain_rows_blocked(source, cnt[rank], b, torch.from_numpy(counts[lo:hi]).cuda(),
+                                                       engine.Params(**params), dist.group.WORLD, block_rows)
+        rounds = res.extra["rounds"]
+        assert rounds >= 3 and max(nr for _, nr in asked) <= block_rows
+        assert len(asked) == 2 * rounds + rounds * rounds          # two statistics passes + one operand per (query, round)
+        np.testing.assert_array_equal(idx.cpu().numpy(), want["nbr_idx"][lo:hi])
+        np.testing.assert_array_equal(d2.cpu().numpy(), want["nbr_d2"][lo:hi])
+        np.testing.assert_allclose(cn.cpu().numpy(), want["dipcn"][lo:hi], rtol=DIPCN_REL)
+        np.testing.assert_array_equal(res.scale_q.cpu().numpy(), want["scale_q"][lo:hi])
+        assert res.rw == len(want["sel"]) and res.r_use == want["r_use"]
+        out.put((rank, "ok"))
+    except Exception as exc:
+        out.put((rank, f"{type(exc).__name__}: {str(exc)[:400]}"))
+    finally:
+        dist.destroy_process_group()
+
+
 def _run(world, seed, n, b, params, worker=None):
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
@@ -110,3 +148,17 @@ def test_bins_chain_reduce_scatter(world):
         pytest.skip(f"needs {world} GPUs")
     # n not divisible by world (padded reduce-scatter rows), k > rows per rank
     _run(world, 33, 601, 4000, dict(num_neighbors=350, n_nbr=300), worker=_worker_bins)
+
+
+def test_blocked_chain_single_rank():
+    """Query blocks x rounds on one GPU (every kernel of the out-of-core path; the ring degenerates to hop 0)."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    _run(1, 34, 530, 3000, dict(num_neighbors=300, n_nbr=40, block_rows=150), worker=_worker_blocked)
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_blocked_chain_ring(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    _run(world, 35, 1001, 4000, dict(num_neighbors=350, n_nbr=300, block_rows=130), worker=_worker_blocked)

@@ -87,3 +87,78 @@ def test_ring_over_gloo_matches_global_knn(world, n_total):
     for p in procs:
         p.join(timeout=60)
     assert res == {r: "ok" for r in range(world)}
+
+
+# ---- query blocks x rounds x ring hops (cohorts larger than aggregate HBM) -------------------------------------------
+def test_block_layout():
+    rounds, blocks = ring.block_layout([10, 9, 9], 4)
+    assert rounds == 3 and blocks[0] == ([4, 3, 3], [0, 4, 7]) and blocks[1] == ([3, 3, 3], [0, 3, 6])
+    assert ring.block_layout([5, 5], 100)[0] == 1
+    with pytest.raises(ValueError):
+        ring.block_layout([40, 2], 10)          # a rank with fewer rows than rounds cannot take part in every round
+
+
+def _worker_blocked(rank, world, port, n_total, kdim, k, block_rows, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(11)
+        full = rng.integers(-200, 201, size=(n_total, kdim)).astype(np.int64)
+        counts, offsets = ring.shard_rows(n_total, world)
+        rounds, blocks = ring.block_layout(counts, block_rows)
+        my_cnt, my_off = blocks[rank]
+        best = [[] for _ in range(counts[rank])]
+        state, calls, loads = {}, [], []
+
+        def rows_of(r, bi):
+            lo = offsets[r] + blocks[r][1][bi]
+            return lo, lo + blocks[r][0][bi]
+
+        def load_query(qi):
+            state["qi"] = qi
+
+        def load_ref(qi, ri):
+            loads.append((qi, ri))
+            lo, hi = rows_of(rank, ri)
+            return torch.from_numpy(full[lo:hi].astype(np.float32).copy())      # "regenerated" on demand
+
+        def block(qi, ri, step, src, flat, n_ref, r_gid0):
+            assert qi == state["qi"]
+            calls.append((qi, ri, step, src))
+            lo, hi = rows_of(src, ri)
+            assert (r_gid0, n_ref) == (lo, hi - lo)
+            ref = flat.view(n_ref, kdim).numpy().astype(np.int64)
+            np.testing.assert_array_equal(ref, full[lo:hi])                      # the right block arrived intact
+            qlo, qhi = rows_of(rank, qi)
+            d2 = ((full[qlo:qhi, None, :] - ref[None, :, :]) ** 2).sum(axis=2)
+            for i in range(qhi - qlo):
+                li = qlo - offsets[rank] + i
+                cand = best[li] + [(int(d2[i, j]), r_gid0 + j) for j in range(n_ref) if r_gid0 + j != qlo + i]
+                best[li] = sorted(cand)[:k]
+
+        ring.ring_knn_blocked(rounds, blocks, offsets, dist.group.WORLD, load_query, load_ref, block, flat_per_row=kdim)
+        assert loads == [(qi, ri) for qi in range(rounds) for ri in range(rounds)]        # one regeneration per round
+        assert len(calls) == rounds * rounds * world and len(set(calls)) == len(calls)     # W Gram blocks per round
+        for i in range(counts[rank]):
+            g = offsets[rank] + i
+            dd = ((full[g][None, :] - full) ** 2).sum(axis=1)
+            assert best[i] == sorted((int(dd[j]), j) for j in range(n_total) if j != g)[:k]
+        out.put((rank, "ok"))
+    except Exception as exc:
+        out.put((rank, f"{type(exc).__name__}: {exc}"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_total,block_rows", [(1, 11, 4), (2, 23, 5), (3, 31, 4)])
+def test_blocked_ring_over_gloo_matches_global_knn(world, n_total, block_rows):
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_blocked, args=(r, world, port, n_total, 32, 5, block_rows, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(out.get(timeout=180) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert res == {r: "ok" for r in range(world)}
