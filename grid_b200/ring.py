@@ -274,12 +274,16 @@ def block_operand(res, depth: torch.Tensor, row0: int, p):
 
 
 def run_chain_rows_blocked(source, n_local: int, b: int, counts_local: torch.Tensor, p, group, block_rows: int,
-                           impl: int = 0):
+                           impl: int = 0, resident_blocks: int = 0):
     """normalize -> kNN -> dipCN for the n_local rows this rank owns WITHOUT holding them: `source(row0, nrows)` returns
     the fp32 depth block [nrows, ld] of local rows row0.. (on the device) each time it is asked.
 
     Same kernels and arithmetic as run_chain_rows; per-bin sums are accumulated block by block (fp64 partials are added
     in block order, then all-reduced).  Returns (NormResult without operand, idx [n_local, k] global ids, d2, dipcn).
+
+    resident_blocks: keep the operands of my first m blocks in HBM once they have been made (they are asked for once per
+    query block; a cyclic access pattern, so pinning a prefix beats any replacement policy).  m = rounds is the in-core
+    schedule of run_chain_rows; 0 regenerates everything.
     """
     from . import engine as E
     from ._lib import call, load, ptr
@@ -375,10 +379,17 @@ def run_chain_rows_blocked(source, n_local: int, b: int, counts_local: torch.Ten
     res.extra["info"] = info
     kdim = (rw + 63) // 64 * 64
 
+    pinned = {}
+
     def operand(bi):
         """fp16 k-blocked operand and exact row norms of my block bi, from a fresh copy of its source rows."""
+        if bi in pinned:
+            return pinned[bi]
         depth, nr, ld = fetch(bi)
-        return block_operand(res, depth, my_off[bi], p)
+        out = block_operand(res, depth, my_off[bi], p)
+        if bi < resident_blocks:
+            pinned[bi] = out
+        return out
 
     # ---- step 5: query blocks x rounds x ring hops -----------------------------------------------------------------
     k = max(1, min(p.num_neighbors, n_total - 1)) if n_total > 1 else 1

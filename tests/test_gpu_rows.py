@@ -86,7 +86,7 @@ def _worker_blocked(rank, world, port, seed, n, b, params, out):
         from grid_b200 import engine, ring
 
         params = dict(params)
-        block_rows = params.pop("block_rows")
+        block_rows, resident = params.pop("block_rows"), params.pop("resident_blocks", 0)
         h = synth.depth_hundredths(seed, n, b)
         counts = synth.read_counts(seed, n, [42599, 1000])
         want = O.chain_arrays(h / 100.0, counts, **params)
@@ -99,10 +99,13 @@ def _worker_blocked(rank, world, port, seed, n, b, params, out):
             return engine.synth_depth(seed, nr, b, row0=lo + r0)
 
         res, idx, d2, cn = ring.run_chain_rows_blocked(source, cnt[rank], b, torch.from_numpy(counts[lo:hi]).cuda(),
-                                                       engine.Params(**params), dist.group.WORLD, block_rows)
+                                                       engine.Params(**params), dist.group.WORLD, block_rows,
+                                                       resident_blocks=resident)
         rounds = res.extra["rounds"]
         assert rounds >= 3 and max(nr for _, nr in asked) <= block_rows
-        assert len(asked) == 2 * rounds + rounds * rounds          # two statistics passes + one operand per (query, round)
+        # two statistics passes + one operand per (query block, round), minus the re-uses of the pinned prefix
+        m = min(resident, rounds)
+        assert len(asked) == 2 * rounds + rounds * rounds - (rounds * m - m)
         np.testing.assert_array_equal(idx.cpu().numpy(), want["nbr_idx"][lo:hi])
         np.testing.assert_array_equal(d2.cpu().numpy(), want["nbr_d2"][lo:hi])
         np.testing.assert_allclose(cn.cpu().numpy(), want["dipcn"][lo:hi], rtol=DIPCN_REL)
@@ -150,15 +153,16 @@ def test_bins_chain_reduce_scatter(world):
     _run(world, 33, 601, 4000, dict(num_neighbors=350, n_nbr=300), worker=_worker_bins)
 
 
-def test_blocked_chain_single_rank():
+@pytest.mark.parametrize("resident", [0, 2, 99])
+def test_blocked_chain_single_rank(resident):
     """Query blocks x rounds on one GPU (every kernel of the out-of-core path; the ring degenerates to hop 0)."""
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
-    _run(1, 34, 530, 3000, dict(num_neighbors=300, n_nbr=40, block_rows=150), worker=_worker_blocked)
+    _run(1, 34, 530, 3000, dict(num_neighbors=300, n_nbr=40, block_rows=150, resident_blocks=resident), worker=_worker_blocked)
 
 
 @pytest.mark.parametrize("world", [2, 4])
 def test_blocked_chain_ring(world):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    _run(world, 35, 1001, 4000, dict(num_neighbors=350, n_nbr=300, block_rows=130), worker=_worker_blocked)
+    _run(world, 35, 1001, 4000, dict(num_neighbors=350, n_nbr=300, block_rows=130, resident_blocks=1), worker=_worker_blocked)
