@@ -66,6 +66,22 @@ def find_bed_gz_for_individual(individual_id: str, mosdepth_dir) -> Path:
     return hits[0] if hits else Path(mosdepth_dir) / f"{individual_id}.regions.bed.gz"
 
 
+def find_bed_gz_for_individuals(individual_ids, mosdepth_dir) -> list[Path]:
+    """find_bed_gz_for_individual for many ids from ONE directory listing: the reference globs the directory once per
+    sample (N^2 name matches -- 1.3 s of a 1 000-sample step); the first match in directory order is the same."""
+    root = Path(mosdepth_dir)
+    listing = list(root.glob("*regions.bed.gz"))              # pathlib's own order: what every per-id glob walks through
+    stems = [p.name[: -len("regions.bed.gz")] for p in listing]
+    out = []
+    for sid in individual_ids:
+        if any(c in sid for c in "*?[") or not sid:           # glob metacharacters in an id: let pathlib interpret them
+            out.append(find_bed_gz_for_individual(sid, root))
+            continue
+        hit = next((p for p, stem in zip(listing, stems) if sid in stem), None)
+        out.append(hit if hit is not None else root / f"{sid}.regions.bed.gz")
+    return out
+
+
 def parse_regions_text(text: bytes, chrom, start, end, excluded) -> tuple[np.ndarray, np.ndarray, np.ndarray]:
     """Host parser of one sample's decompressed mosdepth text -> (starts, ends, hundredths) after the line filters
     of normalize_mosdepth.py:262-285: chromosome prefix, >= 4 fields, depth > 0, window overlap (closed), kb mask.

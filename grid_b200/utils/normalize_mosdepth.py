@@ -14,8 +14,8 @@ from pathlib import Path
 import numpy as np
 
 from .. import io as gio
-from ..io import (find_bed_gz_for_individual, load_repeat_mask, map_mosdepth_files_to_samples,  # noqa: F401  (reference names)
-                  norm_chrom)
+from ..io import (find_bed_gz_for_individual, find_bed_gz_for_individuals, load_repeat_mask,  # noqa: F401  (reference names)
+                  map_mosdepth_files_to_samples, norm_chrom)
 from .utils import get_samples, log, progress_bar, setup_output_file
 
 
@@ -26,9 +26,10 @@ def pack_depth_matrix(individuals: dict, mosdepth_dir, chrom, start, end, exclud
     (normalize_mosdepth.py:379-416).  Unreadable files contribute nothing (:286-287, :353-355).
     """
     ids = sorted(individuals)
+    path_of = dict(zip(ids, find_bed_gz_for_individuals(ids, mosdepth_dir)))
 
     def one(sid):
-        path = find_bed_gz_for_individual(sid, mosdepth_dir)
+        path = path_of[sid]
         if not path.exists():
             return None
         try:
@@ -92,7 +93,7 @@ def pack_depth_matrix_device(individuals: dict, mosdepth_dir, chrom, start, end,
     want = norm_chrom(chrom).encode() if chrom else b""
     if len(want) > 32:
         return None
-    paths = [find_bed_gz_for_individual(sid, mosdepth_dir) for sid in ids]
+    paths = find_bed_gz_for_individuals(ids, mosdepth_dir)
     cached: dict[int, bytes | None] = {}  # texts inflated ahead of the stream (to size the grid): used once, then dropped
 
     def inflate(i):

@@ -68,6 +68,19 @@ def test_neighbor_file_matches_oracle_writer(tmp_path):
     assert nid == ids and lists[2] == [("S1", 30.0)]
 
 
+def test_one_directory_listing_finds_what_the_per_sample_glob_finds(tmp_path):
+    names = ["S1_LPA.regions.bed.gz", "S10_LPA.regions.bed.gz", "xS2y.regions.bed.gz", "S3.regions.bed.gz.csi", "S4regions.bed.gz",
+             "S5.regions.bed.gz", "S5_b.regions.bed.gz", ".hidden_S6.regions.bed.gz", "S7.mosdepth.global.dist.txt", "regions.bed.gz",
+             "S[8].regions.bed.gz", "S9.other.gz"]
+    for n in names:
+        (tmp_path / n).write_bytes(b"")
+    ids = ["S1", "S10", "S2", "S3", "S4", "S5", "S6", "S7", "S[8]", "S?", "S9", "regions", "nobody", "S"]
+    want = [gio.find_bed_gz_for_individual(i, tmp_path) for i in ids]          # the reference's lookup, one glob per id
+    assert gio.find_bed_gz_for_individuals(ids, tmp_path) == want
+    assert want[0].name in ("S1_LPA.regions.bed.gz", "S10_LPA.regions.bed.gz")   # (the substring alias the reference has)
+    assert want[ids.index("nobody")] == tmp_path / "nobody.regions.bed.gz"
+
+
 def test_install_rebinds_reference_steps(monkeypatch):
     pkg = types.ModuleType("grid")
     utils = types.ModuleType("grid.utils")
