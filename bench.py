@@ -384,8 +384,12 @@ def main():
     # Libraries write banners to file descriptor 1 (NCCL prints its version there at NCCL_DEBUG=WARN): keep the real
     # stdout for the result line only and send everything else that lands on fd 1 to stderr.
     sys.stdout.flush()
-    _RESULT_FD = os.dup(1)
-    os.dup2(2, 1)
+    try:
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        _RESULT_FD = saved
+    except OSError:  # no usable stderr: leave stdout as it is
+        _RESULT_FD = 1
     if a.impl == "reference":
         run_reference(a)
     else:
