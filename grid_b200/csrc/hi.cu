@@ -151,9 +151,13 @@ extern "C" int gridb200_hi_phase(const double* irr, int64_t n, const int64_t* nb
     const int64_t want = (2 * n + 255) / 256;  // the snapshot copy is the widest phase
     const unsigned grid = (unsigned)(want < (int64_t)sms * per_sm ? want : (int64_t)sms * per_sm);
     void* args[] = {&irr, &nbr_ptr, &nbr_hap, &nbr_w, &order, &level_ptr_dev, &n_levels, &n_iters, &n, &hap, &old_ws};
-    G2_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_hi_sweeps), dim3(grid), dim3(256), args, 0, st));
-    g_launches.fetch_add(1, std::memory_order_relaxed);
-    return 0;
+    const cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(k_hi_sweeps), dim3(grid), dim3(256), args, 0, st);
+    if (e == cudaSuccess) {
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+      return 0;
+    }
+    // the grid cannot be made co-resident right now (e.g. the device is shared): nothing has run; one launch per level
+    (void)cudaGetLastError();
   }
   for (int it = 0; it < n_iters && n_levels > 0; ++it) {
     G2_CUDA(cudaMemcpyAsync(old_ws, hap, (size_t)n * 2 * sizeof(double), cudaMemcpyDeviceToDevice, st));
