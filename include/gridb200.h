@@ -320,7 +320,8 @@ GRIDB200_API int gridb200_hi_phase(const double* irr, int64_t n, const int64_t* 
                       const double* nbr_w, const int32_t* order, const int64_t* level_ptr_host, int32_t n_levels,
                       int32_t n_iters, double* hap, double* old_ws, void* stream);
 
-/* One in-place relaxation pass of the level schedule: level[i] (>= 0 for samples that take part, -1 otherwise; start
+/* One in-place relaxation pass of the level schedule gridb200_hi_phase needs to keep the visiting order of the reference's
+ * sweep (`for i in range(N)`, hi_inference.py:186-233) while running samples in parallel: level[i] (>= 0 for samples that take part, -1 otherwise; start
  * from 0 / -1) becomes 1 + max level over neighbour samples j < i that take part (0 if none); *changed (device) is set to
  * 1 when any level moved.  Repeat until a pass leaves *changed at 0 (at most depth + 1 passes). */
 GRIDB200_API int gridb200_hi_level_pass(const int64_t* nbr_ptr, const int32_t* nbr_hap, int64_t n, int32_t* level,
