@@ -348,16 +348,23 @@ def dipcn(counts: torch.Tensor, has_count: torch.Tensor, scale_q: torch.Tensor, 
     return out
 
 
-def synth_depth(seed: int, n: int, b: int, row0: int = 0, col0: int = 0, device="cuda", ld: int | None = None):
-    """Device-generated synthetic depth matrix, bit-identical to grid_b200.synth.depth_matrix."""
+def synth_depth(seed: int, n: int, b: int, row0: int = 0, col0: int = 0, device="cuda", ld: int | None = None,
+                out: torch.Tensor | None = None):
+    """Device-generated synthetic depth matrix, bit-identical to grid_b200.synth.depth_matrix.
+    out: optional flat fp32 buffer of at least n * ld elements to build the matrix in (callers that regenerate blocks
+    of slightly different heights over and over keep one buffer instead of tens of GB of allocator churn)."""
     from . import synth
 
     ld = ld or (b + 3) // 4 * 4
     c, rc = synth.row_params(seed, n, row0)
     bc, rb = synth.col_params(seed, b, col0)
-    dev = torch.device(device)
+    dev = torch.device(device) if out is None else out.device
     tc, trc, tb, trb = (torch.from_numpy(a).to(dev) for a in (c, rc, bc, rb))
-    depth = torch.empty((n, ld), dtype=torch.float32, device=dev)
+    if out is None:
+        depth = torch.empty((n, ld), dtype=torch.float32, device=dev)
+    else:
+        assert out.dtype == torch.float32 and out.is_contiguous() and out.numel() >= n * ld
+        depth = out.view(-1)[: n * ld].view(n, ld)
     if ld > b:
         depth[:, b:] = 0
     call("gridb200_synth_depth", seed, n, b, row0, col0, ptr(tc), ptr(trc), ptr(tb), ptr(trb), ptr(depth), ld, _stream())

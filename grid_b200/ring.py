@@ -252,16 +252,21 @@ def ring_knn_blocked(rounds: int, blocks, rank_offsets: list[int], group, load_q
                      flat_per_row, bufs=bufs)
 
 
-def block_operand(res, depth: torch.Tensor, row0: int, p):
+def block_operand(res, depth: torch.Tensor, row0: int, p, out: torch.Tensor | None = None):
     """(zh [kdim/64, nr, 64] fp16, norms [nr] int64) of the local rows row0.. whose depth block is `depth`, with the
-    cohort statistics held in `res` (a NormResult of run_chain_rows_blocked)."""
+    cohort statistics held in `res` (a NormResult of run_chain_rows_blocked).  out: optional flat fp16 buffer of at
+    least nr * kdim elements to build the operand in."""
     from . import engine as E
     from ._lib import call, ptr
 
     nr, ld = E.check_depth(depth, res.b)
     dev = depth.device
     kdim = (res.rw + 63) // 64 * 64
-    zh = torch.empty((kdim // 64, nr, 64), dtype=torch.float16, device=dev)
+    if out is None:
+        zh = torch.empty((kdim // 64, nr, 64), dtype=torch.float16, device=dev)
+    else:
+        assert out.dtype == torch.float16 and out.is_contiguous() and out.numel() >= nr * kdim
+        zh = out.view(-1)[: nr * kdim].view(kdim // 64, nr, 64)
     if kdim > res.rw:
         zh[-1, :, res.rw % 64:] = 0
     norms = torch.zeros(nr, dtype=torch.int64, device=dev)
@@ -380,16 +385,21 @@ def run_chain_rows_blocked(source, n_local: int, b: int, counts_local: torch.Ten
     kdim = (rw + 63) // 64 * 64
 
     pinned = {}
+    # two reusable operand buffers (query block, reference block) sized for my largest block: blocks differ by a row,
+    # and tens of GB allocated afresh at a new size every round is how a caching allocator runs out of room
+    slots = {}
 
-    def operand(bi):
+    def operand(bi, slot):
         """fp16 k-blocked operand and exact row norms of my block bi, from a fresh copy of its source rows."""
         if bi in pinned:
             return pinned[bi]
         depth, nr, ld = fetch(bi)
-        out = block_operand(res, depth, my_off[bi], p)
         if bi < resident_blocks:
-            pinned[bi] = out
-        return out
+            pinned[bi] = block_operand(res, depth, my_off[bi], p)
+            return pinned[bi]
+        if slot not in slots:
+            slots[slot] = torch.empty(max(my_cnt) * kdim, dtype=torch.float16, device=dev)
+        return block_operand(res, depth, my_off[bi], p, out=slots[slot])
 
     # ---- step 5: query blocks x rounds x ring hops -----------------------------------------------------------------
     k = max(1, min(p.num_neighbors, n_total - 1)) if n_total > 1 else 1
@@ -404,12 +414,12 @@ def run_chain_rows_blocked(source, n_local: int, b: int, counts_local: torch.Ten
     def load_query(qi):
         flush_query()
         cur.clear()
-        zq, nq = operand(qi)
+        zq, nq = operand(qi, "query")
         bd2, bidx = E.knn_init(my_cnt[qi], k, dev)
         cur.update(qi=qi, zq=zq, nq=nq, best_d2=bd2, best_idx=bidx)
 
     def load_ref(qi, ri):
-        cur["zr"], nr_ = (cur["zq"], cur["nq"]) if ri == qi else operand(ri)   # my own block: the symmetric Gram case
+        cur["zr"], nr_ = (cur["zq"], cur["nq"]) if ri == qi else operand(ri, "ref")   # own block: the symmetric Gram case
         cnts = [blocks[r][0][ri] for r in range(world)]
         cur["norms_round"] = _all_gather_rows(nr_, cnts, group) if world > 1 else nr_
         cur["round_off"] = [sum(cnts[:r]) for r in range(world)]

@@ -44,8 +44,13 @@ p = engine.Params(num_neighbors=a.k, n_nbr=a.n_nbr)
 counts = torch.from_numpy(synth.read_counts(SEED, a.samples, [42599])[off[rank]:off[rank] + cnt[rank]]).to(dev)
 
 
+_, _layout = ring.block_layout(cnt, a.block_rows)
+_depth_buf = torch.empty(max(_layout[rank][0]) * ((a.bins + 3) // 4 * 4), dtype=torch.float32, device=dev)
+
+
 def source(r0, nr):
-    return engine.synth_depth(SEED, nr, a.bins, off[rank] + r0, 0, device=dev)
+    """One reusable fp32 block (the chain consumes a block before it asks for the next one)."""
+    return engine.synth_depth(SEED, nr, a.bins, off[rank] + r0, 0, out=_depth_buf)
 
 
 def barrier():
