@@ -14,6 +14,7 @@ Running the binary is out of scope; the reduction is done here for a whole batch
 """
 from __future__ import annotations
 
+import gzip
 import io
 from concurrent.futures import ThreadPoolExecutor
 from pathlib import Path
@@ -112,8 +113,6 @@ def region_coverage_batch(paths, chrom: str, start: int, end: int, threads: int 
             t = futs.pop(0).result()
             if t is None or want is None or b"\r" in t:  # (carriage returns end lines in text mode: rare enough to replay)
                 try:  # let the reference's own failure mode surface (missing file, bad gzip, ...)
-                    import gzip
-
                     with gzip.open(paths[i], "rb") as fh:
                         results[i] = _replay(fh.read(), chrom, start, end)
                 except Exception as e:
