@@ -81,6 +81,19 @@ def test_one_directory_listing_finds_what_the_per_sample_glob_finds(tmp_path):
     assert want[ids.index("nobody")] == tmp_path / "nobody.regions.bed.gz"
 
 
+def test_one_directory_listing_random_names(tmp_path):
+    """Seeded random cohorts of overlapping ids (prefixes of each other, with and without region suffixes)."""
+    rng = np.random.default_rng(3)
+    alphabet = ["S", "1", "2", "0", "_", "a", "."]
+    ids = sorted({"".join(rng.choice(alphabet, size=int(rng.integers(1, 6)))) for _ in range(60)} - {".", ".."})
+    for sid in ids[::2]:
+        suffix = str(rng.choice(["", "_LPA", ".x", "regions"]))
+        (tmp_path / f"{sid}{suffix}.regions.bed.gz").write_bytes(b"")
+    want = [gio.find_bed_gz_for_individual(i, tmp_path) for i in ids]
+    assert gio.find_bed_gz_for_individuals(ids, tmp_path) == want
+    assert sum(p.exists() for p in want) >= len(ids) // 2
+
+
 def test_install_rebinds_reference_steps(monkeypatch):
     pkg = types.ModuleType("grid")
     utils = types.ModuleType("grid.utils")
