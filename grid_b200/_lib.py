@@ -38,6 +38,8 @@ SIGNATURES = {
     "gridb200_gram_set_max_pairs": (C.c_int, [C.c_int]),
     "gridb200_topk_init": (C.c_int, [_vp, _vp, _i64, _i32, _vp]),
     "gridb200_topk_merge": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _i32, _vp, _vp, _vp]),
+    "gridb200_topk_merge_t": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _i32, _vp, _vp, _vp]),
+    "gridb200_topk_merge_lists": (C.c_int, [_vp, _vp, _i64, _i32, _i32, _vp, _vp, _vp]),
     "gridb200_dipcn": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _i64, _i32, _i64, _i32, _i32, _vp, _i64, _vp, _vp]),
     "gridb200_synth_depth": (C.c_int, [_u64, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp]),
     "gridb200_ingest_ws_bytes": (_sz, [_i64]),

@@ -107,7 +107,8 @@ extern "C" int gridb200_dipcn(const int32_t* counts, int64_t n_all, int64_t g, i
   G2_REQUIRE(n_all > 0 && g > 0 && nq > 0 && k > 0 && n_nbr > 0 && ldc >= g && ldo >= g, GRIDB200_EINVAL, "bad shape");
   G2_REQUIRE(q_gid0 >= 0 && q_gid0 + nq <= n_all, GRIDB200_EINVAL, "query rows outside the cohort");
   G2_REQUIRE(rule == GRIDB200_DIPCN_PIPELINE || rule == GRIDB200_DIPCN_EXON, GRIDB200_EINVAL, "unknown dipCN rule %d", rule);
-  G2_REQUIRE(n_nbr <= 12000, GRIDB200_EINVAL, "n_nbr too large for the shared-memory list");
+  n_nbr = n_nbr < k ? n_nbr : k;  // a list holds k entries: a larger budget changes nothing (and sizes the shared list)
+  G2_REQUIRE(n_nbr <= 12000, GRIDB200_EINVAL, "min(n_nbr, k) = %d too large for the shared-memory list", n_nbr);
   cudaStream_t st = as_stream(stream);
   const int64_t cells = n_all * g;
   k_dipcn_scaled<<<(unsigned)((cells + 255) / 256), 256, 0, st>>>(counts, n_all, g, ldc, scale_q, t_ws);

@@ -571,10 +571,13 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
              vmax);
   G2_REQUIRE(nq < (1LL << 31) && nr < (1LL << 31) && kdim < (1LL << 31), GRIDB200_EINVAL, "shape exceeds int32");
   cudaStream_t st = as_stream(stream);
-  static int sms = 0;
+  // SM count and the >48 KB shared-memory opt-in are per DEVICE: cached per device index, not per process
+  static std::atomic<int> sms_of[64];
+  int dev = 0;
+  G2_CUDA(cudaGetDevice(&dev));
+  G2_REQUIRE(dev >= 0 && dev < 64, GRIDB200_ENODEV, "device index %d outside the per-device cache", dev);
+  int sms = sms_of[dev].load();
   if (!sms) {
-    int dev = 0;
-    G2_CUDA(cudaGetDevice(&dev));
     cudaDeviceProp prop;
     G2_CUDA(cudaGetDeviceProperties(&prop, dev));
     G2_REQUIRE(prop.major == 10, GRIDB200_ENODEV, "tcgen05 path needs an sm_100 device (found sm_%d%d)", prop.major,
@@ -583,6 +586,7 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
     G2_CUDA(cudaFuncSetAttribute(k_gram_tc_pair<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     G2_REQUIRE(prop.multiProcessorCount <= PACE_SLOTS, GRIDB200_ENODEV, "more SMs than pacing slots");
     sms = prop.multiProcessorCount;
+    sms_of[dev].store(sms);
   }
   const int64_t nkb = kdim / BK;
   CUtensorMap mq, mr;

@@ -63,6 +63,16 @@ class NormResult:
 
 
 PROFILE: dict | None = None  # bench.py sets this to {} to collect per-stage CUDA-event timings
+GRAM_ELEMS: int = 0          # output elements of the Gram tiles launched so far (flops = 2 * K * elements); bench.py resets it
+
+
+def gram_tile_elems(nq: int, nr: int, symmetric: bool) -> int:
+    """Elements of the 256 x 256 output tiles gridb200_gram computes for an nq x nr block, clipped to the block:
+    all of them, or -- same operand on both sides -- only the tiles on or above the diagonal."""
+    if not symmetric:
+        return nq * nr
+    sizes = [min(256, nq - e) for e in range(0, nq, 256)]
+    return sum(sizes[i] * sizes[j] for i in range(len(sizes)) for j in range(i, len(sizes)))
 
 
 class _mark:
@@ -252,36 +262,73 @@ def knn_init(nq: int, k: int, dev):
     return best_d2, best_idx
 
 
+TOPK_MAX_KEYS = 8192  # candidates + k per gridb200_topk_merge* call (shared-memory sort)
+
+
+def check_k(k: int) -> None:
+    """The k-best merge sorts k + candidates <= 8192 keys in shared memory and takes candidates in chunks of 8192 - k:
+    refuse a k that leaves no room instead of looping forever or writing empty lists."""
+    if not 0 < k <= TOPK_MAX_KEYS // 2:
+        raise ValueError(f"num_neighbors = {k}: the device k-best merge supports 1 <= k <= {TOPK_MAX_KEYS // 2} "
+                         "(the reference accepts any value; cohorts that need more are not supported on the GPU path)")
+
+
+def merge_lists(src_d2: torch.Tensor, src_idx: torch.Tensor, best_d2: torch.Tensor, best_idx: torch.Tensor) -> None:
+    """Merge candidate lists [n, src_k] (idx < 0 = empty) into the running k-best lists [n, k] of the same rows."""
+    n, k = best_d2.shape
+    assert src_d2.shape[0] == n and src_d2.is_contiguous() and src_idx.is_contiguous() and best_d2.is_contiguous()
+    if n:
+        call("gridb200_topk_merge_lists", ptr(src_d2), ptr(src_idx), n, src_d2.shape[1], k, ptr(best_d2), ptr(best_idx),
+             _stream())
+
+
 def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torch.Tensor, norms_r: torch.Tensor,
               r_gid0: int, kdim: int, vmax: int, best_d2: torch.Tensor, best_idx: torch.Tensor, impl: int = 0,
-              group=None, max_block_bytes: int = 2 << 30) -> None:
+              group=None, max_block_bytes: int = 2 << 30, q_range: tuple[int, int] | None = None,
+              r_range: tuple[int, int] | None = None, t_lists: tuple[torch.Tensor, torch.Tensor] | None = None) -> None:
     """Merge the reference rows of ``zh_r`` (global ids r_gid0..) into the running lists of the query rows of
     ``zh_q`` (global ids q_gid0..).  Operands are k-blocked [kdim/64, rows, 64]; the N x N distances only ever
-    exist as query-block x reference-shard Gram tiles (<= max_block_bytes)."""
+    exist as query-block x reference-shard Gram tiles (<= max_block_bytes).
+
+    q_range / r_range: restrict the block to query rows [a, b) / reference rows [c, d) of the operands (norms, global
+    ids and best_* keep indexing the WHOLE operand's rows).
+    t_lists = (t_d2, t_idx) [rows of zh_r, k]: also merge, through the block's transpose, the query rows into the
+    running lists of the REFERENCE rows -- the half ring's way of computing every pair of samples once."""
     for t in (zh_q, zh_r):
         assert t.dim() == 3 and t.shape[2] == 64 and t.is_contiguous() and t.shape[0] * 64 == kdim, "zh is [kdim/64, n, 64]"
-    nq_all, nr = zh_q.shape[1], zh_r.shape[1]
+    nq_all, nr_all = zh_q.shape[1], zh_r.shape[1]
+    qa, qz = q_range or (0, nq_all)
+    ra, rz = r_range or (0, nr_all)
+    nr = rz - ra
+    if qz <= qa or nr <= 0:
+        return
     k = best_d2.shape[1]
+    check_k(k)
     dev, st = zh_q.device, _stream()
     if impl == 0 and vmax > 511:
         impl = 1  # |v| > 511: a 64-wide fp32 chunk is no longer exact; the integer SIMT kernel takes over (still GPU)
     ldd = (nr + 1) // 2 * 2
-    qb = max(1, min(nq_all, max_block_bytes // (8 * ldd)))
-    rchunk = 8192 - k
+    qb = max(1, min(qz - qa, max_block_bytes // (8 * ldd)))
+    rchunk = TOPK_MAX_KEYS - k
     world, rank = 1, 0
     if group is not None:
         import torch.distributed as dist
 
         world, rank = dist.get_world_size(group), dist.get_rank(group)
-    for q0 in range(0, nq_all, qb):
-        nq = min(qb, nq_all - q0)
+        assert q_range is None and r_range is None and t_lists is None, "sub-blocks are a row-sharded (ring) feature"
+    zr_ptr = zh_r.data_ptr() + ra * 64 * 2
+    global GRAM_ELEMS
+    for q0 in range(qa, qz, qb):
+        nq = min(qb, qz - q0)
         m = -(-nq // world)  # query rows per rank after the reduce-scatter
         dot = torch.empty((m * world, ldd), dtype=torch.int64, device=dev)
         if m * world > nq:
             dot[nq:].zero_()
         with _mark("gram"):
-            call("gridb200_gram", zh_q.data_ptr() + q0 * 64 * 2, nq, nq_all, ptr(zh_r), nr, nr, kdim, vmax, ptr(dot), ldd,
+            call("gridb200_gram", zh_q.data_ptr() + q0 * 64 * 2, nq, nq_all, zr_ptr, nr, nr_all, kdim, vmax, ptr(dot), ldd,
                  0, impl, st)
+        GRAM_ELEMS += gram_tile_elems(nq, nr, impl == 0 and q0 == 0 and ra == 0 and nq == nr == nq_all == nr_all
+                                      and zh_q.data_ptr() == zh_r.data_ptr())
         if world > 1:
             # bin-sharded: every rank holds a partial of the whole block.  Reduce-scatter it by query rows, merge the
             # k-best lists of MY rows only, then all-gather the (small) lists -- instead of all-reducing the block and
@@ -298,8 +345,16 @@ def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torc
                     break
                 n_r = min(rchunk, nr - r0)
                 call("gridb200_topk_merge", mine.data_ptr() + r0 * 8, ldd, n_mine, n_r,
-                     norms_q.data_ptr() + (q0 + r_lo) * 8, norms_r.data_ptr() + r0 * 8, q_gid0 + q0 + r_lo, r_gid0 + r0, k,
-                     best_d2.data_ptr() + (q0 + r_lo) * k * 8, best_idx.data_ptr() + (q0 + r_lo) * k * 4, st)
+                     norms_q.data_ptr() + (q0 + r_lo) * 8, norms_r.data_ptr() + (ra + r0) * 8, q_gid0 + q0 + r_lo,
+                     r_gid0 + ra + r0, k, best_d2.data_ptr() + (q0 + r_lo) * k * 8, best_idx.data_ptr() + (q0 + r_lo) * k * 4, st)
+            if t_lists is not None:  # the same block read by columns: lists of the reference rows, query rows as candidates
+                t_d2, t_idx = t_lists
+                assert t_d2.shape == (nr_all, k) and t_d2.is_contiguous() and t_idx.is_contiguous()
+                for c0 in range(0, nq, rchunk):
+                    n_c = min(rchunk, nq - c0)
+                    call("gridb200_topk_merge_t", dot.data_ptr() + c0 * ldd * 8, ldd, n_c, nr,
+                         norms_q.data_ptr() + (q0 + c0) * 8, norms_r.data_ptr() + ra * 8, q_gid0 + q0 + c0, r_gid0 + ra, k,
+                         t_d2.data_ptr() + ra * k * 8, t_idx.data_ptr() + ra * k * 4, st)
         if world > 1:
             part_d2 = torch.zeros((m, k), dtype=torch.int64, device=dev)
             part_idx = torch.zeros((m, k), dtype=torch.int32, device=dev)

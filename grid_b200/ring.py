@@ -32,28 +32,69 @@ def ring_source(rank: int, step: int, world: int) -> int:
     return (rank - step) % world
 
 
+class HalfRingOps:
+    """What the half ring needs from the device besides the block kernel (CUDA: engine.knn_init / engine.merge_lists;
+    the CPU tests pass numpy stand-ins).
+
+    new_lists(nrows) -> (d2 int64 [nrows, k], idx int32 [nrows, k]), empty (d2 = +inf, idx = -1)
+    merge(row_lo, d2, idx)    merge candidate lists for the rows row_lo.. of the CURRENT REFERENCE BLOCK of this rank
+                              (= all its rows in the in-core ring) into its running lists
+    """
+
+    def __init__(self, new_lists, merge):
+        self.new_lists, self.merge = new_lists, merge
+
+
+def half_ring_hops(world: int) -> int:
+    """Last hop of the half ring: every unordered pair of ranks meets once within hops 0..world // 2."""
+    return world // 2
+
+
 def ring_knn(shard: torch.Tensor, shard_rows_max: int, counts: list[int], offsets: list[int], group, block_fn,
-             flat_per_row: int, bufs=None) -> None:
-    """Drive the ring: call block_fn(step, src_rank, ref_shard_view, n_ref, r_gid0) for every hop.
+             flat_per_row: int, bufs=None, half: HalfRingOps | None = None, rel: int = 0) -> None:
+    """Drive the ring.
 
     shard          this rank's reference shard, a contiguous tensor whose storage is `counts[rank] * flat_per_row`
                    elements (any layout the block kernel understands -- it is only ever moved, never indexed here)
     shard_rows_max max(counts): the two ring buffers are sized for the largest shard
-    block_fn       consumes the shard resident at this hop; must not keep a reference past the following hop
     bufs           optional pair of flat receive buffers of at least shard_rows_max * flat_per_row elements
+
+    half = None (the full ring): block_fn(step, src_rank, ref_shard_view, n_ref, r_gid0) is called for all `world` hops;
+    every rank multiplies its rows with every shard, so each pair of samples is computed twice across the ranks.
+
+    half given (the HALF ring, what the CUDA path runs): the squared distance is symmetric, so the block rank a computes
+    against the shard of rank b also holds, read by columns, everything b needs to know about a's rows.  Hops run only
+    to world // 2; on hop t >= 1 the block kernel is asked to ALSO fill k-best lists for the shard's rows
+    (block_fn(step, src, view, n_ref, r_gid0, q_range, r_range, t_lists)), those lists (n_ref x k x 12 bytes instead of
+    a 33 GB shard) go straight to the shard's owner, and the lists this rank's rows earned on rank + t arrive and are
+    merged (`half.merge`).  With an even world the two ranks of a pair meet on the same (last) hop: the lower rank
+    takes all its rows x the first half of the peer's, the higher one its second half x all of the peer's rows.
+    rel: sign(reference block index - query block index) in the blocked schedule (0 in core): blocks of the same rank
+    (hop 0) and of a rank's opposite (last hop of an even world) are computed only for rel >= 0 -- the mirror image is
+    the peer's (or this rank's own) rel > 0 case -- and read both ways.  block_fn must not keep a reference past the
+    following hop.
     """
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     cur = shard.reshape(-1)
-    if world == 1:
-        block_fn(0, rank, cur, counts[rank], offsets[rank])
-        return
-    if bufs is None:  # (a caller that runs many rings passes its two buffers in, sized for its largest shard)
+    if half is None:
+        if world == 1:
+            block_fn(0, rank, cur, counts[rank], offsets[rank])
+            return
+        hops = world - 1
+    else:
+        hops = half_ring_hops(world)
+        even = world % 2 == 0
+        if rel < 0 and even:
+            hops -= 1  # the opposite rank's block is its rel > 0 case
+    if world > 1 and hops > 0 and bufs is None:  # (a caller that runs many rings passes its two buffers in)
         bufs = [torch.empty(shard_rows_max * flat_per_row, dtype=shard.dtype, device=shard.device) for _ in range(2)]
-    nxt_rank, prv_rank = dist.get_global_rank(group, (rank + 1) % world), dist.get_global_rank(group, (rank - 1) % world)
-    for step in range(world):
+    nxt_rank = dist.get_global_rank(group, (rank + 1) % world) if world > 1 else rank
+    prv_rank = dist.get_global_rank(group, (rank - 1) % world) if world > 1 else rank
+    pending = []  # list exchanges in flight: (works, row_lo, recv_d2, recv_idx, keep-alive)
+    for step in range(hops + 1):
         src = ring_source(rank, step, world)
         works = []
-        if step + 1 < world:
+        if step < hops:
             # pass the resident shard on and receive the next one into the other buffer WHILE this hop computes;
             # the collective library orders the transfer after everything already queued on the current stream,
             # i.e. after the previous hop's kernels have finished with the buffer being overwritten
@@ -62,10 +103,48 @@ def ring_knn(shard: torch.Tensor, shard_rows_max: int, counts: list[int], offset
             send_view = cur[: counts[src] * flat_per_row]
             ops = [dist.P2POp(dist.isend, send_view, nxt_rank, group), dist.P2POp(dist.irecv, recv_view, prv_rank, group)]
             works = dist.batch_isend_irecv(ops)
-        block_fn(step, src, cur[: counts[src] * flat_per_row], counts[src], offsets[src])
+        view = cur[: counts[src] * flat_per_row]
+        if half is None:
+            block_fn(step, src, view, counts[src], offsets[src])
+        elif step == 0:
+            if rel == 0:
+                block_fn(0, src, view, counts[src], offsets[src], None, None, None)       # own block: symmetric kernel
+            elif rel > 0:  # another block of my own rows: both readings stay here
+                t = half.new_lists(counts[src])
+                block_fn(0, src, view, counts[src], offsets[src], None, None, t)
+                half.merge(0, t[0], t[1])
+        else:
+            dst = (rank + step) % world                          # the rank that meets MY shard on this hop
+            middle = even and step == world // 2
+            q_range = r_range = None
+            send_rows, recv_rows = (0, counts[src]), (0, counts[rank])
+            if middle and rel == 0:
+                if rank < src:   # lower rank of the pair: all my rows x the first half of the peer's
+                    r_range = send_rows = (0, counts[src] // 2)
+                else:            # higher rank: my second half x all of the peer's rows
+                    q_range = (counts[rank] // 2, counts[rank])
+                    recv_rows = (0, counts[rank] // 2)
+            t = half.new_lists(counts[src])
+            block_fn(step, src, view, counts[src], offsets[src], q_range, r_range, t)
+            out = [x[send_rows[0]:send_rows[1]] for x in t]
+            got = [x[recv_rows[0]:recv_rows[1]] for x in half.new_lists(counts[rank])]
+            ops = []
+            if send_rows[1] > send_rows[0]:
+                ops += [dist.P2POp(dist.isend, x, dist.get_global_rank(group, src), group) for x in out]
+            if recv_rows[1] > recv_rows[0]:
+                ops += [dist.P2POp(dist.irecv, x, dist.get_global_rank(group, dst), group) for x in got]
+            if ops:
+                pending.append((dist.batch_isend_irecv(ops), recv_rows, got, out))
         for w in works:
             w.wait()
-        if step + 1 < world:
+        # lists that arrived for the PREVIOUS hop are merged now, behind this hop's kernels: nobody waits for a peer
+        while len(pending) > (1 if step < hops else 0):
+            lw, rows, got, _keep = pending.pop(0)
+            for w in lw:
+                w.wait()
+            if rows[1] > rows[0]:
+                half.merge(rows[0], got[0], got[1])
+        if step < hops:
             cur = bufs[(step + 1) % 2]
 
 
@@ -178,21 +257,28 @@ def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, g
     k = max(1, min(p.num_neighbors, n_total - 1)) if n_total > 1 else 1
     best_d2, best_idx = E.knn_init(n, k, dev)
 
-    def block(step, src, flat, n_ref, r_gid0):
+    def block(step, src, flat, n_ref, r_gid0, q_range=None, r_range=None, t_lists=None):
         ref = zh if step == 0 else flat.view(kdim // 64, n_ref, 64)  # hop 0 is the symmetric (same-operand) case
         E.knn_block(zh, norms, offsets[rank], ref, norms_all[r_gid0:r_gid0 + n_ref], r_gid0, kdim, p.zclip, best_d2,
-                    best_idx, impl=impl)
+                    best_idx, impl=impl, q_range=q_range, r_range=r_range, t_lists=t_lists)
+
+    def merge(lo, d2_in, idx_in):
+        with E._mark("merge_lists"):
+            E.merge_lists(d2_in, idx_in, best_d2[lo:lo + d2_in.shape[0]], best_idx[lo:lo + d2_in.shape[0]])
 
     # The Gram kernel shares the GPU with NCCL's send/recv kernel while a transfer is in flight.  Its default
     # schedule (cluster launch control) adapts to the SMs it gets.  GRIDB200_RING_COMM_SMS=<n> instead selects the
-    # static schedule on all but n SMs (A/B aid).
+    # static schedule on all but n SMs (A/B aid).  GRIDB200_RING=full runs all W hops (every pair twice: A/B aid).
     import os
 
     comm_sms = int(os.environ.get("GRIDB200_RING_COMM_SMS", "0")) if world > 1 else 0
     sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    full_ring = os.environ.get("GRIDB200_RING", "half") == "full"
+    half = None if full_ring else HalfRingOps(lambda m: E.knn_init(m, k, dev), merge)
+    res.extra.update(ring_schedule="full" if full_ring else "half", ring_hops=(world - 1) if full_ring else half_ring_hops(world))
     call("gridb200_gram_set_max_pairs", max(1, (sms - comm_sms) // 2) if comm_sms else 0)
     try:
-        ring_knn(zh, max(counts), counts, offsets, group, block, flat_per_row=kdim)
+        ring_knn(zh, max(counts), counts, offsets, group, block, flat_per_row=kdim, half=half)
     finally:
         call("gridb200_gram_set_max_pairs", 0)
 
@@ -228,13 +314,17 @@ def block_layout(counts: list[int], block_rows: int):
 
 
 def ring_knn_blocked(rounds: int, blocks, rank_offsets: list[int], group, load_query, load_ref, block_fn,
-                     flat_per_row: int, dtype=None, device=None) -> None:
+                     flat_per_row: int, dtype=None, device=None, half: HalfRingOps | None = None) -> None:
     """The schedule above, device-agnostic (the CPU tests drive it over gloo with a numpy block kernel).
 
     blocks[r] = (counts, offsets) of rank r's blocks within its own rows; rank_offsets[r] = its first global row.
     load_query(qi)                     make query block qi resident
     load_ref(qi, ri) -> flat tensor    this rank's block ri in ring layout (counts[ri] * flat_per_row elements)
-    block_fn(qi, ri, step, src, flat, n_ref, r_gid0)   as ring_knn's, told which query block and round it serves
+    block_fn(qi, ri, step, src, flat, n_ref, r_gid0[, q_range, r_range, t_lists])   as ring_knn's, told which query
+                                       block and round it serves
+    half: run every (query block, round) as a HALF ring (see ring_knn): block pairs are computed once -- (qi, ri) and
+          (ri, qi) meet the same pairs of samples from both sides, so blocks of the same rank and of opposite ranks are
+          taken for ri >= qi only -- and read both ways.  `half.merge(ri, row_lo, d2, idx)` gets the round as well.
     """
     world = dist.get_world_size(group)
     biggest = max(max(b[0]) for b in blocks)
@@ -242,14 +332,19 @@ def ring_knn_blocked(rounds: int, blocks, rank_offsets: list[int], group, load_q
     for qi in range(rounds):
         load_query(qi)
         for ri in range(rounds):
+            rel = (ri > qi) - (ri < qi)
+            if half is not None and rel < 0 and world < 3:
+                continue  # hop 0 and the opposite rank's hop are somebody's rel > 0 case; no other hop exists
             shard = load_ref(qi, ri)
             if bufs is None and world > 1:
                 bufs = [torch.empty(biggest * flat_per_row, dtype=shard.dtype, device=shard.device) for _ in range(2)]
             cnts = [blocks[r][0][ri] for r in range(world)]
             offs = [rank_offsets[r] + blocks[r][1][ri] for r in range(world)]
+            ops = None if half is None else HalfRingOps(half.new_lists, lambda lo, d2, idx, ri=ri: half.merge(ri, lo, d2, idx))
             ring_knn(shard, max(cnts), cnts, offs, group,
-                     lambda step, src, flat, n_ref, r_gid0, qi=qi, ri=ri: block_fn(qi, ri, step, src, flat, n_ref, r_gid0),
-                     flat_per_row, bufs=bufs)
+                     lambda step, src, flat, n_ref, r_gid0, *more, qi=qi, ri=ri: block_fn(qi, ri, step, src, flat, n_ref,
+                                                                                        r_gid0, *more),
+                     flat_per_row, bufs=bufs, half=ops, rel=rel)
 
 
 def block_operand(res, depth: torch.Tensor, row0: int, p, out: torch.Tensor | None = None):
@@ -402,21 +497,22 @@ def run_chain_rows_blocked(source, n_local: int, b: int, counts_local: torch.Ten
         return block_operand(res, depth, my_off[bi], p, out=slots[slot])
 
     # ---- step 5: query blocks x rounds x ring hops -----------------------------------------------------------------
-    k = max(1, min(p.num_neighbors, n_total - 1)) if n_total > 1 else 1
-    idx_all, d2_all = torch.empty((n, k), **i32), torch.empty((n, k), **i64)
-    cur = {}
+    # The running lists of ALL my rows stay resident (n x k x 12 bytes): the half ring merges candidates into the rows of
+    # the reference block as well as into those of the query block.
+    import os
 
-    def flush_query():
-        if cur:
-            sl = slice(my_off[cur["qi"]], my_off[cur["qi"]] + my_cnt[cur["qi"]])
-            idx_all[sl], d2_all[sl] = cur["best_idx"], cur["best_d2"]
+    k = max(1, min(p.num_neighbors, n_total - 1)) if n_total > 1 else 1
+    d2_all, idx_all = E.knn_init(n, k, dev)
+    cur = {}
+    full_ring = os.environ.get("GRIDB200_RING", "half") == "full"
+
+    def rows_of(bi):
+        return slice(my_off[bi], my_off[bi] + my_cnt[bi])
 
     def load_query(qi):
-        flush_query()
         cur.clear()
         zq, nq = operand(qi, "query")
-        bd2, bidx = E.knn_init(my_cnt[qi], k, dev)
-        cur.update(qi=qi, zq=zq, nq=nq, best_d2=bd2, best_idx=bidx)
+        cur.update(qi=qi, zq=zq, nq=nq, best_d2=d2_all[rows_of(qi)], best_idx=idx_all[rows_of(qi)])
 
     def load_ref(qi, ri):
         cur["zr"], nr_ = (cur["zq"], cur["nq"]) if ri == qi else operand(ri, "ref")   # own block: the symmetric Gram case
@@ -425,14 +521,20 @@ def run_chain_rows_blocked(source, n_local: int, b: int, counts_local: torch.Ten
         cur["round_off"] = [sum(cnts[:r]) for r in range(world)]
         return cur["zr"]
 
-    def block_fn(qi, ri, step, src, flat, n_ref, r_gid0):
+    def block_fn(qi, ri, step, src, flat, n_ref, r_gid0, q_range=None, r_range=None, t_lists=None):
         ref = cur["zr"] if step == 0 else flat.view(kdim // 64, n_ref, 64)
         nr_ = cur["norms_round"][cur["round_off"][src]:cur["round_off"][src] + n_ref]
         E.knn_block(cur["zq"], cur["nq"], offsets[rank] + my_off[qi], ref, nr_, r_gid0, kdim, p.zclip, cur["best_d2"],
-                    cur["best_idx"], impl=impl)
+                    cur["best_idx"], impl=impl, q_range=q_range, r_range=r_range, t_lists=t_lists)
 
-    ring_knn_blocked(rounds, blocks, offsets, group, load_query, load_ref, block_fn, flat_per_row=kdim)
-    flush_query()
+    def merge(ri, lo, d2_in, idx_in):
+        a0 = my_off[ri] + lo
+        with E._mark("merge_lists"):
+            E.merge_lists(d2_in, idx_in, d2_all[a0:a0 + d2_in.shape[0]], idx_all[a0:a0 + d2_in.shape[0]])
+
+    half = None if full_ring else HalfRingOps(lambda m: E.knn_init(m, k, dev), merge)
+    res.extra.update(ring_schedule="full" if full_ring else "half")
+    ring_knn_blocked(rounds, blocks, offsets, group, load_query, load_ref, block_fn, flat_per_row=kdim, half=half)
     cur.clear()
 
     # ---- step 6 --------------------------------------------------------------------------------------------------------

@@ -179,11 +179,22 @@ GRIDB200_API int gridb200_gram_set_max_pairs(int pairs);
  * (find_neighbors.py:218-219); merge into the running k-best lists, ascending by (d2, global index) -- the
  * order sklearn's heap + sort yields when no two candidates tie, lower index first among exact ties.
  * best_d2 [nq,k] / best_idx [nq,k] must be initialised with gridb200_topk_init before the first block.
- * nr + k <= 8192 per call. */
+ * nr + k <= 8192 per call.  Candidates are filtered against the list's current k-th entry before anything is sorted. */
 GRIDB200_API int gridb200_topk_init(int64_t* best_d2, int32_t* best_idx, int64_t nq, int32_t k, void* stream);
 GRIDB200_API int gridb200_topk_merge(const int64_t* dot, int64_t ldd, int64_t nq, int64_t nr,
                         const int64_t* normq, const int64_t* normr, int64_t q_gid0, int64_t r_gid0,
                         int32_t k, int64_t* best_d2, int32_t* best_idx, void* stream);
+/* The same block read through its TRANSPOSE: the lists best_d2/best_idx [nr,k] belong to the nr REFERENCE rows (global
+ * ids r_gid0..) and the nq query rows (q_gid0..) are the candidates.  The squared distance is symmetric, so a rank that
+ * has multiplied its rows with a peer's shard can hand the peer its k best instead of the peer recomputing the block
+ * (the half ring of grid_b200/ring.py; same find_neighbors.py:207-227 semantics per list).  nq + k <= 8192 per call. */
+GRIDB200_API int gridb200_topk_merge_t(const int64_t* dot, int64_t ldd, int64_t nq, int64_t nr,
+                          const int64_t* normq, const int64_t* normr, int64_t q_gid0, int64_t r_gid0,
+                          int32_t k, int64_t* best_d2, int32_t* best_idx, void* stream);
+/* Merge candidate lists src_d2/src_idx [n, src_k] (entries with idx < 0 are empty; no sample may already be in the
+ * destination list of its row) into the running lists best_d2/best_idx [n, k].  src_k + k <= 8192. */
+GRIDB200_API int gridb200_topk_merge_lists(const int64_t* src_d2, const int32_t* src_idx, int64_t n, int32_t src_k,
+                              int32_t k, int64_t* best_d2, int32_t* best_idx, void* stream);
 
 /* ------------------------------------------------------------------ step 6: compute_dipcn ---------------- */
 

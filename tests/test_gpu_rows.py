@@ -103,9 +103,17 @@ def _worker_blocked(rank, world, port, seed, n, b, params, out):
                                                        resident_blocks=resident)
         rounds = res.extra["rounds"]
         assert rounds >= 3 and max(nr for _, nr in asked) <= block_rows
-        # two statistics passes + one operand per (query block, round), minus the re-uses of the pinned prefix
-        m = min(resident, rounds)
-        assert len(asked) == 2 * rounds + rounds * rounds - (rounds * m - m)
+        # two statistics passes + one operand per (query block, round) the half ring runs (with fewer than three ranks
+        # the rounds below the diagonal are somebody's mirror image and are not even regenerated), minus the re-uses of
+        # the pinned prefix
+        pinned, made = set(), 0
+        for qi in range(rounds):
+            for bi in [qi] + [ri for ri in range(rounds) if ri != qi and not (world < 3 and ri < qi)]:
+                if bi not in pinned:
+                    made += 1
+                    if bi < resident:
+                        pinned.add(bi)
+        assert len(asked) == 2 * rounds + made
         np.testing.assert_array_equal(idx.cpu().numpy(), want["nbr_idx"][lo:hi])
         np.testing.assert_array_equal(d2.cpu().numpy(), want["nbr_d2"][lo:hi])
         np.testing.assert_allclose(cn.cpu().numpy(), want["dipcn"][lo:hi], rtol=DIPCN_REL)
@@ -166,3 +174,40 @@ def test_blocked_chain_ring(world):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     _run(world, 35, 1001, 4000, dict(num_neighbors=350, n_nbr=300, block_rows=130, resident_blocks=1), worker=_worker_blocked)
+
+
+def test_transposed_and_list_merges_match_numpy():
+    """gridb200_topk_merge_t reads a Gram block by columns; gridb200_topk_merge_lists merges two k-best lists."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from grid_b200 import engine
+    from grid_b200._lib import call, ptr
+
+    rng = np.random.default_rng(5)
+    nq, nr, kdim, k = 300, 170, 128, 40
+    q = rng.integers(-200, 201, size=(nq, kdim)).astype(np.int64)
+    r = rng.integers(-200, 201, size=(nr, kdim)).astype(np.int64)
+    r[7] = q[11]                                                                   # exact tie partners
+    dot = torch.from_numpy(q @ r.T).cuda().contiguous()
+    nqv, nrv = torch.from_numpy((q * q).sum(1)).cuda(), torch.from_numpy((r * r).sum(1)).cuda()
+    d2 = (q * q).sum(1)[:, None] + (r * r).sum(1)[None, :] - 2 * (q @ r.T)
+    st = torch.cuda.current_stream().cuda_stream
+    # lists of the reference rows (global ids 1000..), candidates = query rows (global ids 50..), in two candidate chunks
+    t_d2, t_idx = engine.knn_init(nr, k, "cuda")
+    for c0 in (0, 128):
+        n_c = min(128, nq - c0) if c0 == 0 else nq - c0
+        call("gridb200_topk_merge_t", dot.data_ptr() + c0 * nr * 8, nr, n_c, nr, nqv.data_ptr() + c0 * 8, ptr(nrv), 50 + c0,
+             1000, k, ptr(t_d2), ptr(t_idx), st)
+    for j in range(nr):
+        want = sorted((int(d2[i, j]), 50 + i) for i in range(nq))[:k]
+        assert [(int(a), int(b)) for a, b in zip(t_d2[j].tolist(), t_idx[j].tolist())] == want
+    # merging two disjoint halves of the candidates through lists gives the same lists
+    a_d2, a_idx = engine.knn_init(nr, k, "cuda")
+    b_d2, b_idx = engine.knn_init(nr, k, "cuda")
+    call("gridb200_topk_merge_t", ptr(dot), nr, 150, nr, ptr(nqv), ptr(nrv), 50, 1000, k, ptr(a_d2), ptr(a_idx), st)
+    call("gridb200_topk_merge_t", dot.data_ptr() + 150 * nr * 8, nr, nq - 150, nr, nqv.data_ptr() + 150 * 8, ptr(nrv), 200,
+         1000, k, ptr(b_d2), ptr(b_idx), st)
+    engine.merge_lists(b_d2, b_idx, a_d2, a_idx)
+    assert torch.equal(a_d2, t_d2) and torch.equal(a_idx, t_idx)
+    with pytest.raises(ValueError, match="num_neighbors"):
+        engine.check_k(5000)

@@ -162,3 +162,167 @@ def test_blocked_ring_over_gloo_matches_global_knn(world, n_total, block_rows):
     for p in procs:
         p.join(timeout=60)
     assert res == {r: "ok" for r in range(world)}
+
+
+# ---- the HALF ring: every pair of samples computed once, lists for the peer's rows read off the block's transpose ------
+INF = np.iinfo(np.int64).max
+
+
+class _NumpyLists:
+    """Stand-in for the CUDA k-best kernels: sorted (d2, idx) lists as torch CPU tensors (they travel through gloo)."""
+
+    def __init__(self, k):
+        self.k = k
+
+    def new(self, m):
+        return torch.full((m, self.k), INF, dtype=torch.int64), torch.full((m, self.k), -1, dtype=torch.int32)
+
+    def merge_rows(self, d2_t, idx_t, rows, cand):
+        """cand[i] = list of (d2, gid) for list row rows[i]."""
+        for i, row in enumerate(rows):
+            have = [(int(d), int(j)) for d, j in zip(d2_t[row].tolist(), idx_t[row].tolist()) if j >= 0]
+            assert not {j for _, j in have} & {j for _, j in cand[i]}, "a pair of samples met twice"
+            best = sorted(have + cand[i])[:self.k]
+            d2_t[row] = torch.tensor([d for d, _ in best] + [INF] * (self.k - len(best)), dtype=torch.int64)
+            idx_t[row] = torch.tensor([j for _, j in best] + [-1] * (self.k - len(best)), dtype=torch.int32)
+
+    def merge_lists(self, dst_d2, dst_idx, lo, src_d2, src_idx):
+        cand = [[(int(d), int(j)) for d, j in zip(src_d2[i].tolist(), src_idx[i].tolist()) if j >= 0]
+                for i in range(src_d2.shape[0])]
+        self.merge_rows(dst_d2, dst_idx, range(lo, lo + src_d2.shape[0]), cand)
+
+
+def _block_numpy(L, full, q_gid0, nq_all, r_gid0, n_ref, q_range, r_range, best, t_lists, symmetric):
+    qa, qz = q_range or (0, nq_all)
+    ra, rz = r_range or (0, n_ref)
+    q, r = full[q_gid0 + qa:q_gid0 + qz], full[r_gid0 + ra:r_gid0 + rz]
+    d2 = ((q[:, None, :] - r[None, :, :]) ** 2).sum(axis=2)
+    cand = [[(int(d2[i, j]), r_gid0 + ra + j) for j in range(rz - ra) if r_gid0 + ra + j != q_gid0 + qa + i]
+            for i in range(qz - qa)]
+    L.merge_rows(best[0], best[1], range(qa, qz), cand)
+    if t_lists is not None:
+        assert not symmetric
+        cand_t = [[(int(d2[i, j]), q_gid0 + qa + i) for i in range(qz - qa)] for j in range(rz - ra)]
+        L.merge_rows(t_lists[0], t_lists[1], range(ra, rz), cand_t)
+
+
+def _worker_half(rank, world, port, n_total, kdim, k, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(17)
+        full = rng.integers(-200, 201, size=(n_total, kdim)).astype(np.int64)
+        full[3] = full[n_total - 2]                                                # an exact duplicate across ranks (ties)
+        counts, offsets = ring.shard_rows(n_total, world)
+        L = _NumpyLists(k)
+        best = L.new(counts[rank])
+        shard = torch.from_numpy(full[offsets[rank]:offsets[rank] + counts[rank]].astype(np.float32).copy())
+        hops = []
+
+        def block(step, src, flat, n_ref, r_gid0, q_range, r_range, t_lists):
+            hops.append((step, src, q_range, r_range))
+            np.testing.assert_array_equal(flat.view(n_ref, kdim).numpy().astype(np.int64), full[r_gid0:r_gid0 + n_ref])
+            _block_numpy(L, full, offsets[rank], counts[rank], r_gid0, n_ref, q_range, r_range, best, t_lists, step == 0)
+
+        ops = ring.HalfRingOps(L.new, lambda lo, d2, idx: L.merge_lists(best[0], best[1], lo, d2, idx))
+        ring.ring_knn(shard, max(counts), counts, offsets, dist.group.WORLD, block, flat_per_row=kdim, half=ops)
+        assert [h[0] for h in hops] == list(range(world // 2 + 1))                 # half the hops
+        for i in range(counts[rank]):
+            g = offsets[rank] + i
+            dd = ((full[g][None, :] - full) ** 2).sum(axis=1)
+            want = sorted((int(dd[j]), j) for j in range(n_total) if j != g)[:k]
+            got = [(int(d), int(j)) for d, j in zip(best[0][i].tolist(), best[1][i].tolist()) if j >= 0]
+            assert got == want, (rank, i)
+        out.put((rank, "ok"))
+    except Exception as exc:
+        import traceback
+
+        out.put((rank, f"{type(exc).__name__}: {exc} {traceback.format_exc()[-800:]}"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_total", [(1, 7), (2, 9), (3, 10), (4, 14), (5, 11)])
+def test_half_ring_over_gloo_matches_global_knn(world, n_total):
+    """Odd and even worlds (the even ones split the opposite rank's block), uneven shards, a shard of one row."""
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_half, args=(r, world, port, n_total, 24, 4, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(out.get(timeout=180) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert res == {r: "ok" for r in range(world)}
+
+
+def _worker_half_blocked(rank, world, port, n_total, kdim, k, block_rows, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rng = np.random.default_rng(19)
+        full = rng.integers(-200, 201, size=(n_total, kdim)).astype(np.int64)
+        counts, offsets = ring.shard_rows(n_total, world)
+        rounds, blocks = ring.block_layout(counts, block_rows)
+        my_cnt, my_off = blocks[rank]
+        L = _NumpyLists(k)
+        best = L.new(counts[rank])                                                 # all my rows' lists stay resident
+        state, calls, loads = {}, [], []
+
+        def rows_of(r, bi):
+            lo = offsets[r] + blocks[r][1][bi]
+            return lo, lo + blocks[r][0][bi]
+
+        def load_query(qi):
+            state["qi"] = qi
+
+        def load_ref(qi, ri):
+            loads.append((qi, ri))
+            lo, hi = rows_of(rank, ri)
+            return torch.from_numpy(full[lo:hi].astype(np.float32).copy())
+
+        def block(qi, ri, step, src, flat, n_ref, r_gid0, q_range, r_range, t_lists):
+            assert qi == state["qi"]
+            calls.append((qi, ri, step, src))
+            lo, hi = rows_of(src, ri)
+            assert (r_gid0, n_ref) == (lo, hi - lo)
+            qlo, qhi = rows_of(rank, qi)
+            view = (best[0][my_off[qi]:my_off[qi] + my_cnt[qi]], best[1][my_off[qi]:my_off[qi] + my_cnt[qi]])
+            _block_numpy(L, full, qlo, qhi - qlo, r_gid0, n_ref, q_range, r_range, view, t_lists, step == 0 and qi == ri)
+
+        ops = ring.HalfRingOps(L.new, lambda ri, lo, d2, idx: L.merge_lists(best[0], best[1], my_off[ri] + lo, d2, idx))
+        ring.ring_knn_blocked(rounds, blocks, offsets, dist.group.WORLD, load_query, load_ref, block, flat_per_row=kdim,
+                              half=ops)
+        full_ring_blocks = rounds * rounds * world
+        assert len(set(calls)) == len(calls) and len(calls) <= full_ring_blocks // 2 + rounds * rounds
+        if world < 3:                                                              # lower-triangle rounds are not even regenerated
+            assert loads == [(qi, ri) for qi in range(rounds) for ri in range(qi, rounds)]
+        for i in range(counts[rank]):
+            g = offsets[rank] + i
+            dd = ((full[g][None, :] - full) ** 2).sum(axis=1)
+            want = sorted((int(dd[j]), j) for j in range(n_total) if j != g)[:k]
+            got = [(int(d), int(j)) for d, j in zip(best[0][i].tolist(), best[1][i].tolist()) if j >= 0]
+            assert got == want, (rank, i)
+        out.put((rank, "ok"))
+    except Exception as exc:
+        import traceback
+
+        out.put((rank, f"{type(exc).__name__}: {exc} {traceback.format_exc()[-800:]}"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n_total,block_rows", [(1, 11, 4), (2, 23, 5), (3, 31, 4), (4, 41, 4)])
+def test_half_blocked_ring_over_gloo_matches_global_knn(world, n_total, block_rows):
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_half_blocked, args=(r, world, port, n_total, 16, 5, block_rows, out))
+             for r in range(world)]
+    for p in procs:
+        p.start()
+    res = dict(out.get(timeout=180) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+    assert res == {r: "ok" for r in range(world)}

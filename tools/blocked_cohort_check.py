@@ -4,13 +4,15 @@ BASELINE config 4, scaled to the GPUs at hand: timing, where the time goes, and 
     torchrun --nproc-per-node W tools/blocked_cohort_check.py --samples 40000 --bins 2900000 --block-rows 5000 --k 200
 
 No rank ever holds its rows: every block is regenerated from the synthetic source when it is needed (two statistics
-passes, then once per (query block, round)).  After the timed step `--check` query rows of rank 0 are verified against
-exact brute-force distances to ALL samples (every rank regenerates its blocks' operands once more and measures them with
-fp64 matmuls of small integers): ids and d2 must match bit for bit.  One JSON line on rank 0."""
+passes, then once per (query block, round) the half ring runs).  After the timed step `--check` query rows PER RANK
+(spread over every rank's ownership range) are verified with oracle/cohort_check.py -- a chunked fp64 restatement of the
+oracle that regenerates the cohort from the synthetic source: ids and d2 bit for bit, %.2f scales of every row, step-4
+statistics, dipCN within 1e-5.  One JSON line on rank 0; exit status 1 on a mismatch."""
 import argparse
 import json
 import os
 import sys
+import time
 
 import torch
 import torch.distributed as dist
@@ -26,7 +28,7 @@ ap.add_argument("--k", type=int, default=200)
 ap.add_argument("--n-nbr", type=int, default=200)
 ap.add_argument("--steps", type=int, default=1)
 ap.add_argument("--warmup", type=int, default=0)
-ap.add_argument("--check", type=int, default=4)
+ap.add_argument("--check", type=int, default=8, help="query rows verified per rank")
 ap.add_argument("--resident-blocks", type=int, default=0, help="operands of the first m blocks stay in HBM")
 a = ap.parse_args()
 
@@ -35,7 +37,6 @@ os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
 os.environ.setdefault("MASTER_PORT", "29577")
 torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
-os.environ["NCCL_DEBUG"] = os.environ.get("GRIDB200_NCCL_DEBUG", "WARN")
 dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
 group = dist.group.WORLD
 cnt, off = ring.shard_rows(a.samples, world)
@@ -72,6 +73,7 @@ def one_step():
 for _ in range(a.warmup):
     one_step()
 engine.PROFILE = {}
+engine.GRAM_ELEMS = 0
 total_ms = 0.0
 for _ in range(a.steps):
     (res, idx, d2, cn), t_ms = one_step()
@@ -82,55 +84,58 @@ stages = engine.profile_summary(a.steps)
 engine.PROFILE = None
 peak_gb = torch.cuda.max_memory_allocated() / 1e9
 
-# ---- sampled exact check: rank 0's query rows against every row of the cohort ---------------------------------------
+# ---- sampled check: `--check` query rows of EVERY rank against the fp64 checker (cohort regenerated from the source) ----
+import numpy as np  # noqa: E402
+
+from oracle import cohort_check as C  # noqa: E402
+
 rounds, blocks = res.extra["rounds"], res.extra["blocks"]
-my_cnt, my_off = blocks[rank]
-nq = min(a.check, my_cnt[0]) if rank == 0 else min(a.check, blocks[0][0][0])
-kdim = (res.rw + 63) // 64 * 64
-rows = torch.linspace(0, blocks[0][0][0] - 1, nq).long().to(dev)          # inside rank 0's first block
-q = torch.empty((kdim // 64, nq, 64), dtype=torch.float16, device=dev)
-qn = torch.empty(nq, dtype=torch.int64, device=dev)
+t0 = time.perf_counter()
+counts_all = synth.read_counts(SEED, a.samples, [42599])
+qrows = C.spread_rows(a.samples, world, a.check, off, cnt)
+chk = C.CohortCheck(lambda r0, nr, c0, nc: engine.synth_depth(SEED, nr, nc, r0, c0, device=dev), a.samples, a.bins,
+                    dict(num_neighbors=a.k, n_nbr=a.n_nbr), dev, group=group, sharding="rows",
+                    rows=(off[rank], off[rank] + cnt[rank]))
+out = chk.run(qrows)
+mine = [t for t, q in enumerate(qrows) if off[rank] <= q < off[rank] + cnt[rank]]
+loc = torch.tensor([qrows[t] - off[rank] for t in mine], dtype=torch.int64, device=dev)
+ids_ok = bool(np.array_equal(idx[loc].cpu().numpy(), out["idx"][mine]))
+d2_ok = bool(np.array_equal(d2[loc].cpu().numpy(), out["d2"][mine]))
+want_cn = C.dipcn_rows(counts_all, out["scale_q"], [qrows[t] for t in mine], out["idx"][mine], a.n_nbr)
+rel = float(np.nanmax(np.abs(cn[loc].cpu().numpy() - want_cn) / np.abs(want_cn))) if mine else 0.0
+ties = set(out["tie_rows"].tolist())
+sq = res.scale_q.cpu().numpy()
+bad = [i for i in np.nonzero(sq != out["scale_q"][off[rank]:off[rank] + cnt[rank]])[0].tolist() if i + off[rank] not in ties]
+sel_ok = res.rw == len(out["sel"]) and res.r_use == out["r_use"]
+flags = torch.tensor([float(ids_ok), float(d2_ok), float(not bad), float(sel_ok), -rel], dtype=torch.float64, device=dev)
+dist.all_reduce(flags, op=dist.ReduceOp.MIN, group=group)
+fl = flags.tolist()
+ok = all(x == 1.0 for x in fl[:4]) and -fl[4] <= 1e-5
+check_s = time.perf_counter() - t0
 if rank == 0:
-    zh0, n0 = ring.block_operand(res, source(my_off[0], my_cnt[0]), my_off[0], p)
-    q.copy_(zh0[:, rows, :])
-    qn.copy_(n0[rows])
-    del zh0
-dist.broadcast(q, src=0, group=group)
-dist.broadcast(qn, src=0, group=group)
-qd = q.permute(1, 0, 2).reshape(nq, -1).double()
-d2_local = torch.empty((nq, cnt[rank]), dtype=torch.int64, device=dev)
-for bi in range(rounds):
-    zh, nrm = ring.block_operand(res, source(my_off[bi], my_cnt[bi]), my_off[bi], p)
-    for r0 in range(0, my_cnt[bi], 512):                                   # fp64 matmul of small integers: exact
-        blk = zh[:, r0:r0 + 512, :].permute(1, 0, 2).reshape(-1, kdim).double()
-        dots = qd @ blk.T
-        d2_local[:, my_off[bi] + r0:my_off[bi] + r0 + blk.shape[0]] = \
-            (qn.double()[:, None] + nrm[r0:r0 + blk.shape[0]].double()[None, :] - 2.0 * dots).round().long()
-    del zh
-d2_all = ring._all_gather_rows(d2_local.T.contiguous(), cnt, group).T       # [nq, N]
-ok, detail = True, ""
-if rank == 0:
-    big = torch.iinfo(torch.int64).max
-    for t in range(nq):
-        row = d2_all[t].clone()
-        row[off[0] + int(rows[t])] = big                                     # self excluded
-        key = row * (a.samples + 1) + torch.arange(a.samples, device=dev)    # (d2, index) order
-        want = torch.argsort(key)[: idx.shape[1]]
-        if not (torch.equal(want.int(), idx[rows[t]]) and torch.equal(row[want], d2[rows[t]])):
-            ok, detail = False, f"query row {int(rows[t])} differs"
-            break
     t_s = float(ms.item()) / 1e3
     gram_ms = stages.get("gram", {}).get("ms", 0.0)
-    useful = 2.0 * cnt[0] * a.samples * res.rw                               # this rank's share of 2 N^2 Ru
+    executed = 2.0 * engine.GRAM_ELEMS / max(1, a.steps) * res.rw              # what the tensor pipe did on this rank
+    useful = 2.0 * cnt[0] * a.samples * res.rw                                   # this rank's share of 2 N^2 Ru
+    peak = 1378.5
+    try:
+        peak = json.loads(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                            "MEASURED_PEAKS.json")).read()).get("bf16_tflops_sustained", peak)
+    except Exception:
+        pass
     line = {"workload": f"blocked out-of-core ring: {a.samples} synthetic samples x {a.bins} bins, k={a.k}, "
                         f"block_rows={a.block_rows} ({rounds} rounds)", "n_gpus": world, "s_per_step": round(t_s, 3),
-            "samples_per_s": round(a.samples / t_s, 1), "selected_bins": res.rw,
+            "samples_per_s": round(a.samples / t_s, 1), "selected_bins": res.rw, "schedule": res.extra.get("ring_schedule"),
             "stages_rank0_ms": {k2: round(v["ms"], 1) for k2, v in stages.items()},
+            "gram_tflops_rank0": round(executed / (gram_ms * 1e-3) / 1e12, 1) if gram_ms else None,
+            "gram_frac_of_tensor_peak": round(executed / (gram_ms * 1e-3) / 1e12 / peak, 3) if gram_ms else None,
             "gram_tflops_rank0_full_equiv": round(useful / (gram_ms * 1e-3) / 1e12, 1) if gram_ms else None,
             "regeneration_share": round((stages.get("source", {}).get("ms", 0.0) + stages.get("transform", {}).get("ms", 0.0))
                                         / (t_s * 1e3), 3),
             "resident_blocks": a.resident_blocks, "hbm_gb_peak_rank0": round(peak_gb, 1),
-            "checked_rows": nq, "exact_match": ok, "detail": detail}
+            "checked_rows": len(qrows), "checked_rows_per_rank": a.check, "ids_exact": fl[0] == 1.0, "d2_exact": fl[1] == 1.0,
+            "scale_q_exact": fl[2] == 1.0, "selected_bins_equal": fl[3] == 1.0, "dipcn_max_rel": -fl[4],
+            "exact_match": ok, "check_seconds": round(check_s, 1)}
     print(json.dumps(line), flush=True)
 dist.destroy_process_group()
 sys.exit(0 if ok else 1)

@@ -33,7 +33,6 @@ a = ap.parse_args()
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
 dev = torch.device("cuda", local)
-os.environ["NCCL_DEBUG"] = os.environ.get("GRIDB200_NCCL_DEBUG", "WARN")
 dist.init_process_group("nccl", device_id=dev)
 group = dist.group.WORLD
 cnt, off = ring.shard_rows(a.samples, world)
