@@ -385,6 +385,7 @@ def parity_check(n_total, b_total, params, dev, group, sharding, rows, bins, per
     ties = set(out["tie_rows"].tolist())
     bad = [i for i in np.nonzero(sq != want_sq)[0].tolist() if (i + row0) not in ties]
     flags["scale_q_exact"] = not bad
+    examples = [{"row": int(i + row0), "got": float(sq[i]), "want": float(want_sq[i])} for i in bad[:4]]
     flags["selected_bins_equal"] = bool(res.rw == len(out["sel"]) and res.r_use == out["r_use"])
     vec = torch.tensor([float(all(flags.values())), -rel] + [float(flags[k]) for k in sorted(flags)], dtype=torch.float64, device=dev)
     if group is not None:
@@ -394,6 +395,7 @@ def parity_check(n_total, b_total, params, dev, group, sharding, rows, bins, per
     rec.update({k: bool(v[2 + i]) for i, k in enumerate(sorted(flags))})
     rec.update({"dipcn_max_rel": -v[1], "dipcn_tol": DIPCN_REL, "scale_rows_checked": n_total, "scale_tie_rows": len(ties),
                 "codes_checked_per_rank": len(mine) * (out["sel_local"][1] - out["sel_local"][0]) if sharding != "rows" else None,
+                "scale_mismatches_this_rank": len(bad), "scale_mismatch_examples": examples,
                 "ok": bool(v[0]) and -v[1] <= DIPCN_REL,
                 "checker": "oracle/cohort_check.py: chunked fp64 restatement of oracle.chain_arrays, cohort regenerated from the "
                            "synthetic source, exact int64 distances of the query rows to ALL rows",

@@ -73,6 +73,27 @@ struct Work {
   int64_t nq, nr, ldd;
 };
 
+// Fused k-best epilogue (gridb200_gram_topk): instead of writing the block of dot products, a finished tile forms
+// d2 = |q|^2 + |r|^2 - 2 q.r in int64 and keeps only what can still enter a list -- d2 <= tau of its query row, or
+// <= tau of its reference row (the half ring wants the block read both ways) -- appending (d2, id) to small per-row
+// candidate buffers.  The distances themselves never reach memory.
+struct Fused {
+  const long long* norm_q;   // exact norms of the nq query rows / nr reference rows of this block
+  const long long* norm_r;
+  const long long* tau_q;    // current k-th best d2 of every query row (element i at tau_q[i * tau_q_stride]); +inf = take all
+  const long long* tau_r;    // ... of every reference row; nullptr = no lists for the reference rows
+  int64_t tau_q_stride, tau_r_stride;
+  long long* cq_d2;          // candidates of the query rows: [nq, cap] (d2, id), cq_cnt[nq] = appended so far (may exceed cap)
+  int* cq_id;
+  int* cq_cnt;
+  long long* cr_d2;          // candidates of the reference rows: [nr, cap]
+  int* cr_id;
+  int* cr_cnt;
+  int cap;
+  int64_t q_gid0, r_gid0;    // global sample ids of query row 0 / reference row 0
+  long long* scratch;        // [SMs][128][256] int64: private carries of the tile a CTA is working on
+};
+
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -296,10 +317,10 @@ __device__ __forceinline__ int next_item(int item, int npairs, int nitems, uint3
   return nxt;
 }
 
-template <bool kDynamic>
+template <bool kDynamic, bool kFused>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_r, const Work w,
-               long long* __restrict__ dot) {
+               long long* __restrict__ dot, const Fused f) {
   extern __shared__ unsigned char smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // 128B-swizzle atoms need 1024-byte alignment
   const uint32_t bars = base + STAGES * STAGE_BYTES;
@@ -438,6 +459,11 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
     int acc = 0, since_check = 0;
     uint32_t acc_phase = 0;
     Cursor cur;
+    // fused: carries of this thread's 128 elements live in a private slab of global memory (L2), [element][thread] so
+    // that a warp's accesses coalesce; a bit per element says whether its slot has been written for the current tile
+    uint32_t carried[EPI_COLS / 32];
+    long long* scr = nullptr;
+    if (kFused) scr = f.scratch + (size_t)sm_id() * (CTA_ROWS * TN) + (threadIdx.x - EPI_WARP0 * 32);
     for (int item = pair_id; item >= 0 && item < nitems;
          item = next_item<kDynamic, true>(item, npairs, nitems, clc_full0, clc_empty0, clc_resp0, cur, lane)) {
       int ks, tm, tn;
@@ -447,6 +473,10 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
       const int64_t col0 = (int64_t)tn * TN + half * EPI_COLS;
       long long* out = dot + row * w.ldd + col0;           // dot[row, col0 + i]
       const bool row_ok = row < w.nq;
+      if (kFused) {
+#pragma unroll
+        for (int g = 0; g < EPI_COLS / 32; ++g) carried[g] = 0;
+      }
       for (int c0 = kb0; c0 < kb1; c0 += w.ck) {
         mbar_wait(tfull0 + 8 * acc, acc_phase);
         tc_fence_after();
@@ -474,17 +504,55 @@ k_gram_tc_pair(const __grid_constant__ CUtensorMap map_q, const __grid_constant_
 #pragma unroll
           for (int i = 0; i < EPI_COLS; ++i) {
             if ((unsigned)(acc32[i] + 0x70000000) > 0xE0000000u) {
-              if (row_ok && col0 + i < w.nr) red_add_s64(out + i, (long long)acc32[i]);
+              if (kFused) {
+                const bool had = (carried[i >> 5] >> (i & 31)) & 1u;
+                scr[i * (CTA_ROWS * 2)] = (had ? scr[i * (CTA_ROWS * 2)] : 0LL) + (long long)acc32[i];
+                carried[i >> 5] |= 1u << (i & 31);
+              } else if (row_ok && col0 + i < w.nr) {
+                red_add_s64(out + i, (long long)acc32[i]);
+              }
               acc32[i] = 0;
             }
           }
         }
       }
       since_check = 0;
+      if (kFused) {
+        // the tile is complete in registers (+ carries): distances, threshold tests, candidate appends
+        const long long nq_i = row_ok ? f.norm_q[row] : 0;
+        const long long tq = row_ok ? f.tau_q[row * f.tau_q_stride] : -1;   // -1: nothing passes
+        const int64_t gid_q = f.q_gid0 + row;
+        const bool want_r = f.tau_r != nullptr;
 #pragma unroll
-      for (int i = 0; i < EPI_COLS; ++i) {
-        if (row_ok && col0 + i < w.nr && acc32[i] != 0) red_add_s64(out + i, (long long)acc32[i]);
-        acc32[i] = 0;
+        for (int i = 0; i < EPI_COLS; ++i) {
+          long long dotv = (long long)acc32[i];
+          if ((carried[i >> 5] >> (i & 31)) & 1u) dotv += scr[i * (CTA_ROWS * 2)];
+          acc32[i] = 0;
+          const int64_t col = col0 + i;
+          if (col < w.nr) {  // warp-uniform
+            const long long nr_j = __ldg(f.norm_r + col);
+            const long long d2 = nq_i + nr_j - 2 * dotv;
+            const int64_t gid_r = f.r_gid0 + col;
+            const bool live = row_ok && gid_q != gid_r;
+            if (live && d2 <= tq) {
+              const int slot = atomicAdd(f.cq_cnt + row, 1);
+              if (slot < f.cap) f.cq_d2[row * f.cap + slot] = d2, f.cq_id[row * f.cap + slot] = (int)gid_r;
+            }
+            if (want_r) {
+              const long long tr = __ldg(f.tau_r + col * f.tau_r_stride);
+              if (live && d2 <= tr) {
+                const int slot = atomicAdd(f.cr_cnt + col, 1);
+                if (slot < f.cap) f.cr_d2[col * f.cap + slot] = d2, f.cr_id[col * f.cap + slot] = (int)gid_q;
+              }
+            }
+          }
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < EPI_COLS; ++i) {
+          if (row_ok && col0 + i < w.nr && acc32[i] != 0) red_add_s64(out + i, (long long)acc32[i]);
+          acc32[i] = 0;
+        }
       }
     }
   }
@@ -560,8 +628,11 @@ extern "C" int gridb200_gram_set_max_pairs(int pairs) {
   return 0;
 }
 
-int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, int64_t nr, int64_t slabr,
-                     int64_t kdim, int32_t vmax, int64_t* dot, int64_t ldd, int accumulate, void* stream) {
+// Shared launcher.  fused == nullptr: dot += Q.R^T as exact int64 (gridb200_gram).  fused given: no dot matrix at all,
+// one work item per tile over the whole K (the int32 -> int64 carry never leaves the pair), k-best filter in the epilogue.
+static int launch_gram(const void* zq, int64_t nq, int64_t slabq, const void* zr, int64_t nr, int64_t slabr,
+                       int64_t kdim, int32_t vmax, int64_t* dot, int64_t ldd, int accumulate, void* stream,
+                       const g2::tc::Fused* fused) {
   using namespace g2;
   using namespace g2::tc;
   // largest chunk (in 64-wide k-blocks) whose partial sums stay strictly below 2^24
@@ -582,8 +653,10 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
     G2_CUDA(cudaGetDeviceProperties(&prop, dev));
     G2_REQUIRE(prop.major == 10, GRIDB200_ENODEV, "tcgen05 path needs an sm_100 device (found sm_%d%d)", prop.major,
                prop.minor);
-    G2_CUDA(cudaFuncSetAttribute(k_gram_tc_pair<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    G2_CUDA(cudaFuncSetAttribute(k_gram_tc_pair<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    G2_CUDA(cudaFuncSetAttribute(k_gram_tc_pair<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    G2_CUDA(cudaFuncSetAttribute(k_gram_tc_pair<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    G2_CUDA(cudaFuncSetAttribute(k_gram_tc_pair<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    G2_CUDA(cudaFuncSetAttribute(k_gram_tc_pair<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
     G2_REQUIRE(prop.multiProcessorCount <= PACE_SLOTS, GRIDB200_ENODEV, "more SMs than pacing slots");
     sms = prop.multiProcessorCount;
     sms_of[dev].store(sms);
@@ -608,7 +681,7 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
   const bool dynamic = !static_sched && !cap;
   Work w;
   w.nq = nq, w.nr = nr, w.ldd = ldd;
-  w.symmetric = (!no_sym && zq == zr && nq == nr && slabq == slabr) ? 1 : 0;
+  w.symmetric = (!fused && !no_sym && zq == zr && nq == nr && slabq == slabr) ? 1 : 0;
   w.tiles_m = (int)((nq + TM - 1) / TM);
   w.tiles_n = (int)((nr + TN - 1) / TN);
   w.ntiles = w.symmetric ? w.tiles_m * (w.tiles_m + 1) / 2 : w.tiles_m * w.tiles_n;
@@ -624,7 +697,7 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
   const int chunks = (w.kb_total + w.ck - 1) / w.ck;
   int best_s = 1;
   double best_eff = 0.0;
-  for (int s = 1; s <= 64 && s * 4 <= std::max(chunks, 4); ++s) {
+  for (int s = 1; !fused && s <= 64 && s * 4 <= std::max(chunks, 4); ++s) {
     const int cps = (chunks + s - 1) / s;          // chunks per split
     const int real_s = (chunks + cps - 1) / cps;   // splits actually needed
     const long long items = (long long)w.ntiles * real_s;
@@ -650,15 +723,18 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
   }
   static std::atomic<unsigned> epoch{0};
   w.epoch = epoch.fetch_add(1) + 1;
-  if (!accumulate) G2_CUDA(cudaMemset2DAsync(dot, ldd * sizeof(int64_t), 0, nr * sizeof(int64_t), nq, st));
+  if (!fused && !accumulate) G2_CUDA(cudaMemset2DAsync(dot, ldd * sizeof(int64_t), 0, nr * sizeof(int64_t), nq, st));
   const long long items = (long long)w.ntiles * w.ksplits;
   G2_REQUIRE(items < (1LL << 30), GRIDB200_EINVAL, "too many work items");
   const int nwork = (int)std::min<long long>(items, workers);
   w.pace_slots = dynamic ? sms : nwork;
-  if (dynamic)  // one cluster per item; the clusters that get SMs cancel the rest and take their items over
-    k_gram_tc_pair<true><<<2 * (unsigned)items, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, reinterpret_cast<long long*>(dot));
-  else
-    k_gram_tc_pair<false><<<2 * nwork, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, reinterpret_cast<long long*>(dot));
+  long long* dotp = reinterpret_cast<long long*>(dot);
+  const Fused f0{};
+  // dynamic: one cluster per item; the clusters that get SMs cancel the rest and take their items over
+  if (fused && dynamic) k_gram_tc_pair<true, true><<<2 * (unsigned)items, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, dotp, *fused);
+  else if (fused) k_gram_tc_pair<false, true><<<2 * nwork, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, dotp, *fused);
+  else if (dynamic) k_gram_tc_pair<true, false><<<2 * (unsigned)items, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, dotp, f0);
+  else k_gram_tc_pair<false, false><<<2 * nwork, NUM_THREADS, SMEM_BYTES, st>>>(mq, mr, w, dotp, f0);
   G2_LAUNCHED();
   if (w.symmetric && w.tiles_m > 1) {
     const unsigned nb = (unsigned)((nq + 31) / 32);
@@ -666,4 +742,38 @@ int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, 
     G2_LAUNCHED();
   }
   return 0;
+}
+
+int gridb200_gram_tc(const void* zq, int64_t nq, int64_t slabq, const void* zr, int64_t nr, int64_t slabr,
+                     int64_t kdim, int32_t vmax, int64_t* dot, int64_t ldd, int accumulate, void* stream) {
+  return launch_gram(zq, nq, slabq, zr, nr, slabr, kdim, vmax, dot, ldd, accumulate, stream, nullptr);
+}
+
+extern "C" size_t gridb200_gram_topk_ws_bytes(void) {
+  return (size_t)g2::tc::PACE_SLOTS * g2::tc::CTA_ROWS * g2::tc::TN * sizeof(long long);  // one carry slab per SM
+}
+
+extern "C" int gridb200_gram_topk(const void* zq, int64_t nq, int64_t slabq, const void* zr, int64_t nr, int64_t slabr,
+                                  int64_t kdim, int32_t vmax, const int64_t* normq, const int64_t* normr, int64_t q_gid0,
+                                  int64_t r_gid0, const int64_t* tau_q, int64_t tau_q_stride, const int64_t* tau_r,
+                                  int64_t tau_r_stride, int32_t cap, int64_t* cq_d2, int32_t* cq_idx, int32_t* cq_cnt,
+                                  int64_t* cr_d2, int32_t* cr_idx, int32_t* cr_cnt, void* ws, size_t ws_bytes,
+                                  void* stream) {
+  using namespace g2;
+  G2_REQUIRE(zq && zr && normq && normr && tau_q && cq_d2 && cq_idx && cq_cnt && ws, GRIDB200_EINVAL, "null pointer");
+  G2_REQUIRE(!tau_r || (cr_d2 && cr_idx && cr_cnt), GRIDB200_EINVAL, "tau_r given without candidate buffers for the reference rows");
+  G2_REQUIRE(nq > 0 && nr > 0 && kdim > 0 && kdim % 64 == 0 && slabq >= nq && slabr >= nr, GRIDB200_EINVAL, "bad shape");
+  G2_REQUIRE(cap > 0 && tau_q_stride > 0 && (!tau_r || tau_r_stride > 0), GRIDB200_EINVAL, "bad capacity / stride");
+  G2_REQUIRE(ws_bytes >= gridb200_gram_topk_ws_bytes(), GRIDB200_EINVAL, "workspace too small");
+  G2_REQUIRE(((reinterpret_cast<uintptr_t>(zq) | reinterpret_cast<uintptr_t>(zr)) & 15) == 0, GRIDB200_EINVAL,
+             "operands must be 16-byte aligned");
+  G2_REQUIRE(q_gid0 + nq < (1LL << 31) && r_gid0 + nr < (1LL << 31), GRIDB200_EINVAL, "indices exceed int32");
+  tc::Fused f{};
+  f.norm_q = reinterpret_cast<const long long*>(normq), f.norm_r = reinterpret_cast<const long long*>(normr);
+  f.tau_q = reinterpret_cast<const long long*>(tau_q), f.tau_r = reinterpret_cast<const long long*>(tau_r);
+  f.tau_q_stride = tau_q_stride, f.tau_r_stride = tau_r_stride;
+  f.cq_d2 = reinterpret_cast<long long*>(cq_d2), f.cq_id = cq_idx, f.cq_cnt = cq_cnt;
+  f.cr_d2 = reinterpret_cast<long long*>(cr_d2), f.cr_id = cr_idx, f.cr_cnt = cr_cnt;
+  f.cap = cap, f.q_gid0 = q_gid0, f.r_gid0 = r_gid0, f.scratch = reinterpret_cast<long long*>(ws);
+  return launch_gram(zq, nq, slabq, zr, nr, slabr, kdim, vmax, nullptr, 0, 1, stream, &f);
 }

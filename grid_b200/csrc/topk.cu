@@ -8,6 +8,8 @@
 //   kRows  : list = query row i,      candidates = the row's entries of a Gram block            (gridb200_topk_merge)
 //   kCols  : list = reference row j,  candidates = the COLUMN j of the block (its transpose)    (gridb200_topk_merge_t)
 //   kLists : list = row i,            candidates = another k-best list for the same row          (gridb200_topk_merge_lists)
+//   kCand  : list = row i,            candidates = the first min(cnt[i], cap) entries of the row's candidate buffer
+//                                     filled by the fused Gram epilogue                            (gridb200_topk_merge_cand)
 // kCols and kLists serve the half ring (grid_b200/ring.py): a rank that has multiplied its rows with a peer's shard
 // extracts the PEER's k best from the transpose and sends those lists instead of the peer recomputing the block.
 #include "common.cuh"
@@ -16,7 +18,7 @@ namespace g2 {
 
 constexpr long long kInfD2 = 0x7fffffffffffffffLL;
 constexpr int kTopkMaxKeys = 8192;
-enum { kRows = 0, kCols = 1, kLists = 2 };
+enum { kRows = 0, kCols = 1, kLists = 2, kCand = 3 };
 
 __device__ __forceinline__ bool pair_less(long long da, int ia, long long db, int ib) {
   return da < db || (da == db && ia < ib);
@@ -40,6 +42,7 @@ struct TopkArgs {
   const long long* src_d2;   // kLists: candidate lists [nlists, src_k]
   const int* src_idx;
   int src_k;
+  const int* src_cnt;        // kCand: entries appended to each row's buffer (may exceed src_k = its capacity)
   int k;
   long long* best_d2;
   int* best_idx;
@@ -66,11 +69,12 @@ __global__ void __launch_bounds__(256) k_topk_merge(const TopkArgs a) {
   const long long tau_d = sd[k - 1];
   const int tau_i = si[k - 1];
   const int64_t self = a.l_gid0 + row;
-  const long long nl = kMode == kLists ? 0 : a.norm_l[row];
-  for (int64_t j = threadIdx.x; j < a.ncand; j += 256) {
+  const long long nl = (kMode == kLists || kMode == kCand) ? 0 : a.norm_l[row];
+  const int64_t ncand = kMode == kCand ? (int64_t)min(a.src_cnt[row], a.src_k) : a.ncand;
+  for (int64_t j = threadIdx.x; j < ncand; j += 256) {
     long long d;
     int id;
-    if (kMode == kLists) {
+    if (kMode == kLists || kMode == kCand) {
       d = a.src_d2[row * a.src_k + j];
       id = a.src_idx[row * a.src_k + j];
       if (id < 0) continue;
@@ -182,4 +186,15 @@ extern "C" int gridb200_topk_merge_lists(const int64_t* src_d2, const int32_t* s
   a.src_d2 = reinterpret_cast<const long long*>(src_d2), a.src_idx = src_idx, a.src_k = src_k, a.ncand = src_k;
   a.k = k, a.best_d2 = reinterpret_cast<long long*>(best_d2), a.best_idx = best_idx;
   return launch_topk<kLists>(a, n, as_stream(stream));
+}
+
+extern "C" int gridb200_topk_merge_cand(const int64_t* cand_d2, const int32_t* cand_idx, const int32_t* cand_cnt, int64_t n,
+                                        int32_t cap, int32_t k, int64_t* best_d2, int32_t* best_idx, void* stream) {
+  G2_REQUIRE(cand_d2 && cand_idx && cand_cnt && best_d2 && best_idx, GRIDB200_EINVAL, "null pointer");
+  G2_REQUIRE(n > 0 && k > 0 && cap > 0 && cap + k <= kTopkMaxKeys, GRIDB200_EINVAL, "bad shape (cap + k must be <= %d)",
+             kTopkMaxKeys);
+  TopkArgs a{};
+  a.src_d2 = reinterpret_cast<const long long*>(cand_d2), a.src_idx = cand_idx, a.src_k = cap, a.src_cnt = cand_cnt;
+  a.k = k, a.best_d2 = reinterpret_cast<long long*>(best_d2), a.best_idx = best_idx;
+  return launch_topk<kCand>(a, n, as_stream(stream));
 }

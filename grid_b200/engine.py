@@ -369,6 +369,95 @@ def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torc
             best_idx[q0:q0 + nq] = all_idx[:nq]
 
 
+FUSED_CAP = 1024          # candidate slots per row of the fused Gram + k-best kernel
+FUSED_MIN_ELEMS = 1 << 22  # "auto": blocks smaller than this keep the dot-matrix path (its split-K fills the SMs better)
+COUNTERS = {"fused_blocks": 0, "fused_overflow": 0, "unfused_blocks": 0}
+_FUSED_WS: dict = {}
+
+
+def fused_mode() -> str:
+    """GRIDB200_FUSED = auto (default) | 1 (every eligible block, whatever its size: tests) | 0 (never)."""
+    import os
+
+    return os.environ.get("GRIDB200_FUSED", "auto")
+
+
+def knn_block_fused(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torch.Tensor, norms_r: torch.Tensor,
+                    r_gid0: int, kdim: int, vmax: int, best_d2: torch.Tensor, best_idx: torch.Tensor,
+                    q_range=None, r_range=None, tau_r: torch.Tensor | None = None, t_lists=None) -> bool:
+    """knn_block through gridb200_gram_topk: the block's distances are filtered against the lists' current k-th entries
+    in the Gram epilogue and never reach memory.  tau_r [rows of zh_r] = current k-th best d2 of the REFERENCE rows
+    (their owner's lists) -- required with t_lists, which then receive only what can still enter those lists.
+    Returns False, having changed nothing, when the block is not eligible (a list without k entries yet: nothing to
+    filter against) or a candidate buffer overflowed; the caller then takes knn_block."""
+    nq_all, nr_all = zh_q.shape[1], zh_r.shape[1]
+    qa, qz = q_range or (0, nq_all)
+    ra, rz = r_range or (0, nr_all)
+    nq, nr = qz - qa, rz - ra
+    k = best_d2.shape[1]
+    cap = min(FUSED_CAP, TOPK_MAX_KEYS - k)
+    if nq <= 0 or nr <= 0:
+        return True
+    if vmax > 511 or cap < 64 or (t_lists is not None and tau_r is None):
+        return False
+    dev, st = zh_q.device, _stream()
+    inf = torch.iinfo(torch.int64).max
+    tau_q = best_d2[qa:qz, k - 1]
+    ready = (tau_q != inf).all()
+    if t_lists is not None:
+        ready = ready & (tau_r[ra:rz] != inf).all()
+    if not bool(ready):  # (one host sync: a list that is not full yet has no threshold -- everything would survive)
+        return False
+    ws = _FUSED_WS.get(dev)
+    if ws is None:
+        ws = _FUSED_WS[dev] = _ws(_lib.load().gridb200_gram_topk_ws_bytes(), dev)
+    i32 = dict(dtype=torch.int32, device=dev)
+    cq_d2 = torch.empty((nq, cap), dtype=torch.int64, device=dev)
+    cq_idx, cq_cnt = torch.empty((nq, cap), **i32), torch.zeros(nq, **i32)
+    cr_d2 = cr_idx = cr_cnt = None
+    if t_lists is not None:
+        cr_d2 = torch.empty((nr, cap), dtype=torch.int64, device=dev)
+        cr_idx, cr_cnt = torch.empty((nr, cap), **i32), torch.zeros(nr, **i32)
+    global GRAM_ELEMS
+    with _mark("gram"):
+        call("gridb200_gram_topk", zh_q.data_ptr() + qa * 64 * 2, nq, nq_all, zh_r.data_ptr() + ra * 64 * 2, nr, nr_all,
+             kdim, vmax, norms_q.data_ptr() + qa * 8, norms_r.data_ptr() + ra * 8, q_gid0 + qa, r_gid0 + ra,
+             best_d2.data_ptr() + (qa * k + k - 1) * 8, k, (tau_r.data_ptr() + ra * 8) if t_lists is not None else None, 1,
+             cap, ptr(cq_d2), ptr(cq_idx), ptr(cq_cnt), ptr(cr_d2), ptr(cr_idx), ptr(cr_cnt), ptr(ws), ws.numel(), st)
+    GRAM_ELEMS += nq * nr
+    over = (cq_cnt > cap).any()
+    if t_lists is not None:
+        over = over | (cr_cnt > cap).any()
+    if bool(over):  # a row met more than `cap` samples closer than its k-th best: redo the block with the dot matrix
+        COUNTERS["fused_overflow"] += 1
+        return False
+    with _mark("topk"):
+        call("gridb200_topk_merge_cand", ptr(cq_d2), ptr(cq_idx), ptr(cq_cnt), nq, cap, k, best_d2.data_ptr() + qa * k * 8,
+             best_idx.data_ptr() + qa * k * 4, st)
+        if t_lists is not None:
+            t_d2, t_idx = t_lists
+            call("gridb200_topk_merge_cand", ptr(cr_d2), ptr(cr_idx), ptr(cr_cnt), nr, cap, k, t_d2.data_ptr() + ra * k * 8,
+                 t_idx.data_ptr() + ra * k * 4, st)
+    COUNTERS["fused_blocks"] += 1
+    return True
+
+
+def knn_block_auto(zh_q, norms_q, q_gid0, zh_r, norms_r, r_gid0, kdim, vmax, best_d2, best_idx, impl=0, q_range=None,
+                   r_range=None, t_lists=None, tau_r=None, symmetric=False) -> None:
+    """One block of the ring schedules: the fused Gram + k-best kernel where it applies (a rectangular block between
+    different sample sets whose lists already hold k entries), the dot-matrix path otherwise or on overflow."""
+    mode = fused_mode()
+    nq = (q_range[1] - q_range[0]) if q_range else zh_q.shape[1]
+    nr = (r_range[1] - r_range[0]) if r_range else zh_r.shape[1]
+    want = impl == 0 and not symmetric and mode != "0" and (mode == "1" or nq * nr >= FUSED_MIN_ELEMS)
+    if want and knn_block_fused(zh_q, norms_q, q_gid0, zh_r, norms_r, r_gid0, kdim, vmax, best_d2, best_idx, q_range=q_range,
+                                r_range=r_range, tau_r=tau_r, t_lists=t_lists):
+        return
+    COUNTERS["unfused_blocks"] += 1
+    knn_block(zh_q, norms_q, q_gid0, zh_r, norms_r, r_gid0, kdim, vmax, best_d2, best_idx, impl=impl, q_range=q_range,
+              r_range=r_range, t_lists=t_lists)
+
+
 def knn(zh: torch.Tensor, kdim: int, norms: torch.Tensor, k: int, vmax: int, impl: int = 0, group=None,
         max_block_bytes: int = 2 << 30):
     """Exact k nearest neighbours of every row among all rows (self excluded): (idx[n,k] int32, d2[n,k] int64).

@@ -259,8 +259,14 @@ def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, g
 
     def block(step, src, flat, n_ref, r_gid0, q_range=None, r_range=None, t_lists=None):
         ref = zh if step == 0 else flat.view(kdim // 64, n_ref, 64)  # hop 0 is the symmetric (same-operand) case
-        E.knn_block(zh, norms, offsets[rank], ref, norms_all[r_gid0:r_gid0 + n_ref], r_gid0, kdim, p.zclip, best_d2,
-                    best_idx, impl=impl, q_range=q_range, r_range=r_range, t_lists=t_lists)
+        tau_r = None
+        if t_lists is not None and E.fused_mode() != "0":
+            # the shard owner's current k-th best distances: what the fused epilogue filters the peer's candidates against
+            # (every rank is at the same hop; a value that is a hop stale only lets a few more candidates through)
+            tau_r = _all_gather_rows(best_d2[:, k - 1].contiguous(), counts, group)[r_gid0:r_gid0 + n_ref]
+        E.knn_block_auto(zh, norms, offsets[rank], ref, norms_all[r_gid0:r_gid0 + n_ref], r_gid0, kdim, p.zclip, best_d2,
+                         best_idx, impl=impl, q_range=q_range, r_range=r_range, t_lists=t_lists, tau_r=tau_r,
+                         symmetric=step == 0)
 
     def merge(lo, d2_in, idx_in):
         with E._mark("merge_lists"):
@@ -519,13 +525,20 @@ def run_chain_rows_blocked(source, n_local: int, b: int, counts_local: torch.Ten
         cnts = [blocks[r][0][ri] for r in range(world)]
         cur["norms_round"] = _all_gather_rows(nr_, cnts, group) if world > 1 else nr_
         cur["round_off"] = [sum(cnts[:r]) for r in range(world)]
+        # current k-th best distances of every rank's block ri: the fused epilogue's filter for the reference rows
+        tau = d2_all[rows_of(ri), k - 1].contiguous()
+        cur["tau_round"] = (_all_gather_rows(tau, cnts, group) if world > 1 else tau) if E.fused_mode() != "0" else None
         return cur["zr"]
 
     def block_fn(qi, ri, step, src, flat, n_ref, r_gid0, q_range=None, r_range=None, t_lists=None):
         ref = cur["zr"] if step == 0 else flat.view(kdim // 64, n_ref, 64)
         nr_ = cur["norms_round"][cur["round_off"][src]:cur["round_off"][src] + n_ref]
-        E.knn_block(cur["zq"], cur["nq"], offsets[rank] + my_off[qi], ref, nr_, r_gid0, kdim, p.zclip, cur["best_d2"],
-                    cur["best_idx"], impl=impl, q_range=q_range, r_range=r_range, t_lists=t_lists)
+        tau_r = None
+        if cur["tau_round"] is not None:
+            tau_r = cur["tau_round"][cur["round_off"][src]:cur["round_off"][src] + n_ref]
+        E.knn_block_auto(cur["zq"], cur["nq"], offsets[rank] + my_off[qi], ref, nr_, r_gid0, kdim, p.zclip, cur["best_d2"],
+                         cur["best_idx"], impl=impl, q_range=q_range, r_range=r_range, t_lists=t_lists, tau_r=tau_r,
+                         symmetric=step == 0 and qi == ri)
 
     def merge(ri, lo, d2_in, idx_in):
         a0 = my_off[ri] + lo

@@ -196,6 +196,29 @@ GRIDB200_API int gridb200_topk_merge_t(const int64_t* dot, int64_t ldd, int64_t 
 GRIDB200_API int gridb200_topk_merge_lists(const int64_t* src_d2, const int32_t* src_idx, int64_t n, int32_t src_k,
                               int32_t k, int64_t* best_d2, int32_t* best_idx, void* stream);
 
+/* The Gram block and the k-best filter in ONE kernel: the distances never reach memory.  Same operands and exact
+ * arithmetic as gridb200_gram (impl 0; one work item per 256 x 256 tile over the whole K, the int32 -> int64 carry stays
+ * with the CTA pair), but a finished tile forms d2 = normq[i] + normr[j] - 2*dot in int64 in the epilogue and appends
+ * (d2, id) only where it can still enter a list: to the candidate buffer of query row i when d2 <= tau_q[i*tau_q_stride]
+ * (tau = the row's current k-th best d2; +inf takes everything), and -- when tau_r is given: the half ring reads every
+ * block both ways -- to that of reference row j when d2 <= tau_r[j*tau_r_stride].  The row's own sample is skipped by
+ * global id.  This is sklearn's ArgKmin keeping per-row heaps while it walks the distance chunks, instead of a stored
+ * N x N matrix (find_neighbors.py:207-213).  cq_* / cr_*: [rows, cap] buffers + per-row counters (zeroed by the caller;
+ * a counter above cap means candidates were dropped: the caller must redo that block through gridb200_gram +
+ * gridb200_topk_merge).  gridb200_topk_merge_cand then merges a buffer into the running lists.  ws: carry slabs,
+ * gridb200_gram_topk_ws_bytes() bytes.  vmax <= 511. */
+GRIDB200_API size_t gridb200_gram_topk_ws_bytes(void);
+GRIDB200_API int gridb200_gram_topk(const void* zq_f16, int64_t nq, int64_t slabq, const void* zr_f16, int64_t nr,
+                       int64_t slabr, int64_t kdim, int32_t vmax, const int64_t* normq, const int64_t* normr,
+                       int64_t q_gid0, int64_t r_gid0, const int64_t* tau_q, int64_t tau_q_stride,
+                       const int64_t* tau_r, int64_t tau_r_stride, int32_t cap,
+                       int64_t* cq_d2, int32_t* cq_idx, int32_t* cq_cnt,
+                       int64_t* cr_d2, int32_t* cr_idx, int32_t* cr_cnt, void* ws, size_t ws_bytes, void* stream);
+/* Merge the first min(cand_cnt[i], cap) entries of each row's candidate buffer [n, cap] into the running lists [n, k]
+ * (cap + k <= 8192). */
+GRIDB200_API int gridb200_topk_merge_cand(const int64_t* cand_d2, const int32_t* cand_idx, const int32_t* cand_cnt,
+                             int64_t n, int32_t cap, int32_t k, int64_t* best_d2, int32_t* best_idx, void* stream);
+
 /* ------------------------------------------------------------------ step 6: compute_dipcn ---------------- */
 
 /* out[i,g] = (counts[q0+i,g]/scale[q0+i]) / mean over contributing neighbours j of counts[j,g]/scale[j]; NaN where

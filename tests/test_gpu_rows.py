@@ -169,6 +169,24 @@ def test_blocked_chain_single_rank(resident):
     _run(1, 34, 530, 3000, dict(num_neighbors=300, n_nbr=40, block_rows=150, resident_blocks=resident), worker=_worker_blocked)
 
 
+@pytest.mark.parametrize("fused", ["1", "0"])
+def test_blocked_chain_single_rank_fused_epilogue(fused, monkeypatch):
+    """The same schedule with the fused Gram + k-best kernel forced on every eligible block (k = 60 < block rows, so the
+    lists fill and later blocks are filtered in the epilogue), and with it switched off: identical results."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    monkeypatch.setenv("GRIDB200_FUSED", fused)          # spawned workers inherit the environment
+    _run(1, 36, 530, 3000, dict(num_neighbors=60, n_nbr=40, block_rows=150, resident_blocks=0), worker=_worker_blocked)
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_rows_chain_ring_fused_epilogue(world, monkeypatch):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    monkeypatch.setenv("GRIDB200_FUSED", "1")
+    _run(world, 37, 901, 4000, dict(num_neighbors=100, n_nbr=80))
+
+
 @pytest.mark.parametrize("world", [2, 4])
 def test_blocked_chain_ring(world):
     if torch.cuda.device_count() < world:
