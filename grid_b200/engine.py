@@ -152,10 +152,14 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
     _all_reduce(rowcnt, group)
     raw_mean, scale_q, row_factor = torch.empty(n, **f64), torch.empty(n, **f64), torch.empty(n, **f64)
     call("gridb200_row_scales", ptr(rowsum), ptr(rowcnt), n, ptr(raw_mean), ptr(scale_q), ptr(row_factor), st)
-    if group is None:  # exact %.2f ties take numpy's own mean (needs whole rows: not available when bins are sharded,
-        #                where rows are millions of bins long and an exact tie has probability ~1/bins)
+    # exact %.2f ties take numpy's own mean: a pairwise fp64 sum over the WHOLE row, replayed for the tie rows only
+    n_tie_t = None
+    if group is None:
         call("gridb200_row_means_exact", ptr(depth), n, b, ld, ptr(valid), ptr(rowsum), ptr(rowcnt), ptr(raw_mean),
              ptr(scale_q), st)
+    else:  # bins are sharded: rows are not whole on any rank; ties are known exactly from the all-reduced integer sums
+        tie = (rowcnt > 0) & ((2 * rowsum) % (2 * rowcnt.to(torch.int64)).clamp(min=1) == rowcnt)
+        n_tie_t = tie.sum()
 
     sd, sd2 = torch.empty(b, **f64), torch.empty(b, **f64)
     ws = _ws(_lib.load().gridb200_col_norm_stats_ws_bytes(n, b), dev)
@@ -165,7 +169,10 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
     mu, s2, ratio = torch.empty(b, **f64), torch.empty(b, **f64), torch.empty(b, **f64)
     # samples without any valid bin are dropped by the reference before normalising (filter_empty_samples,
     # normalize_mosdepth.py:576-600); they contribute nothing here either, only N in the ddof=1 divisor changes
-    n_eff = int((rowcnt > 0).sum())
+    counts_host = torch.stack([(rowcnt > 0).sum(), n_tie_t if n_tie_t is not None else rowcnt.new_zeros(())]).tolist()
+    n_eff = int(counts_host[0])
+    if counts_host[1]:
+        _sharded_tie_means(depth, b, valid, rowsum, rowcnt, raw_mean, scale_q, tie, group)
     call("gridb200_col_finalize", ptr(sd), ptr(sd2), ptr(colcnt), ptr(valid), b, n_eff, ptr(mu), ptr(s2), ptr(ratio), st)
 
     # selection runs on the whole cohort's ratio vector (every rank redundantly)
@@ -237,6 +244,45 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
     res.zq, res.zh, res.kdim, res.norms = zq, zh, ldh, norms
     res.extra["sat"] = sat
     return res
+
+
+def _sharded_tie_means(depth, b, valid, rowsum, rowcnt, raw_mean, scale_q, tie, group) -> None:
+    """Bin-sharded cohorts: the rows whose exact mean sits on a %.2f tie (known from the all-reduced integer sums) are
+    assembled whole on every rank -- a few rows x all bins -- and numpy's pairwise sum is replayed for them
+    (gridb200_row_means_exact), so that single- and multi-GPU runs print the same scales.  Ties are rare (about one
+    row in `bins`), so the exchange is a few rows of fp32."""
+    import torch.distributed as dist
+
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    dev = depth.device
+    rows = torch.nonzero(tie).flatten()
+    nt = rows.numel()
+    sizes = torch.zeros(world, dtype=torch.int64, device=dev)
+    sizes[rank] = b
+    dist.all_reduce(sizes, group=group)
+    sizes = sizes.tolist()
+    bmax, btot = max(sizes), sum(sizes)
+    mine = torch.zeros((nt, bmax), dtype=torch.float32, device=dev)
+    mine[:, :b] = depth[rows, :b]
+    vmine = torch.zeros(bmax, dtype=torch.uint8, device=dev)
+    vmine[:b] = valid
+    got = torch.empty((world, nt, bmax), dtype=torch.float32, device=dev)
+    vgot = torch.empty((world, bmax), dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(got, mine, group=group)
+    dist.all_gather_into_tensor(vgot, vmine, group=group)
+    ldf = (btot + 3) // 4 * 4
+    full = torch.zeros((nt, ldf), dtype=torch.float32, device=dev)
+    vfull = torch.zeros(btot, dtype=torch.uint8, device=dev)
+    at = 0
+    for r in range(world):  # ranks are ordered by bin range
+        full[:, at:at + sizes[r]] = got[r, :, :sizes[r]]
+        vfull[at:at + sizes[r]] = vgot[r, :sizes[r]]
+        at += sizes[r]
+    rs, rc = rowsum[rows].contiguous(), rowcnt[rows].contiguous()
+    rm, sq = raw_mean[rows].contiguous(), scale_q[rows].contiguous()
+    call("gridb200_row_means_exact", ptr(full), nt, btot, ldf, ptr(vfull), ptr(rs), ptr(rc), ptr(rm), ptr(sq), _stream())
+    raw_mean[rows] = rm
+    scale_q[rows] = sq
 
 
 def prepare_from_zq(zq: torch.Tensor, rw: int, keep: torch.Tensor | None, zclip: int):

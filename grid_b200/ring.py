@@ -163,6 +163,55 @@ def _all_gather_rows(t: torch.Tensor, counts: list[int], group) -> torch.Tensor:
     return torch.cat([out[r * mx: r * mx + counts[r]] for r in range(world)])
 
 
+def knn_rows(zh: torch.Tensor, kdim: int, norms: torch.Tensor, counts: list[int], offsets: list[int], num_neighbors: int,
+             vmax: int, group, impl: int = 0, extra: dict | None = None):
+    """Exact k nearest neighbours of this rank's rows among ALL ranks' rows (self excluded) by the half ring.
+    zh [kdim/64, n_local, 64]: this rank's k-blocked operand, norms [n_local] its exact row norms; counts/offsets: the
+    row blocks of all ranks.  Returns (idx [n_local, k] int32 GLOBAL ids, d2 [n_local, k] int64), (d2, index) order."""
+    from . import engine as E
+    from ._lib import call
+
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    n, dev = zh.shape[1], zh.device
+    n_total = sum(counts)
+    extra = extra if extra is not None else {}
+    norms_all = _all_gather_rows(norms, counts, group)
+    k = max(1, min(num_neighbors, n_total - 1)) if n_total > 1 else 1
+    best_d2, best_idx = E.knn_init(n, k, dev)
+
+    def block(step, src, flat, n_ref, r_gid0, q_range=None, r_range=None, t_lists=None):
+        ref = zh if step == 0 else flat.view(kdim // 64, n_ref, 64)  # hop 0 is the symmetric (same-operand) case
+        tau_r = None
+        if t_lists is not None and E.fused_mode() != "0":
+            # the shard owner's current k-th best distances: what the fused epilogue filters the peer's candidates against
+            # (every rank is at the same hop; a value that is a hop stale only lets a few more candidates through)
+            tau_r = _all_gather_rows(best_d2[:, k - 1].contiguous(), counts, group)[r_gid0:r_gid0 + n_ref]
+        E.knn_block_auto(zh, norms, offsets[rank], ref, norms_all[r_gid0:r_gid0 + n_ref], r_gid0, kdim, vmax, best_d2,
+                         best_idx, impl=impl, q_range=q_range, r_range=r_range, t_lists=t_lists, tau_r=tau_r,
+                         symmetric=step == 0)
+
+    def merge(lo, d2_in, idx_in):
+        with E._mark("merge_lists"):
+            E.merge_lists(d2_in, idx_in, best_d2[lo:lo + d2_in.shape[0]], best_idx[lo:lo + d2_in.shape[0]])
+
+    # The Gram kernel shares the GPU with NCCL's send/recv kernel while a transfer is in flight.  Its default
+    # schedule (cluster launch control) adapts to the SMs it gets.  GRIDB200_RING_COMM_SMS=<n> instead selects the
+    # static schedule on all but n SMs (A/B aid).  GRIDB200_RING=full runs all W hops (every pair twice: A/B aid).
+    import os
+
+    comm_sms = int(os.environ.get("GRIDB200_RING_COMM_SMS", "0")) if world > 1 else 0
+    sms = torch.cuda.get_device_properties(dev).multi_processor_count
+    full_ring = os.environ.get("GRIDB200_RING", "half") == "full"
+    half = None if full_ring else HalfRingOps(lambda m: E.knn_init(m, k, dev), merge)
+    extra.update(ring_schedule="full" if full_ring else "half", ring_hops=(world - 1) if full_ring else half_ring_hops(world))
+    call("gridb200_gram_set_max_pairs", max(1, (sms - comm_sms) // 2) if comm_sms else 0)
+    try:
+        ring_knn(zh, max(counts), counts, offsets, group, block, flat_per_row=kdim, half=half)
+    finally:
+        call("gridb200_gram_set_max_pairs", 0)
+    return best_idx, best_d2
+
+
 def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, group, impl: int = 0,
                    release_depth: bool = False):
     """normalize -> kNN -> dipCN for the row block this rank holds (depth [n_local, ld], counts_local [n_local, G]).
@@ -253,40 +302,7 @@ def run_chain_rows(depth: torch.Tensor, b: int, counts_local: torch.Tensor, p, g
         del depth
 
     # ---- step 5: ring of reference shards ------------------------------------------------------------------
-    norms_all = _all_gather_rows(norms, counts, group)
-    k = max(1, min(p.num_neighbors, n_total - 1)) if n_total > 1 else 1
-    best_d2, best_idx = E.knn_init(n, k, dev)
-
-    def block(step, src, flat, n_ref, r_gid0, q_range=None, r_range=None, t_lists=None):
-        ref = zh if step == 0 else flat.view(kdim // 64, n_ref, 64)  # hop 0 is the symmetric (same-operand) case
-        tau_r = None
-        if t_lists is not None and E.fused_mode() != "0":
-            # the shard owner's current k-th best distances: what the fused epilogue filters the peer's candidates against
-            # (every rank is at the same hop; a value that is a hop stale only lets a few more candidates through)
-            tau_r = _all_gather_rows(best_d2[:, k - 1].contiguous(), counts, group)[r_gid0:r_gid0 + n_ref]
-        E.knn_block_auto(zh, norms, offsets[rank], ref, norms_all[r_gid0:r_gid0 + n_ref], r_gid0, kdim, p.zclip, best_d2,
-                         best_idx, impl=impl, q_range=q_range, r_range=r_range, t_lists=t_lists, tau_r=tau_r,
-                         symmetric=step == 0)
-
-    def merge(lo, d2_in, idx_in):
-        with E._mark("merge_lists"):
-            E.merge_lists(d2_in, idx_in, best_d2[lo:lo + d2_in.shape[0]], best_idx[lo:lo + d2_in.shape[0]])
-
-    # The Gram kernel shares the GPU with NCCL's send/recv kernel while a transfer is in flight.  Its default
-    # schedule (cluster launch control) adapts to the SMs it gets.  GRIDB200_RING_COMM_SMS=<n> instead selects the
-    # static schedule on all but n SMs (A/B aid).  GRIDB200_RING=full runs all W hops (every pair twice: A/B aid).
-    import os
-
-    comm_sms = int(os.environ.get("GRIDB200_RING_COMM_SMS", "0")) if world > 1 else 0
-    sms = torch.cuda.get_device_properties(dev).multi_processor_count
-    full_ring = os.environ.get("GRIDB200_RING", "half") == "full"
-    half = None if full_ring else HalfRingOps(lambda m: E.knn_init(m, k, dev), merge)
-    res.extra.update(ring_schedule="full" if full_ring else "half", ring_hops=(world - 1) if full_ring else half_ring_hops(world))
-    call("gridb200_gram_set_max_pairs", max(1, (sms - comm_sms) // 2) if comm_sms else 0)
-    try:
-        ring_knn(zh, max(counts), counts, offsets, group, block, flat_per_row=kdim, half=half)
-    finally:
-        call("gridb200_gram_set_max_pairs", 0)
+    best_idx, best_d2 = knn_rows(zh, kdim, norms, counts, offsets, p.num_neighbors, p.zclip, group, impl=impl, extra=res.extra)
 
     # ---- step 6: scaled counts are tiny -> all-gather, then a local gather-reduce ----------------------------
     counts_all = _all_gather_rows(counts_local.contiguous(), counts, group)

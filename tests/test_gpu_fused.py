@@ -84,10 +84,13 @@ def test_fused_sub_ranges_and_refusals(monkeypatch):
     assert int((idx >= 0).sum()) == 0
     engine.knn_block(zq, nQ, 0, za, nA, 5000, kd, 200, d2, idx)
     snap = (d2.clone(), idx.clone())
-    # a buffer of 8 slots cannot hold what a 150-row block sends past a 30-entry list: refused, nothing changed
-    monkeypatch.setattr(engine, "FUSED_CAP", 8)
+    # every row of a block of small-magnitude samples is closer than anything in the lists (d2 ~ |q|^2 against ~ 2|q|^2):
+    # 270 survivors per row do not fit 64 slots -> refused, nothing changed
+    near = rng.integers(-10, 11, size=(270, kdim)).astype(np.int64)
+    zn, _, nN = _operand(near)
+    monkeypatch.setattr(engine, "FUSED_CAP", 64)
     over = engine.COUNTERS["fused_overflow"]
-    assert not engine.knn_block_fused(zq, nQ, 0, zb, nB, 1000, kd, 200, d2, idx)
+    assert not engine.knn_block_fused(zq, nQ, 0, zn, nN, 3000, kd, 200, d2, idx)
     assert engine.COUNTERS["fused_overflow"] == over + 1 and torch.equal(d2, snap[0]) and torch.equal(idx, snap[1])
     monkeypatch.setattr(engine, "FUSED_CAP", 1024)
     # the even-world middle hop: query rows 140.. against reference rows ..135 only

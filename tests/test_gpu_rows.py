@@ -229,3 +229,52 @@ def test_transposed_and_list_merges_match_numpy():
     assert torch.equal(a_d2, t_d2) and torch.equal(a_idx, t_idx)
     with pytest.raises(ValueError, match="num_neighbors"):
         engine.check_k(5000)
+
+
+def _worker_bins_ties(rank, world, port, seed, n, b, params, out):
+    """Bin-sharded step 4 on rows built to sit EXACTLY on %.2f ties: the scales must be numpy's (pairwise sum over the
+    whole row), as on one GPU -- no rank holds a whole row."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), NCCL_DEBUG="WARN")
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from grid_b200 import engine
+
+        rng = np.random.default_rng(seed)
+        h = rng.integers(2500, 5000, size=(n, b)).astype(np.int64)
+        h[rng.random((n, b)) < 0.02] = 0
+        ties = 0
+        for i in range(n):
+            cols = np.nonzero(h[i] > 0)[0]
+            cnt = len(cols)
+            if cnt % 2 or i % 3 == 2:
+                continue
+            h[i, cols[-1]] += (cnt // 2 - int(h[i, cols].sum())) % cnt      # the nudged cell lives on the LAST rank
+            ties += 1
+        assert ties > n // 4
+        x = np.where(h > 0, h / 100.0, np.nan)
+        want_mean = np.nanmean(np.ascontiguousarray(x), axis=1)
+        want_q = np.array([float("%.2f" % v) for v in want_mean])
+        per = -(-(-(-b // world)) // 64) * 64
+        lo, hi = min(b, rank * per), min(b, (rank + 1) * per)
+        ld = (hi - lo + 3) // 4 * 4
+        depth = torch.zeros((n, ld), dtype=torch.float32, device="cuda")
+        depth[:, :hi - lo] = torch.from_numpy((h[:, lo:hi] / 100.0).astype(np.float32)).cuda()
+        res = engine.normalize(depth, hi - lo, engine.Params(**params), want_zq=False, want_zh=False, group=dist.group.WORLD)
+        assert int(res.valid.sum()) == hi - lo                                # every bin passes the depth filter
+        np.testing.assert_array_equal(res.scale_q.cpu().numpy(), want_q)
+        tie_rows = np.array([(2 * int(s)) % (2 * int(c)) == int(c) for s, c in zip(h.sum(1), (h > 0).sum(1))])
+        assert tie_rows.sum() == ties
+        np.testing.assert_array_equal(res.raw_mean.cpu().numpy()[tie_rows], want_mean[tie_rows])
+        out.put((rank, "ok"))
+    except Exception as exc:
+        out.put((rank, f"{type(exc).__name__}: {str(exc)[:400]}"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+def test_bin_sharded_scales_on_exact_ties(world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    _run(world, 38, 48, 1000, dict(min_depth=20.0, max_depth=100.0), worker=_worker_bins_ties)

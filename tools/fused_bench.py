@@ -19,15 +19,22 @@ g = torch.Generator(device="cuda").manual_seed(1)
 
 
 def operand(n):
-    z = torch.randint(-200, 201, (kdim // 64, n, 64), device="cuda", generator=g, dtype=torch.int32)
-    norms = (z.to(torch.int64) ** 2).sum(dim=(0, 2))
-    return z.to(torch.float16), norms
+    """k-blocked fp16 operand [kdim/64, n, 64] of random integers and its exact row norms (built slab by slab)."""
+    zh = torch.empty((kdim // 64, n, 64), dtype=torch.float16, device="cuda")
+    norms = torch.zeros(n, dtype=torch.int64, device="cuda")
+    step = max(1, (1 << 26) // (n * 64))
+    for b0 in range(0, kdim // 64, step):
+        z = torch.randint(-200, 201, (min(step, kdim // 64 - b0), n, 64), device="cuda", generator=g, dtype=torch.int32)
+        zh[b0:b0 + z.shape[0]] = z.to(torch.float16)
+        norms += (z.to(torch.int64) ** 2).sum(dim=(0, 2))
+    return zh, norms
 
 
+# the lists are bootstrapped against blocks as large as the ones under test: what the own-shard hop of a ring leaves behind
 zq, nQ = operand(nq)
 zb, nB = operand(nr)
-za, nA = operand(max(2 * k, 512))
-zc, nC = operand(max(2 * k, 512))
+za, nA = operand(nr)
+zc, nC = operand(nq)
 
 
 def boot():
