@@ -78,8 +78,18 @@ def find_neighbors(config, console):
             extreme = int(np.sum(ratios > sigma2_max))
             if extreme and console:
                 log(console, f"Removed {extreme} / {rw} regions with sigma2ratio > {sigma2_max}", style="warning")
-            zh, kdim, norms = engine.prepare_from_zq(tzq, rw, keep, p.zclip)
-            tidx, td2 = engine.knn(zh, kdim, norms, n_neighbors, p.zclip)
+            from .. import multigpu
+
+            devices = multigpu.configured_devices(config)    # additive key gpu.devices: several GPUs for the search
+            if devices:
+                mode = multigpu.knn_sharding(config, n)
+                log(console, f"Neighbour search on {len(devices)} GPUs ({mode}-sharded)", style="info")
+                hidx, hd2 = multigpu.knn(tzq[:, :rw].cpu().contiguous(), keep.cpu(), n_neighbors, p.zclip, devices, mode)
+                tidx, td2 = hidx.to(dev), hd2.to(dev)
+            else:
+                engine.check_k(max(1, min(n_neighbors, n - 1)))
+                zh, kdim, norms = engine.prepare_from_zq(tzq, rw, keep, p.zclip)
+                tidx, td2 = engine.knn(zh, kdim, norms, n_neighbors, p.zclip)
             idx = tidx.cpu().numpy()
         progress.advance(task, n)
     if tidx is not None and config.get("gpu", {}).get("device_text", True):  # entries formatted on the GPU

@@ -229,7 +229,24 @@ def normalize_mosdepth(config, console):
         log(console, "No valid samples with regions found.", style="danger")
         sys.exit(1)
     p = engine.Params(min_depth=min_depth, max_depth=max_depth, top_frac=top_frac)
-    res = engine.normalize(depth, b, p, want_zq=True, want_zh=False)
+    from .. import multigpu
+
+    devices = multigpu.configured_devices(config)        # additive key gpu.devices: bin-sharded over several GPUs
+    if devices and b >= 4 * len(devices):
+        from types import SimpleNamespace
+
+        log(console, f"Normalising on {len(devices)} GPUs (bin-sharded)", style="info")
+        zq_h, rw_, mu_h, ratio_h, raw_h, rowcnt_h = multigpu.normalize(depth.cpu(), b, p, devices)
+        sel_pos = torch.zeros(max(rw_, 1), dtype=torch.int32)  # only its length of non-negative entries is used below
+        zq_d = None
+        if rw_:  # same layout as engine.normalize's: rows padded to a multiple of 8 codes with NA
+            zq_d = torch.full((zq_h.shape[0], (rw_ + 7) // 8 * 8), gio.ZQ_NA, dtype=torch.int16, device=depth.device)
+            zq_d[:, :rw_] = zq_h.to(depth.device)
+        res = SimpleNamespace(extra={"rowcnt": torch.from_numpy(rowcnt_h)}, sel_pos=sel_pos[:rw_], rw=rw_,
+                              mu=torch.from_numpy(mu_h), ratio=torch.from_numpy(ratio_h), raw_mean=torch.from_numpy(raw_h),
+                              zq=zq_d)
+    else:
+        res = engine.normalize(depth, b, p, want_zq=True, want_zh=False)
     rows = np.nonzero(res.extra["rowcnt"].cpu().numpy() > 0)[0]  # filter_empty_samples (:576-600)
     if len(rows) < len(ids):
         log(console, f"Removed {len(ids) - len(rows)} samples with 0 regions", style="warning")

@@ -5,7 +5,8 @@
 
 The reference is pure Python, so "building" it is copying the modules steps 4-6 import --
 grid/__init__.py, grid/utils/{__init__,utils,mosdepth,normalize_mosdepth,find_neighbors,compute_dipcn}.py --
-byte for byte from where they lie under /root/reference into oracle/_ref/grid/...  oracle/_ref/ is git-ignored
+and pipeline.py / utils/hi_inference.py (so that a GPU test can drive the reference's real run_wgs_pipeline with
+grid_b200.install()) -- byte for byte from where they lie under /root/reference into oracle/_ref/grid/...  oracle/_ref/ is git-ignored
 (no reference source enters the history) but not gpurun-ignored, so it travels to the GPU box, where
 `bench.py --impl reference` and the `cpu_baseline` leg import the reference's OWN normalize_matrix,
 select_high_variance_regions, filter_regions_by_variance, find_neighbors_sklearn, save_neighbors and
@@ -21,8 +22,8 @@ from pathlib import Path
 HERE = Path(__file__).resolve().parent
 SRC = Path("/root/reference/grid")
 DST = HERE / "_ref" / "grid"
-FILES = ["__init__.py", "utils/__init__.py", "utils/utils.py", "utils/mosdepth.py", "utils/normalize_mosdepth.py",
-         "utils/find_neighbors.py", "utils/compute_dipcn.py"]
+FILES = ["__init__.py", "pipeline.py", "utils/__init__.py", "utils/utils.py", "utils/mosdepth.py",
+         "utils/normalize_mosdepth.py", "utils/find_neighbors.py", "utils/compute_dipcn.py", "utils/hi_inference.py"]
 
 
 def make(verbose: bool = True) -> bool:
