@@ -191,7 +191,9 @@ def test_rows_chain_ring_fused_epilogue(world, monkeypatch):
 def test_blocked_chain_ring(world):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    _run(world, 35, 1001, 4000, dict(num_neighbors=350, n_nbr=300, block_rows=130, resident_blocks=1), worker=_worker_blocked)
+    # (at least three rounds per rank: 1001 rows over `world` ranks in blocks of at most block_rows)
+    _run(world, 35, 1001, 4000, dict(num_neighbors=350, n_nbr=300, block_rows=260 // world, resident_blocks=1),
+         worker=_worker_blocked)
 
 
 def test_transposed_and_list_merges_match_numpy():
