@@ -44,6 +44,9 @@ SIGNATURES = {
     "gridb200_gram_topk": (C.c_int, [_vp, _i64, _i64, _vp, _i64, _i64, _i64, _i32, _vp, _vp, _i64, _i64, _vp, _i64, _vp, _i64,
                                      _i32, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gridb200_topk_merge_cand": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _i32, _vp, _vp, _vp]),
+    "gridb200_split_tf32": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _vp, _vp]),
+    "gridb200_gram_f32": (C.c_int, [_vp, _vp, _i64, _i64, _vp, _vp, _i64, _i64, _i64, _vp, _i64, _vp]),
+    "gridb200_topk_merge_f32": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _i32, _vp, _vp, _vp]),
     "gridb200_dipcn": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _i64, _i32, _i64, _i32, _i32, _vp, _i64, _vp, _vp]),
     "gridb200_synth_depth": (C.c_int, [_u64, _i64, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _vp]),
     "gridb200_ingest_ws_bytes": (_sz, [_i64]),

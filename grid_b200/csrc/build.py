@@ -7,7 +7,7 @@ from concurrent.futures import ThreadPoolExecutor
 from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
-SOURCES = ["api.cu", "normalize.cu", "select.cu", "knn_simt.cu", "gram_tc.cu", "topk.cu", "dipcn.cu", "synth.cu", "ingest.cu", "textio.cu", "hi.cu", "region.cu", "nbrio.cu"]
+SOURCES = ["api.cu", "normalize.cu", "select.cu", "knn_simt.cu", "gram_tc.cu", "gram_f32.cu", "topk.cu", "dipcn.cu", "synth.cu", "ingest.cu", "textio.cu", "hi.cu", "region.cu", "nbrio.cu"]
 LIB = HERE / "libgridb200.so"
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC",

@@ -10,6 +10,9 @@
 //   kLists : list = row i,            candidates = another k-best list for the same row          (gridb200_topk_merge_lists)
 //   kCand  : list = row i,            candidates = the first min(cnt[i], cap) entries of the row's candidate buffer
 //                                     filled by the fused Gram epilogue                            (gridb200_topk_merge_cand)
+//   kRowsF32: list = query row i,     candidates = the row's entries of an fp32 Gram block (3xTF32 general path); the
+//                                     squared distance is formed in fp64 and ordered through its bit pattern
+//                                                                                                (gridb200_topk_merge_f32)
 // kCols and kLists serve the half ring (grid_b200/ring.py): a rank that has multiplied its rows with a peer's shard
 // extracts the PEER's k best from the transpose and sends those lists instead of the peer recomputing the block.
 #include "common.cuh"
@@ -18,7 +21,7 @@ namespace g2 {
 
 constexpr long long kInfD2 = 0x7fffffffffffffffLL;
 constexpr int kTopkMaxKeys = 8192;
-enum { kRows = 0, kCols = 1, kLists = 2, kCand = 3 };
+enum { kRows = 0, kCols = 1, kLists = 2, kCand = 3, kRowsF32 = 4 };
 
 __device__ __forceinline__ bool pair_less(long long da, int ia, long long db, int ib) {
   return da < db || (da == db && ia < ib);
@@ -43,6 +46,9 @@ struct TopkArgs {
   const int* src_idx;
   int src_k;
   const int* src_cnt;        // kCand: entries appended to each row's buffer (may exceed src_k = its capacity)
+  const float* dotf;         // kRowsF32: fp32 Gram block and fp64 norms
+  const double* normd_l;
+  const double* normd_c;
   int k;
   long long* best_d2;
   int* best_idx;
@@ -69,7 +75,8 @@ __global__ void __launch_bounds__(256) k_topk_merge(const TopkArgs a) {
   const long long tau_d = sd[k - 1];
   const int tau_i = si[k - 1];
   const int64_t self = a.l_gid0 + row;
-  const long long nl = (kMode == kLists || kMode == kCand) ? 0 : a.norm_l[row];
+  const long long nl = (kMode == kLists || kMode == kCand || kMode == kRowsF32) ? 0 : a.norm_l[row];
+  const double nld = kMode == kRowsF32 ? a.normd_l[row] : 0.0;
   const int64_t ncand = kMode == kCand ? (int64_t)min(a.src_cnt[row], a.src_k) : a.ncand;
   for (int64_t j = threadIdx.x; j < ncand; j += 256) {
     long long d;
@@ -78,6 +85,13 @@ __global__ void __launch_bounds__(256) k_topk_merge(const TopkArgs a) {
       d = a.src_d2[row * a.src_k + j];
       id = a.src_idx[row * a.src_k + j];
       if (id < 0) continue;
+    } else if (kMode == kRowsF32) {
+      const int64_t gid = a.c_gid0 + j;
+      if (gid == self) continue;
+      // a non-negative double orders like its bit pattern read as int64: the integer k-best machinery serves unchanged
+      const double dd = fmax(0.0, nld + a.normd_c[j] - 2.0 * (double)a.dotf[row * a.ldd + j]);
+      d = __double_as_longlong(dd);
+      id = (int)gid;
     } else {
       const int64_t gid = a.c_gid0 + j;
       if (gid == self) continue;
@@ -197,4 +211,18 @@ extern "C" int gridb200_topk_merge_cand(const int64_t* cand_d2, const int32_t* c
   a.src_d2 = reinterpret_cast<const long long*>(cand_d2), a.src_idx = cand_idx, a.src_k = cap, a.src_cnt = cand_cnt;
   a.k = k, a.best_d2 = reinterpret_cast<long long*>(best_d2), a.best_idx = best_idx;
   return launch_topk<kCand>(a, n, as_stream(stream));
+}
+
+extern "C" int gridb200_topk_merge_f32(const float* dot, int64_t ldd, int64_t nq, int64_t nr, const double* normq,
+                                       const double* normr, int64_t q_gid0, int64_t r_gid0, int32_t k, int64_t* best_d2,
+                                       int32_t* best_idx, void* stream) {
+  G2_REQUIRE(dot && normq && normr && best_d2 && best_idx, GRIDB200_EINVAL, "null pointer");
+  G2_REQUIRE(nq > 0 && nr > 0 && k > 0 && ldd >= nr, GRIDB200_EINVAL, "bad shape");
+  G2_REQUIRE(nr + k <= kTopkMaxKeys, GRIDB200_EINVAL, "candidates + k = %lld exceeds %d per call", (long long)(nr + k),
+             kTopkMaxKeys);
+  G2_REQUIRE(r_gid0 + nr < (1LL << 31) && q_gid0 + nq < (1LL << 31), GRIDB200_EINVAL, "indices exceed int32");
+  TopkArgs a{};
+  a.dotf = dot, a.ldd = ldd, a.ncand = nr, a.normd_l = normq, a.normd_c = normr, a.l_gid0 = q_gid0, a.c_gid0 = r_gid0;
+  a.k = k, a.best_d2 = reinterpret_cast<long long*>(best_d2), a.best_idx = best_idx;
+  return launch_topk<kRowsF32>(a, nq, as_stream(stream));
 }

@@ -521,6 +521,40 @@ def knn(zh: torch.Tensor, kdim: int, norms: torch.Tensor, k: int, vmax: int, imp
     return best_idx, best_d2
 
 
+def knn_f32(x: torch.Tensor, k: int, max_block_bytes: int = 2 << 30):
+    """Exact-to-fp32 k nearest neighbours (self excluded) of the rows of an UNQUANTISED fp32 matrix x [n, r] on the tensor
+    cores with 3xTF32 split precision (north_star step (c) as stated; gram_f32.cu).  The pipeline's own matrices are
+    quantised by the %.2f hand-off and go through knn(); this entry serves callers that skip the text round trip.
+    Returns (idx [n, k] int32, d2 [n, k] float64 squared Euclidean distances), ascending by (d2, index)."""
+    if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1):
+        raise ValueError("x must be a 2-D fp32 CUDA tensor with unit column stride")
+    n, r = x.shape
+    k = max(1, min(k, n - 1)) if n > 1 else 1
+    check_k(k)
+    dev, st = x.device, _stream()
+    kdim = (r + 31) // 32 * 32
+    hi = torch.empty((kdim // 32, n, 32), dtype=torch.float32, device=dev)
+    lo = torch.empty_like(hi)
+    norms = torch.empty(n, dtype=torch.float64, device=dev)
+    call("gridb200_split_tf32", ptr(x), n, r, x.stride(0), ptr(hi), ptr(lo), n, ptr(norms), st)
+    best_d2, best_idx = knn_init(n, k, dev)
+    ldd = (n + 3) // 4 * 4
+    qb = max(1, min(n, max_block_bytes // (4 * ldd)))
+    rchunk = TOPK_MAX_KEYS - k
+    for q0 in range(0, n, qb):
+        nq = min(qb, n - q0)
+        dot = torch.empty((nq, ldd), dtype=torch.float32, device=dev)
+        with _mark("gram_f32"):
+            call("gridb200_gram_f32", hi.data_ptr() + q0 * 32 * 4, lo.data_ptr() + q0 * 32 * 4, nq, n, ptr(hi), ptr(lo), n, n,
+                 kdim, ptr(dot), ldd, st)
+        with _mark("topk"):
+            for r0 in range(0, n, rchunk):
+                n_r = min(rchunk, n - r0)
+                call("gridb200_topk_merge_f32", dot.data_ptr() + r0 * 4, ldd, nq, n_r, norms.data_ptr() + q0 * 8,
+                     norms.data_ptr() + r0 * 8, q0, r0, k, best_d2.data_ptr() + q0 * k * 8, best_idx.data_ptr() + q0 * k * 4, st)
+    return best_idx, best_d2.view(torch.float64)
+
+
 def dipcn(counts: torch.Tensor, has_count: torch.Tensor, scale_q: torch.Tensor, nbr_idx: torch.Tensor, n_nbr: int,
           q_gid0: int = 0, rule: str = "pipeline"):
     """Step 6 on device arrays: counts[n_all,g] int32, has_count[n_all] uint8, scale_q[n_all] f64 for the WHOLE cohort,

@@ -219,6 +219,24 @@ GRIDB200_API int gridb200_gram_topk(const void* zq_f16, int64_t nq, int64_t slab
 GRIDB200_API int gridb200_topk_merge_cand(const int64_t* cand_d2, const int32_t* cand_idx, const int32_t* cand_cnt,
                              int64_t n, int32_t cap, int32_t k, int64_t* best_d2, int32_t* best_idx, void* stream);
 
+/* ---- general fp32 path (north_star's 3xTF32): unquantised operands ----------------------------------------------
+ * The pipeline's operands are quantised by the %.2f hand-off and take the exact fp16 kernel above.  A caller that holds
+ * UNROUNDED fp32 z-scores (the matrix find_neighbors.py:57-65 would feed sklearn without the text round trip) uses these:
+ * gridb200_split_tf32 splits a row-major fp32 matrix x[n, ldx] into tf32 hi and lo parts (x = hi + lo exactly, hi has
+ * 10 mantissa bits) in the k-blocked layout [kdim/32, slab, 32] (kdim = k rounded up to 32, zero padded) and returns the
+ * fp64 row norms; gridb200_gram_f32 forms dot = Qhi.Rhi + Qhi.Rlo + Qlo.Rhi on tcgen05 (kind::tf32, fp32 TMEM
+ * accumulators, chunked summation) -- the -2*X.Y^T term of EuclideanArgKmin at fp32 accuracy; gridb200_topk_merge_f32 forms
+ * d2 = normq[i] + normr[j] - 2*dot in fp64 (clamped at 0) and merges into the running lists, whose best_d2 entries then
+ * hold the BIT PATTERNS of those doubles (a non-negative double orders like its bits read as int64). */
+GRIDB200_API int gridb200_split_tf32(const float* x, int64_t n, int64_t k, int64_t ldx, float* hi, float* lo,
+                        int64_t slab, double* norms, void* stream);
+GRIDB200_API int gridb200_gram_f32(const float* qhi, const float* qlo, int64_t nq, int64_t slabq,
+                      const float* rhi, const float* rlo, int64_t nr, int64_t slabr, int64_t kdim,
+                      float* dot, int64_t ldd, void* stream);
+GRIDB200_API int gridb200_topk_merge_f32(const float* dot, int64_t ldd, int64_t nq, int64_t nr,
+                            const double* normq, const double* normr, int64_t q_gid0, int64_t r_gid0,
+                            int32_t k, int64_t* best_d2, int32_t* best_idx, void* stream);
+
 /* ------------------------------------------------------------------ step 6: compute_dipcn ---------------- */
 
 /* out[i,g] = (counts[q0+i,g]/scale[q0+i]) / mean over contributing neighbours j of counts[j,g]/scale[j]; NaN where

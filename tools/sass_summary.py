@@ -10,8 +10,8 @@ import sys
 from pathlib import Path
 
 ROOT = Path(__file__).resolve().parents[1]
-obj = Path(sys.argv[1]) if len(sys.argv) > 1 else ROOT / "grid_b200/csrc/build/gram_tc.cu.o"
-dst = Path(sys.argv[2]) if len(sys.argv) > 2 else ROOT / "profiles/r02_sass_gram_tc.txt"
+obj = Path(sys.argv[1]).resolve() if len(sys.argv) > 1 else ROOT / "grid_b200/csrc/build/gram_tc.cu.o"
+dst = Path(sys.argv[2]).resolve() if len(sys.argv) > 2 else ROOT / "profiles/r02_sass_gram_tc.txt"
 txt = subprocess.run(["cuobjdump", "-sass", str(obj)], capture_output=True, text=True, check=True).stdout
 KEYS = ("UTCHMMA", "LDTM", "UTMALDG", "UTCBAR", "UGETNEXTWORKID", "UTCATOMSWS", "SYNCS", "ATOMG", "RED", "STL", "LDL", "F2I",
         "ERRBAR", "MEMBAR", "UCGABAR")
