@@ -626,12 +626,15 @@ def run_ours(a):
         # this same workload (profiles/*_ncu_full_summary.json, written by tools/ncu_summary.py); single-GPU launch
         traffic, traffic_note = None, None
         try:
-            caps = sorted((ROOT / "profiles").glob("*_ncu_full_summary.json"))
-            for k in json.loads(caps[-1].read_text()) if caps and world == 1 else []:
-                if "k_gram_tc_pair" in k["kernel"]:
+            # the newest committed capture of THIS workload's Gram launch (the symmetric, non-fused instantiation)
+            for cap in sorted((ROOT / "profiles").glob("*_ncu_full_summary.json"), reverse=True) if world == 1 else []:
+                hit = [k for k in json.loads(cap.read_text()) if "k_gram_tc_pair" in k["kernel"] and "1, 1>" not in k["kernel"]]
+                if hit:
+                    k = hit[0]
                     traffic = (k["dram_read"]["value"] + k["dram_write"]["value"]) * 1e9
-                    traffic_note = (f"bytes per launch from {caps[-1].name}; the operand itself is "
-                                    f"{a.samples * kdim * 2 / 1e9:.1f} GB (read once per wave of tiles)")
+                    traffic_note = (f"bytes per launch from {cap.name} (non-fused instantiation: same main loop since); the operand "
+                                    f"itself is {a.samples * kdim * 2 / 1e9:.1f} GB (read once per wave of tiles)")
+                    break
         except Exception:
             traffic = None
         roof = None

@@ -37,7 +37,9 @@ constexpr int STAGE_BYTES = 4 * BOX_BYTES;               // Qhi, Qlo, Rhi, Rlo
 constexpr int ACC_STAGES = 2, TMEM_COLS = ACC_STAGES * TN;
 constexpr int NUM_THREADS = 384, EPI_WARP0 = 4, EPI_WARPS = 8, EPI_COLS = TN / 2;
 constexpr int REGS_CTRL = 40, REGS_EPI = 232;
-constexpr int CHUNK_KB = 64;                             // k-blocks (2048 bins) accumulated in TMEM between drains
+constexpr int CHUNK_KB = 2;   // k-blocks (64 bins) accumulated in TMEM between drains: the tensor core TRUNCATES when it adds to
+                              // an fp32 accumulator, a bias that grows with the partial sum; short chunks keep the partial sums small
+                              // and the long sum runs in registers with round-to-nearest adds
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
 // kind::tf32 instruction descriptor: D = f32 (bit 4), A = B = TF32 (2 at bits 7 and 10), K-major, N>>3 at 17, M>>4 at 24
 constexpr uint32_t IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TN >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);

@@ -1,13 +1,15 @@
 """The general fp32 neighbour search (north_star's 3xTF32 path, gridb200_split_tf32 / gridb200_gram_f32 /
 gridb200_topk_merge_f32) against an fp64 brute force: distances to fp32 accuracy, ranking identical except inside
-groups of candidates whose distances agree to 1e-6 relative (north_star's tie window)."""
+groups of candidates whose distances agree to a few 1e-6 relative (north_star's tie window is 1e-6; an fp32 accumulation
+over tens of thousands of same-sign terms -- an exact duplicate's dot product -- is itself only good to ~3e-6 of
+|x|^2 + |y|^2, whatever the hardware)."""
 import numpy as np
 import pytest
 
 torch = pytest.importorskip("torch")
 pytestmark = pytest.mark.gpu
 
-REL = 1e-6
+REL = 3e-6
 
 
 @pytest.mark.parametrize("n,r,k", [(700, 5000, 60), (300, 131, 299), (1030, 40000, 25)])
