@@ -67,4 +67,4 @@ def test_split_is_exact_and_3xtf32_beats_1xtf32():
     zero = torch.zeros_like(lo)
     call("gridb200_gram_f32", ptr(hi), ptr(zero), n, n, ptr(hi), ptr(zero), n, n, r, ptr(dot), n, st)
     err1 = np.abs(dot.cpu().numpy() - exact).max()
-    assert err3 < 2e-3 and err1 > 20 * err3, (err1, err3)
+    assert err3 < 8e-3 and err1 > 20 * err3, (err1, err3)   # the diagonal (4096 same-sign terms) has ulp 4.9e-4
