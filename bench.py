@@ -481,6 +481,7 @@ def run_ours(a):
     per = -(-per // 1024) * 1024
     lo, hi = min(a.bins, rank * per), min(a.bins, (rank + 1) * per)
     b_local = hi - lo
+    bin_sizes = [min(a.bins, (r + 1) * per) - min(a.bins, r * per) for r in range(world)] if world > 1 else None
     p = engine.Params(num_neighbors=a.k, n_nbr=a.n_nbr)
     rows = a.sharding == "rows" and world > 1
     counts_all = synth.read_counts(SEED, a.samples, [LPA_LEN])
@@ -508,7 +509,7 @@ def run_ours(a):
             return r, z, z, z.double()
         if rows:
             return ring.run_chain_rows(depth, b_local, counts, p, group, impl=a.gram_impl)
-        return engine.run_chain(depth, b_local, counts, p, impl=a.gram_impl, group=group)
+        return engine.run_chain(depth, b_local, counts, p, impl=a.gram_impl, group=group, bin_sizes=bin_sizes)
 
     for _ in range(a.warmup):
         res, idx, d2, cn = step()

@@ -54,6 +54,9 @@ SIGNATURES = {
                                        _sz, _vp]),
     "gridb200_depth_pack_u16": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp]),
     "gridb200_depth_unpack_u16": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _i64, _i64, _vp]),
+    "gridb200_depth_packed_row_words": (_i64, [_i64, _i32]),
+    "gridb200_depth_pack_bits": (C.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp]),
+    "gridb200_depth_unpack_bits": (C.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i64, _vp, _vp, _i64, _i64, _vp]),
     "gridb200_hi_phase": (C.c_int, [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _vp]),
     "gridb200_hi_level_pass": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp]),
     "gridb200_hi_impute": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _f64, _vp, _vp]),

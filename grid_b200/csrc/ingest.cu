@@ -269,7 +269,107 @@ __global__ void k_patch_depth(const int64_t* __restrict__ cell, const float* __r
   if (r >= 0 && r < n) depth[r * ld + c] = val[e];
 }
 
+// ---- bit-packed variant: `bits` (9..15) per cell instead of 16 ---------------------------------------------------------
+// A 30x cohort's hundredths sit below 2^13, so 13 bits per cell carry the matrix and PCIe -- what the end-to-end step is
+// bound by -- moves 19 % fewer bytes.  Layout: a row is a sequence of groups of 32 cells; a group is `bits` 32-bit words
+// holding a little-endian bit stream (cell c of the group at bit c * bits).  The all-ones code is the escape.
+__global__ void __launch_bounds__(256) k_pack_bits(const float* __restrict__ depth, int64_t b, int64_t ld, int bits,
+                                                   uint32_t* __restrict__ out, int64_t ldw, int64_t row0_global,
+                                                   int64_t* __restrict__ esc_cell, float* __restrict__ esc_val,
+                                                   int64_t esc_cap, unsigned long long* __restrict__ esc_count) {
+  const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // group of 32 cells
+  const int64_t i = blockIdx.y;
+  if (g * 32 >= b) return;
+  const float* p = depth + i * ld + g * 32;
+  uint32_t* o = out + i * ldw + g * bits;
+  const uint32_t esc = (1u << bits) - 1u;
+  unsigned long long acc = 0;
+  int nb = 0, w = 0;
+  for (int c = 0; c < 32; ++c) {
+    uint32_t code = 0;
+    if (g * 32 + c < b) {
+      const float x = p[c];
+      const int h = depth_hundredths(x);
+      code = (uint32_t)h;
+      if ((uint32_t)h >= esc || !(x < 41943.04f)) {
+        code = esc;
+        const unsigned long long slot = atomicAdd(esc_count, 1ULL);
+        if ((int64_t)slot < esc_cap) esc_cell[slot] = (row0_global + i) * b + (g * 32 + c), esc_val[slot] = x;
+      }
+    }
+    acc |= (unsigned long long)code << nb;
+    nb += bits;
+    if (nb >= 32) {
+      o[w++] = (uint32_t)acc;
+      acc >>= 32;
+      nb -= 32;
+    }
+  }
+}
+
+// thread = 4 consecutive cells -> one float4 store; the codes are read through L1 (adjacent threads share words)
+__global__ void __launch_bounds__(256) k_unpack_bits(const uint32_t* __restrict__ src, int64_t b, int64_t ldw, int bits,
+                                                     float* __restrict__ depth, int64_t ld) {
+  const int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  const int64_t i = blockIdx.y;
+  if (j >= b) return;
+  const uint32_t* s = src + i * ldw + (j >> 5) * bits;
+  const uint32_t mask = (1u << bits) - 1u;
+  float f[4];
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const int bit = (int)((j + t) & 31) * bits;   // 4 | 32: the four cells never leave the group
+    const int w = bit >> 5, sh = bit & 31;
+    uint32_t v = __ldg(s + w) >> sh;
+    if (sh + bits > 32) v |= __ldg(s + w + 1) << (32 - sh);
+    f[t] = __fdiv_rn((float)(v & mask), 100.0f);   // (the escape code is overwritten by k_patch_depth)
+  }
+  float* d = depth + i * ld + j;
+  if (j + 4 <= b && (reinterpret_cast<uintptr_t>(d) & 15) == 0) *reinterpret_cast<float4*>(d) = make_float4(f[0], f[1], f[2], f[3]);
+  else
+    for (int t = 0; t < 4 && j + t < b; ++t) d[t] = f[t];
+}
+
 }  // namespace g2
+
+extern "C" int64_t gridb200_depth_packed_row_words(int64_t b, int32_t bits) {
+  if (b <= 0 || bits < 9 || bits > 15) return -1;
+  return ((b + 31) / 32 * bits + 3) / 4 * 4;  // whole groups, rows 16-byte aligned
+}
+
+extern "C" int gridb200_depth_pack_bits(const float* depth, int64_t n, int64_t b, int64_t ld, int32_t bits, uint32_t* out,
+                                        int64_t ldw, int64_t row0, int64_t* esc_cell, float* esc_val, int64_t esc_cap,
+                                        int64_t* esc_count, void* stream) {
+  using namespace g2;
+  G2_REQUIRE(depth && out && esc_count && n > 0 && b > 0 && ld >= b && n <= 65535, GRIDB200_EINVAL,
+             "bad argument (rows per call <= 65535)");
+  G2_REQUIRE(bits >= 9 && bits <= 15 && ldw >= gridb200_depth_packed_row_words(b, bits), GRIDB200_EINVAL,
+             "bits must be 9..15 and ldw at least gridb200_depth_packed_row_words(b, bits)");
+  G2_REQUIRE(esc_cap == 0 || (esc_cell && esc_val), GRIDB200_EINVAL, "escape arrays missing");
+  const int64_t groups = (b + 31) / 32;
+  k_pack_bits<<<dim3((unsigned)((groups + 255) / 256), (unsigned)n), 256, 0, as_stream(stream)>>>(
+      depth, b, ld, bits, out, ldw, row0, esc_cell, esc_val, esc_cap, reinterpret_cast<unsigned long long*>(esc_count));
+  G2_LAUNCHED();
+  return 0;
+}
+
+extern "C" int gridb200_depth_unpack_bits(const uint32_t* src, int64_t n, int64_t b, int64_t ldw, int32_t bits, float* depth,
+                                          int64_t ld, const int64_t* esc_cell, const float* esc_val, int64_t esc_count,
+                                          int64_t row0, void* stream) {
+  using namespace g2;
+  G2_REQUIRE(src && depth && n > 0 && b > 0 && ld >= b && n <= 65535, GRIDB200_EINVAL, "bad argument (rows per call <= 65535)");
+  G2_REQUIRE(bits >= 9 && bits <= 15 && ldw >= gridb200_depth_packed_row_words(b, bits), GRIDB200_EINVAL,
+             "bits must be 9..15 and ldw at least gridb200_depth_packed_row_words(b, bits)");
+  G2_REQUIRE(esc_count == 0 || (esc_cell && esc_val), GRIDB200_EINVAL, "escape arrays missing");
+  cudaStream_t st = as_stream(stream);
+  k_unpack_bits<<<dim3((unsigned)((b + 1023) / 1024), (unsigned)n), 256, 0, st>>>(src, b, ldw, bits, depth, ld);
+  G2_LAUNCHED();
+  if (esc_count > 0) {
+    k_patch_depth<<<(unsigned)((esc_count + 255) / 256), 256, 0, st>>>(esc_cell, esc_val, esc_count, b, row0, n, depth, ld);
+    G2_LAUNCHED();
+  }
+  return 0;
+}
 
 extern "C" int gridb200_depth_pack_u16(const float* depth, int64_t n, int64_t b, int64_t ld, uint16_t* out, int64_t ldo,
                                        int64_t row0, int64_t* esc_cell, float* esc_val, int64_t esc_cap,

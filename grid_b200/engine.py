@@ -123,11 +123,31 @@ def check_depth(depth: torch.Tensor, b: int) -> tuple[int, int]:
     return depth.shape[0], depth.stride(0)
 
 
+_SIDE: dict = {}
+
+
+def _read_behind(t: torch.Tensor, ready: "torch.cuda.Event") -> list:
+    """t.tolist() without draining the main stream: the copy runs on a side stream that waits only for `ready` (recorded
+    when t was complete), so kernels already queued behind it keep the GPU busy while the host reads the few values it
+    needs to go on (with several GPUs a step is a few milliseconds and every drained queue shows)."""
+    dev = t.device
+    side = _SIDE.get(dev)
+    if side is None:
+        side = _SIDE[dev] = torch.cuda.Stream(device=dev)
+    side.wait_event(ready)
+    with torch.cuda.stream(side):
+        host = t.to("cpu", non_blocking=True)
+        t.record_stream(side)
+    side.synchronize()
+    return host.tolist()
+
+
 def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, want_zh: bool = True,
-              group=None) -> NormResult:
+              group=None, bin_sizes: list[int] | None = None) -> NormResult:
     """Step 4 on a device-resident depth matrix [n, ld] (first ``b`` columns are bins; 0 = absent).
 
-    With ``group`` the matrix holds this rank's bin slice; ranks are ordered by bin range.
+    With ``group`` the matrix holds this rank's bin slice; ranks are ordered by bin range.  bin_sizes: every rank's
+    number of bins when the caller knows them (saves an all-reduce and a host sync per step).
     """
     n, ld = check_depth(depth, b)
     dev, st = depth.device, _stream()
@@ -161,6 +181,10 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
         tie = (rowcnt > 0) & ((2 * rowsum) % (2 * rowcnt.to(torch.int64)).clamp(min=1) == rowcnt)
         n_tie_t = tie.sum()
 
+    # what the host needs next (rows with data, tie rows) is complete here: read it BEHIND the statistics pass
+    counts_dev = torch.stack([(rowcnt > 0).sum(), n_tie_t if n_tie_t is not None else rowcnt.new_zeros(())])
+    counts_ready = torch.cuda.Event()
+    counts_ready.record()
     sd, sd2 = torch.empty(b, **f64), torch.empty(b, **f64)
     ws = _ws(_lib.load().gridb200_col_norm_stats_ws_bytes(n, b), dev)
     with _mark("col_norm"):
@@ -169,7 +193,7 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
     mu, s2, ratio = torch.empty(b, **f64), torch.empty(b, **f64), torch.empty(b, **f64)
     # samples without any valid bin are dropped by the reference before normalising (filter_empty_samples,
     # normalize_mosdepth.py:576-600); they contribute nothing here either, only N in the ddof=1 divisor changes
-    counts_host = torch.stack([(rowcnt > 0).sum(), n_tie_t if n_tie_t is not None else rowcnt.new_zeros(())]).tolist()
+    counts_host = _read_behind(counts_dev, counts_ready)
     n_eff = int(counts_host[0])
     if counts_host[1]:
         _sharded_tie_means(depth, b, valid, rowsum, rowcnt, raw_mean, scale_q, tie, group)
@@ -180,10 +204,14 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
         import torch.distributed as dist
 
         world, rank = dist.get_world_size(group), dist.get_rank(group)
-        sizes = torch.zeros(world, **i64)
-        sizes[rank] = b
-        dist.all_reduce(sizes, group=group)
-        sizes = sizes.tolist()
+        if bin_sizes is not None:
+            sizes = [int(x) for x in bin_sizes]
+            assert len(sizes) == world and sizes[rank] == b, "bin_sizes must list every rank's bins"
+        else:
+            sizes = torch.zeros(world, **i64)
+            sizes[rank] = b
+            dist.all_reduce(sizes, group=group)
+            sizes = sizes.tolist()
         bmax = max(sizes)
         mine = torch.full((bmax,), float("nan"), **f64)
         mine[:b] = ratio
@@ -595,9 +623,10 @@ def synth_depth(seed: int, n: int, b: int, row0: int = 0, col0: int = 0, device=
     return depth
 
 
-def run_chain(depth: torch.Tensor, b: int, counts: torch.Tensor, p: Params, impl: int = 0, group=None):
+def run_chain(depth: torch.Tensor, b: int, counts: torch.Tensor, p: Params, impl: int = 0, group=None,
+              bin_sizes: list[int] | None = None):
     """normalize -> kNN -> dipCN with everything resident on the device (the benchmarked path)."""
-    res = normalize(depth, b, p, want_zq=False, want_zh=True, group=group)
+    res = normalize(depth, b, p, want_zq=False, want_zh=True, group=group, bin_sizes=bin_sizes)
     if res.rw == 0:
         raise ValueError("no bins selected")
     if res.zh is None:  # this rank's slice holds no selected bin: contribute a zero partial
@@ -610,43 +639,70 @@ def run_chain(depth: torch.Tensor, b: int, counts: torch.Tensor, p: Params, impl
     return res, idx, d2, cn
 
 
-# ---- packed host format (uint16 hundredths + escape list): 2 bytes per cell over PCIe --------------------------
+# ---- packed host format (hundredths in 16 or fewer bits + escape list): 2 bytes or less per cell over PCIe ---------------
 @dataclass
 class PackedDepth:
-    """Host-resident depth matrix: codes[n, ld] uint16 hundredths in pinned memory (0 = absent, 0xFFFF = see escapes),
-    escapes = (cell index = row * b + bin, fp32 value) for depths >= 655.35."""
+    """Host-resident depth matrix in pinned memory.  bits == 16: codes[n, ld] uint16 hundredths (0 = absent, 0xFFFF = see
+    escapes).  bits in 9..15: codes[n, ldw] int32 words, groups of 32 cells bit-packed (gridb200_depth_pack_bits; the
+    all-ones code = see escapes).  escapes = (cell index = row * b + bin, fp32 value) for depths that do not fit."""
 
     codes: torch.Tensor
     n: int
     b: int
     esc_cell: torch.Tensor
     esc_val: torch.Tensor
+    bits: int = 16
 
     @property
     def nbytes(self) -> int:
-        return self.codes.numel() * 2 + self.esc_cell.numel() * 12
+        return self.codes.numel() * self.codes.element_size() + self.esc_cell.numel() * 12
 
 
-def pack_depth(depth: torch.Tensor, b: int, chunk_rows: int = 256, pin: bool = True) -> PackedDepth:
-    """Device fp32 depth[n, ld] -> PackedDepth on the host (export / side-car / bench set-up)."""
+def choose_bits(depth: torch.Tensor, b: int, max_escape_frac: float = 2e-4) -> int:
+    """Smallest code width (13..16 bits) that leaves at most max_escape_frac of the cells to the escape list, judged on
+    a sample of rows (a 30x cohort fits 13 bits: depths below 81.91)."""
+    n = depth.shape[0]
+    rows = torch.linspace(0, n - 1, min(n, 64)).long().to(depth.device)
+    h = torch.round(depth[rows, :b].double() * 100.0)
+    for bits in (13, 14, 15):
+        if float((h >= (1 << bits) - 1).double().mean()) <= max_escape_frac:
+            return bits
+    return 16
+
+
+def pack_depth(depth: torch.Tensor, b: int, chunk_rows: int = 256, pin: bool = True, bits: int | str = 16) -> PackedDepth:
+    """Device fp32 depth[n, ld] -> PackedDepth on the host (export / side-car / bench set-up).  bits: 16, 9..15, or
+    "auto" (choose_bits)."""
     n, ld = depth.shape[0], depth.stride(0)
     dev = depth.device
-    ldo = (b + 7) // 8 * 8
-    codes = torch.empty((n, ldo), dtype=torch.uint16, pin_memory=pin)
+    if bits == "auto":
+        bits = choose_bits(depth, b)
+    bits = int(bits)
+    if bits == 16:
+        ldo, dt = (b + 7) // 8 * 8, torch.uint16
+    else:
+        ldo, dt = int(_lib.load().gridb200_depth_packed_row_words(b, bits)), torch.int32
+        if ldo < 0:
+            raise ValueError(f"bits = {bits}: must be 16 or 9..15")
+    codes = torch.empty((n, ldo), dtype=dt, pin_memory=pin)
     cap = 1 << 16
     while True:
         esc_cell = torch.empty(cap, dtype=torch.int64, device=dev)
         esc_val = torch.empty(cap, dtype=torch.float32, device=dev)
         cnt = torch.zeros(1, dtype=torch.int64, device=dev)
-        stage = torch.empty((min(chunk_rows, n), ldo), dtype=torch.uint16, device=dev)
+        stage = torch.empty((min(chunk_rows, n), ldo), dtype=dt, device=dev)
         for r0 in range(0, n, chunk_rows):
             c = min(chunk_rows, n - r0)
-            call("gridb200_depth_pack_u16", depth.data_ptr() + r0 * ld * 4, c, b, ld, ptr(stage), ldo, r0, ptr(esc_cell),
-                 ptr(esc_val), cap, ptr(cnt), _stream())
+            if bits == 16:
+                call("gridb200_depth_pack_u16", depth.data_ptr() + r0 * ld * 4, c, b, ld, ptr(stage), ldo, r0, ptr(esc_cell),
+                     ptr(esc_val), cap, ptr(cnt), _stream())
+            else:
+                call("gridb200_depth_pack_bits", depth.data_ptr() + r0 * ld * 4, c, b, ld, bits, ptr(stage), ldo, r0,
+                     ptr(esc_cell), ptr(esc_val), cap, ptr(cnt), _stream())
             codes[r0:r0 + c].copy_(stage[:c])
         m = int(cnt.item())
         if m <= cap:
-            return PackedDepth(codes, n, b, esc_cell[:m].cpu(), esc_val[:m].cpu())
+            return PackedDepth(codes, n, b, esc_cell[:m].cpu(), esc_val[:m].cpu(), bits)
         cap = m
 
 
@@ -657,10 +713,10 @@ def upload_packed(packed: PackedDepth, depth: torch.Tensor, chunk_rows: int = 12
     dev = depth.device
     lds = packed.codes.stride(0)
     chunk_rows = max(1, min(chunk_rows, n, 65535))
-    key = (dev, chunk_rows, lds)
+    key = (dev, chunk_rows, lds, packed.codes.dtype)
     st = _UPLOAD_STATE.get(key)
     if st is None:
-        st = {"stage": [torch.empty((chunk_rows, lds), dtype=torch.uint16, device=dev) for _ in range(2)],
+        st = {"stage": [torch.empty((chunk_rows, lds), dtype=packed.codes.dtype, device=dev) for _ in range(2)],
               "copy": torch.cuda.Stream(device=dev), "done": [torch.cuda.Event() for _ in range(2)],
               "free": [torch.cuda.Event() for _ in range(2)]}
         _UPLOAD_STATE.clear()
@@ -678,8 +734,12 @@ def upload_packed(packed: PackedDepth, depth: torch.Tensor, chunk_rows: int = 12
             st["stage"][s][:c].copy_(packed.codes[r0:r0 + c], non_blocking=True)
             st["done"][s].record(st["copy"])
         main.wait_event(st["done"][s])
-        call("gridb200_depth_unpack_u16", ptr(st["stage"][s]), c, b, lds, depth.data_ptr() + r0 * ld * 4, ld,
-             ptr(esc_cell), ptr(esc_val), n_esc, r0, main.cuda_stream)
+        if packed.bits == 16:
+            call("gridb200_depth_unpack_u16", ptr(st["stage"][s]), c, b, lds, depth.data_ptr() + r0 * ld * 4, ld,
+                 ptr(esc_cell), ptr(esc_val), n_esc, r0, main.cuda_stream)
+        else:
+            call("gridb200_depth_unpack_bits", ptr(st["stage"][s]), c, b, lds, packed.bits, depth.data_ptr() + r0 * ld * 4, ld,
+                 ptr(esc_cell), ptr(esc_val), n_esc, r0, main.cuda_stream)
         st["free"][s].record(main)
     return depth
 

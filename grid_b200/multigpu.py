@@ -117,7 +117,8 @@ def _w_normalize(rank, world, group, payload):
     depth = torch.zeros((depth_host.shape[0], ld), dtype=torch.float32, device=dev)
     if nb:
         depth[:, :nb] = depth_host[:, lo:hi].to(dev)
-    res = engine.normalize(depth, max(nb, 1), p, want_zq=True, want_zh=False, group=group) if nb else None
+    sizes = [z - a for a, z in bin_slices(b, world, 4)]
+    res = engine.normalize(depth, max(nb, 1), p, want_zq=True, want_zh=False, group=group, bin_sizes=sizes) if nb else None
     if res is None:
         raise ValueError(f"gpu.devices: {world} devices for {b} bins leaves a rank without bins; use fewer devices")
     sel = torch.nonzero(res.sel_pos >= 0).flatten()

@@ -296,6 +296,18 @@ GRIDB200_API int gridb200_depth_unpack_u16(const uint16_t* src, int64_t n, int64
                               int64_t ld, const int64_t* esc_cell, const float* esc_val, int64_t esc_count,
                               int64_t row0, void* stream);
 
+/* The same with `bits` (9..15) per cell: a 30x cohort's hundredths sit below 2^13, and the end-to-end step is bound by
+ * PCIe.  A row is a sequence of groups of 32 cells, a group `bits` little-endian 32-bit words (cell c at bit c*bits);
+ * the all-ones code is the escape; rows are ldw words apart, ldw >= gridb200_depth_packed_row_words(b, bits)
+ * (whole groups, 16-byte aligned).  Unpacking yields the same bit-identical fp32 matrix. */
+GRIDB200_API int64_t gridb200_depth_packed_row_words(int64_t b, int32_t bits);
+GRIDB200_API int gridb200_depth_pack_bits(const float* depth, int64_t n, int64_t b, int64_t ld, int32_t bits, uint32_t* out,
+                             int64_t ldw, int64_t row0, int64_t* esc_cell, float* esc_val, int64_t esc_cap,
+                             int64_t* esc_count, void* stream);
+GRIDB200_API int gridb200_depth_unpack_bits(const uint32_t* src, int64_t n, int64_t b, int64_t ldw, int32_t bits,
+                               float* depth, int64_t ld, const int64_t* esc_cell, const float* esc_val,
+                               int64_t esc_count, int64_t row0, void* stream);
+
 /* ------------------------------------------------------------------ step-4 hand-off text --- */
 
 /* The N x Rw body of the step-4 file, on the device.  Codes are the int16 hundredths gridb200_transform writes
