@@ -51,8 +51,9 @@ def parse_args():
     ap.add_argument("--cpu-budget", type=float, default=0.0,
                     help="seconds of CPU work the CPU arm may use (default: 150 for --impl reference, 25 for the cpu_baseline leg)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--host-format", choices=["u16", "f32"], default="u16",
-                    help="e2e host buffer: packed uint16 hundredths + escape list (the product's host format) or raw fp32")
+    ap.add_argument("--host-format", choices=["packed", "u16", "f32"], default="packed",
+                    help="e2e host buffer: the product's host format -- hundredths bit-packed in the smallest width that fits "
+                         "the cohort (13 bits for a 30x cohort) + escape list --, its 16-bit variant, or raw fp32")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-check", action="store_true", help="debug: skip the parity check (the line says so)")
     ap.add_argument("--check-rows", type=int, default=64, help="query rows verified after the timed region (>= 64 by default)")
@@ -547,8 +548,8 @@ def run_ours(a):
     e2e = None
     if not a.no_e2e:
         try:
-            if a.host_format == "u16":
-                host = engine.pack_depth(depth, b_local)
+            if a.host_format in ("packed", "u16"):
+                host = engine.pack_depth(depth, b_local, bits="auto" if a.host_format == "packed" else 16)
                 host_bytes = host.nbytes
             else:
                 host = torch.empty(depth.shape, dtype=torch.float32, pin_memory=True)
@@ -558,7 +559,7 @@ def run_ours(a):
                     torch.empty((cn.shape[0], 1), dtype=torch.float64, pin_memory=True)]
 
             def e2e_step():
-                if a.host_format == "u16":
+                if a.host_format != "f32":
                     engine.upload_packed(host, depth)
                 else:
                     depth.copy_(host, non_blocking=True)
@@ -585,8 +586,11 @@ def run_ours(a):
             e2e = {"value": a.samples / (float(te.item()) / 1e3), "unit": "samples/s",
                    "h2d_bytes_per_step": int(h2d.item()), "d2h_bytes_per_step": int(sum(o.numel() * o.element_size() for o in outs)),
                    "ms_per_step": float(te.item()),
-                   "host_format": "uint16 hundredths + escape list, unpacked on the device (bit-identical fp32 matrix)"
-                   if a.host_format == "u16" else "fp32"}
+                   "host_format": (f"hundredths in {host.bits} bits per cell + escape list ({host.esc_cell.numel()} cells), unpacked "
+                                   "on the device (bit-identical fp32 matrix)") if a.host_format != "f32" else "fp32",
+                   # the end-to-end steps went through the host format: same cohort, so the same lists as the checked step
+                   "results_equal_checked_step": bool(torch.equal(outs[0], idx.cpu()) and torch.equal(outs[1], cn.cpu()))
+                   if (rank == 0 or rows) else None}
             del host
         except Exception as exc:  # e.g. not enough pinned host memory on this box
             e2e = {"value": None, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,

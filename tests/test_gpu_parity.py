@@ -576,6 +576,33 @@ def test_packed_host_format_round_trips_bit_for_bit(eng):
     assert float(out[3, 4]) == np.float32(12.34)
 
 
+@pytest.mark.parametrize("bits", [9, 13, 15, "auto"])
+def test_bit_packed_host_format_round_trips_bit_for_bit(eng, bits):
+    """Hundredths in 9..15 bits per cell (groups of 32 cells, little-endian bit stream) + escape list -> the same fp32
+    matrix: ragged last group, values on both sides of the escape code, absent cells, odd chunking."""
+    n, b = 130, 4099
+    depth = eng.synth_depth(12, n, b)
+    width = eng.choose_bits(depth, b) if bits == "auto" else bits
+    if bits == "auto":
+        assert width == 13                                   # a 30x cohort: depths below 81.91
+    esc = ((1 << width) - 1) / 100.0
+    depth[5, 17] = esc                  # first value that needs an escape
+    depth[5, 18] = esc - 0.01           # last that does not
+    depth[129, 4098] = 12345.67
+    depth[0, 0] = 0.0                   # absent
+    depth[7, 31], depth[7, 32] = 0.01, 0.02   # group boundary
+    want = depth.clone()
+    packed = eng.pack_depth(depth, b, chunk_rows=50, bits=bits)
+    assert packed.bits == width and packed.codes.dtype == torch.int32
+    assert packed.codes.shape[1] == ((b + 31) // 32 * width + 3) // 4 * 4
+    n_esc = int((torch.round(want[:, :b].double() * 100) >= (1 << width) - 1).sum())
+    assert packed.esc_cell.numel() == n_esc and {5 * b + 17, 129 * b + 4098} <= set(packed.esc_cell.tolist())
+    out = torch.full_like(depth, -1.0)
+    eng.upload_packed(packed, out, chunk_rows=37)
+    torch.cuda.synchronize()
+    assert torch.equal(out[:, :b].view(torch.int32), want[:, :b].view(torch.int32))
+
+
 def test_handoff_is_dropped_when_the_file_changes(tmp_path, eng):
     """A step-4 file rewritten by somebody else (here: the oracle) between the steps must be parsed, not trusted."""
     from grid_b200 import handoff as H
