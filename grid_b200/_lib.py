@@ -30,6 +30,7 @@ SIGNATURES = {
     "gridb200_col_finalize": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _vp, _vp]),
     "gridb200_select_ws_bytes": (_sz, [_i64]),
     "gridb200_select": (C.c_int, [_vp, _i64, _f64, _vp, _vp, _vp, _sz, _vp]),
+    "gridb200_select_static": (C.c_int, [_vp, _i64, _f64, _vp, _vp, _vp]),
     "gridb200_knn_col_filter": (C.c_int, [_vp, _vp, _i64, _f64, _f64, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gridb200_transform": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _i32, _vp, _i64, _vp, _i64,
                                      _vp, _vp, _vp]),

@@ -360,3 +360,53 @@ extern "C" int gridb200_knn_col_filter(const double* ratio, const int32_t* sel_p
   G2_LAUNCHED();
   return 0;
 }
+
+// ---- allocation-free variant (no counterpart in the reference) ------------
+// Callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) get
+// gridb200_select with its scratch in a file-scope device array instead of a caller-provided workspace.  The array is
+// sized for GRIDB200_SELECT_STATIC_MAX_BINS bins (selection state + radix histograms + one int per 2048-bin scan tile:
+// about 33 KB); every GPU that loads the library holds it until exit.  In host code `g_select_scratch` is only a stand-in
+// for the symbol: the device address comes from cudaGetSymbolAddress, once per device, with that device current.
+// Every call shares the array (it keeps the last call's contents; what must start at zero is cleared at the start of a
+// call, exactly as in gridb200_select), so calls that overlap on one GPU -- two streams -- race.
+namespace g2 {
+constexpr int64_t kSelectStaticMaxBins = GRIDB200_SELECT_STATIC_MAX_BINS;
+constexpr size_t kSelectStaticBytes =
+    kStateBytes + kHistBytes + (((size_t)(kSelectStaticMaxBins / kScanTile + 2) * sizeof(int) + 255) / 256) * 256;
+static __device__ __align__(256) unsigned char g_select_scratch[kSelectStaticBytes];
+}  // namespace g2
+
+extern "C" int gridb200_select_static(const double* ratio, int64_t b, double top_frac, int32_t* sel_pos, double* info,
+                                      void* stream) {
+  G2_REQUIRE(ratio && sel_pos && info && b > 0, GRIDB200_EINVAL, "bad argument");
+  G2_REQUIRE(b <= kSelectStaticMaxBins, GRIDB200_EINVAL,
+             "gridb200_select_static: %lld bins exceed the built-in scratch (GRIDB200_SELECT_STATIC_MAX_BINS = %lld); use "
+             "gridb200_select with a caller-provided workspace", (long long)b, (long long)kSelectStaticMaxBins);
+  static std::atomic<unsigned char*> addr_of[64];  // device address of the scratch array, per device
+  int dev = 0;
+  G2_CUDA(cudaGetDevice(&dev));
+  G2_REQUIRE(dev >= 0 && dev < 64, GRIDB200_ENODEV, "device index %d outside the per-device cache", dev);
+  unsigned char* w = addr_of[dev].load();
+  if (!w) {
+    void* p = nullptr;
+    G2_CUDA(cudaGetSymbolAddress(&p, g_select_scratch));
+    G2_REQUIRE(p != nullptr && (reinterpret_cast<uintptr_t>(p) & 255) == 0, GRIDB200_ECUDA, "scratch symbol address unusable");
+    w = static_cast<unsigned char*>(p);
+    addr_of[dev].store(w);
+  }
+  cudaStream_t st = as_stream(stream);
+  SelState* state = reinterpret_cast<SelState*>(w);
+  unsigned* hist = reinterpret_cast<unsigned*>(w + kStateBytes);
+  int* block_sums = reinterpret_cast<int*>(w + kStateBytes + kHistBytes);
+  if (int e = run_select(ratio, b, /*mode=*/0, /*kind=*/0, top_frac, nullptr, state, hist, st)) return e;  // (clears state + hist)
+  k_norm_select_finish<<<1, 1, 0, st>>>(state, info);
+  G2_LAUNCHED();
+  const int64_t nblk = (b + kScanTile - 1) / kScanTile;
+  k_flag_count<<<(unsigned)nblk, 1024, 0, st>>>(ratio, b, info, block_sums);
+  G2_LAUNCHED();
+  k_scan_block_sums<<<1, 1024, 0, st>>>(block_sums, nblk, info);
+  G2_LAUNCHED();
+  k_write_pos<<<(unsigned)nblk, 1024, 0, st>>>(ratio, b, info, block_sums, sel_pos);
+  G2_LAUNCHED();
+  return 0;
+}

@@ -122,6 +122,17 @@ GRIDB200_API size_t gridb200_select_ws_bytes(int64_t b);
 GRIDB200_API int gridb200_select(const double* ratio, int64_t b, double top_frac, int32_t* sel_pos, double* info,
                     void* ws, size_t ws_bytes, void* stream);
 
+/* gridb200_select without a workspace argument.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  The scratch (selection state, radix histograms, scan-tile sums: about 33 KB) is a file-scope
+ * `static __device__` array inside the library, held by every GPU that loads it until exit; the entry point calls no
+ * cudaMalloc / cudaFree / allocating routine.  Same inputs, outputs and arithmetic as gridb200_select.
+ * Limit: b <= GRIDB200_SELECT_STATIC_MAX_BINS (larger -> GRIDB200_EINVAL with a message naming the limit).
+ * Every call on a GPU shares the one array: calls that overlap on the GPU (different streams) race; serialise them. */
+#define GRIDB200_SELECT_STATIC_MAX_BINS 4194304
+GRIDB200_API int gridb200_select_static(const double* ratio, int64_t b, double top_frac, int32_t* sel_pos, double* info,
+                           void* stream);
+
 /* find_neighbors' region filter on the %.3f-rounded ratios of the selected bins (find_neighbors.py:128-175):
  * keep[j] = 1 iff sel_pos[j] >= 0 and finite(rq) and rq >= sigma2_min and rq <= sigma2_max, where
  * rq = float("%.3f" % ratio[j]) and sigma2_min = sorted(finite rq)[min(int(Rw*(1-frac_r)), n_finite-1)];
