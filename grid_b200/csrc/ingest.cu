@@ -330,7 +330,41 @@ __global__ void __launch_bounds__(256) k_unpack_bits(const uint32_t* __restrict_
     for (int t = 0; t < 4 && j + t < b; ++t) d[t] = f[t];
 }
 
+// bit-packed codes -> the 2-byte DEVICE matrix (uint16 hundredths; the width's escape code becomes 0xFFFF): what the
+// step-4 kernels read when the matrix is kept in 2 bytes per cell (gridb200_*_u16)
+__global__ void __launch_bounds__(256) k_unpack_bits_u16(const uint32_t* __restrict__ src, int64_t b, int64_t ldw, int bits,
+                                                         uint16_t* __restrict__ out, int64_t ldo) {
+  const int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  const int64_t i = blockIdx.y;
+  if (j >= b) return;
+  const uint32_t* s = src + i * ldw + (j >> 5) * bits;
+  const uint32_t mask = (1u << bits) - 1u;
+  uint32_t c[4];
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const int bit = (int)((j + t) & 31) * bits;
+    const int w = bit >> 5, sh = bit & 31;
+    uint32_t v = __ldg(s + w) >> sh;
+    if (sh + bits > 32) v |= __ldg(s + w + 1) << (32 - sh);
+    v &= mask;
+    c[t] = (j + t < b) ? (v == mask ? 0xFFFFu : v) : 0u;
+  }
+  *reinterpret_cast<uint2*>(out + i * ldo + j) = make_uint2(c[0] | (c[1] << 16), c[2] | (c[3] << 16));  // ldo % 4 == 0
+}
+
 }  // namespace g2
+
+extern "C" int gridb200_depth_unpack_bits_u16(const uint32_t* src, int64_t n, int64_t b, int64_t ldw, int32_t bits,
+                                              uint16_t* out, int64_t ldo, void* stream) {
+  using namespace g2;
+  G2_REQUIRE(src && out && n > 0 && b > 0 && n <= 65535, GRIDB200_EINVAL, "bad argument (rows per call <= 65535)");
+  G2_REQUIRE(bits >= 9 && bits <= 15 && ldw >= ((b + 31) / 32 * bits), GRIDB200_EINVAL, "bits must be 9..15 and ldw cover whole groups");
+  G2_REQUIRE(ldo >= (b + 3) / 4 * 4 && ldo % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0, GRIDB200_EINVAL,
+             "output rows must be 8-byte aligned with ldo a multiple of 4 and >= roundup4(b)");
+  k_unpack_bits_u16<<<dim3((unsigned)((b + 1023) / 1024), (unsigned)n), 256, 0, as_stream(stream)>>>(src, b, ldw, bits, out, ldo);
+  G2_LAUNCHED();
+  return 0;
+}
 
 extern "C" int64_t gridb200_depth_packed_row_words(int64_t b, int32_t bits) {
   if (b <= 0 || bits < 9 || bits > 15) return -1;

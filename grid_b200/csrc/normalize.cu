@@ -12,6 +12,74 @@ namespace g2 {
 constexpr int kThreads = 256;
 constexpr int kColsPerBlock = kThreads * 4;
 
+// ---------------------------------------------------------------------------------------------------------
+// Two storage types of the depth matrix share every kernel below (template parameter T):
+//   float     the packed fp32 matrix (0.0f = absent), 4 bytes per cell: hundredths recovered with one FFMA per cell
+//   uint16_t  the hundredths themselves (0 = absent), 2 bytes per cell: half the HBM traffic of the three step-4
+//             passes.  The code 0xFFFF is an escape: the cell's true hundredths (>= 65535, i.e. depth >= 655.35) are in a
+//             table sorted by cell key (global row * b + bin), looked up by binary search -- rare by construction.
+// Both yield the SAME integers h, so everything downstream is bit-identical.
+// ---------------------------------------------------------------------------------------------------------
+struct Esc {
+  const long long* key;  // sorted cell keys (esc_row0 + row) * b + bin
+  const int* h;          // true hundredths of those cells
+  long long n;
+  long long row0;        // global row of the matrix's row 0
+  long long b;           // bins per row in the key
+};
+
+__device__ __noinline__ int esc_lookup(const Esc& e, int64_t row, int64_t col) {
+  const long long want = (e.row0 + row) * e.b + col;
+  long long lo = 0, hi = e.n;
+  while (lo < hi) {
+    const long long mid = (lo + hi) >> 1;
+    if (e.key[mid] < want) lo = mid + 1;
+    else hi = mid;
+  }
+  return (lo < e.n && e.key[lo] == want) ? e.h[lo] : 65535;
+}
+
+template <typename T>
+struct Cells;
+
+template <>
+struct Cells<float> {
+  using Raw = float4;
+  static constexpr bool kEsc = false;
+  static __device__ __forceinline__ Raw zero() { return make_float4(0.f, 0.f, 0.f, 0.f); }
+  static __device__ __forceinline__ Raw load(const float* p) { return ld_stream(reinterpret_cast<const float4*>(p)); }
+  static __device__ __forceinline__ Raw load_cached(const float* p) { return *reinterpret_cast<const float4*>(p); }
+  static __device__ __forceinline__ void hund(const Raw& v, const Esc&, int64_t, int64_t, int (&h)[4]) {
+    h[0] = depth_hundredths(v.x), h[1] = depth_hundredths(v.y), h[2] = depth_hundredths(v.z), h[3] = depth_hundredths(v.w);
+  }
+  static __device__ __forceinline__ int hund1(const float* p, const Esc&, int64_t, int64_t) { return depth_hundredths(*p); }
+};
+
+template <>
+struct Cells<uint16_t> {
+  using Raw = uint2;
+  static constexpr bool kEsc = true;
+  static __device__ __forceinline__ Raw zero() { return make_uint2(0u, 0u); }
+  static __device__ __forceinline__ Raw load(const uint16_t* p) {
+    uint2 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(r.x), "=r"(r.y) : "l"(p));
+    return r;
+  }
+  static __device__ __forceinline__ Raw load_cached(const uint16_t* p) { return *reinterpret_cast<const uint2*>(p); }
+  static __device__ __forceinline__ void hund(const Raw& v, const Esc& e, int64_t row, int64_t col, int (&h)[4]) {
+    h[0] = (int)(v.x & 0xFFFFu), h[1] = (int)(v.x >> 16), h[2] = (int)(v.y & 0xFFFFu), h[3] = (int)(v.y >> 16);
+    if (__vcmpeq2(v.x, 0xFFFFFFFFu) | __vcmpeq2(v.y, 0xFFFFFFFFu)) {  // some cell of the four is an escape: rare
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        if (h[q] == 0xFFFF) h[q] = esc_lookup(e, row, col + q);
+    }
+  }
+  static __device__ __forceinline__ int hund1(const uint16_t* p, const Esc& e, int64_t row, int64_t col) {
+    const int h = *p;
+    return h == 0xFFFF ? esc_lookup(e, row, col) : h;
+  }
+};
+
 // rows per slab so that the grid has at least ~8 blocks per SM when the bin count alone cannot provide them
 static int64_t pick_row_slab(int64_t n, int64_t col_blocks, int64_t min_rows) {
   const int64_t want_blocks = (int64_t)kSMs * 8;
@@ -37,8 +105,8 @@ __device__ __forceinline__ void row_partial(unsigned* lo, unsigned* hi, int* cnt
   asm volatile("red.shared.add.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(cnt)), "r"((unsigned)rc) : "memory");
 }
 
-template <bool kRows>
-__global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ depth, int64_t n, int64_t b,
+template <bool kRows, typename T>
+__global__ void __launch_bounds__(kThreads) k_col_raw(const T* __restrict__ depth, const Esc esc, int64_t n, int64_t b,
                                                       int64_t ld, int64_t rows_per_slab,
                                                       unsigned long long* __restrict__ colsum,
                                                       int* __restrict__ colcnt,
@@ -57,8 +125,9 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ 
   const int64_t r1 = min(n, r0 + rows_per_slab);
   unsigned long long s[4] = {0, 0, 0, 0};
   int c[4] = {0, 0, 0, 0};
-  const float* p = depth + r0 * ld + (live ? j0 : 0);
-  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  using C = Cells<T>;
+  const T* p = depth + r0 * ld + (live ? j0 : 0);
+  const typename C::Raw zero4 = C::zero();
   for (int64_t base = r0; base < r1; base += 512) {  // uint32 partials cannot overflow within 512 rows
     const int64_t lim = (r1 < base + 512 ? r1 : base + 512);
     if (kRows) {
@@ -68,14 +137,15 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ 
     unsigned ps[4] = {0, 0, 0, 0};
     int64_t i = base;
     for (; i + 8 <= lim; i += 8) {
-      float4 v[8];
+      typename C::Raw v[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) v[u] = live ? ld_stream(reinterpret_cast<const float4*>(p + u * ld)) : zero4;
+      for (int u = 0; u < 8; ++u) v[u] = live ? C::load(p + u * ld) : zero4;
       p += 8 * ld;
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
-        const int h0 = depth_hundredths(v[u].x), h1 = depth_hundredths(v[u].y);
-        const int h2 = depth_hundredths(v[u].z), h3 = depth_hundredths(v[u].w);
+        int hh[4];
+        C::hund(v[u], esc, i + u, j0, hh);
+        const int h0 = hh[0], h1 = hh[1], h2 = hh[2], h3 = hh[3];
         ps[0] += h0; ps[1] += h1; ps[2] += h2; ps[3] += h3;
         const int k0 = h0 > 0, k1 = h1 > 0, k2 = h2 > 0, k3 = h3 > 0;
         c[0] += k0; c[1] += k1; c[2] += k2; c[3] += k3;
@@ -87,10 +157,11 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const float* __restrict__ 
       }
     }
     for (; i < lim; ++i) {
-      const float4 v = live ? ld_stream(reinterpret_cast<const float4*>(p)) : zero4;
+      const typename C::Raw v = live ? C::load(p) : zero4;
       p += ld;
-      const int h0 = depth_hundredths(v.x), h1 = depth_hundredths(v.y);
-      const int h2 = depth_hundredths(v.z), h3 = depth_hundredths(v.w);
+      int hh[4];
+      C::hund(v, esc, i, j0, hh);
+      const int h0 = hh[0], h1 = hh[1], h2 = hh[2], h3 = hh[3];
       ps[0] += h0; ps[1] += h1; ps[2] += h2; ps[3] += h3;
       const int k0 = h0 > 0, k1 = h1 > 0, k2 = h2 > 0, k3 = h3 > 0;
       c[0] += k0; c[1] += k1; c[2] += k2; c[3] += k3;
@@ -148,8 +219,9 @@ constexpr int kRowUnroll = 16;
 constexpr int kRowChunk = kThreads * 4 * kRowUnroll;  // 16384 bins per block
 constexpr int64_t kRowGridY = 32;                     // rows are strided over this many blocks per bin chunk
 
-__global__ void __launch_bounds__(kThreads) k_row_stats(const float* __restrict__ depth, int64_t b, int64_t ld,
-                                                        const uint8_t* __restrict__ valid,
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_row_stats(const T* __restrict__ depth, const Esc esc, int64_t row_base,
+                                                        int64_t b, int64_t ld, const uint8_t* __restrict__ valid,
                                                         unsigned long long* __restrict__ rowsum,
                                                         int* __restrict__ rowcnt, const int* __restrict__ skip_if,
                                                         int64_t nrows) {
@@ -160,14 +232,15 @@ __global__ void __launch_bounds__(kThreads) k_row_stats(const float* __restrict_
   __shared__ unsigned long long ss[kThreads / 32];
   __shared__ int sc[kThreads / 32];
   for (int64_t row = blockIdx.y; row < nrows; row += gridDim.y) {
-  const float* p = depth + row * ld;
-  float4 v[kRowUnroll];
+  using C = Cells<T>;
+  const T* p = depth + row * ld;
+  typename C::Raw v[kRowUnroll];
   uint32_t m[kRowUnroll];
 #pragma unroll
   for (int u = 0; u < kRowUnroll; ++u) {
     const int64_t j = c0 + ((int64_t)u * kThreads + threadIdx.x) * 4;
     if (j < b) {  // ld >= roundup4(b): the 16-byte load stays inside the row
-      v[u] = ld_stream(reinterpret_cast<const float4*>(p + j));
+      v[u] = C::load(p + j);
       if (j + 4 <= b) {
         m[u] = *reinterpret_cast<const uint32_t*>(valid + j);
       } else {
@@ -175,7 +248,7 @@ __global__ void __launch_bounds__(kThreads) k_row_stats(const float* __restrict_
         for (int q = 0; q < 4 && j + q < b; ++q) m[u] |= (uint32_t)valid[j + q] << (8 * q);
       }
     } else {
-      v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      v[u] = C::zero();
       m[u] = 0;
     }
   }
@@ -183,10 +256,12 @@ __global__ void __launch_bounds__(kThreads) k_row_stats(const float* __restrict_
   int c = 0;
 #pragma unroll
   for (int u = 0; u < kRowUnroll; ++u) {
-    const int h0 = (m[u] & 0x000000ffu) ? depth_hundredths(v[u].x) : 0;
-    const int h1 = (m[u] & 0x0000ff00u) ? depth_hundredths(v[u].y) : 0;
-    const int h2 = (m[u] & 0x00ff0000u) ? depth_hundredths(v[u].z) : 0;
-    const int h3 = (m[u] & 0xff000000u) ? depth_hundredths(v[u].w) : 0;
+    int hh[4];
+    C::hund(v[u], esc, row_base + row, c0 + ((int64_t)u * kThreads + threadIdx.x) * 4, hh);
+    const int h0 = (m[u] & 0x000000ffu) ? hh[0] : 0;
+    const int h1 = (m[u] & 0x0000ff00u) ? hh[1] : 0;
+    const int h2 = (m[u] & 0x00ff0000u) ? hh[2] : 0;
+    const int h3 = (m[u] & 0xff000000u) ? hh[3] : 0;
     s += (unsigned)(h0 + h1) + (unsigned)(h2 + h3);
     c += (h0 > 0) + (h1 > 0) + (h2 > 0) + (h3 > 0);
   }
@@ -237,7 +312,8 @@ __global__ void k_row_mode(const int* __restrict__ nbad, int64_t b, int* __restr
   mode[0] = ((int64_t)nbad[0] * 8 <= b) ? 1 : 0;
 }
 
-__global__ void __launch_bounds__(kThreads) k_row_fix(const float* __restrict__ depth, int64_t ld,
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_row_fix(const T* __restrict__ depth, const Esc esc, int64_t ld,
                                                       const int* __restrict__ bad, const int* __restrict__ nbad,
                                                       const int* __restrict__ mode,
                                                       const unsigned long long* __restrict__ rowsum_all,
@@ -247,11 +323,11 @@ __global__ void __launch_bounds__(kThreads) k_row_fix(const float* __restrict__ 
   if (!mode[0]) return;
   const int64_t row = blockIdx.x;
   const int nb = nbad[0];
-  const float* p = depth + row * ld;
+  const T* p = depth + row * ld;
   unsigned long long s = 0;
   int c = 0;
   for (int t = threadIdx.x; t < nb; t += kThreads) {
-    const int h = depth_hundredths(p[bad[t]]);
+    const int h = Cells<T>::hund1(p + bad[t], esc, row, bad[t]);
     s += (unsigned)h;
     c += h > 0;
   }
@@ -301,18 +377,23 @@ __global__ void k_row_scales(const long long* __restrict__ rowsum, const int* __
 // DOUBLE_pairwise_sum: blocks of <= 128 with 8 strided accumulators, halves split at a multiple of 8) over the
 // row's valid bins in column order, NaN cells as 0.0, exactly as nansum does.
 // ---------------------------------------------------------------------------------------------------------
+template <typename T>
 struct RowCursor {
-  const float* row;
+  const T* row;
   const uint8_t* valid;
   int64_t j;
+  Esc esc;
+  int64_t i;
   __device__ double next() {  // value of the next valid bin: depth as the double the reference parsed, absent -> 0.0
     while (!valid[j]) ++j;
-    const int h = depth_hundredths(row[j++]);
+    const int h = Cells<T>::hund1(row + j, esc, i, j);
+    ++j;
     return h ? __ddiv_rn((double)h, 100.0) : 0.0;
   }
 };
 
-__device__ double numpy_pairwise_leaf(RowCursor& c, int64_t n) {  // n <= 128
+template <typename T>
+__device__ double numpy_pairwise_leaf(RowCursor<T>& c, int64_t n) {  // n <= 128
   if (n < 8) {
     double res = 0.0;
     for (int64_t i = 0; i < n; ++i) res = __dadd_rn(res, c.next());
@@ -331,7 +412,8 @@ __device__ double numpy_pairwise_leaf(RowCursor& c, int64_t n) {  // n <= 128
 
 // sum(n) = n <= 128 ? leaf(n) : sum(n2) + sum(n - n2), n2 = n/2 rounded down to a multiple of 8; the elements are
 // consumed strictly in order, so the recursion runs over an explicit stack (depth <= log2(n))
-__device__ double numpy_pairwise_sum(RowCursor& c, int64_t n) {
+template <typename T>
+__device__ double numpy_pairwise_sum(RowCursor<T>& c, int64_t n) {
   struct Frame {
     int64_t n;
     double left;
@@ -366,7 +448,8 @@ __device__ double numpy_pairwise_sum(RowCursor& c, int64_t n) {
   return ret;
 }
 
-__global__ void k_row_mean_ties(const float* __restrict__ depth, int64_t n, int64_t b, int64_t ld,
+template <typename T>
+__global__ void k_row_mean_ties(const T* __restrict__ depth, const Esc esc, int64_t n, int64_t b, int64_t ld,
                                 const uint8_t* __restrict__ valid, const long long* __restrict__ rowsum,
                                 const int* __restrict__ rowcnt, double* __restrict__ raw_mean,
                                 double* __restrict__ scale_q) {
@@ -376,7 +459,7 @@ __global__ void k_row_mean_ties(const float* __restrict__ depth, int64_t n, int6
   if (cnt <= 0 || s <= 0 || (2 * s) % (2 * cnt) != cnt) return;  // mean in hundredths = s / cnt is not k + 1/2
   int64_t nvalid = 0;
   for (int64_t j = 0; j < b; ++j) nvalid += valid[j] != 0;
-  RowCursor c{depth + i * ld, valid, 0};
+  RowCursor<T> c{depth + i * ld, valid, 0, esc, i};
   const double m = __ddiv_rn(__dadd_rn(0.0, numpy_pairwise_sum(c, nvalid)), (double)cnt);
   if (raw_mean) raw_mean[i] = m;
   if (scale_q) scale_q[i] = printf_round(m, 100.0) / 100.0;
@@ -386,7 +469,8 @@ __global__ void k_row_mean_ties(const float* __restrict__ depth, int64_t n, int6
 // K4: sd[j] = sum_i (y_ij - 1), sd2[j] = sum_i (y_ij - 1)^2 over present cells (shifted-data variance).
 // Deterministic: with several row slabs each slab writes its own partial, reduced in slab order afterwards.
 // ---------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kThreads) k_col_norm(const float* __restrict__ depth, int64_t n, int64_t b,
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_col_norm(const T* __restrict__ depth, const Esc esc, int64_t n, int64_t b,
                                                        int64_t ld, int64_t rows_per_slab,
                                                        const uint8_t* __restrict__ valid,
                                                        const double* __restrict__ row_factor,
@@ -404,21 +488,23 @@ __global__ void __launch_bounds__(kThreads) k_col_norm(const float* __restrict__
   if (any) {
     const int64_t r0 = (int64_t)blockIdx.y * rows_per_slab;
     const int64_t r1 = min(n, r0 + rows_per_slab);
-    const float* p = depth + r0 * ld + j0;
+    using C = Cells<T>;
+    constexpr int kU = sizeof(T) == 2 ? 8 : 4;  // rows in flight: the 2-byte cells need twice the loads for the same bytes
+    const T* p = depth + r0 * ld + j0;
     int64_t i = r0;
-    for (; i + 4 <= r1; i += 4) {
-      float4 v[4];
-      double f[4];
+    for (; i + kU <= r1; i += kU) {
+      typename C::Raw v[kU];
+      double f[kU];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        v[u] = ld_stream(reinterpret_cast<const float4*>(p + u * ld));
+      for (int u = 0; u < kU; ++u) {
+        v[u] = C::load(p + u * ld);
         f[u] = row_factor[i + u];
       }
-      p += 4 * ld;
+      p += kU * ld;
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int h[4] = {depth_hundredths(v[u].x), depth_hundredths(v[u].y), depth_hundredths(v[u].z),
-                          depth_hundredths(v[u].w)};
+      for (int u = 0; u < kU; ++u) {
+        int h[4];
+        C::hund(v[u], esc, i + u, j0, h);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           if (h[q] > 0) {  // a row with no valid bin has f = NaN but then also no present cell
@@ -430,10 +516,11 @@ __global__ void __launch_bounds__(kThreads) k_col_norm(const float* __restrict__
       }
     }
     for (; i < r1; ++i) {
-      const float4 v = ld_stream(reinterpret_cast<const float4*>(p));
+      const typename C::Raw v = C::load(p);
       const double f = row_factor[i];
       p += ld;
-      const int h[4] = {depth_hundredths(v.x), depth_hundredths(v.y), depth_hundredths(v.z), depth_hundredths(v.w)};
+      int h[4];
+      C::hund(v, esc, i, j0, h);
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         if (h[q] > 0) {
@@ -576,23 +663,26 @@ __device__ __forceinline__ int quantise_fast(int h, double f, double negmu, doub
 
 // One batch of kRows rows for this thread's 4 bins.  kRows is a compile-time constant for the full batches (no row
 // guards in the unrolled body); the ragged last batch of a slab takes the generic instantiation with nr < kTB.
-template <bool kZq, bool kZh, bool kFull>
-__device__ __forceinline__ void transform_batch(const float4 (&v)[kTB], int nr, const double* __restrict__ sf,
-                                                const double (&negmu)[4], const double (&a100)[4], const int (&zc)[4],
-                                                const uint32_t (&aq)[4], const uint32_t (&ah)[4],
-                                                unsigned* __restrict__ part, bool lane0, const float* __restrict__ colp,
-                                                int64_t ld, unsigned long long* __restrict__ sat) {
+template <bool kZq, bool kZh, bool kFull, typename T>
+__device__ __forceinline__ void transform_batch(const typename Cells<T>::Raw (&v)[kTB], int nr,
+                                                const double* __restrict__ sf, const double (&negmu)[4],
+                                                const double (&a100)[4], const int (&zc)[4], const uint32_t (&aq)[4],
+                                                const uint32_t (&ah)[4], unsigned* __restrict__ part, bool lane0,
+                                                const T* __restrict__ colp, int64_t ld,
+                                                unsigned long long* __restrict__ sat, const Esc& esc, int64_t row0,
+                                                int64_t j0) {
   unsigned rare_rows = 0;
 #pragma unroll
   for (int u = 0; u < kTB; ++u) {
     if (!kFull && u >= nr) break;
     const double f = sf[u];
-    const float vv[4] = {v[u].x, v[u].y, v[u].z, v[u].w};
+    int hh[4];
+    Cells<T>::hund(v[u], esc, row0 + u, j0, hh);
     bool rare = false;
     int vsq = 0;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      const int h = depth_hundredths(vv[q]);
+      const int h = hh[q];
       bool neg;
       int z = quantise_fast(h, f, negmu[q], a100[q], rare, neg);
       if (kZq) {
@@ -618,12 +708,12 @@ __device__ __forceinline__ void transform_batch(const float4 (&v)[kTB], int nr, 
     const int u = __ffs(rare_rows) - 1;
     rare_rows &= rare_rows - 1;
     const double f = sf[u];
-    const float4 x = *reinterpret_cast<const float4*>(colp + (int64_t)u * ld);
-    const float vv[4] = {x.x, x.y, x.z, x.w};
+    int hh[4];
+    Cells<T>::hund(Cells<T>::load_cached(colp + (int64_t)u * ld), esc, row0 + u, j0, hh);
     int delta = 0;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-      const int h = depth_hundredths(vv[q]);
+      const int h = hh[q];
       if (h == 0 || !(f == f) || a100[q] == 0.0) continue;  // absent cell / unselected bin: nothing was kept
       bool r2 = false, neg;
       const int zf = quantise_fast(h, f, negmu[q], a100[q], r2, neg);
@@ -641,8 +731,8 @@ __device__ __forceinline__ void transform_batch(const float4 (&v)[kTB], int nr, 
   }
 }
 
-template <bool kZq, bool kZh>
-__global__ void __launch_bounds__(kThreads, 2) k_transform(const float* __restrict__ depth, int64_t n, int64_t b,
+template <bool kZq, bool kZh, typename T>
+__global__ void __launch_bounds__(kThreads, 2) k_transform(const T* __restrict__ depth, const Esc esc, int64_t n, int64_t b,
                                                            int64_t ld, const double* __restrict__ row_factor,
                                                            const double* __restrict__ mu,
                                                            const int32_t* __restrict__ sel_pos,
@@ -698,34 +788,36 @@ __global__ void __launch_bounds__(kThreads, 2) k_transform(const float* __restri
     aq[q] = (uint32_t)__cvta_generic_to_shared(s_zq) + 2 * off;
     ah[q] = (uint32_t)__cvta_generic_to_shared(s_zh) + 2 * off;
   }
-  const float* colp = depth + (j0 < b ? j0 : 0) + r0 * ld;
+  using C = Cells<T>;
+  const T* colp = depth + (j0 < b ? j0 : 0) + r0 * ld;
   const int warp = threadIdx.x >> 5;
   const bool lane0 = (threadIdx.x & 31) == 0;
   constexpr uint32_t kBufBytes = kTB * kStageRow * 2;
 
-  float4 v[kTB];
+  typename C::Raw v[kTB];
   if (any) {
 #pragma unroll
-    for (int u = 0; u < kTB; ++u)
-      v[u] = u < nrow ? ld_stream(reinterpret_cast<const float4*>(colp + (int64_t)u * ld)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int u = 0; u < kTB; ++u) v[u] = u < nrow ? C::load(colp + (int64_t)u * ld) : C::zero();
   }
   int buf = 0;
   for (int rb = 0; rb < nrow; rb += kTB, buf ^= 1) {
     const int nr = min(kTB, nrow - rb);
     if (any) {
       unsigned* part = s_part + (kZh ? warp * kTransformSlab + rb : 0);
-      const float* src = colp + (int64_t)rb * ld;
-      if (nr == kTB) transform_batch<kZq, kZh, true>(v, nr, s_f + rb, negmu, a100, zc, aq, ah, part, lane0, src, ld, sat);
-      else transform_batch<kZq, kZh, false>(v, nr, s_f + rb, negmu, a100, zc, aq, ah, part, lane0, src, ld, sat);
+      const T* src = colp + (int64_t)rb * ld;
+      if (nr == kTB)
+        transform_batch<kZq, kZh, true, T>(v, nr, s_f + rb, negmu, a100, zc, aq, ah, part, lane0, src, ld, sat, esc, r0 + rb, j0);
+      else
+        transform_batch<kZq, kZh, false, T>(v, nr, s_f + rb, negmu, a100, zc, aq, ah, part, lane0, src, ld, sat, esc, r0 + rb, j0);
       // next batch: in flight during the barrier and the copy-out
       const int rn = rb + kTB;
       if (rn + kTB <= nrow) {
 #pragma unroll
-        for (int u = 0; u < kTB; ++u) v[u] = ld_stream(reinterpret_cast<const float4*>(colp + (int64_t)(rn + u) * ld));
+        for (int u = 0; u < kTB; ++u) v[u] = C::load(colp + (int64_t)(rn + u) * ld);
       } else {
 #pragma unroll
         for (int u = 0; u < kTB; ++u)
-          if (rn + u < nrow) v[u] = ld_stream(reinterpret_cast<const float4*>(colp + (int64_t)(rn + u) * ld));
+          if (rn + u < nrow) v[u] = C::load(colp + (int64_t)(rn + u) * ld);
       }
     } else if (kZh) {
       for (int u = 0; u < nr; ++u)
@@ -782,13 +874,19 @@ __global__ void __launch_bounds__(kThreads) k_knn_prepare(const int16_t* __restr
 
 using namespace g2;
 
-static int check_matrix(const void* p, int64_t n, int64_t b, int64_t ld) {
+static int check_matrix(const void* p, int64_t n, int64_t b, int64_t ld, int align = 16) {
   G2_REQUIRE(p != nullptr, GRIDB200_EINVAL, "depth matrix pointer is null");
   G2_REQUIRE(n > 0 && b > 0, GRIDB200_EINVAL, "empty matrix (n=%lld, b=%lld)", (long long)n, (long long)b);
   G2_REQUIRE(ld >= b && ld % 4 == 0, GRIDB200_EINVAL, "leading dimension %lld must be >= b=%lld and a multiple of 4",
              (long long)ld, (long long)b);
-  G2_REQUIRE((reinterpret_cast<uintptr_t>(p) & 15) == 0, GRIDB200_EINVAL, "depth matrix must be 16-byte aligned");
+  G2_REQUIRE((reinterpret_cast<uintptr_t>(p) & (align - 1)) == 0, GRIDB200_EINVAL, "depth matrix must be %d-byte aligned", align);
   G2_REQUIRE(n < (1LL << 31) && b < (1LL << 40), GRIDB200_EINVAL, "matrix too large");
+  return 0;
+}
+
+static int make_esc(Esc& e, const int64_t* key, const int32_t* h, int64_t n_esc, int64_t row0, int64_t b_key) {
+  G2_REQUIRE(n_esc >= 0 && (n_esc == 0 || (key && h)) && row0 >= 0 && b_key > 0, GRIDB200_EINVAL, "bad escape table");
+  e.key = reinterpret_cast<const long long*>(key), e.h = h, e.n = n_esc, e.row0 = row0, e.b = b_key;
   return 0;
 }
 
@@ -805,15 +903,16 @@ extern "C" int gridb200_col_raw_stats(const float* depth, int64_t n, int64_t b, 
     G2_CUDA(cudaMemsetAsync(colsum, 0, b * sizeof(int64_t), st));
     G2_CUDA(cudaMemsetAsync(colcnt, 0, b * sizeof(int32_t), st));
   }
-  k_col_raw<false><<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(
-      depth, n, b, ld, rows, reinterpret_cast<unsigned long long*>(colsum), colcnt, nullptr, nullptr);
+  k_col_raw<false, float><<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(
+      depth, Esc{}, n, b, ld, rows, reinterpret_cast<unsigned long long*>(colsum), colcnt, nullptr, nullptr);
   G2_LAUNCHED();
   return 0;
 }
 
-extern "C" int gridb200_col_row_raw_stats(const float* depth, int64_t n, int64_t b, int64_t ld, int64_t* colsum,
-                                          int32_t* colcnt, int64_t* rowsum_all, int32_t* rowcnt_all, void* stream) {
-  if (int e = check_matrix(depth, n, b, ld)) return e;
+template <typename T>
+static int col_row_raw_impl(const T* depth, const Esc& esc, int64_t n, int64_t b, int64_t ld, int64_t* colsum,
+                            int32_t* colcnt, int64_t* rowsum_all, int32_t* rowcnt_all, void* stream) {
+  if (int e = check_matrix(depth, n, b, ld, 4 * (int)sizeof(T))) return e;
   G2_REQUIRE(colsum && colcnt && rowsum_all && rowcnt_all, GRIDB200_EINVAL, "null output");
   cudaStream_t st = as_stream(stream);
   const int64_t cb = (b + kColsPerBlock - 1) / kColsPerBlock;
@@ -826,19 +925,25 @@ extern "C" int gridb200_col_row_raw_stats(const float* depth, int64_t n, int64_t
   }
   G2_CUDA(cudaMemsetAsync(rowsum_all, 0, n * sizeof(int64_t), st));
   G2_CUDA(cudaMemsetAsync(rowcnt_all, 0, n * sizeof(int32_t), st));
-  k_col_raw<true><<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(
-      depth, n, b, ld, rows, reinterpret_cast<unsigned long long*>(colsum), colcnt,
+  k_col_raw<true, T><<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(
+      depth, esc, n, b, ld, rows, reinterpret_cast<unsigned long long*>(colsum), colcnt,
       reinterpret_cast<unsigned long long*>(rowsum_all), rowcnt_all);
   G2_LAUNCHED();
   return 0;
 }
 
+extern "C" int gridb200_col_row_raw_stats(const float* depth, int64_t n, int64_t b, int64_t ld, int64_t* colsum,
+                                          int32_t* colcnt, int64_t* rowsum_all, int32_t* rowcnt_all, void* stream) {
+  return col_row_raw_impl<float>(depth, Esc{}, n, b, ld, colsum, colcnt, rowsum_all, rowcnt_all, stream);
+}
+
 extern "C" size_t gridb200_row_stats_fused_ws_bytes(int64_t b) { return (size_t)(b > 0 ? b : 0) * 4 + 256; }
 
-extern "C" int gridb200_row_stats_fused(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
-                                        const int32_t* colcnt, const int64_t* rowsum_all, const int32_t* rowcnt_all,
-                                        int64_t* rowsum, int32_t* rowcnt, void* ws, size_t ws_bytes, void* stream) {
-  if (int e = check_matrix(depth, n, b, ld)) return e;
+template <typename T>
+static int row_stats_fused_impl(const T* depth, const Esc& esc, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                                const int32_t* colcnt, const int64_t* rowsum_all, const int32_t* rowcnt_all,
+                                int64_t* rowsum, int32_t* rowcnt, void* ws, size_t ws_bytes, void* stream) {
+  if (int e = check_matrix(depth, n, b, ld, 4 * (int)sizeof(T))) return e;
   G2_REQUIRE(valid && colcnt && rowsum_all && rowcnt_all && rowsum && rowcnt, GRIDB200_EINVAL, "null argument");
   G2_REQUIRE((reinterpret_cast<uintptr_t>(valid) & 3) == 0, GRIDB200_EINVAL, "valid flags must be 4-byte aligned");
   G2_REQUIRE(ws && ws_bytes >= gridb200_row_stats_fused_ws_bytes(b), GRIDB200_EINVAL,
@@ -857,15 +962,23 @@ extern "C" int gridb200_row_stats_fused(const float* depth, int64_t n, int64_t b
   const int64_t chunks = (b + kRowChunk - 1) / kRowChunk;
   for (int64_t r0 = 0; r0 < n; r0 += 65535) {  // gridDim.y limit
     const int64_t rows = std::min<int64_t>(65535, n - r0);
-    k_row_stats<<<dim3((unsigned)chunks, (unsigned)std::min<int64_t>(rows, kRowGridY)), kThreads, 0, st>>>(
-        depth + r0 * ld, b, ld, valid, reinterpret_cast<unsigned long long*>(rowsum) + r0, rowcnt + r0, flags + 1, rows);
+    k_row_stats<T><<<dim3((unsigned)chunks, (unsigned)std::min<int64_t>(rows, kRowGridY)), kThreads, 0, st>>>(
+        depth + r0 * ld, esc, r0, b, ld, valid, reinterpret_cast<unsigned long long*>(rowsum) + r0, rowcnt + r0, flags + 1,
+        rows);
     G2_LAUNCHED();
   }
-  k_row_fix<<<(unsigned)n, kThreads, 0, st>>>(depth, ld, bad, flags, flags + 1,
-                                              reinterpret_cast<const unsigned long long*>(rowsum_all), rowcnt_all,
-                                              reinterpret_cast<unsigned long long*>(rowsum), rowcnt);
+  k_row_fix<T><<<(unsigned)n, kThreads, 0, st>>>(depth, esc, ld, bad, flags, flags + 1,
+                                                 reinterpret_cast<const unsigned long long*>(rowsum_all), rowcnt_all,
+                                                 reinterpret_cast<unsigned long long*>(rowsum), rowcnt);
   G2_LAUNCHED();
   return 0;
+}
+
+extern "C" int gridb200_row_stats_fused(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                                        const int32_t* colcnt, const int64_t* rowsum_all, const int32_t* rowcnt_all,
+                                        int64_t* rowsum, int32_t* rowcnt, void* ws, size_t ws_bytes, void* stream) {
+  return row_stats_fused_impl<float>(depth, Esc{}, n, b, ld, valid, colcnt, rowsum_all, rowcnt_all, rowsum, rowcnt, ws,
+                                     ws_bytes, stream);
 }
 
 extern "C" int gridb200_depth_filter(const int64_t* colsum, const int32_t* colcnt, int64_t b, double min_depth,
@@ -888,8 +1001,9 @@ extern "C" int gridb200_row_stats(const float* depth, int64_t n, int64_t b, int6
   const int64_t chunks = (b + kRowChunk - 1) / kRowChunk;
   for (int64_t r0 = 0; r0 < n; r0 += 65535) {  // gridDim.y limit
     const int64_t rows = std::min<int64_t>(65535, n - r0);
-    k_row_stats<<<dim3((unsigned)chunks, (unsigned)std::min<int64_t>(rows, kRowGridY)), kThreads, 0, st>>>(
-        depth + r0 * ld, b, ld, valid, reinterpret_cast<unsigned long long*>(rowsum) + r0, rowcnt + r0, nullptr, rows);
+    k_row_stats<float><<<dim3((unsigned)chunks, (unsigned)std::min<int64_t>(rows, kRowGridY)), kThreads, 0, st>>>(
+        depth + r0 * ld, Esc{}, r0, b, ld, valid, reinterpret_cast<unsigned long long*>(rowsum) + r0, rowcnt + r0, nullptr,
+        rows);
     G2_LAUNCHED();
   }
   return 0;
@@ -904,15 +1018,22 @@ extern "C" int gridb200_row_scales(const int64_t* rowsum, const int32_t* rowcnt,
   return 0;
 }
 
+template <typename T>
+static int row_means_exact_impl(const T* depth, const Esc& esc, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                                const int64_t* rowsum, const int32_t* rowcnt, double* raw_mean, double* scale_q,
+                                void* stream) {
+  if (int e = check_matrix(depth, n, b, ld, 4 * (int)sizeof(T))) return e;
+  G2_REQUIRE(valid && rowsum && rowcnt, GRIDB200_EINVAL, "null argument");
+  k_row_mean_ties<T><<<(unsigned)((n + 63) / 64), 64, 0, as_stream(stream)>>>(
+      depth, esc, n, b, ld, valid, reinterpret_cast<const long long*>(rowsum), rowcnt, raw_mean, scale_q);
+  G2_LAUNCHED();
+  return 0;
+}
+
 extern "C" int gridb200_row_means_exact(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
                                         const int64_t* rowsum, const int32_t* rowcnt, double* raw_mean,
                                         double* scale_q, void* stream) {
-  if (int e = check_matrix(depth, n, b, ld)) return e;
-  G2_REQUIRE(valid && rowsum && rowcnt, GRIDB200_EINVAL, "null argument");
-  k_row_mean_ties<<<(unsigned)((n + 63) / 64), 64, 0, as_stream(stream)>>>(
-      depth, n, b, ld, valid, reinterpret_cast<const long long*>(rowsum), rowcnt, raw_mean, scale_q);
-  G2_LAUNCHED();
-  return 0;
+  return row_means_exact_impl<float>(depth, Esc{}, n, b, ld, valid, rowsum, rowcnt, raw_mean, scale_q, stream);
 }
 
 static int64_t col_norm_slab_rows(int64_t n, int64_t b) {
@@ -928,10 +1049,10 @@ extern "C" size_t gridb200_col_norm_stats_ws_bytes(int64_t n, int64_t b) {
   return slabs > 1 ? (size_t)slabs * (size_t)b * 2 * sizeof(double) : 0;
 }
 
-extern "C" int gridb200_col_norm_stats(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
-                                       const double* row_factor, double* sd, double* sd2, void* ws,
-                                       size_t ws_bytes, void* stream) {
-  if (int e = check_matrix(depth, n, b, ld)) return e;
+template <typename T>
+static int col_norm_impl(const T* depth, const Esc& esc, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                         const double* row_factor, double* sd, double* sd2, void* ws, size_t ws_bytes, void* stream) {
+  if (int e = check_matrix(depth, n, b, ld, 4 * (int)sizeof(T))) return e;
   G2_REQUIRE(valid && row_factor && sd && sd2, GRIDB200_EINVAL, "null argument");
   cudaStream_t st = as_stream(stream);
   const int64_t cb = (b + kColsPerBlock - 1) / kColsPerBlock;
@@ -939,20 +1060,26 @@ extern "C" int gridb200_col_norm_stats(const float* depth, int64_t n, int64_t b,
   const int64_t slabs = (n + rows - 1) / rows;
   G2_REQUIRE(slabs <= 65535, GRIDB200_EINVAL, "too many row slabs");
   if (slabs == 1) {
-    k_col_norm<<<dim3((unsigned)cb, 1), kThreads, 0, st>>>(depth, n, b, ld, rows, valid, row_factor, sd, sd2);
+    k_col_norm<T><<<dim3((unsigned)cb, 1), kThreads, 0, st>>>(depth, esc, n, b, ld, rows, valid, row_factor, sd, sd2);
     G2_LAUNCHED();
   } else {
     G2_REQUIRE(ws && ws_bytes >= gridb200_col_norm_stats_ws_bytes(n, b), GRIDB200_EINVAL,
                "workspace too small: need %zu bytes", gridb200_col_norm_stats_ws_bytes(n, b));
     double* p1 = static_cast<double*>(ws);
     double* p2 = p1 + slabs * b;
-    k_col_norm<<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(depth, n, b, ld, rows, valid, row_factor,
-                                                                          p1, p2);
+    k_col_norm<T><<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(depth, esc, n, b, ld, rows, valid, row_factor,
+                                                                             p1, p2);
     G2_LAUNCHED();
     k_reduce_slabs<<<(unsigned)((b + 255) / 256), 256, 0, st>>>(p1, p2, b, (int)slabs, sd, sd2);
     G2_LAUNCHED();
   }
   return 0;
+}
+
+extern "C" int gridb200_col_norm_stats(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
+                                       const double* row_factor, double* sd, double* sd2, void* ws,
+                                       size_t ws_bytes, void* stream) {
+  return col_norm_impl<float>(depth, Esc{}, n, b, ld, valid, row_factor, sd, sd2, ws, ws_bytes, stream);
 }
 
 extern "C" int gridb200_col_finalize(const double* sd, const double* sd2, const int32_t* colcnt,
@@ -965,11 +1092,12 @@ extern "C" int gridb200_col_finalize(const double* sd, const double* sd2, const 
   return 0;
 }
 
-extern "C" int gridb200_transform(const float* depth, int64_t n, int64_t b, int64_t ld, const double* row_factor,
-                                  const double* mu, const int32_t* sel_pos, const uint8_t* keep,
-                                  const double* info, int32_t zclip, int16_t* zq, int64_t ldq, void* zh,
-                                  int64_t ldh, int64_t* norms, unsigned long long* sat, void* stream) {
-  if (int e = check_matrix(depth, n, b, ld)) return e;
+template <typename T>
+static int transform_impl(const T* depth, const Esc& esc, int64_t n, int64_t b, int64_t ld, const double* row_factor,
+                          const double* mu, const int32_t* sel_pos, const uint8_t* keep, const double* info,
+                          int32_t zclip, int16_t* zq, int64_t ldq, void* zh, int64_t ldh, int64_t* norms,
+                          unsigned long long* sat, void* stream) {
+  if (int e = check_matrix(depth, n, b, ld, 4 * (int)sizeof(T))) return e;
   G2_REQUIRE(row_factor && mu && sel_pos && info && sat, GRIDB200_EINVAL, "null argument");
   G2_REQUIRE(zq || zh, GRIDB200_EINVAL, "at least one of zq / zh must be requested");
   G2_REQUIRE(!zh || (norms && zclip > 0 && zclip <= 2048), GRIDB200_EINVAL,
@@ -988,15 +1116,73 @@ extern "C" int gridb200_transform(const float* depth, int64_t n, int64_t b, int6
   // both outputs wanted (tests, small cohorts): two launches, so that one block's double-buffered staging stays
   // inside the 48 KB static shared-memory limit; the second launch does not count saturations again
   if (zq) {
-    k_transform<true, false><<<grid, kThreads, 0, st>>>(depth, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip,
-                                                        zq, ldq, zhp, ldh, np, sat);
+    k_transform<true, false, T><<<grid, kThreads, 0, st>>>(depth, esc, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip,
+                                                           zq, ldq, zhp, ldh, np, sat);
     if (zh) G2_LAUNCHED();
   }
   if (zh)
-    k_transform<false, true><<<grid, kThreads, 0, st>>>(depth, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip,
-                                                        zq, ldq, zhp, ldh, np, zq ? nullptr : sat);
+    k_transform<false, true, T><<<grid, kThreads, 0, st>>>(depth, esc, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip,
+                                                           zq, ldq, zhp, ldh, np, zq ? nullptr : sat);
   G2_LAUNCHED();
   return 0;
+}
+
+extern "C" int gridb200_transform(const float* depth, int64_t n, int64_t b, int64_t ld, const double* row_factor,
+                                  const double* mu, const int32_t* sel_pos, const uint8_t* keep,
+                                  const double* info, int32_t zclip, int16_t* zq, int64_t ldq, void* zh,
+                                  int64_t ldh, int64_t* norms, unsigned long long* sat, void* stream) {
+  return transform_impl<float>(depth, Esc{}, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip, zq, ldq, zh, ldh, norms,
+                               sat, stream);
+}
+
+// ---- the same five passes on the 2-byte matrix (uint16 hundredths, 0 = absent, 0xFFFF = see the escape table) ----------
+extern "C" int gridb200_col_row_raw_stats_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld,
+                                              const int64_t* esc_key, const int32_t* esc_h, int64_t n_esc, int64_t esc_row0,
+                                              int64_t esc_b, int64_t* colsum, int32_t* colcnt, int64_t* rowsum_all,
+                                              int32_t* rowcnt_all, void* stream) {
+  Esc esc;
+  if (int e = make_esc(esc, esc_key, esc_h, n_esc, esc_row0, esc_b)) return e;
+  return col_row_raw_impl<uint16_t>(depth, esc, n, b, ld, colsum, colcnt, rowsum_all, rowcnt_all, stream);
+}
+
+extern "C" int gridb200_row_stats_fused_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld, const int64_t* esc_key,
+                                            const int32_t* esc_h, int64_t n_esc, int64_t esc_row0, int64_t esc_b,
+                                            const uint8_t* valid, const int32_t* colcnt, const int64_t* rowsum_all,
+                                            const int32_t* rowcnt_all, int64_t* rowsum, int32_t* rowcnt, void* ws,
+                                            size_t ws_bytes, void* stream) {
+  Esc esc;
+  if (int e = make_esc(esc, esc_key, esc_h, n_esc, esc_row0, esc_b)) return e;
+  return row_stats_fused_impl<uint16_t>(depth, esc, n, b, ld, valid, colcnt, rowsum_all, rowcnt_all, rowsum, rowcnt, ws,
+                                        ws_bytes, stream);
+}
+
+extern "C" int gridb200_row_means_exact_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld, const int64_t* esc_key,
+                                            const int32_t* esc_h, int64_t n_esc, int64_t esc_row0, int64_t esc_b,
+                                            const uint8_t* valid, const int64_t* rowsum, const int32_t* rowcnt,
+                                            double* raw_mean, double* scale_q, void* stream) {
+  Esc esc;
+  if (int e = make_esc(esc, esc_key, esc_h, n_esc, esc_row0, esc_b)) return e;
+  return row_means_exact_impl<uint16_t>(depth, esc, n, b, ld, valid, rowsum, rowcnt, raw_mean, scale_q, stream);
+}
+
+extern "C" int gridb200_col_norm_stats_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld, const int64_t* esc_key,
+                                           const int32_t* esc_h, int64_t n_esc, int64_t esc_row0, int64_t esc_b,
+                                           const uint8_t* valid, const double* row_factor, double* sd, double* sd2,
+                                           void* ws, size_t ws_bytes, void* stream) {
+  Esc esc;
+  if (int e = make_esc(esc, esc_key, esc_h, n_esc, esc_row0, esc_b)) return e;
+  return col_norm_impl<uint16_t>(depth, esc, n, b, ld, valid, row_factor, sd, sd2, ws, ws_bytes, stream);
+}
+
+extern "C" int gridb200_transform_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld, const int64_t* esc_key,
+                                      const int32_t* esc_h, int64_t n_esc, int64_t esc_row0, int64_t esc_b,
+                                      const double* row_factor, const double* mu, const int32_t* sel_pos,
+                                      const uint8_t* keep, const double* info, int32_t zclip, int16_t* zq, int64_t ldq,
+                                      void* zh, int64_t ldh, int64_t* norms, unsigned long long* sat, void* stream) {
+  Esc esc;
+  if (int e = make_esc(esc, esc_key, esc_h, n_esc, esc_row0, esc_b)) return e;
+  return transform_impl<uint16_t>(depth, esc, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip, zq, ldq, zh, ldh, norms,
+                                  sat, stream);
 }
 
 extern "C" int gridb200_knn_prepare(const int16_t* zq, int64_t n, int64_t rw, int64_t ldq, const uint8_t* keep,

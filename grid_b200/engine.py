@@ -117,10 +117,89 @@ def _all_reduce(t: torch.Tensor, group) -> None:
         dist.all_reduce(t, group=group)
 
 
-def check_depth(depth: torch.Tensor, b: int) -> tuple[int, int]:
+@dataclass
+class Depth16:
+    """The depth matrix in 2 bytes per cell on the device: codes [n, ld] uint16 hundredths (0 = absent, 0xFFFF = escape),
+    esc_key / esc_h = sorted cell keys (row0 + row) * esc_b + bin and true hundredths of the escape cells (depth >=
+    655.35).  Every step-4 entry point has a _u16 twin that reads this and returns bit-identical results with half the
+    HBM traffic."""
+
+    codes: torch.Tensor
+    b: int
+    esc_key: torch.Tensor | None = None
+    esc_h: torch.Tensor | None = None
+    row0: int = 0
+    esc_b: int = 0
+
+    @property
+    def device(self):
+        return self.codes.device
+
+    @property
+    def shape(self):
+        return self.codes.shape
+
+    def stride(self, d):
+        return self.codes.stride(d)
+
+    @property
+    def n_esc(self) -> int:
+        return 0 if self.esc_key is None else int(self.esc_key.numel())
+
+    def set_escapes(self, cell: torch.Tensor, val: torch.Tensor) -> None:
+        """Escape list as PackedDepth carries it (cell = global_row * b + bin, fp32 depth) -> the kernels' sorted table."""
+        dev = self.codes.device
+        if cell.numel() == 0:
+            self.esc_key = self.esc_h = None
+            return
+        hundred = torch.full((1,), 100.0, dtype=torch.float64)
+        h = torch.round(val.cpu().double() * hundred).clamp(max=(1 << 22) - 1).to(torch.int32)
+        key, order = torch.sort(cell.cpu().to(torch.int64))
+        self.esc_key, self.esc_h = key.to(dev), h[order].to(dev)
+
+
+def check_depth(depth, b: int) -> tuple[int, int]:
+    if isinstance(depth, Depth16):
+        c = depth.codes
+        if not (c.is_cuda and c.dtype == torch.uint16 and c.dim() == 2 and c.stride(1) == 1 and c.stride(0) % 4 == 0):
+            raise ValueError("Depth16.codes must be a 2-D uint16 CUDA tensor with unit column stride and ld % 4 == 0")
+        return c.shape[0], c.stride(0)
     if not (depth.is_cuda and depth.dtype == torch.float32 and depth.dim() == 2 and depth.stride(1) == 1):
         raise ValueError("depth must be a 2-D fp32 CUDA tensor with unit column stride")
     return depth.shape[0], depth.stride(0)
+
+
+def _dcall(name: str, depth, n: int, b: int, ld: int, *rest) -> None:
+    """call(name, depth, n, b, ld, ...) for either storage type of the depth matrix."""
+    if isinstance(depth, Depth16):
+        call(name + "_u16", ptr(depth.codes), n, b, ld, ptr(depth.esc_key), ptr(depth.esc_h), depth.n_esc, depth.row0,
+             depth.esc_b or depth.b, *rest)
+    else:
+        call(name, ptr(depth), n, b, ld, *rest)
+
+
+def to_depth16(depth: torch.Tensor, b: int, row0: int = 0, esc_b: int | None = None) -> Depth16:
+    """fp32 device matrix -> Depth16 (device to device; escapes collected by the pack kernel)."""
+    n, ld = check_depth(depth, b)
+    dev = depth.device
+    ldo = (b + 7) // 8 * 8
+    codes = torch.zeros((n, ldo), dtype=torch.int16, device=dev).view(torch.uint16)
+    cap = 1 << 16
+    while True:
+        esc_cell = torch.empty(cap, dtype=torch.int64, device=dev)
+        esc_val = torch.empty(cap, dtype=torch.float32, device=dev)
+        cnt = torch.zeros(1, dtype=torch.int64, device=dev)
+        for r0 in range(0, n, 65535):
+            c = min(65535, n - r0)
+            call("gridb200_depth_pack_u16", depth.data_ptr() + r0 * ld * 4, c, b, ld, codes.data_ptr() + r0 * ldo * 2, ldo,
+                 row0 + r0, ptr(esc_cell), ptr(esc_val), cap, ptr(cnt), _stream())
+        m = int(cnt.item())
+        if m <= cap:
+            break
+        cap = m
+    d16 = Depth16(codes, b, row0=row0, esc_b=esc_b or b)
+    d16.set_escapes(esc_cell[:m], esc_val[:m])
+    return d16
 
 
 _SIDE: dict = {}
@@ -159,14 +238,14 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
     # bins then only need the few bins that failed the depth filter (gridb200_row_stats_fused decides on the device)
     rowsum_all, rowcnt_all = torch.empty(n, **i64), torch.empty(n, dtype=torch.int32, device=dev)
     with _mark("col_raw"):
-        call("gridb200_col_row_raw_stats", ptr(depth), n, b, ld, ptr(colsum), ptr(colcnt), ptr(rowsum_all),
+        _dcall("gridb200_col_row_raw_stats", depth, n, b, ld, ptr(colsum), ptr(colcnt), ptr(rowsum_all),
              ptr(rowcnt_all), st)
     call("gridb200_depth_filter", ptr(colsum), ptr(colcnt), b, float(p.min_depth), float(p.max_depth), ptr(valid), st)
 
     rowsum, rowcnt = torch.empty(n, **i64), torch.empty(n, dtype=torch.int32, device=dev)
     ws0 = _ws(_lib.load().gridb200_row_stats_fused_ws_bytes(b), dev)
     with _mark("row_stats"):
-        call("gridb200_row_stats_fused", ptr(depth), n, b, ld, ptr(valid), ptr(colcnt), ptr(rowsum_all), ptr(rowcnt_all),
+        _dcall("gridb200_row_stats_fused", depth, n, b, ld, ptr(valid), ptr(colcnt), ptr(rowsum_all), ptr(rowcnt_all),
              ptr(rowsum), ptr(rowcnt), ptr(ws0), ws0.numel(), st)
     _all_reduce(rowsum, group)
     _all_reduce(rowcnt, group)
@@ -175,7 +254,7 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
     # exact %.2f ties take numpy's own mean: a pairwise fp64 sum over the WHOLE row, replayed for the tie rows only
     n_tie_t = None
     if group is None:
-        call("gridb200_row_means_exact", ptr(depth), n, b, ld, ptr(valid), ptr(rowsum), ptr(rowcnt), ptr(raw_mean),
+        _dcall("gridb200_row_means_exact", depth, n, b, ld, ptr(valid), ptr(rowsum), ptr(rowcnt), ptr(raw_mean),
              ptr(scale_q), st)
     else:  # bins are sharded: rows are not whole on any rank; ties are known exactly from the all-reduced integer sums
         tie = (rowcnt > 0) & ((2 * rowsum) % (2 * rowcnt.to(torch.int64)).clamp(min=1) == rowcnt)
@@ -188,7 +267,7 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
     sd, sd2 = torch.empty(b, **f64), torch.empty(b, **f64)
     ws = _ws(_lib.load().gridb200_col_norm_stats_ws_bytes(n, b), dev)
     with _mark("col_norm"):
-        call("gridb200_col_norm_stats", ptr(depth), n, b, ld, ptr(valid), ptr(row_factor), ptr(sd), ptr(sd2), ptr(ws),
+        _dcall("gridb200_col_norm_stats", depth, n, b, ld, ptr(valid), ptr(row_factor), ptr(sd), ptr(sd2), ptr(ws),
              ws.numel(), st)
     mu, s2, ratio = torch.empty(b, **f64), torch.empty(b, **f64), torch.empty(b, **f64)
     # samples without any valid bin are dropped by the reference before normalising (filter_empty_samples,
@@ -265,7 +344,7 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
             zh[-1, :, rw_local % 64:] = 0
         norms = torch.zeros(n, **i64)
     with _mark("transform"):
-        call("gridb200_transform", ptr(depth), n, b, ld, ptr(row_factor), ptr(mu), ptr(sel_pos), ptr(keep), ptr(info),
+        _dcall("gridb200_transform", depth, n, b, ld, ptr(row_factor), ptr(mu), ptr(sel_pos), ptr(keep), ptr(info),
              p.zclip, ptr(zq), ldq, ptr(zh), n, ptr(norms), ptr(sat), st)
     if want_zh:
         _all_reduce(norms, group)
@@ -291,7 +370,16 @@ def _sharded_tie_means(depth, b, valid, rowsum, rowcnt, raw_mean, scale_q, tie, 
     sizes = sizes.tolist()
     bmax, btot = max(sizes), sum(sizes)
     mine = torch.zeros((nt, bmax), dtype=torch.float32, device=dev)
-    mine[:, :b] = depth[rows, :b]
+    if isinstance(depth, Depth16):  # (rare path) codes -> the fp32 values the text would have given: h / 100 correctly rounded
+        hh = depth.codes.view(torch.int16)[rows, :b].to(torch.int32) & 0xFFFF
+        if depth.n_esc:
+            keys = ((depth.row0 + rows)[:, None] * (depth.esc_b or depth.b) + torch.arange(b, device=dev)[None, :])
+            at = torch.searchsorted(depth.esc_key, keys.reshape(-1)).clamp(max=depth.n_esc - 1).reshape(keys.shape)
+            hit = (hh == 0xFFFF) & (depth.esc_key[at] == keys)
+            hh = torch.where(hit, depth.esc_h[at], hh)
+        mine[:, :b] = hh.to(torch.float32) / torch.full((1,), 100.0, dtype=torch.float32, device=dev)
+    else:
+        mine[:, :b] = depth[rows, :b]
     vmine = torch.zeros(bmax, dtype=torch.uint8, device=dev)
     vmine[:b] = valid
     got = torch.empty((world, nt, bmax), dtype=torch.float32, device=dev)
@@ -742,6 +830,53 @@ def upload_packed(packed: PackedDepth, depth: torch.Tensor, chunk_rows: int = 12
                  ptr(esc_cell), ptr(esc_val), n_esc, r0, main.cuda_stream)
         st["free"][s].record(main)
     return depth
+
+
+def upload_packed16(packed: PackedDepth, out: Depth16, chunk_rows: int = 128) -> Depth16:
+    """PackedDepth (host) -> the 2-byte device matrix `out` (preallocated codes [n, ld], ld = roundup8(b)).  16-bit host
+    codes ARE the device format (plain copies); narrower widths are widened by gridb200_depth_unpack_bits_u16 chunk by
+    chunk while the next chunk is in flight on a copy stream."""
+    n, b = packed.n, packed.b
+    codes = out.codes
+    dev, ldo = codes.device, codes.stride(0)
+    assert codes.shape[0] == n and out.b == b
+    main = torch.cuda.current_stream(dev)
+    out.row0, out.esc_b = 0, b
+    out.set_escapes(packed.esc_cell, packed.esc_val)
+    if packed.bits == 16:
+        assert packed.codes.stride(0) == ldo, "16-bit host codes are copied as they are: same leading dimension"
+        codes.copy_(packed.codes, non_blocking=True)
+        return out
+    lds = packed.codes.stride(0)
+    chunk_rows = max(1, min(chunk_rows, n, 65535))
+    key = (dev, chunk_rows, lds, packed.codes.dtype)
+    st = _UPLOAD_STATE.get(key)
+    if st is None:
+        st = {"stage": [torch.empty((chunk_rows, lds), dtype=packed.codes.dtype, device=dev) for _ in range(2)],
+              "copy": torch.cuda.Stream(device=dev), "done": [torch.cuda.Event() for _ in range(2)],
+              "free": [torch.cuda.Event() for _ in range(2)]}
+        _UPLOAD_STATE.clear()
+        _UPLOAD_STATE[key] = st
+    for s_ in range(2):
+        st["free"][s_].record(main)
+    for t, r0 in enumerate(range(0, n, chunk_rows)):
+        s_, c = t & 1, min(chunk_rows, n - r0)
+        with torch.cuda.stream(st["copy"]):
+            st["copy"].wait_event(st["free"][s_])
+            st["stage"][s_][:c].copy_(packed.codes[r0:r0 + c], non_blocking=True)
+            st["done"][s_].record(st["copy"])
+        main.wait_event(st["done"][s_])
+        call("gridb200_depth_unpack_bits_u16", ptr(st["stage"][s_]), c, b, lds, packed.bits, codes.data_ptr() + r0 * ldo * 2,
+             ldo, main.cuda_stream)
+        st["free"][s_].record(main)
+    if out.n_esc:  # escapes of the narrow host width that DO fit 16 bits go back into the matrix; the rest stay in the table
+        fits = out.esc_h < 0xFFFF
+        if bool(fits.any()):
+            k = out.esc_key[fits]
+            codes.view(torch.int16).view(-1)[(k // b) * ldo + (k % b)] = out.esc_h[fits].to(torch.int16)   # (wraps: bit pattern)
+            keep = ~fits
+            out.esc_key, out.esc_h = (out.esc_key[keep], out.esc_h[keep]) if bool(keep.any()) else (None, None)
+    return out
 
 
 _UPLOAD_STATE: dict = {}

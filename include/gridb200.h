@@ -319,6 +319,38 @@ GRIDB200_API int gridb200_depth_unpack_bits(const uint32_t* src, int64_t n, int6
                                float* depth, int64_t ld, const int64_t* esc_cell, const float* esc_val,
                                int64_t esc_count, int64_t row0, void* stream);
 
+/* ---- the depth matrix in 2 bytes per cell ON THE DEVICE ------------------------------------------------------------
+ * uint16 hundredths, 0 = absent, rows ld elements apart (ld % 4 == 0, 8-byte aligned rows): the three step-4 passes then
+ * read half the bytes of the fp32 matrix.  The code 0xFFFF is an escape: the cell's true hundredths (depth >= 655.35;
+ * < 2^22 like everywhere) are in a table sorted by key (esc_row0 + row) * esc_b + bin -- esc_key [n_esc] ascending,
+ * esc_h [n_esc] -- which the kernels search only when they meet the code.  Same integers, so every result is
+ * bit-identical to the fp32 entry point of the same name (same reference lines).  gridb200_depth_pack_u16 produces the
+ * matrix from fp32, gridb200_depth_unpack_bits_u16 from the bit-packed host format (its escape code becomes 0xFFFF). */
+GRIDB200_API int gridb200_depth_unpack_bits_u16(const uint32_t* src, int64_t n, int64_t b, int64_t ldw, int32_t bits,
+                                   uint16_t* out, int64_t ldo, void* stream);
+GRIDB200_API int gridb200_col_row_raw_stats_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld,
+                                   const int64_t* esc_key, const int32_t* esc_h, int64_t n_esc, int64_t esc_row0,
+                                   int64_t esc_b, int64_t* colsum, int32_t* colcnt, int64_t* rowsum_all,
+                                   int32_t* rowcnt_all, void* stream);
+GRIDB200_API int gridb200_row_stats_fused_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld,
+                                 const int64_t* esc_key, const int32_t* esc_h, int64_t n_esc, int64_t esc_row0,
+                                 int64_t esc_b, const uint8_t* valid, const int32_t* colcnt, const int64_t* rowsum_all,
+                                 const int32_t* rowcnt_all, int64_t* rowsum, int32_t* rowcnt, void* ws, size_t ws_bytes,
+                                 void* stream);
+GRIDB200_API int gridb200_row_means_exact_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld,
+                                 const int64_t* esc_key, const int32_t* esc_h, int64_t n_esc, int64_t esc_row0,
+                                 int64_t esc_b, const uint8_t* valid, const int64_t* rowsum, const int32_t* rowcnt,
+                                 double* raw_mean, double* scale_q, void* stream);
+GRIDB200_API int gridb200_col_norm_stats_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld,
+                                const int64_t* esc_key, const int32_t* esc_h, int64_t n_esc, int64_t esc_row0,
+                                int64_t esc_b, const uint8_t* valid, const double* row_factor, double* sd, double* sd2,
+                                void* ws, size_t ws_bytes, void* stream);
+GRIDB200_API int gridb200_transform_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld,
+                           const int64_t* esc_key, const int32_t* esc_h, int64_t n_esc, int64_t esc_row0, int64_t esc_b,
+                           const double* row_factor, const double* mu, const int32_t* sel_pos, const uint8_t* keep,
+                           const double* info, int32_t zclip, int16_t* zq, int64_t ldq, void* zh, int64_t ldh,
+                           int64_t* norms, unsigned long long* sat, void* stream);
+
 /* ------------------------------------------------------------------ step-4 hand-off text --- */
 
 /* The N x Rw body of the step-4 file, on the device.  Codes are the int16 hundredths gridb200_transform writes
