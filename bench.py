@@ -54,6 +54,9 @@ def parse_args():
     ap.add_argument("--host-format", choices=["packed", "u16", "f32"], default="packed",
                     help="e2e host buffer: the product's host format -- hundredths bit-packed in the smallest width that fits "
                          "the cohort (13 bits for a 30x cohort) + escape list --, its 16-bit variant, or raw fp32")
+    ap.add_argument("--device-format", choices=["u16", "f32"], default="u16",
+                    help="resident form of the depth matrix: uint16 hundredths + escape table (2 bytes per cell, the default; "
+                         "bit-identical results) or the packed fp32 matrix (4 bytes per cell)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-check", action="store_true", help="debug: skip the parity check (the line says so)")
     ap.add_argument("--check-rows", type=int, default=64, help="query rows verified after the timed region (>= 64 by default)")
@@ -497,6 +500,11 @@ def run_ours(a):
     else:
         depth = engine.synth_depth(SEED, a.samples, b_local, 0, lo, device=dev)
         counts = torch.from_numpy(counts_all).to(dev)
+        if a.device_format == "u16":   # the matrix stays resident in 2 bytes per cell (engine.Depth16)
+            d32 = depth
+            depth = engine.to_depth16(d32, b_local)
+            del d32
+            torch.cuda.empty_cache()
 
     def barrier():
         if group is not None:
@@ -548,18 +556,28 @@ def run_ours(a):
     e2e = None
     if not a.no_e2e:
         try:
+            u16_dev = isinstance(depth, engine.Depth16)
+            # (the host buffer is built from the fp32 form of the same synthetic cohort, regenerated for the purpose)
+            d32 = engine.synth_depth(SEED, a.samples, b_local, 0, lo, device=dev) if u16_dev else depth
             if a.host_format in ("packed", "u16"):
-                host = engine.pack_depth(depth, b_local, bits="auto" if a.host_format == "packed" else 16)
+                host = engine.pack_depth(d32, b_local, bits="auto" if a.host_format == "packed" else 16)
                 host_bytes = host.nbytes
             else:
+                if u16_dev:
+                    raise ValueError("--host-format f32 needs --device-format f32")
                 host = torch.empty(depth.shape, dtype=torch.float32, pin_memory=True)
                 host.copy_(depth)
                 host_bytes = host.numel() * 4
+            if u16_dev:
+                del d32
+                torch.cuda.empty_cache()
             outs = [torch.empty((idx.shape[0], idx.shape[1]), dtype=torch.int32, pin_memory=True),
                     torch.empty((cn.shape[0], 1), dtype=torch.float64, pin_memory=True)]
 
             def e2e_step():
-                if a.host_format != "f32":
+                if u16_dev:
+                    engine.upload_packed16(host, depth)
+                elif a.host_format != "f32":
                     engine.upload_packed(host, depth)
                 else:
                     depth.copy_(host, non_blocking=True)
@@ -587,7 +605,8 @@ def run_ours(a):
                    "h2d_bytes_per_step": int(h2d.item()), "d2h_bytes_per_step": int(sum(o.numel() * o.element_size() for o in outs)),
                    "ms_per_step": float(te.item()),
                    "host_format": (f"hundredths in {host.bits} bits per cell + escape list ({host.esc_cell.numel()} cells), unpacked "
-                                   "on the device (bit-identical fp32 matrix)") if a.host_format != "f32" else "fp32",
+                                   "on the device into the " + ("2-byte matrix" if u16_dev else "bit-identical fp32 matrix"))
+                   if a.host_format != "f32" else "fp32",
                    # the end-to-end steps went through the host format: same cohort, so the same lists as the checked step
                    "results_equal_checked_step": bool(torch.equal(outs[0], idx.cpu()) and torch.equal(outs[1], cn.cpu()))
                    if (rank == 0 or rows) else None}
@@ -608,6 +627,7 @@ def run_ours(a):
     rw, rw_local, kdim = res.rw, res.rw_local, res.kdim
     nq0 = idx.shape[0] if rows else a.samples
     cells = nq0 * b_local
+    cellb = 2 if isinstance(depth, engine.Depth16) else 4
     ring_rec = None
     if world > 1 and not a.no_ring and not rows and not a.norm_only:
         del depth, res, idx, d2, cn
@@ -653,7 +673,7 @@ def run_ours(a):
                     "full_matrix_equivalent_tflops": full_flops / (gram_ms * 1e-3) / 1e12, "symmetric": sym}
         norm_ms = sum(stages.get(s, {}).get("ms", 0.0) for s in ("col_raw", "row_stats", "col_norm", "transform"))
         stage_roof = {}
-        for s, byts in (("col_raw", 4), ("row_stats", 4), ("col_norm", 4), ("transform", 6)):
+        for s, byts in (("col_raw", cellb), ("row_stats", cellb), ("col_norm", cellb), ("transform", cellb + 2)):
             if s in stages:
                 g = cells * byts / (stages[s]["ms"] * 1e-3) / 1e9
                 stage_roof[s] = {"ms": stages[s]["ms"], "GB/s": g, "frac_hbm": g / hbm_peak, "bytes_per_cell": byts}
@@ -662,13 +682,18 @@ def run_ours(a):
             "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64 (normalise) + f16 x f16 -> exact int64 (kNN)", "data": "synthetic",
             "config": {"workload": workload_name(a), "sharding": f"{'rows (ring)' if rows else 'bins'} x{world}", "l2": "inputs_exceed_l2 (depth matrix "
-                       f"{cells * 4 / 1e9:.1f} GB per GPU)", "selected_bins": rw, "gram_impl": a.gram_impl, "norm_only_debug": a.norm_only},
+                       f"{cells * cellb / 1e9:.1f} GB per GPU)", "device_format": "u16 hundredths + escape table" if cellb == 2 else "fp32",
+                       "selected_bins": rw, "gram_impl": a.gram_impl, "norm_only_debug": a.norm_only},
             "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": int(launches), "roofline": roof,
             "parity_check": check if check is not None else {"skipped": True},
-            "stages": stages, "normalize_roofline": {"algorithmic_bytes_per_cell": 16, "ms": norm_ms,
-                                                     "GB/s": (16 * cells / (norm_ms * 1e-3) / 1e9) if norm_ms else None,
-                                                     "frac": (16 * cells / (norm_ms * 1e-3) / 1e9 / hbm_peak) if norm_ms else None,
-                                                     "peak": hbm_peak, "per_kernel": stage_roof},
+            "stages": stages, "normalize_roofline": {
+                # three reads of the matrix + one 2-byte write per cell: 16 B with the fp32 matrix (SURVEY 8d's figure),
+                # 8 B with the 2-byte matrix -- the fraction is taken on the bytes the chosen storage has to move
+                "algorithmic_bytes_per_cell": 3 * cellb + (4 if cellb == 4 else 2), "ms": norm_ms,
+                "GB/s": ((3 * cellb + (4 if cellb == 4 else 2)) * cells / (norm_ms * 1e-3) / 1e9) if norm_ms else None,
+                "frac": ((3 * cellb + (4 if cellb == 4 else 2)) * cells / (norm_ms * 1e-3) / 1e9 / hbm_peak) if norm_ms else None,
+                "fp32_accounting_equivalent_GB/s": (16 * cells / (norm_ms * 1e-3) / 1e9) if norm_ms else None,
+                "peak": hbm_peak, "per_kernel": stage_roof},
         }
         if ring_rec is not None:
             line["ring"] = ring_rec

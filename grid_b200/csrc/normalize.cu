@@ -90,6 +90,35 @@ static int64_t pick_row_slab(int64_t n, int64_t col_blocks, int64_t min_rows) {
   return rows < 1 ? 1 : rows;
 }
 
+// Cells per thread of the two streaming statistics passes (K1, K4): 16 bytes per load for either storage -- 4 fp32 cells
+// or 8 uint16 cells.  (With 8-byte loads the 2-byte matrix had half the bytes in flight and the passes took as long as on
+// fp32: latency-bound instead of HBM-bound.)
+template <typename T>
+struct Wide : Cells<T> {
+  static constexpr int kN = 4;
+};
+template <>
+struct Wide<uint16_t> {
+  using Raw = uint4;
+  static constexpr int kN = 8;
+  static __device__ __forceinline__ Raw zero() { return make_uint4(0u, 0u, 0u, 0u); }
+  static __device__ __forceinline__ Raw load(const uint16_t* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+  }
+  static __device__ __forceinline__ void hund(const Raw& v, const Esc& e, int64_t row, int64_t col, int (&h)[8]) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int t = 0; t < 4; ++t) h[2 * t] = (int)(w[t] & 0xFFFFu), h[2 * t + 1] = (int)(w[t] >> 16);
+    if ((__vcmpeq2(v.x, 0xFFFFFFFFu) | __vcmpeq2(v.y, 0xFFFFFFFFu)) | (__vcmpeq2(v.z, 0xFFFFFFFFu) | __vcmpeq2(v.w, 0xFFFFFFFFu))) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        if (h[q] == 0xFFFF) h[q] = esc_lookup(e, row, col + q);
+    }
+  }
+};
+
 // ---------------------------------------------------------------------------------------------------------
 // K1: colsum[j] = sum_i h_ij, colcnt[j] = #{h_ij > 0}; with kRows also the per-sample totals over ALL bins
 // (rowsum_all[i] = sum_j h_ij, rowcnt_all[i] = #{h_ij > 0}), which let step K3 skip its full pass over the matrix
@@ -117,15 +146,18 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const T* __restrict__ dept
   // addresses at config 2 -- was what held this pass at 0.75 of HBM speed)
   __shared__ unsigned s_lo[kRows ? 512 : 1], s_hi[kRows ? 512 : 1];  // sums split at bit 16: plain 32-bit reductions
   __shared__ int s_rc[kRows ? 512 : 1];
-  const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
+  using C = Wide<T>;
+  constexpr int kN = C::kN;
+  const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * kN;
   const bool live = j0 < b;  // dead threads of the last block stay for the collectives and barriers (they add zeros)
   if (!kRows && !live) return;
   const bool lane0 = (threadIdx.x & 31) == 0;
   const int64_t r0 = (int64_t)blockIdx.y * rows_per_slab;
   const int64_t r1 = min(n, r0 + rows_per_slab);
-  unsigned long long s[4] = {0, 0, 0, 0};
-  int c[4] = {0, 0, 0, 0};
-  using C = Cells<T>;
+  unsigned long long s[kN];
+  int c[kN];
+#pragma unroll
+  for (int q = 0; q < kN; ++q) s[q] = 0, c[q] = 0;
   const T* p = depth + r0 * ld + (live ? j0 : 0);
   const typename C::Raw zero4 = C::zero();
   for (int64_t base = r0; base < r1; base += 512) {  // uint32 partials cannot overflow within 512 rows
@@ -134,7 +166,29 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const T* __restrict__ dept
       for (int t = threadIdx.x; t < 512; t += kThreads) s_lo[t] = 0, s_hi[t] = 0, s_rc[t] = 0;
       __syncthreads();
     }
-    unsigned ps[4] = {0, 0, 0, 0};
+    unsigned ps[kN];
+#pragma unroll
+    for (int q = 0; q < kN; ++q) ps[q] = 0;
+    // one row's cells of this thread: per-bin partials, and (kRows) the warp's share of the row total into shared memory
+    auto take = [&](const typename C::Raw& v, int64_t row) {
+      int hh[kN];
+      C::hund(v, esc, row, j0, hh);
+      unsigned hs = 0;
+      int ks = 0;
+#pragma unroll
+      for (int q = 0; q < kN; ++q) {
+        ps[q] += hh[q];
+        const int k = hh[q] > 0;
+        c[q] += k;
+        hs += (unsigned)hh[q];
+        ks += k;
+      }
+      if (kRows) {  // 32 lanes x kN bins x h < 2^22 fit 32 bits
+        const unsigned rs = __reduce_add_sync(0xffffffffu, hs);
+        const int rc = __reduce_add_sync(0xffffffffu, ks);
+        if (lane0 && rc) row_partial(&s_lo[row - base], &s_hi[row - base], &s_rc[row - base], rs, rc);
+      }
+    };
     int64_t i = base;
     for (; i + 8 <= lim; i += 8) {
       typename C::Raw v[8];
@@ -142,37 +196,15 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const T* __restrict__ dept
       for (int u = 0; u < 8; ++u) v[u] = live ? C::load(p + u * ld) : zero4;
       p += 8 * ld;
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        int hh[4];
-        C::hund(v[u], esc, i + u, j0, hh);
-        const int h0 = hh[0], h1 = hh[1], h2 = hh[2], h3 = hh[3];
-        ps[0] += h0; ps[1] += h1; ps[2] += h2; ps[3] += h3;
-        const int k0 = h0 > 0, k1 = h1 > 0, k2 = h2 > 0, k3 = h3 > 0;
-        c[0] += k0; c[1] += k1; c[2] += k2; c[3] += k3;
-        if (kRows) {  // 128 bins x h < 2^22 fit 32 bits
-          const unsigned rs = __reduce_add_sync(0xffffffffu, (unsigned)(h0 + h1) + (unsigned)(h2 + h3));
-          const int rc = __reduce_add_sync(0xffffffffu, (k0 + k1) + (k2 + k3));
-          if (lane0 && rc) row_partial(&s_lo[i + u - base], &s_hi[i + u - base], &s_rc[i + u - base], rs, rc);
-        }
-      }
+      for (int u = 0; u < 8; ++u) take(v[u], i + u);
     }
     for (; i < lim; ++i) {
       const typename C::Raw v = live ? C::load(p) : zero4;
       p += ld;
-      int hh[4];
-      C::hund(v, esc, i, j0, hh);
-      const int h0 = hh[0], h1 = hh[1], h2 = hh[2], h3 = hh[3];
-      ps[0] += h0; ps[1] += h1; ps[2] += h2; ps[3] += h3;
-      const int k0 = h0 > 0, k1 = h1 > 0, k2 = h2 > 0, k3 = h3 > 0;
-      c[0] += k0; c[1] += k1; c[2] += k2; c[3] += k3;
-      if (kRows) {
-        const unsigned rs = __reduce_add_sync(0xffffffffu, (unsigned)(h0 + h1) + (unsigned)(h2 + h3));
-        const int rc = __reduce_add_sync(0xffffffffu, (k0 + k1) + (k2 + k3));
-        if (lane0 && rc) row_partial(&s_lo[i - base], &s_hi[i - base], &s_rc[i - base], rs, rc);
-      }
+      take(v, i);
     }
 #pragma unroll
-    for (int q = 0; q < 4; ++q) s[q] += ps[q];
+    for (int q = 0; q < kN; ++q) s[q] += ps[q];
     if (kRows) {
       __syncthreads();
       for (int t = threadIdx.x; t < (int)(lim - base); t += kThreads) {
@@ -186,7 +218,7 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const T* __restrict__ dept
   }
   if (!live) return;
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
+  for (int q = 0; q < kN; ++q) {
     if (j0 + q < b) {
       if (gridDim.y == 1) {
         colsum[j0 + q] = s[q];
@@ -475,66 +507,61 @@ __global__ void __launch_bounds__(kThreads) k_col_norm(const T* __restrict__ dep
                                                        const uint8_t* __restrict__ valid,
                                                        const double* __restrict__ row_factor,
                                                        double* __restrict__ out_sd, double* __restrict__ out_sd2) {
-  const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4;
+  using C = Wide<T>;
+  constexpr int kN = C::kN;
+  const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * kN;
   if (j0 >= b) return;
-  bool ok[4];
+  bool ok[kN];
   bool any = false;
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
+  for (int q = 0; q < kN; ++q) {
     ok[q] = (j0 + q < b) && valid[j0 + q];
     any |= ok[q];
   }
-  double s1[4] = {0, 0, 0, 0}, s2[4] = {0, 0, 0, 0};
+  double s1[kN], s2[kN];
+#pragma unroll
+  for (int q = 0; q < kN; ++q) s1[q] = 0.0, s2[q] = 0.0;
   if (any) {
     const int64_t r0 = (int64_t)blockIdx.y * rows_per_slab;
     const int64_t r1 = min(n, r0 + rows_per_slab);
-    using C = Cells<T>;
-    constexpr int kU = sizeof(T) == 2 ? 8 : 4;  // rows in flight: the 2-byte cells need twice the loads for the same bytes
-    const T* p = depth + r0 * ld + j0;
-    int64_t i = r0;
-    for (; i + kU <= r1; i += kU) {
-      typename C::Raw v[kU];
-      double f[kU];
+    // rows are taken strictly in order per bin, whatever the storage: sd / sd2 are bit-identical for fp32 and uint16
+    auto take = [&](const typename C::Raw& v, double f, int64_t row) {
+      int h[kN];
+      C::hund(v, esc, row, j0, h);
 #pragma unroll
-      for (int u = 0; u < kU; ++u) {
-        v[u] = C::load(p + u * ld);
-        f[u] = row_factor[i + u];
-      }
-      p += kU * ld;
-#pragma unroll
-      for (int u = 0; u < kU; ++u) {
-        int h[4];
-        C::hund(v[u], esc, i + u, j0, h);
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          if (h[q] > 0) {  // a row with no valid bin has f = NaN but then also no present cell
-            const double d = fma(u32_to_double(h[q]), f[u], -1.0);
-            s1[q] += d;
-            s2[q] = fma(d, d, s2[q]);
-          }
-        }
-      }
-    }
-    for (; i < r1; ++i) {
-      const typename C::Raw v = C::load(p);
-      const double f = row_factor[i];
-      p += ld;
-      int h[4];
-      C::hund(v, esc, i, j0, h);
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        if (h[q] > 0) {
+      for (int q = 0; q < kN; ++q) {
+        if (h[q] > 0) {  // a row with no valid bin has f = NaN but then also no present cell
           const double d = fma(u32_to_double(h[q]), f, -1.0);
           s1[q] += d;
           s2[q] = fma(d, d, s2[q]);
         }
       }
+    };
+    const T* p = depth + r0 * ld + j0;
+    int64_t i = r0;
+    for (; i + 4 <= r1; i += 4) {
+      typename C::Raw v[4];
+      double f[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        v[u] = C::load(p + u * ld);
+        f[u] = row_factor[i + u];
+      }
+      p += 4 * ld;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) take(v[u], f[u], i + u);
+    }
+    for (; i < r1; ++i) {
+      const typename C::Raw v = C::load(p);
+      const double f = row_factor[i];
+      p += ld;
+      take(v, f, i);
     }
   }
   double* o1 = out_sd + (int64_t)blockIdx.y * b;
   double* o2 = out_sd2 + (int64_t)blockIdx.y * b;
 #pragma unroll
-  for (int q = 0; q < 4; ++q) {
+  for (int q = 0; q < kN; ++q) {
     if (j0 + q < b) {
       o1[j0 + q] = ok[q] ? s1[q] : 0.0;
       o2[j0 + q] = ok[q] ? s2[q] : 0.0;
@@ -912,10 +939,11 @@ extern "C" int gridb200_col_raw_stats(const float* depth, int64_t n, int64_t b, 
 template <typename T>
 static int col_row_raw_impl(const T* depth, const Esc& esc, int64_t n, int64_t b, int64_t ld, int64_t* colsum,
                             int32_t* colcnt, int64_t* rowsum_all, int32_t* rowcnt_all, void* stream) {
-  if (int e = check_matrix(depth, n, b, ld, 4 * (int)sizeof(T))) return e;
+  if (int e = check_matrix(depth, n, b, ld, 16)) return e;
+  G2_REQUIRE(ld % Wide<T>::kN == 0, GRIDB200_EINVAL, "leading dimension must be a multiple of %d", Wide<T>::kN);
   G2_REQUIRE(colsum && colcnt && rowsum_all && rowcnt_all, GRIDB200_EINVAL, "null output");
   cudaStream_t st = as_stream(stream);
-  const int64_t cb = (b + kColsPerBlock - 1) / kColsPerBlock;
+  const int64_t cb = (b + kThreads * Wide<T>::kN - 1) / (kThreads * Wide<T>::kN);
   const int64_t rows = pick_row_slab(n, cb, 64);
   const int64_t slabs = (n + rows - 1) / rows;
   G2_REQUIRE(slabs <= 65535, GRIDB200_EINVAL, "too many row slabs");
@@ -1052,11 +1080,12 @@ extern "C" size_t gridb200_col_norm_stats_ws_bytes(int64_t n, int64_t b) {
 template <typename T>
 static int col_norm_impl(const T* depth, const Esc& esc, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
                          const double* row_factor, double* sd, double* sd2, void* ws, size_t ws_bytes, void* stream) {
-  if (int e = check_matrix(depth, n, b, ld, 4 * (int)sizeof(T))) return e;
+  if (int e = check_matrix(depth, n, b, ld, 16)) return e;
+  G2_REQUIRE(ld % Wide<T>::kN == 0, GRIDB200_EINVAL, "leading dimension must be a multiple of %d", Wide<T>::kN);
   G2_REQUIRE(valid && row_factor && sd && sd2, GRIDB200_EINVAL, "null argument");
   cudaStream_t st = as_stream(stream);
-  const int64_t cb = (b + kColsPerBlock - 1) / kColsPerBlock;
-  const int64_t rows = col_norm_slab_rows(n, b);
+  const int64_t cb = (b + kThreads * Wide<T>::kN - 1) / (kThreads * Wide<T>::kN);
+  const int64_t rows = col_norm_slab_rows(n, b);  // (the row slabs depend on b only: the same partial sums for either storage)
   const int64_t slabs = (n + rows - 1) / rows;
   G2_REQUIRE(slabs <= 65535, GRIDB200_EINVAL, "too many row slabs");
   if (slabs == 1) {

@@ -283,6 +283,47 @@ __global__ void k_keep(const double* __restrict__ rq, const int32_t* __restrict_
 
 __global__ void k_ruse_to_double(const unsigned long long* r_use, double* info2) { info2[0] = (double)*r_use; }
 
+// kind 1 with frac_r >= 1: the wanted rank is int(Rw * (1 - frac_r)) clamped at 0 -- the MINIMUM of the finite values (the
+// reference's default, find_neighbors.py:160-163).  One pass instead of the eight of the radix select.
+__global__ void k_sel_min(const double* __restrict__ vals, int64_t n, SelState* st, unsigned long long* __restrict__ minkey) {
+  unsigned long long m = ~0ULL;
+  int c = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const double v = vals[i];
+    if (isfinite(v)) {
+      const unsigned long long k = key_of(v);
+      m = k < m ? k : m;
+      ++c;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long y = __shfl_xor_sync(0xffffffffu, m, o);
+    m = y < m ? y : m;
+  }
+  c = warp_sum(c);
+  if ((threadIdx.x & 31) == 0 && c) {
+    atomicMin(minkey, m);
+    atomicAdd(&st->count, (unsigned long long)c);
+  }
+}
+__global__ void k_sel_min_finish(SelState* st, const unsigned long long* minkey) {
+  st->error = 0;
+  st->ntargets = st->count ? 1 : 0;
+  if (st->count) st->value[0] = value_of(*minkey);
+}
+
+static int run_select_min(const double* vals, int64_t n, SelState* st, unsigned* hist, cudaStream_t stream) {
+  G2_CUDA(cudaMemsetAsync(st, 0, kStateBytes, stream));
+  G2_CUDA(cudaMemsetAsync(hist, 0xFF, sizeof(unsigned long long), stream));  // the running minimum key lives in hist[0..1]
+  const int blocks = (int)std::min<int64_t>((n + kSelThreads * 8 - 1) / (kSelThreads * 8), (int64_t)kSMs * 4);
+  k_sel_min<<<blocks, kSelThreads, 0, stream>>>(vals, n, st, reinterpret_cast<unsigned long long*>(hist));
+  G2_LAUNCHED();
+  k_sel_min_finish<<<1, 1, 0, stream>>>(st, reinterpret_cast<const unsigned long long*>(hist));
+  G2_LAUNCHED();
+  return 0;
+}
+
 static int run_select(const double* vals, int64_t n, int mode, int kind, double param, const double* info,
                       SelState* st, unsigned* hist, cudaStream_t stream) {
   G2_CUDA(cudaMemsetAsync(st, 0, kStateBytes + kHistBytes, stream));
@@ -352,7 +393,11 @@ extern "C" int gridb200_knn_col_filter(const double* ratio, const int32_t* sel_p
   double* rq = reinterpret_cast<double*>(after + 256);
   k_round3<<<(unsigned)((b + 255) / 256), 256, 0, st>>>(ratio, sel_pos, b, rq);
   G2_LAUNCHED();
-  if (int e = run_select(rq, b, /*mode=*/1, /*kind=*/1, frac_r, info, state, hist, st)) return e;
+  if (frac_r >= 1.0) {
+    if (int e = run_select_min(rq, b, state, hist, st)) return e;
+  } else if (int e = run_select(rq, b, /*mode=*/1, /*kind=*/1, frac_r, info, state, hist, st)) {
+    return e;
+  }
   G2_CUDA(cudaMemsetAsync(r_use, 0, sizeof(unsigned long long), st));
   k_keep<<<(unsigned)((b + 255) / 256), 256, 0, st>>>(rq, sel_pos, b, state, sigma2_max, keep, r_use, info2);
   G2_LAUNCHED();

@@ -49,7 +49,7 @@ def test_u16_storage_gives_bit_identical_step4(eng, n, b):
     for t, (i, j) in enumerate(cells):
         depth[i, j] = [655.35, 700.0, 1234.56, 41000.0, 655.36][t % 5]          # need the escape table
     depth[3, 5], depth[3, 6] = 655.34, 0.0                                       # last value that fits; an absent cell
-    depth[:, 40:44] *= 4.0                                                        # bins that FAIL the depth filter (mean > 100)...
+    depth[:, 40:44] *= 8.0                                                        # bins that FAIL the depth filter (mean > 100)...
     depth[:, 40:44] = torch.round(depth[:, 40:44] * 100) / 100
     depth[7, 41], depth[8, 43] = 900.0, 2000.5                                   # ... with escapes inside them
     want = len({c for c in cells} | {(7, 41), (8, 43)})
