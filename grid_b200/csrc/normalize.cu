@@ -52,6 +52,7 @@ struct Cells<float> {
   static __device__ __forceinline__ void hund(const Raw& v, const Esc&, int64_t, int64_t, int (&h)[4]) {
     h[0] = depth_hundredths(v.x), h[1] = depth_hundredths(v.y), h[2] = depth_hundredths(v.z), h[3] = depth_hundredths(v.w);
   }
+  static __device__ __forceinline__ void hund_exact(const Raw& v, const Esc& e, int64_t r, int64_t c, int (&h)[4]) { hund(v, e, r, c, h); }
   static __device__ __forceinline__ int hund1(const float* p, const Esc&, int64_t, int64_t) { return depth_hundredths(*p); }
 };
 
@@ -66,8 +67,13 @@ struct Cells<uint16_t> {
     return r;
   }
   static __device__ __forceinline__ Raw load_cached(const uint16_t* p) { return *reinterpret_cast<const uint2*>(p); }
-  static __device__ __forceinline__ void hund(const Raw& v, const Esc& e, int64_t row, int64_t col, int (&h)[4]) {
+  // the streaming passes take the CODES (an escape cell counts as 65535) and small patch kernels put the true values in
+  // afterwards (k_esc_*): any escape test inside the hot loops cost two instructions per cell and forty registers
+  static __device__ __forceinline__ void hund(const Raw& v, const Esc&, int64_t, int64_t, int (&h)[4]) {
     h[0] = (int)(v.x & 0xFFFFu), h[1] = (int)(v.x >> 16), h[2] = (int)(v.y & 0xFFFFu), h[3] = (int)(v.y >> 16);
+  }
+  static __device__ __forceinline__ void hund_exact(const Raw& v, const Esc& e, int64_t row, int64_t col, int (&h)[4]) {
+    hund(v, e, row, col, h);
     if (__vcmpeq2(v.x, 0xFFFFFFFFu) | __vcmpeq2(v.y, 0xFFFFFFFFu)) {  // some cell of the four is an escape: rare
 #pragma unroll
       for (int q = 0; q < 4; ++q)
@@ -107,15 +113,10 @@ struct Wide<uint16_t> {
     asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
     return r;
   }
-  static __device__ __forceinline__ void hund(const Raw& v, const Esc& e, int64_t row, int64_t col, int (&h)[8]) {
+  static __device__ __forceinline__ void hund(const Raw& v, const Esc&, int64_t, int64_t, int (&h)[8]) {
     const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-    for (int t = 0; t < 4; ++t) h[2 * t] = (int)(w[t] & 0xFFFFu), h[2 * t + 1] = (int)(w[t] >> 16);
-    if ((__vcmpeq2(v.x, 0xFFFFFFFFu) | __vcmpeq2(v.y, 0xFFFFFFFFu)) | (__vcmpeq2(v.z, 0xFFFFFFFFu) | __vcmpeq2(v.w, 0xFFFFFFFFu))) {
-#pragma unroll
-      for (int q = 0; q < 8; ++q)
-        if (h[q] == 0xFFFF) h[q] = esc_lookup(e, row, col + q);
-    }
+    for (int t = 0; t < 4; ++t) h[2 * t] = (int)(w[t] & 0xFFFFu), h[2 * t + 1] = (int)(w[t] >> 16);  // codes (see Cells)
   }
 };
 
@@ -289,7 +290,7 @@ __global__ void __launch_bounds__(kThreads) k_row_stats(const T* __restrict__ de
 #pragma unroll
   for (int u = 0; u < kRowUnroll; ++u) {
     int hh[4];
-    C::hund(v[u], esc, row_base + row, c0 + ((int64_t)u * kThreads + threadIdx.x) * 4, hh);
+    C::hund_exact(v[u], esc, row_base + row, c0 + ((int64_t)u * kThreads + threadIdx.x) * 4, hh);
     const int h0 = (m[u] & 0x000000ffu) ? hh[0] : 0;
     const int h1 = (m[u] & 0x0000ff00u) ? hh[1] : 0;
     const int h2 = (m[u] & 0x00ff0000u) ? hh[2] : 0;
@@ -897,6 +898,92 @@ __global__ void __launch_bounds__(kThreads) k_knn_prepare(const int16_t* __restr
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Escape patches of the 2-byte matrix.  The streaming kernels above took every escape cell as the code 65535; these small
+// kernels (one thread or warp per escape cell / column) put the true hundredths H in, so that every result equals the
+// fp32 path's bit for bit.
+// ---------------------------------------------------------------------------------------------------------
+// K1 patch: integer sums, exact in any order
+__global__ void k_esc_raw(const Esc esc, int64_t n, unsigned long long* __restrict__ colsum,
+                          unsigned long long* __restrict__ rowsum_all) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= esc.n) return;
+  const long long row = esc.key[e] / esc.b - esc.row0, col = esc.key[e] % esc.b;
+  if (row < 0 || row >= n) return;
+  const unsigned long long extra = (unsigned long long)(esc.h[e] - 65535);
+  atomicAdd(&colsum[col], extra);
+  atomicAdd(&rowsum_all[row], extra);
+}
+
+// K4 patch: the bins that hold an escape are summed again, rows strictly in order (as the streaming kernel does per bin),
+// one warp per (bin, row slab): 32 rows are fetched at once, lane 0 adds them one after the other.
+__global__ void k_esc_col_norm(const uint16_t* __restrict__ depth, const Esc esc, const int* __restrict__ cols, int64_t ncols,
+                               int64_t n, int64_t b, int64_t ld, int64_t rows_per_slab, const uint8_t* __restrict__ valid,
+                               const double* __restrict__ row_factor, double* __restrict__ out_sd,
+                               double* __restrict__ out_sd2) {
+  const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= ncols) return;
+  const int64_t j = cols[w];
+  if (j < 0 || j >= b || !valid[j]) return;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_slab, r1 = min(n, r0 + rows_per_slab);
+  double s1 = 0.0, s2 = 0.0;
+  for (int64_t base = r0; base < r1; base += 32) {
+    const int64_t i = base + lane;
+    int h = 0;
+    double f = 0.0;
+    if (i < r1) {
+      h = Cells<uint16_t>::hund1(depth + i * ld + j, esc, i, j);
+      f = row_factor[i];
+    }
+    const int cnt = (int)min((int64_t)32, r1 - base);
+    for (int t = 0; t < cnt; ++t) {
+      const int ht = __shfl_sync(0xffffffffu, h, t);
+      const double ft = __shfl_sync(0xffffffffu, f, t);
+      if (ht > 0) {
+        const double d = fma(u32_to_double((unsigned)ht), ft, -1.0);
+        s1 += d;
+        s2 = fma(d, d, s2);
+      }
+    }
+  }
+  if (lane == 0) {
+    out_sd[(int64_t)blockIdx.y * b + j] = s1;
+    out_sd2[(int64_t)blockIdx.y * b + j] = s2;
+  }
+}
+
+// K7 patch: one thread per escape cell recomputes the cell's code from H (the exact quantiser the rare path uses)
+__global__ void k_esc_transform(const Esc esc, int64_t n, int64_t b, const double* __restrict__ row_factor,
+                                const double* __restrict__ mu, const int32_t* __restrict__ sel_pos,
+                                const uint8_t* __restrict__ keep, const double* __restrict__ info, int zclip,
+                                int16_t* __restrict__ zq, int64_t ldq, __half* __restrict__ zh, int64_t ldh,
+                                unsigned long long* __restrict__ norms, unsigned long long* __restrict__ sat) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= esc.n) return;
+  const long long row = esc.key[e] / esc.b - esc.row0, col = esc.key[e] % esc.b;
+  if (row < 0 || row >= n || col >= b) return;
+  const int pos = sel_pos[col];
+  if (pos < 0) return;
+  const double f = row_factor[row];
+  if (!(f == f)) return;
+  const double m = mu[col], a100 = 100.0 * (info[0] / sqrt(m));
+  unsigned long long sat_true = 0, sat_coded = 0;
+  const double w_true = fma(u32_to_double((unsigned)esc.h[e]), f, -m), w_coded = fma(u32_to_double(65535u), f, -m);
+  const int z_true = quantise_slow(w_true, a100, nullptr), z_coded = quantise_slow(w_coded, a100, nullptr);
+  sat_true = fabs(round_even(w_true * a100)) > 32766.0, sat_coded = fabs(round_even(w_coded * a100)) > 32766.0;
+  if (zq) zq[row * ldq + pos] = (int16_t)((z_true == 0 && w_true * a100 < 0.0) ? -32767 : z_true);
+  if (zh) {
+    const int zc = (keep ? keep[col] != 0 : true) ? zclip : 0;
+    const int c_true = max(-zc, min(zc, z_true)), c_coded = max(-zc, min(zc, z_coded));
+    if (c_true != c_coded) {
+      zh[(((int64_t)pos >> 6) * ldh + row) * 64 + (pos & 63)] = __int2half_rn(c_true);
+      atomicAdd(&norms[row], (unsigned long long)(long long)(c_true * c_true - c_coded * c_coded));
+    }
+  }
+  if (sat && sat_true > sat_coded) atomicAdd(sat, 1ULL);
+}
+
 }  // namespace g2
 
 using namespace g2;
@@ -957,6 +1044,11 @@ static int col_row_raw_impl(const T* depth, const Esc& esc, int64_t n, int64_t b
       depth, esc, n, b, ld, rows, reinterpret_cast<unsigned long long*>(colsum), colcnt,
       reinterpret_cast<unsigned long long*>(rowsum_all), rowcnt_all);
   G2_LAUNCHED();
+  if (Cells<T>::kEsc && esc.n > 0) {
+    k_esc_raw<<<(unsigned)((esc.n + 255) / 256), 256, 0, st>>>(esc, n, reinterpret_cast<unsigned long long*>(colsum),
+                                                                reinterpret_cast<unsigned long long*>(rowsum_all));
+    G2_LAUNCHED();
+  }
   return 0;
 }
 
@@ -1078,8 +1170,26 @@ extern "C" size_t gridb200_col_norm_stats_ws_bytes(int64_t n, int64_t b) {
 }
 
 template <typename T>
-static int col_norm_impl(const T* depth, const Esc& esc, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
-                         const double* row_factor, double* sd, double* sd2, void* ws, size_t ws_bytes, void* stream) {
+static int col_norm_patch(const T*, const Esc&, const int32_t*, int64_t, int64_t, int64_t, int64_t, int64_t, int64_t,
+                          const uint8_t*, const double*, double*, double*, cudaStream_t) {
+  return 0;
+}
+template <>
+int col_norm_patch<uint16_t>(const uint16_t* depth, const Esc& esc, const int32_t* cols, int64_t ncols, int64_t n, int64_t b,
+                             int64_t ld, int64_t rows, int64_t slabs, const uint8_t* valid, const double* row_factor,
+                             double* o1, double* o2, cudaStream_t st) {
+  if (esc.n == 0) return 0;
+  G2_REQUIRE(cols && ncols > 0, GRIDB200_EINVAL, "escape cells need the list of their bins (esc_cols)");
+  k_esc_col_norm<<<dim3((unsigned)((ncols * 32 + 127) / 128), (unsigned)slabs), 128, 0, st>>>(
+      depth, esc, cols, ncols, n, b, ld, rows, valid, row_factor, o1, o2);
+  G2_LAUNCHED();
+  return 0;
+}
+
+template <typename T>
+static int col_norm_impl(const T* depth, const Esc& esc, const int32_t* esc_cols, int64_t n_esc_cols, int64_t n, int64_t b,
+                         int64_t ld, const uint8_t* valid, const double* row_factor, double* sd, double* sd2, void* ws,
+                         size_t ws_bytes, void* stream) {
   if (int e = check_matrix(depth, n, b, ld, 16)) return e;
   G2_REQUIRE(ld % Wide<T>::kN == 0, GRIDB200_EINVAL, "leading dimension must be a multiple of %d", Wide<T>::kN);
   G2_REQUIRE(valid && row_factor && sd && sd2, GRIDB200_EINVAL, "null argument");
@@ -1091,6 +1201,7 @@ static int col_norm_impl(const T* depth, const Esc& esc, int64_t n, int64_t b, i
   if (slabs == 1) {
     k_col_norm<T><<<dim3((unsigned)cb, 1), kThreads, 0, st>>>(depth, esc, n, b, ld, rows, valid, row_factor, sd, sd2);
     G2_LAUNCHED();
+    if (int e = col_norm_patch<T>(depth, esc, esc_cols, n_esc_cols, n, b, ld, rows, 1, valid, row_factor, sd, sd2, st)) return e;
   } else {
     G2_REQUIRE(ws && ws_bytes >= gridb200_col_norm_stats_ws_bytes(n, b), GRIDB200_EINVAL,
                "workspace too small: need %zu bytes", gridb200_col_norm_stats_ws_bytes(n, b));
@@ -1099,6 +1210,7 @@ static int col_norm_impl(const T* depth, const Esc& esc, int64_t n, int64_t b, i
     k_col_norm<T><<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(depth, esc, n, b, ld, rows, valid, row_factor,
                                                                              p1, p2);
     G2_LAUNCHED();
+    if (int e = col_norm_patch<T>(depth, esc, esc_cols, n_esc_cols, n, b, ld, rows, slabs, valid, row_factor, p1, p2, st)) return e;
     k_reduce_slabs<<<(unsigned)((b + 255) / 256), 256, 0, st>>>(p1, p2, b, (int)slabs, sd, sd2);
     G2_LAUNCHED();
   }
@@ -1108,7 +1220,7 @@ static int col_norm_impl(const T* depth, const Esc& esc, int64_t n, int64_t b, i
 extern "C" int gridb200_col_norm_stats(const float* depth, int64_t n, int64_t b, int64_t ld, const uint8_t* valid,
                                        const double* row_factor, double* sd, double* sd2, void* ws,
                                        size_t ws_bytes, void* stream) {
-  return col_norm_impl<float>(depth, Esc{}, n, b, ld, valid, row_factor, sd, sd2, ws, ws_bytes, stream);
+  return col_norm_impl<float>(depth, Esc{}, nullptr, 0, n, b, ld, valid, row_factor, sd, sd2, ws, ws_bytes, stream);
 }
 
 extern "C" int gridb200_col_finalize(const double* sd, const double* sd2, const int32_t* colcnt,
@@ -1153,6 +1265,11 @@ static int transform_impl(const T* depth, const Esc& esc, int64_t n, int64_t b, 
     k_transform<false, true, T><<<grid, kThreads, 0, st>>>(depth, esc, n, b, ld, row_factor, mu, sel_pos, keep, info, zclip,
                                                            zq, ldq, zhp, ldh, np, zq ? nullptr : sat);
   G2_LAUNCHED();
+  if (Cells<T>::kEsc && esc.n > 0) {
+    k_esc_transform<<<(unsigned)((esc.n + 255) / 256), 256, 0, st>>>(esc, n, b, row_factor, mu, sel_pos, keep, info, zclip, zq,
+                                                                      ldq, zhp, ldh, np, sat);
+    G2_LAUNCHED();
+  }
   return 0;
 }
 
@@ -1196,11 +1313,11 @@ extern "C" int gridb200_row_means_exact_u16(const uint16_t* depth, int64_t n, in
 
 extern "C" int gridb200_col_norm_stats_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld, const int64_t* esc_key,
                                            const int32_t* esc_h, int64_t n_esc, int64_t esc_row0, int64_t esc_b,
-                                           const uint8_t* valid, const double* row_factor, double* sd, double* sd2,
+                                           const int32_t* esc_cols, int64_t n_esc_cols, const uint8_t* valid, const double* row_factor, double* sd, double* sd2,
                                            void* ws, size_t ws_bytes, void* stream) {
   Esc esc;
   if (int e = make_esc(esc, esc_key, esc_h, n_esc, esc_row0, esc_b)) return e;
-  return col_norm_impl<uint16_t>(depth, esc, n, b, ld, valid, row_factor, sd, sd2, ws, ws_bytes, stream);
+  return col_norm_impl<uint16_t>(depth, esc, esc_cols, n_esc_cols, n, b, ld, valid, row_factor, sd, sd2, ws, ws_bytes, stream);
 }
 
 extern "C" int gridb200_transform_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld, const int64_t* esc_key,

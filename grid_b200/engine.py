@@ -130,6 +130,7 @@ class Depth16:
     esc_h: torch.Tensor | None = None
     row0: int = 0
     esc_b: int = 0
+    esc_cols: torch.Tensor | None = None   # distinct bins (int32, local) that hold an escape cell
 
     @property
     def device(self):
@@ -150,12 +151,13 @@ class Depth16:
         """Escape list as PackedDepth carries it (cell = global_row * b + bin, fp32 depth) -> the kernels' sorted table."""
         dev = self.codes.device
         if cell.numel() == 0:
-            self.esc_key = self.esc_h = None
+            self.esc_key = self.esc_h = self.esc_cols = None
             return
         hundred = torch.full((1,), 100.0, dtype=torch.float64)
         h = torch.round(val.cpu().double() * hundred).clamp(max=(1 << 22) - 1).to(torch.int32)
         key, order = torch.sort(cell.cpu().to(torch.int64))
         self.esc_key, self.esc_h = key.to(dev), h[order].to(dev)
+        self.esc_cols = torch.unique(key % (self.esc_b or self.b)).to(torch.int32).to(dev)
 
 
 def check_depth(depth, b: int) -> tuple[int, int]:
@@ -172,8 +174,11 @@ def check_depth(depth, b: int) -> tuple[int, int]:
 def _dcall(name: str, depth, n: int, b: int, ld: int, *rest) -> None:
     """call(name, depth, n, b, ld, ...) for either storage type of the depth matrix."""
     if isinstance(depth, Depth16):
+        more = ()
+        if name == "gridb200_col_norm_stats":  # its patch kernel re-sums the bins that hold an escape
+            more = (ptr(depth.esc_cols), 0 if depth.esc_cols is None else int(depth.esc_cols.numel()))
         call(name + "_u16", ptr(depth.codes), n, b, ld, ptr(depth.esc_key), ptr(depth.esc_h), depth.n_esc, depth.row0,
-             depth.esc_b or depth.b, *rest)
+             depth.esc_b or depth.b, *more, *rest)
     else:
         call(name, ptr(depth), n, b, ld, *rest)
 
@@ -876,6 +881,7 @@ def upload_packed16(packed: PackedDepth, out: Depth16, chunk_rows: int = 128) ->
             codes.view(torch.int16).view(-1)[(k // b) * ldo + (k % b)] = out.esc_h[fits].to(torch.int16)   # (wraps: bit pattern)
             keep = ~fits
             out.esc_key, out.esc_h = (out.esc_key[keep], out.esc_h[keep]) if bool(keep.any()) else (None, None)
+            out.esc_cols = None if out.esc_key is None else torch.unique(out.esc_key % b).to(torch.int32)
     return out
 
 

@@ -323,8 +323,10 @@ GRIDB200_API int gridb200_depth_unpack_bits(const uint32_t* src, int64_t n, int6
  * uint16 hundredths, 0 = absent, rows ld elements apart (ld % 4 == 0, 8-byte aligned rows): the three step-4 passes then
  * read half the bytes of the fp32 matrix.  The code 0xFFFF is an escape: the cell's true hundredths (depth >= 655.35;
  * < 2^22 like everywhere) are in a table sorted by key (esc_row0 + row) * esc_b + bin -- esc_key [n_esc] ascending,
- * esc_h [n_esc] -- which the kernels search only when they meet the code.  Same integers, so every result is
- * bit-identical to the fp32 entry point of the same name (same reference lines).  gridb200_depth_pack_u16 produces the
+ * esc_h [n_esc].  The streaming kernels take an escape cell as 65535 and small patch kernels (one thread or warp per
+ * escape cell / bin; gridb200_col_norm_stats_u16 also wants esc_cols [n_esc_cols], the distinct bins of the table)
+ * put the true values in, so every result is bit-identical to the fp32 entry point of the same name (same reference
+ * lines) and the hot loops carry no escape test.  gridb200_depth_pack_u16 produces the
  * matrix from fp32, gridb200_depth_unpack_bits_u16 from the bit-packed host format (its escape code becomes 0xFFFF). */
 GRIDB200_API int gridb200_depth_unpack_bits_u16(const uint32_t* src, int64_t n, int64_t b, int64_t ldw, int32_t bits,
                                    uint16_t* out, int64_t ldo, void* stream);
@@ -343,8 +345,8 @@ GRIDB200_API int gridb200_row_means_exact_u16(const uint16_t* depth, int64_t n, 
                                  double* raw_mean, double* scale_q, void* stream);
 GRIDB200_API int gridb200_col_norm_stats_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld,
                                 const int64_t* esc_key, const int32_t* esc_h, int64_t n_esc, int64_t esc_row0,
-                                int64_t esc_b, const uint8_t* valid, const double* row_factor, double* sd, double* sd2,
-                                void* ws, size_t ws_bytes, void* stream);
+                                int64_t esc_b, const int32_t* esc_cols, int64_t n_esc_cols, const uint8_t* valid,
+                                const double* row_factor, double* sd, double* sd2, void* ws, size_t ws_bytes, void* stream);
 GRIDB200_API int gridb200_transform_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld,
                            const int64_t* esc_key, const int32_t* esc_h, int64_t n_esc, int64_t esc_row0, int64_t esc_b,
                            const double* row_factor, const double* mu, const int32_t* sel_pos, const uint8_t* keep,
