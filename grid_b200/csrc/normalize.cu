@@ -232,6 +232,107 @@ __global__ void __launch_bounds__(kThreads) k_col_raw(const T* __restrict__ dept
   }
 }
 
+// K1 on the 2-byte matrix.  Two cells per 32-bit word, never unpacked: run through the generic kernel the pass was
+// ALU-bound at 9 instructions per cell (ncu: ALU pipe 70 %, 96 registers, 4.1 ms against a 2.9 ms HBM floor).  Per word
+// here: a packed 16-bit min against 1 (the two presence bits), one packed add for the counts (512 rows fit a half),
+// one dot-product-accumulate for the low half's sum, one shift-add for the high half's and one dot-product-accumulate
+// for the row total.  The row totals of a warp go to lane (row % 32) and are stored 32 rows at a time into the warp's
+// own shared-memory column -- no shared atomics; the eight columns are summed once per 512-row chunk.  Escape cells
+// count as 65535 here; k_esc_raw adds the rest afterwards.
+__global__ void __launch_bounds__(kThreads, 3) k_col_raw_u16(const uint16_t* __restrict__ depth, int64_t n, int64_t b,
+                                                             int64_t ld, int64_t rows_per_slab,
+                                                             unsigned long long* __restrict__ colsum,
+                                                             int* __restrict__ colcnt,
+                                                             unsigned long long* __restrict__ rowsum_all,
+                                                             int* __restrict__ rowcnt_all) {
+  constexpr int kWarps = kThreads / 32;
+  __shared__ uint2 s_wp[kWarps * 512];  // (row total, packed presence count) per warp and row of the chunk
+  using C = Wide<uint16_t>;
+  const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 8;
+  const bool live = j0 < b;  // dead threads of the last block stay for the collectives and barriers (they add zeros)
+  const int lane = threadIdx.x & 31;
+  uint2* const mycol = s_wp + (threadIdx.x >> 5) * 512;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_slab;
+  const int64_t r1 = min(n, r0 + rows_per_slab);
+  unsigned long long s[8];
+  int c[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) s[q] = 0, c[q] = 0;
+  const uint16_t* p = depth + r0 * ld + (live ? j0 : 0);
+  const uint4 zero4 = C::zero();
+  for (int64_t base = r0; base < r1; base += 512) {  // 32-bit sums and 16-bit counts cannot overflow within 512 rows
+    const int rows = (int)(r1 - base < 512 ? r1 - base : 512);
+    unsigned ps[8], cp[4];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) ps[q] = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) cp[q] = 0;
+    uint2 mine = make_uint2(0u, 0u);
+    auto take = [&](const uint4& v, int slot) {
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+      unsigned hs = 0, km = 0;
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const unsigned m = __vminu2(w[t], 0x00010001u);
+        cp[t] += m;
+        km += m;
+        ps[2 * t] = __dp2a_lo(w[t], 0x0001u, ps[2 * t]);
+        ps[2 * t + 1] += w[t] >> 16;
+        hs = __dp2a_lo(w[t], 0x0101u, hs);
+      }
+      // 32 lanes x 8 cells x 65535 < 2^24; per half at most 4 present cells per lane, so the packed counts survive the sum
+      const unsigned rs = __reduce_add_sync(0xffffffffu, hs);
+      const unsigned rk = __reduce_add_sync(0xffffffffu, km);
+      if (lane == (slot & 31)) mine = make_uint2(rs, rk);
+    };
+    int i = 0;
+    for (; i + 8 <= rows; i += 8) {
+      uint4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = live ? C::load(p + u * ld) : zero4;
+      p += 8 * ld;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) take(v[u], i + u);
+      if (((i + 8) & 31) == 0) mycol[i + 8 - 32 + lane] = mine;
+    }
+    for (; i < rows; ++i) {
+      const uint4 v = live ? C::load(p) : zero4;
+      p += ld;
+      take(v, i);
+    }
+    if (lane < (rows & 31)) mycol[(rows & ~31) + lane] = mine;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) s[q] += ps[q];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) c[2 * q] += (int)(cp[q] & 0xFFFFu), c[2 * q + 1] += (int)(cp[q] >> 16);
+    __syncthreads();
+    for (int t = threadIdx.x; t < rows; t += kThreads) {
+      unsigned rs = 0, rk = 0;  // 8 warps x 2^24, 8 x 128 per half
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) rs += s_wp[w * 512 + t].x, rk += s_wp[w * 512 + t].y;
+      const int rc = (int)((rk & 0xFFFFu) + (rk >> 16));
+      if (rc) {
+        atomicAdd(&rowsum_all[base + t], (unsigned long long)rs);
+        atomicAdd(&rowcnt_all[base + t], rc);
+      }
+    }
+    __syncthreads();
+  }
+  if (!live) return;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    if (j0 + q < b) {
+      if (gridDim.y == 1) {
+        colsum[j0 + q] = s[q];
+        colcnt[j0 + q] = c[q];
+      } else {
+        atomicAdd(&colsum[j0 + q], s[q]);
+        atomicAdd(&colcnt[j0 + q], c[q]);
+      }
+    }
+  }
+}
+
 __global__ void k_depth_filter(const long long* __restrict__ colsum, const int* __restrict__ colcnt, int64_t b,
                                double lo, double hi, uint8_t* __restrict__ valid) {
   const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -540,17 +641,43 @@ __global__ void __launch_bounds__(kThreads) k_col_norm(const T* __restrict__ dep
     };
     const T* p = depth + r0 * ld + j0;
     int64_t i = r0;
-    for (; i + 4 <= r1; i += 4) {
-      typename C::Raw v[4];
-      double f[4];
+    if (sizeof(T) == 2) {
+      // 2-byte cells: the pass is no longer HBM-bound but latency-bound (ncu: 70 % of the stalls on the loads) unless the
+      // next four rows are already in flight while the current four are summed
+      typename C::Raw v[4], w[4];
+      double f[4], g[4];
+      if (i + 4 <= r1) {
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        v[u] = C::load(p + u * ld);
-        f[u] = row_factor[i + u];
+        for (int u = 0; u < 4; ++u) v[u] = C::load(p + u * ld), f[u] = row_factor[i + u];
+        p += 4 * ld;
       }
-      p += 4 * ld;
+      for (; i + 8 <= r1; i += 4) {
 #pragma unroll
-      for (int u = 0; u < 4; ++u) take(v[u], f[u], i + u);
+        for (int u = 0; u < 4; ++u) w[u] = C::load(p + u * ld), g[u] = row_factor[i + 4 + u];
+        p += 4 * ld;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) take(v[u], f[u], i + u);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = w[u], f[u] = g[u];
+      }
+      if (i + 4 <= r1) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) take(v[u], f[u], i + u);
+        i += 4;
+      }
+    } else {
+      for (; i + 4 <= r1; i += 4) {
+        typename C::Raw v[4];
+        double f[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          v[u] = C::load(p + u * ld);
+          f[u] = row_factor[i + u];
+        }
+        p += 4 * ld;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) take(v[u], f[u], i + u);
+      }
     }
     for (; i < r1; ++i) {
       const typename C::Raw v = C::load(p);
@@ -1040,9 +1167,15 @@ static int col_row_raw_impl(const T* depth, const Esc& esc, int64_t n, int64_t b
   }
   G2_CUDA(cudaMemsetAsync(rowsum_all, 0, n * sizeof(int64_t), st));
   G2_CUDA(cudaMemsetAsync(rowcnt_all, 0, n * sizeof(int32_t), st));
-  k_col_raw<true, T><<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(
-      depth, esc, n, b, ld, rows, reinterpret_cast<unsigned long long*>(colsum), colcnt,
-      reinterpret_cast<unsigned long long*>(rowsum_all), rowcnt_all);
+  if constexpr (sizeof(T) == 2) {
+    k_col_raw_u16<<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(
+        depth, n, b, ld, rows, reinterpret_cast<unsigned long long*>(colsum), colcnt,
+        reinterpret_cast<unsigned long long*>(rowsum_all), rowcnt_all);
+  } else {
+    k_col_raw<true, T><<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(
+        depth, esc, n, b, ld, rows, reinterpret_cast<unsigned long long*>(colsum), colcnt,
+        reinterpret_cast<unsigned long long*>(rowsum_all), rowcnt_all);
+  }
   G2_LAUNCHED();
   if (Cells<T>::kEsc && esc.n > 0) {
     k_esc_raw<<<(unsigned)((esc.n + 255) / 256), 256, 0, st>>>(esc, n, reinterpret_cast<unsigned long long*>(colsum),

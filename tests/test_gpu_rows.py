@@ -245,6 +245,7 @@ def _worker_bins_ties(rank, world, port, seed, n, b, params, out):
         rng = np.random.default_rng(seed)
         h = rng.integers(2500, 5000, size=(n, b)).astype(np.int64)
         h[rng.random((n, b)) < 0.02] = 0
+        h[1, 3], h[4, b - 2] = 70000, 123456                                   # cells beyond 16 bits (escape table) in tie rows
         ties = 0
         for i in range(n):
             cols = np.nonzero(h[i] > 0)[0]
@@ -262,6 +263,9 @@ def _worker_bins_ties(rank, world, port, seed, n, b, params, out):
         ld = (hi - lo + 3) // 4 * 4
         depth = torch.zeros((n, ld), dtype=torch.float32, device="cuda")
         depth[:, :hi - lo] = torch.from_numpy((h[:, lo:hi] / 100.0).astype(np.float32)).cuda()
+        params = dict(params)
+        if params.pop("u16", False):     # the 2-byte device matrix: the tie rows are rebuilt from codes + escape table
+            depth = engine.to_depth16(depth, hi - lo)
         res = engine.normalize(depth, hi - lo, engine.Params(**params), want_zq=False, want_zh=False, group=dist.group.WORLD)
         assert int(res.valid.sum()) == hi - lo                                # every bin passes the depth filter
         np.testing.assert_array_equal(res.scale_q.cpu().numpy(), want_q)
@@ -275,8 +279,8 @@ def _worker_bins_ties(rank, world, port, seed, n, b, params, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [1, 2, 4])
-def test_bin_sharded_scales_on_exact_ties(world):
+@pytest.mark.parametrize("world,u16", [(1, False), (2, False), (4, False), (1, True), (2, True)])
+def test_bin_sharded_scales_on_exact_ties(world, u16):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
-    _run(world, 38, 48, 1000, dict(min_depth=20.0, max_depth=100.0), worker=_worker_bins_ties)
+    _run(world, 38, 48, 1000, dict(min_depth=20.0, max_depth=100.0, u16=u16), worker=_worker_bins_ties)
