@@ -87,8 +87,8 @@ struct Cells<uint16_t> {
 };
 
 // rows per slab so that the grid has at least ~8 blocks per SM when the bin count alone cannot provide them
-static int64_t pick_row_slab(int64_t n, int64_t col_blocks, int64_t min_rows) {
-  const int64_t want_blocks = (int64_t)kSMs * 8;
+static int64_t pick_row_slab(int64_t n, int64_t col_blocks, int64_t min_rows, int per_sm = 8) {
+  const int64_t want_blocks = (int64_t)kSMs * per_sm;
   int64_t slabs = (want_blocks + col_blocks - 1) / col_blocks;
   int64_t rows = (n + slabs - 1) / slabs;
   if (rows < min_rows) rows = min_rows;
@@ -641,43 +641,17 @@ __global__ void __launch_bounds__(kThreads) k_col_norm(const T* __restrict__ dep
     };
     const T* p = depth + r0 * ld + j0;
     int64_t i = r0;
-    if (sizeof(T) == 2) {
-      // 2-byte cells: the pass is no longer HBM-bound but latency-bound (ncu: 70 % of the stalls on the loads) unless the
-      // next four rows are already in flight while the current four are summed
-      typename C::Raw v[4], w[4];
-      double f[4], g[4];
-      if (i + 4 <= r1) {
+    for (; i + 4 <= r1; i += 4) {
+      typename C::Raw v[4];
+      double f[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = C::load(p + u * ld), f[u] = row_factor[i + u];
-        p += 4 * ld;
+      for (int u = 0; u < 4; ++u) {
+        v[u] = C::load(p + u * ld);
+        f[u] = row_factor[i + u];
       }
-      for (; i + 8 <= r1; i += 4) {
+      p += 4 * ld;
 #pragma unroll
-        for (int u = 0; u < 4; ++u) w[u] = C::load(p + u * ld), g[u] = row_factor[i + 4 + u];
-        p += 4 * ld;
-#pragma unroll
-        for (int u = 0; u < 4; ++u) take(v[u], f[u], i + u);
-#pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = w[u], f[u] = g[u];
-      }
-      if (i + 4 <= r1) {
-#pragma unroll
-        for (int u = 0; u < 4; ++u) take(v[u], f[u], i + u);
-        i += 4;
-      }
-    } else {
-      for (; i + 4 <= r1; i += 4) {
-        typename C::Raw v[4];
-        double f[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          v[u] = C::load(p + u * ld);
-          f[u] = row_factor[i + u];
-        }
-        p += 4 * ld;
-#pragma unroll
-        for (int u = 0; u < 4; ++u) take(v[u], f[u], i + u);
-      }
+      for (int u = 0; u < 4; ++u) take(v[u], f[u], i + u);
     }
     for (; i < r1; ++i) {
       const typename C::Raw v = C::load(p);
@@ -693,6 +667,87 @@ __global__ void __launch_bounds__(kThreads) k_col_norm(const T* __restrict__ dep
     if (j0 + q < b) {
       o1[j0 + q] = ok[q] ? s1[q] : 0.0;
       o2[j0 + q] = ok[q] ? s2[q] : 0.0;
+    }
+  }
+}
+
+// K4 on the 2-byte matrix.  Same sums in the same order as k_col_norm (rows strictly in order per bin, same slabs), but
+// built for latency instead of bandwidth: at 2 bytes per cell the pass is bound by how many loads are in flight (ncu on
+// the generic kernel: 70 % of the stalls on the loads, DRAM at 36 %).  Four rows are always in flight -- a row's
+// registers are reloaded four rows ahead as soon as it has been summed -- and the per-sample factors of a 512-row chunk
+// sit in shared memory instead of registers, so four blocks fit an SM.
+__global__ void __launch_bounds__(kThreads, 3) k_col_norm_u16(const uint16_t* __restrict__ depth, int64_t n, int64_t b,
+                                                              int64_t ld, int64_t rows_per_slab,
+                                                              const uint8_t* __restrict__ valid,
+                                                              const double* __restrict__ row_factor,
+                                                              double* __restrict__ out_sd, double* __restrict__ out_sd2) {
+  __shared__ double s_f[512];
+  using C = Wide<uint16_t>;
+  const int64_t j0 = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 8;
+  const bool live = j0 < b;  // dead threads of the last block stay for the barriers
+  unsigned okm = 0;
+#pragma unroll
+  for (int q = 0; q < 8; ++q)
+    if (live && j0 + q < b && valid[j0 + q]) okm |= 1u << q;
+  double s1[8], s2[8];
+#pragma unroll
+  for (int q = 0; q < 8; ++q) s1[q] = 0.0, s2[q] = 0.0;
+  const int64_t r0 = (int64_t)blockIdx.y * rows_per_slab;
+  const int64_t r1 = min(n, r0 + rows_per_slab);
+  auto take = [&](const uint4& v, double f) {
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const unsigned h = (q & 1) ? (w[q >> 1] >> 16) : (w[q >> 1] & 0xFFFFu);
+      if (h > 0) {  // a row with no valid bin has f = NaN but then also no present cell
+        const double d = fma(u32_to_double(h), f, -1.0);
+        s1[q] += d;
+        s2[q] = fma(d, d, s2[q]);
+      }
+    }
+  };
+  for (int64_t base = r0; base < r1; base += 512) {
+    const int rows = (int)(r1 - base < 512 ? r1 - base : 512);
+    __syncthreads();
+    for (int t = threadIdx.x; t < rows; t += kThreads) s_f[t] = row_factor[base + t];
+    __syncthreads();
+    if (!okm) continue;
+    const uint16_t* p = depth + base * ld + j0;
+    int i = 0;
+    uint4 v[4];  // rows i .. i+3; each register set is reloaded with row i+4+u as soon as row i+u has been summed
+    if (rows >= 4) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = C::load(p + u * ld);
+      p += 4 * ld;
+    }
+    for (; i + 8 <= rows; i += 4) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint4 cur = v[u];
+        v[u] = C::load(p + u * ld);  // issued BEFORE the sums of row i+u (left after them, ptxas sinks all four to the loop end)
+        take(cur, s_f[i + u]);
+      }
+      p += 4 * ld;
+    }
+    if (i + 4 <= rows) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) take(v[u], s_f[i + u]);
+      i += 4;
+    }
+    for (; i < rows; ++i) {
+      const uint4 x = C::load(p);
+      p += ld;
+      take(x, s_f[i]);
+    }
+  }
+  if (!live) return;
+  double* o1 = out_sd + (int64_t)blockIdx.y * b;
+  double* o2 = out_sd2 + (int64_t)blockIdx.y * b;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    if (j0 + q < b) {
+      o1[j0 + q] = (okm >> q & 1) ? s1[q] : 0.0;
+      o2[j0 + q] = (okm >> q & 1) ? s2[q] : 0.0;
     }
   }
 }
@@ -1158,7 +1213,12 @@ static int col_row_raw_impl(const T* depth, const Esc& esc, int64_t n, int64_t b
   G2_REQUIRE(colsum && colcnt && rowsum_all && rowcnt_all, GRIDB200_EINVAL, "null output");
   cudaStream_t st = as_stream(stream);
   const int64_t cb = (b + kThreads * Wide<T>::kN - 1) / (kThreads * Wide<T>::kN);
-  const int64_t rows = pick_row_slab(n, cb, 64);
+  // 2-byte cells: 3 blocks of 2048 bins per SM are resident, and with one slab every block walks all n rows -- 1417
+  // equal blocks are 3.2 waves at config 2, a fifth of the machine idle in the last.  ~48 blocks per SM (row slabs of
+  // >= 512 rows, a multiple of 32) make the last wave a sixteenth of the run; the sums are integers, so the slab
+  // partials meet in exact atomics.
+  int64_t rows = sizeof(T) == 2 ? pick_row_slab(n, cb, 512, 48) : pick_row_slab(n, cb, 64);
+  if (sizeof(T) == 2 && rows < n) rows = (rows + 31) / 32 * 32;
   const int64_t slabs = (n + rows - 1) / rows;
   G2_REQUIRE(slabs <= 65535, GRIDB200_EINVAL, "too many row slabs");
   if (slabs > 1) {
@@ -1291,7 +1351,14 @@ extern "C" int gridb200_row_means_exact(const float* depth, int64_t n, int64_t b
 
 static int64_t col_norm_slab_rows(int64_t n, int64_t b) {
   const int64_t cb = (b + kColsPerBlock - 1) / kColsPerBlock;
-  if (cb >= (int64_t)kSMs * 4) return n;  // enough bin blocks: one slab, no partial buffers
+  if (cb >= (int64_t)kSMs * 4) {
+    // Plenty of bin blocks -- but with ONE slab every block walks all n rows, and on the 2-byte matrix (2048 bins per
+    // block, 3 blocks resident per SM) config 2 is 3.2 waves of equal blocks: a fifth of the machine idle in the last.
+    // Row slabs of >= 256 rows for ~96 fp32-sized blocks per SM cut the tail to a few percent; the partials are reduced
+    // in slab order (deterministic), at 16 bytes of workspace per bin and slab.
+    const int64_t rows = pick_row_slab(n, cb, 256, 96);
+    return rows >= n ? n : (rows + 31) / 32 * 32;
+  }
   return pick_row_slab(n, cb, 32);
 }
 
@@ -1332,7 +1399,10 @@ static int col_norm_impl(const T* depth, const Esc& esc, const int32_t* esc_cols
   const int64_t slabs = (n + rows - 1) / rows;
   G2_REQUIRE(slabs <= 65535, GRIDB200_EINVAL, "too many row slabs");
   if (slabs == 1) {
-    k_col_norm<T><<<dim3((unsigned)cb, 1), kThreads, 0, st>>>(depth, esc, n, b, ld, rows, valid, row_factor, sd, sd2);
+    if constexpr (sizeof(T) == 2)
+      k_col_norm_u16<<<dim3((unsigned)cb, 1), kThreads, 0, st>>>(depth, n, b, ld, rows, valid, row_factor, sd, sd2);
+    else
+      k_col_norm<T><<<dim3((unsigned)cb, 1), kThreads, 0, st>>>(depth, esc, n, b, ld, rows, valid, row_factor, sd, sd2);
     G2_LAUNCHED();
     if (int e = col_norm_patch<T>(depth, esc, esc_cols, n_esc_cols, n, b, ld, rows, 1, valid, row_factor, sd, sd2, st)) return e;
   } else {
@@ -1340,8 +1410,11 @@ static int col_norm_impl(const T* depth, const Esc& esc, const int32_t* esc_cols
                "workspace too small: need %zu bytes", gridb200_col_norm_stats_ws_bytes(n, b));
     double* p1 = static_cast<double*>(ws);
     double* p2 = p1 + slabs * b;
-    k_col_norm<T><<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(depth, esc, n, b, ld, rows, valid, row_factor,
-                                                                             p1, p2);
+    if constexpr (sizeof(T) == 2)
+      k_col_norm_u16<<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(depth, n, b, ld, rows, valid, row_factor, p1, p2);
+    else
+      k_col_norm<T><<<dim3((unsigned)cb, (unsigned)slabs), kThreads, 0, st>>>(depth, esc, n, b, ld, rows, valid, row_factor,
+                                                                               p1, p2);
     G2_LAUNCHED();
     if (int e = col_norm_patch<T>(depth, esc, esc_cols, n_esc_cols, n, b, ld, rows, slabs, valid, row_factor, p1, p2, st)) return e;
     k_reduce_slabs<<<(unsigned)((b + 255) / 256), 256, 0, st>>>(p1, p2, b, (int)slabs, sd, sd2);
