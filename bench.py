@@ -58,6 +58,9 @@ def parse_args():
                     help="resident form of the depth matrix: uint16 hundredths + escape table (2 bytes per cell, the default; "
                          "bit-identical results) or the packed fp32 matrix (4 bytes per cell)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--timeline", action="store_true",
+                    help="debug: one extra step after the timed region with device/host timestamps of every stage, collective "
+                         "and host read (rank 0's view, key 'timeline')")
     ap.add_argument("--no-check", action="store_true", help="debug: skip the parity check (the line says so)")
     ap.add_argument("--check-rows", type=int, default=64, help="query rows verified after the timed region (>= 64 by default)")
     ap.add_argument("--no-ring", action="store_true", help="skip the row-sharded ring sub-record at N > 1")
@@ -543,6 +546,16 @@ def run_ours(a):
     if group is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
     ms = float(t.item())
+    timeline = None
+    if a.timeline:
+        barrier()
+        engine.TIMELINE = []
+        engine._tick("step >")
+        step()
+        engine._tick("step <")
+        torch.cuda.synchronize()
+        timeline = engine.timeline_summary()
+        engine.TIMELINE = None
 
     # ---- what was timed is checked: >= 64 query rows spread over every rank's range, against the fp64 checker --------
     check = None
@@ -697,6 +710,8 @@ def run_ours(a):
         }
         if ring_rec is not None:
             line["ring"] = ring_rec
+        if timeline is not None:
+            line["timeline"] = {"columns": ["label", "device ms", "host ms"], "rank": 0, "points": timeline}
         if world == 1 and not a.no_cpu:
             try:
                 m = CpuArm(a).measure(a.cpu_budget or 25.0, 1, 1, a.cpu_bins)

@@ -82,15 +82,38 @@ class _mark:
         self.name = name
 
     def __enter__(self):
+        _tick(self.name + " >")
         if PROFILE is not None:
             self.e0 = torch.cuda.Event(enable_timing=True)
             self.e0.record()
 
     def __exit__(self, *exc):
+        _tick(self.name + " <")
         if PROFILE is not None:
             e1 = torch.cuda.Event(enable_timing=True)
             e1.record()
             PROFILE.setdefault(self.name, []).append((self.e0, e1))
+
+
+TIMELINE: list | None = None  # bench.py --timeline: [(label, CUDA event, host perf_counter)] in program order
+
+
+def _tick(label: str) -> None:
+    """A point of the step's timeline (device event + host clock) when TIMELINE is enabled; free otherwise."""
+    if TIMELINE is not None:
+        import time
+
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        TIMELINE.append((label, e, time.perf_counter()))
+
+
+def timeline_summary() -> list:
+    """[(label, device ms since the first tick, host ms since the first tick)] (call after a synchronize)."""
+    if not TIMELINE:
+        return []
+    _, e0, h0 = TIMELINE[0]
+    return [(lab, round(e0.elapsed_time(e), 3), round((h - h0) * 1e3, 3)) for lab, e, h in TIMELINE]
 
 
 def profile_summary(steps: int = 0) -> dict:
@@ -254,6 +277,7 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
              ptr(rowsum), ptr(rowcnt), ptr(ws0), ws0.numel(), st)
     _all_reduce(rowsum, group)
     _all_reduce(rowcnt, group)
+    _tick("rows all-reduced")
     raw_mean, scale_q, row_factor = torch.empty(n, **f64), torch.empty(n, **f64), torch.empty(n, **f64)
     call("gridb200_row_scales", ptr(rowsum), ptr(rowcnt), n, ptr(raw_mean), ptr(scale_q), ptr(row_factor), st)
     # exact %.2f ties take numpy's own mean: a pairwise fp64 sum over the WHOLE row, replayed for the tie rows only
@@ -278,6 +302,7 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
     # samples without any valid bin are dropped by the reference before normalising (filter_empty_samples,
     # normalize_mosdepth.py:576-600); they contribute nothing here either, only N in the ddof=1 divisor changes
     counts_host = _read_behind(counts_dev, counts_ready)
+    _tick("row counts on host")
     n_eff = int(counts_host[0])
     if counts_host[1]:
         _sharded_tie_means(depth, b, valid, rowsum, rowcnt, raw_mean, scale_q, tie, group)
@@ -302,6 +327,7 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
         gathered = torch.empty(world * bmax, **f64)
         dist.all_gather_into_tensor(gathered, mine, group=group)
         ratio_all = torch.cat([gathered[r * bmax:r * bmax + sizes[r]] for r in range(world)])
+        _tick("ratios gathered")
         lo = sum(sizes[:rank])
     else:
         ratio_all, lo = ratio, 0
@@ -324,6 +350,7 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
         sel_pos, keep, rw_local_t = sel_all, keep_all, None
     host = torch.cat([info, info2, (rw_local_t.to(torch.float64).reshape(1) if rw_local_t is not None else info[3:4])]).cpu()
     zscale, rw, r_use, rw_local = float(host[0]), int(host[3]), int(host[4]), int(host[6])
+    _tick("selection on host")
     if rw < 0:
         raise IndexError("list index out of range")  # what the reference's sorted_ratios[int(top_frac*len)] raises
     res = NormResult(n=n, b=b, colsum=colsum, colcnt=colcnt, valid=valid, raw_mean=raw_mean, scale_q=scale_q,
@@ -353,6 +380,7 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
              p.zclip, ptr(zq), ldq, ptr(zh), n, ptr(norms), ptr(sat), st)
     if want_zh:
         _all_reduce(norms, group)
+        _tick("norms all-reduced")
     res.zq, res.zh, res.kdim, res.norms = zq, zh, ldh, norms
     res.extra["sat"] = sat
     return res
@@ -502,6 +530,7 @@ def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torc
             # repeating the whole merge on every rank.
             mine = torch.empty((m, ldd), dtype=torch.int64, device=dev)
             dist.reduce_scatter_tensor(mine, dot, group=group)
+            _tick("dots reduce-scattered")
             r_lo = min(nq, rank * m)
             n_mine = min(nq, r_lo + m) - r_lo
         else:
@@ -534,6 +563,7 @@ def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torc
             dist.all_gather_into_tensor(all_idx, part_idx, group=group)
             best_d2[q0:q0 + nq] = all_d2[:nq]
             best_idx[q0:q0 + nq] = all_idx[:nq]
+            _tick("lists gathered")
 
 
 FUSED_CAP = 1024          # candidate slots per row of the fused Gram + k-best kernel
