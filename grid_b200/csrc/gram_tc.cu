@@ -569,17 +569,29 @@ static int launch_gram(const void* zq, int64_t nq, int64_t slabq, const void* zr
     group_m_env = (e && atoi(e) > 0) ? atoi(e) : 0;
   }
   w.group_m = group_m_env ? group_m_env : 4;
-  // K splits: best wave efficiency over the workers, each split at least 4 chunks long
+  // K splits: the shortest launch under the model  rounds(items over the pairs) x (k-blocks per split + ITEM_COST).
+  // ITEM_COST (in k-block times, ~0.3 us each) is what an item costs beyond its MMAs: 128 uncoalesced 64-bit
+  // reductions per epilogue thread during which the next item's MMAs run out of TMEM stages, the pipeline refill and
+  // the pacing hand-over -- about 60 us, measured as the intercept of launch time against K (3.3 ms at K/8 where
+  // 19.4/8 = 2.4 ms would be proportional).  Wave efficiency alone picked 13 splits for the 91 tiles of N = 3202
+  // (1183 items); with the item cost 4 splits win: -20 % at K = 326 k bins (one rank's share at 8 GPUs).
+  constexpr int ITEM_COST = 192;
   const int chunks = (w.kb_total + w.ck - 1) / w.ck;
   int best_s = 1;
-  double best_eff = 0.0;
+  double best_cost = 0.0;
   for (int s = 1; !fused && s <= 64 && s * 4 <= std::max(chunks, 4); ++s) {
     const int cps = (chunks + s - 1) / s;          // chunks per split
     const int real_s = (chunks + cps - 1) / cps;   // splits actually needed
     const long long items = (long long)w.ntiles * real_s;
-    const double eff = (double)items / (double)(((items + workers - 1) / workers) * workers);
-    if (eff > best_eff + 1e-9) best_eff = eff, best_s = real_s;
+    const double cost = (double)((items + workers - 1) / workers) * (double)(cps * w.ck + ITEM_COST);
+    if (s == 1 || cost < best_cost - 1e-9) best_cost = cost, best_s = real_s;
   }
+  static int splits_env = -1;  // GRIDB200_GRAM_SPLITS: force the number of K splits (measurement switch)
+  if (splits_env < 0) {
+    const char* e = getenv("GRIDB200_GRAM_SPLITS");
+    splits_env = (e && atoi(e) > 0) ? atoi(e) : 0;
+  }
+  if (splits_env && !fused) best_s = std::max(1, std::min(splits_env, chunks));
   const int cps = (chunks + best_s - 1) / best_s;
   w.kb_per_split = cps * w.ck;
   w.ksplits = (w.kb_total + w.kb_per_split - 1) / w.kb_per_split;

@@ -270,13 +270,15 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
              ptr(rowcnt_all), st)
     call("gridb200_depth_filter", ptr(colsum), ptr(colcnt), b, float(p.min_depth), float(p.max_depth), ptr(valid), st)
 
-    rowsum, rowcnt = torch.empty(n, **i64), torch.empty(n, dtype=torch.int32, device=dev)
+    # one buffer: the int32 counts ride behind the int64 sums, two per word, so a bin-sharded run sums both in ONE
+    # all-reduce (the counts are non-negative and their cohort totals fit 31 bits: no carry between the halves)
+    rows_buf = torch.zeros(n + (n + 1) // 2, **i64)
+    rowsum, rowcnt = rows_buf[:n], rows_buf[n:].view(torch.int32)[:n]
     ws0 = _ws(_lib.load().gridb200_row_stats_fused_ws_bytes(b), dev)
     with _mark("row_stats"):
         _dcall("gridb200_row_stats_fused", depth, n, b, ld, ptr(valid), ptr(colcnt), ptr(rowsum_all), ptr(rowcnt_all),
              ptr(rowsum), ptr(rowcnt), ptr(ws0), ws0.numel(), st)
-    _all_reduce(rowsum, group)
-    _all_reduce(rowcnt, group)
+    _all_reduce(rows_buf, group)
     _tick("rows all-reduced")
     raw_mean, scale_q, row_factor = torch.empty(n, **f64), torch.empty(n, **f64), torch.empty(n, **f64)
     call("gridb200_row_scales", ptr(rowsum), ptr(rowcnt), n, ptr(raw_mean), ptr(scale_q), ptr(row_factor), st)
@@ -480,7 +482,8 @@ def merge_lists(src_d2: torch.Tensor, src_idx: torch.Tensor, best_d2: torch.Tens
 def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torch.Tensor, norms_r: torch.Tensor,
               r_gid0: int, kdim: int, vmax: int, best_d2: torch.Tensor, best_idx: torch.Tensor, impl: int = 0,
               group=None, max_block_bytes: int = 2 << 30, q_range: tuple[int, int] | None = None,
-              r_range: tuple[int, int] | None = None, t_lists: tuple[torch.Tensor, torch.Tensor] | None = None) -> None:
+              r_range: tuple[int, int] | None = None, t_lists: tuple[torch.Tensor, torch.Tensor] | None = None,
+              padded: tuple[torch.Tensor, torch.Tensor] | None = None) -> None:
     """Merge the reference rows of ``zh_r`` (global ids r_gid0..) into the running lists of the query rows of
     ``zh_q`` (global ids q_gid0..).  Operands are k-blocked [kdim/64, rows, 64]; the N x N distances only ever
     exist as query-block x reference-shard Gram tiles (<= max_block_bytes).
@@ -488,7 +491,9 @@ def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torc
     q_range / r_range: restrict the block to query rows [a, b) / reference rows [c, d) of the operands (norms, global
     ids and best_* keep indexing the WHOLE operand's rows).
     t_lists = (t_d2, t_idx) [rows of zh_r, k]: also merge, through the block's transpose, the query rows into the
-    running lists of the REFERENCE rows -- the half ring's way of computing every pair of samples once."""
+    running lists of the REFERENCE rows -- the half ring's way of computing every pair of samples once.
+    padded = (d2, idx) [ceil(n / world) * world, k] of which best_d2 / best_idx are the first n rows (bin-sharded runs):
+    the lists are then all-gathered in place, without staging copies."""
     for t in (zh_q, zh_r):
         assert t.dim() == 3 and t.shape[2] == 64 and t.is_contiguous() and t.shape[0] * 64 == kdim, "zh is [kdim/64, n, 64]"
     nq_all, nr_all = zh_q.shape[1], zh_r.shape[1]
@@ -551,7 +556,11 @@ def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torc
                     call("gridb200_topk_merge_t", dot.data_ptr() + c0 * ldd * 8, ldd, n_c, nr,
                          norms_q.data_ptr() + (q0 + c0) * 8, norms_r.data_ptr() + ra * 8, q_gid0 + q0 + c0, r_gid0 + ra, k,
                          t_d2.data_ptr() + ra * k * 8, t_idx.data_ptr() + ra * k * 4, st)
-        if world > 1:
+        if world > 1 and padded is not None and q0 == 0 and nq == nq_all and padded[0].shape[0] == m * world:
+            dist.all_gather_into_tensor(padded[0], padded[0][rank * m:(rank + 1) * m], group=group)
+            dist.all_gather_into_tensor(padded[1], padded[1][rank * m:(rank + 1) * m], group=group)
+            _tick("lists gathered")
+        elif world > 1:
             part_d2 = torch.zeros((m, k), dtype=torch.int64, device=dev)
             part_idx = torch.zeros((m, k), dtype=torch.int32, device=dev)
             if n_mine > 0:
@@ -666,9 +675,17 @@ def knn(zh: torch.Tensor, kdim: int, norms: torch.Tensor, k: int, vmax: int, imp
     assert zh.dim() == 3 and zh.shape[2] == 64 and zh.is_contiguous() and zh.shape[0] * 64 == kdim, "zh is [kdim/64, n, 64]"
     n = zh.shape[1]
     k = max(1, min(k, n - 1)) if n > 1 else 1
-    best_d2, best_idx = knn_init(n, k, zh.device)
+    padded = None
+    if group is not None:
+        import torch.distributed as dist
+
+        world = dist.get_world_size(group)
+        padded = knn_init(-(-n // world) * world, k, zh.device)  # every rank's share of the rows the same size
+        best_d2, best_idx = padded[0][:n], padded[1][:n]
+    else:
+        best_d2, best_idx = knn_init(n, k, zh.device)
     knn_block(zh, norms, 0, zh, norms, 0, kdim, vmax, best_d2, best_idx, impl=impl, group=group,
-              max_block_bytes=max_block_bytes)
+              max_block_bytes=max_block_bytes, padded=padded)
     return best_idx, best_d2
 
 
