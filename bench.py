@@ -270,6 +270,28 @@ def run_reference(a):
 
 
 # ------------------------------------------------------------------------------------------------ clocks
+def bind_to_gpu_numa_node(index: int):
+    """Multi-GPU runs: pin this rank's threads to the CPUs NVML names as local to its GPU, so the pinned host buffers of
+    the end-to-end leg are first-touched on the GPU's own NUMA node (eight ranks pulling their inputs across the socket
+    link held the 8-GPU e2e at 21 GB/s per GPU where one GPU alone reaches 55).  Returns a description or None."""
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        phys = int(vis.split(",")[index]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else index
+        h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+        cpus = {64 * w + bit for w, word in enumerate(words) for bit in range(64) if (int(word) >> bit) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return {"cpus": len(cpus), "first": min(cpus), "last": max(cpus)}
+    except Exception as exc:  # no NVML / not permitted: run unbound, say so
+        return {"error": f"{type(exc).__name__}: {exc}"[:120]}
+
+
 class ClockSampler:
     """SM clock and throttle reasons sampled DURING the timed region (NVML every ~10 ms; nvidia-smi as a fallback)."""
 
@@ -478,6 +500,7 @@ def run_ours(a):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     group = None
+    numa = bind_to_gpu_numa_node(local) if world > 1 else None   # before any pinned allocation (first touch)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)     # NCCL_DEBUG is whatever the launcher set: fd 1 is parked on stderr
         group = dist.group.WORLD
@@ -623,6 +646,8 @@ def run_ours(a):
                    # the end-to-end steps went through the host format: same cohort, so the same lists as the checked step
                    "results_equal_checked_step": bool(torch.equal(outs[0], idx.cpu()) and torch.equal(outs[1], cn.cpu()))
                    if (rank == 0 or rows) else None}
+            if numa is not None:
+                e2e["host_threads_bound_to_gpu_numa_node"] = numa
             del host
         except Exception as exc:  # e.g. not enough pinned host memory on this box
             e2e = {"value": None, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
