@@ -1,7 +1,8 @@
 // Order statistics and compaction over the per-bin ratio vector (length b, up to a few million):
 //   - median + top_frac threshold of the finite ratios  (normalize_mosdepth.py:460-468, :479-499)
 //   - sigma2_min of the %.3f-rounded ratios             (find_neighbors.py:128-175)
-// Implemented as an 8-pass MSB radix select on order-preserving 64-bit keys.  Each pass is one multi-block
+// Implemented as an 8-pass MSB radix select on order-preserving 64-bit keys (the last four passes on the few keys that
+// still match a target after the fourth, collected on the way: k_sel_tail).  Each full pass is one multi-block
 // kernel: warp-aggregated shared-memory histograms for up to 3 target ranks at once, merged with global
 // atomics; the last block to finish picks the digit of every target.  No host round trip, no sort.
 #include "common.cuh"
@@ -17,7 +18,12 @@ struct SelState {
   int ntargets;
   int error;
   int pad;
+  unsigned int ncand;      // keys collected for the tail (may exceed kCandCap: then `overflow` is set and nothing is used)
+  unsigned int overflow;
+  unsigned int tail_done;  // passes 4-7 were done on the collected keys: the full-vector passes return at once
 };
+constexpr int kCollectPass = 3;        // the pass that also collects the keys matching a target's 24-bit prefix
+constexpr unsigned kCandCap = 1u << 16;  // keys the tail kernel will take (a few hundred are typical for 3e6 ratios)
 constexpr size_t kStateBytes = 256;
 constexpr size_t kHistBytes = 8 * 3 * 256 * sizeof(unsigned);
 constexpr int kSelThreads = 256;
@@ -72,11 +78,13 @@ __global__ void k_sel_ranks(SelState* st, int kind, double param, const double* 
 }
 
 __global__ void __launch_bounds__(kSelThreads) k_sel_pass(const double* __restrict__ vals, int64_t n, int mode,
-                                                          int pass, SelState* st, unsigned* __restrict__ hist_all) {
+                                                          int pass, SelState* st, unsigned* __restrict__ hist_all,
+                                                          unsigned long long* __restrict__ cand) {
   __shared__ unsigned sh[3][256];
   __shared__ bool s_last;
   const int nt = st->ntargets;
-  if (nt == 0) return;
+  if (nt == 0 || st->tail_done) return;
+  const bool collect = cand != nullptr && pass == kCollectPass;
   for (int t = threadIdx.x; t < 3 * 256; t += kSelThreads) (&sh[0][0])[t] = 0;
   __syncthreads();
   const int shift = 56 - 8 * pass;
@@ -93,12 +101,14 @@ __global__ void __launch_bounds__(kSelThreads) k_sel_pass(const double* __restri
   const int64_t nround = ((n + stride - 1) / stride) * stride;  // keep warps converged for match_any
   for (int64_t i = (int64_t)blockIdx.x * kSelThreads + threadIdx.x; i < nround; i += stride) {
     const double v = i < n ? vals[i] : nan("");
-    const bool cand = i < n && is_candidate(v, mode);
+    const bool is_cand = i < n && is_candidate(v, mode);
     const unsigned long long key = key_of(v);
     const unsigned digit = (unsigned)(key >> shift) & 0xffu;
+    bool any_hit = false;
     for (int t = 0; t < nt; ++t) {
       if (alias[t] != t) continue;
-      const bool hit = cand && (pass == 0 || (key >> (shift + 8)) == (pre[t] >> (shift + 8)));
+      const bool hit = is_cand && (pass == 0 || (key >> (shift + 8)) == (pre[t] >> (shift + 8)));
+      any_hit |= hit;
       const unsigned ballot = __ballot_sync(0xffffffffu, hit);
       if (!ballot) continue;
       if (hit) {
@@ -106,6 +116,20 @@ __global__ void __launch_bounds__(kSelThreads) k_sel_pass(const double* __restri
         if ((threadIdx.x & 31) == __ffs(peers) - 1) {
           const unsigned cnt = __popc(peers);
           atomicAdd(&sh[t][digit], cnt);
+        }
+      }
+    }
+    if (collect) {  // the keys that still match some target's prefix: the last four passes run on this list alone
+      const unsigned ballot = __ballot_sync(0xffffffffu, any_hit);
+      if (ballot) {
+        unsigned base = 0;
+        const int lane = threadIdx.x & 31;
+        if (lane == 0) base = atomicAdd(&st->ncand, (unsigned)__popc(ballot));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        const unsigned slot = base + __popc(ballot & ((1u << lane) - 1u));
+        if (any_hit) {
+          if (slot < kCandCap) cand[slot] = key;
+          else st->overflow = 1u;
         }
       }
     }
@@ -142,6 +166,56 @@ __global__ void __launch_bounds__(kSelThreads) k_sel_pass(const double* __restri
     if (pass == 7) st->value[t] = value_of(p);
   }
   if (threadIdx.x == 0) st->done = 0;
+}
+
+// Passes kCollectPass+1 .. 7 on the collected keys, all in ONE block and one launch (each full-vector pass is a grid of
+// 592 blocks that re-reads the 23 MB vector to count a few hundred survivors: ~25 us apiece).
+__global__ void __launch_bounds__(1024) k_sel_tail(const unsigned long long* __restrict__ cand, SelState* st) {
+  __shared__ unsigned sh[3][256];
+  __shared__ unsigned long long s_pre[3], s_rank[3];
+  const int nt = st->ntargets;
+  if (nt == 0 || st->overflow) return;  // the full-vector passes take over
+  const unsigned nc = st->ncand;
+  if (threadIdx.x < 3) s_pre[threadIdx.x] = st->prefix[threadIdx.x], s_rank[threadIdx.x] = st->rank[threadIdx.x];
+  for (int pass = kCollectPass + 1; pass < 8; ++pass) {
+    for (int t = threadIdx.x; t < 3 * 256; t += 1024) (&sh[0][0])[t] = 0;
+    __syncthreads();
+    const int shift = 56 - 8 * pass;
+    unsigned long long pre[3];
+    for (int t = 0; t < 3; ++t) pre[t] = s_pre[t];
+    int alias[3] = {0, 1, 2};
+    for (int t = 1; t < nt; ++t)
+      for (int u = t - 1; u >= 0; --u)
+        if ((pre[u] >> (shift + 8)) == (pre[t] >> (shift + 8))) alias[t] = alias[u];
+    for (unsigned i = threadIdx.x; i < nc; i += 1024) {
+      const unsigned long long key = cand[i];
+      const unsigned digit = (unsigned)(key >> shift) & 0xffu;
+      for (int t = 0; t < nt; ++t)
+        if (alias[t] == t && (key >> (shift + 8)) == (pre[t] >> (shift + 8))) atomicAdd(&sh[t][digit], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < nt) {
+      const int t = threadIdx.x;
+      unsigned long long r = s_rank[t];
+      const unsigned* h = sh[alias[t]];
+      int d = 0;
+      for (; d < 255; ++d) {
+        const unsigned c = h[d];
+        if (r < c) break;
+        r -= c;
+      }
+      s_rank[t] = r;
+      s_pre[t] = pre[t] | ((unsigned long long)d << shift);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x < nt) {
+    const int t = threadIdx.x;
+    st->rank[t] = s_rank[t];
+    st->prefix[t] = s_pre[t];
+    st->value[t] = value_of(s_pre[t]);
+  }
+  if (threadIdx.x == 0) st->tail_done = 1u;
 }
 
 // zscale / threshold from the three order statistics
@@ -324,8 +398,9 @@ static int run_select_min(const double* vals, int64_t n, SelState* st, unsigned*
   return 0;
 }
 
+// cand: room for kCandCap keys, or nullptr (all eight passes over the whole vector, as the allocation-free variant does)
 static int run_select(const double* vals, int64_t n, int mode, int kind, double param, const double* info,
-                      SelState* st, unsigned* hist, cudaStream_t stream) {
+                      SelState* st, unsigned* hist, cudaStream_t stream, unsigned long long* cand = nullptr) {
   G2_CUDA(cudaMemsetAsync(st, 0, kStateBytes + kHistBytes, stream));
   const int blocks = (int)std::min<int64_t>((n + kSelThreads * 8 - 1) / (kSelThreads * 8), (int64_t)kSMs * 4);
   k_sel_count<<<blocks, kSelThreads, 0, stream>>>(vals, n, mode, st);
@@ -333,8 +408,12 @@ static int run_select(const double* vals, int64_t n, int mode, int kind, double 
   k_sel_ranks<<<1, 1, 0, stream>>>(st, kind, param, info);
   G2_LAUNCHED();
   for (int pass = 0; pass < 8; ++pass) {
-    k_sel_pass<<<blocks, kSelThreads, 0, stream>>>(vals, n, mode, pass, st, hist);
+    k_sel_pass<<<blocks, kSelThreads, 0, stream>>>(vals, n, mode, pass, st, hist, cand);
     G2_LAUNCHED();
+    if (cand && pass == kCollectPass) {
+      k_sel_tail<<<1, 1024, 0, stream>>>(cand, st);
+      G2_LAUNCHED();
+    }
   }
   return 0;
 }
@@ -343,11 +422,20 @@ static int run_select(const double* vals, int64_t n, int mode, int kind, double 
 
 using namespace g2;
 
+// where the tail's key list lives inside a gridb200_select_ws_bytes(b) workspace
+static unsigned long long* select_cand(void* ws, int64_t b) {
+  const size_t nblk = (size_t)((b + kScanTile - 1) / kScanTile) + 1;
+  size_t bytes = kStateBytes + kHistBytes + ((nblk * sizeof(int) + 255) / 256) * 256 + 256 + (size_t)b * sizeof(double);
+  bytes = (bytes + 255) / 256 * 256;
+  return reinterpret_cast<unsigned long long*>(static_cast<char*>(ws) + bytes);
+}
+
 extern "C" size_t gridb200_select_ws_bytes(int64_t b) {
   if (b <= 0) return 0;
   const size_t nblk = (size_t)((b + kScanTile - 1) / kScanTile) + 1;
   size_t bytes = kStateBytes + kHistBytes + ((nblk * sizeof(int) + 255) / 256) * 256 + 256;
   bytes += (size_t)b * sizeof(double);  // rounded ratios for the kNN filter
+  bytes = (bytes + 255) / 256 * 256 + (size_t)kCandCap * sizeof(unsigned long long);  // keys of the select's tail
   return bytes;
 }
 
@@ -363,7 +451,7 @@ extern "C" int gridb200_select(const double* ratio, int64_t b, double top_frac, 
   SelState* state = reinterpret_cast<SelState*>(w);
   unsigned* hist = reinterpret_cast<unsigned*>(w + kStateBytes);
   int* block_sums = reinterpret_cast<int*>(w + kStateBytes + kHistBytes);
-  if (int e = run_select(ratio, b, /*mode=*/0, /*kind=*/0, top_frac, nullptr, state, hist, st)) return e;
+  if (int e = run_select(ratio, b, /*mode=*/0, /*kind=*/0, top_frac, nullptr, state, hist, st, select_cand(ws, b))) return e;
   k_norm_select_finish<<<1, 1, 0, st>>>(state, info);
   G2_LAUNCHED();
   const int64_t nblk = (b + kScanTile - 1) / kScanTile;
@@ -395,7 +483,7 @@ extern "C" int gridb200_knn_col_filter(const double* ratio, const int32_t* sel_p
   G2_LAUNCHED();
   if (frac_r >= 1.0) {
     if (int e = run_select_min(rq, b, state, hist, st)) return e;
-  } else if (int e = run_select(rq, b, /*mode=*/1, /*kind=*/1, frac_r, info, state, hist, st)) {
+  } else if (int e = run_select(rq, b, /*mode=*/1, /*kind=*/1, frac_r, info, state, hist, st, select_cand(ws, b))) {
     return e;
   }
   G2_CUDA(cudaMemsetAsync(r_use, 0, sizeof(unsigned long long), st));

@@ -250,11 +250,13 @@ def _read_behind(t: torch.Tensor, ready: "torch.cuda.Event") -> list:
 
 
 def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, want_zh: bool = True,
-              group=None, bin_sizes: list[int] | None = None) -> NormResult:
+              group=None, bin_sizes: list[int] | None = None, defer_norms: bool = False) -> NormResult:
     """Step 4 on a device-resident depth matrix [n, ld] (first ``b`` columns are bins; 0 = absent).
 
     With ``group`` the matrix holds this rank's bin slice; ranks are ordered by bin range.  bin_sizes: every rank's
     number of bins when the caller knows them (saves an all-reduce and a host sync per step).
+    defer_norms (bin-sharded): the all-reduce of the row norms is started but not waited for -- the Gram kernel does not
+    read them -- and its handle is left in ``extra["norms_pending"]`` for the caller to wait on before the k-best merge.
     """
     n, ld = check_depth(depth, b)
     dev, st = depth.device, _stream()
@@ -380,7 +382,11 @@ def normalize(depth: torch.Tensor, b: int, p: Params, want_zq: bool = False, wan
     with _mark("transform"):
         _dcall("gridb200_transform", depth, n, b, ld, ptr(row_factor), ptr(mu), ptr(sel_pos), ptr(keep), ptr(info),
              p.zclip, ptr(zq), ldq, ptr(zh), n, ptr(norms), ptr(sat), st)
-    if want_zh:
+    if want_zh and group is not None and defer_norms:
+        import torch.distributed as dist
+
+        res.extra["norms_pending"] = dist.all_reduce(norms, group=group, async_op=True)
+    elif want_zh:
         _all_reduce(norms, group)
         _tick("norms all-reduced")
     res.zq, res.zh, res.kdim, res.norms = zq, zh, ldh, norms
@@ -483,7 +489,7 @@ def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torc
               r_gid0: int, kdim: int, vmax: int, best_d2: torch.Tensor, best_idx: torch.Tensor, impl: int = 0,
               group=None, max_block_bytes: int = 2 << 30, q_range: tuple[int, int] | None = None,
               r_range: tuple[int, int] | None = None, t_lists: tuple[torch.Tensor, torch.Tensor] | None = None,
-              padded: tuple[torch.Tensor, torch.Tensor] | None = None) -> None:
+              padded: tuple[torch.Tensor, torch.Tensor] | None = None, pending=None) -> None:
     """Merge the reference rows of ``zh_r`` (global ids r_gid0..) into the running lists of the query rows of
     ``zh_q`` (global ids q_gid0..).  Operands are k-blocked [kdim/64, rows, 64]; the N x N distances only ever
     exist as query-block x reference-shard Gram tiles (<= max_block_bytes).
@@ -493,7 +499,8 @@ def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torc
     t_lists = (t_d2, t_idx) [rows of zh_r, k]: also merge, through the block's transpose, the query rows into the
     running lists of the REFERENCE rows -- the half ring's way of computing every pair of samples once.
     padded = (d2, idx) [ceil(n / world) * world, k] of which best_d2 / best_idx are the first n rows (bin-sharded runs):
-    the lists are then all-gathered in place, without staging copies."""
+    the lists are then all-gathered in place, without staging copies.
+    pending: handle of an asynchronous collective the norms still depend on; waited for after the Gram launch."""
     for t in (zh_q, zh_r):
         assert t.dim() == 3 and t.shape[2] == 64 and t.is_contiguous() and t.shape[0] * 64 == kdim, "zh is [kdim/64, n, 64]"
     nq_all, nr_all = zh_q.shape[1], zh_r.shape[1]
@@ -529,6 +536,10 @@ def knn_block(zh_q: torch.Tensor, norms_q: torch.Tensor, q_gid0: int, zh_r: torc
                  0, impl, st)
         GRAM_ELEMS += gram_tile_elems(nq, nr, impl == 0 and q0 == 0 and ra == 0 and nq == nr == nq_all == nr_all
                                       and zh_q.data_ptr() == zh_r.data_ptr())
+        if pending is not None:  # (the row norms' all-reduce ran beside the Gram kernel)
+            pending.wait()
+            pending = None
+            _tick("norms all-reduced")
         if world > 1:
             # bin-sharded: every rank holds a partial of the whole block.  Reduce-scatter it by query rows, merge the
             # k-best lists of MY rows only, then all-gather the (small) lists -- instead of all-reducing the block and
@@ -665,7 +676,7 @@ def knn_block_auto(zh_q, norms_q, q_gid0, zh_r, norms_r, r_gid0, kdim, vmax, bes
 
 
 def knn(zh: torch.Tensor, kdim: int, norms: torch.Tensor, k: int, vmax: int, impl: int = 0, group=None,
-        max_block_bytes: int = 2 << 30):
+        max_block_bytes: int = 2 << 30, pending=None):
     """Exact k nearest neighbours of every row among all rows (self excluded): (idx[n,k] int32, d2[n,k] int64).
 
     zh is the k-blocked operand [kdim/64, n, 64] written by gridb200_transform / gridb200_knn_prepare.
@@ -685,7 +696,7 @@ def knn(zh: torch.Tensor, kdim: int, norms: torch.Tensor, k: int, vmax: int, imp
     else:
         best_d2, best_idx = knn_init(n, k, zh.device)
     knn_block(zh, norms, 0, zh, norms, 0, kdim, vmax, best_d2, best_idx, impl=impl, group=group,
-              max_block_bytes=max_block_bytes, padded=padded)
+              max_block_bytes=max_block_bytes, padded=padded, pending=pending)
     return best_idx, best_d2
 
 
@@ -766,14 +777,15 @@ def synth_depth(seed: int, n: int, b: int, row0: int = 0, col0: int = 0, device=
 def run_chain(depth: torch.Tensor, b: int, counts: torch.Tensor, p: Params, impl: int = 0, group=None,
               bin_sizes: list[int] | None = None):
     """normalize -> kNN -> dipCN with everything resident on the device (the benchmarked path)."""
-    res = normalize(depth, b, p, want_zq=False, want_zh=True, group=group, bin_sizes=bin_sizes)
+    res = normalize(depth, b, p, want_zq=False, want_zh=True, group=group, bin_sizes=bin_sizes, defer_norms=True)
+    pending = res.extra.pop("norms_pending", None)
     if res.rw == 0:
         raise ValueError("no bins selected")
     if res.zh is None:  # this rank's slice holds no selected bin: contribute a zero partial
         res.zh = torch.zeros((1, res.n, 64), dtype=torch.float16, device=depth.device)
         res.kdim, res.norms = 64, torch.zeros(res.n, dtype=torch.int64, device=depth.device)
         _all_reduce(res.norms, group)
-    idx, d2 = knn(res.zh, res.kdim, res.norms, p.num_neighbors, p.zclip, impl=impl, group=group)
+    idx, d2 = knn(res.zh, res.kdim, res.norms, p.num_neighbors, p.zclip, impl=impl, group=group, pending=pending)
     has = torch.ones(res.n, dtype=torch.uint8, device=depth.device)
     cn = dipcn(counts, has, res.scale_q, idx, p.n_nbr)
     return res, idx, d2, cn
