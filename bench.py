@@ -51,9 +51,10 @@ def parse_args():
     ap.add_argument("--cpu-budget", type=float, default=0.0,
                     help="seconds of CPU work the CPU arm may use (default: 150 for --impl reference, 25 for the cpu_baseline leg)")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--host-format", choices=["packed", "u16", "f32"], default="packed",
-                    help="e2e host buffer: the product's host format -- hundredths bit-packed in the smallest width that fits "
-                         "the cohort (13 bits for a 30x cohort) + escape list --, its 16-bit variant, or raw fp32")
+    ap.add_argument("--host-format", choices=["packed", "abs", "u16", "f32"], default="packed",
+                    help="e2e host buffer: the product's host format -- bit-packed codes in the smallest form that fits the "
+                         "cohort: absolute hundredths (13 bits for a 30x cohort) or residuals against sample depth x bin bias "
+                         "(11 bits), + escape list --, 'abs' = absolute codes only, its 16-bit variant, or raw fp32")
     ap.add_argument("--device-format", choices=["u16", "f32"], default="u16",
                     help="resident form of the depth matrix: uint16 hundredths + escape table (2 bytes per cell, the default; "
                          "bit-identical results) or the packed fp32 matrix (4 bytes per cell)")
@@ -595,8 +596,8 @@ def run_ours(a):
             u16_dev = isinstance(depth, engine.Depth16)
             # (the host buffer is built from the fp32 form of the same synthetic cohort, regenerated for the purpose)
             d32 = engine.synth_depth(SEED, a.samples, b_local, 0, lo, device=dev) if u16_dev else depth
-            if a.host_format in ("packed", "u16"):
-                host = engine.pack_depth(d32, b_local, bits="auto" if a.host_format == "packed" else 16)
+            if a.host_format in ("packed", "abs", "u16"):
+                host = engine.pack_depth(d32, b_local, bits={"packed": "best", "abs": "auto", "u16": 16}[a.host_format])
                 host_bytes = host.nbytes
             else:
                 if u16_dev:
@@ -640,7 +641,9 @@ def run_ours(a):
             e2e = {"value": a.samples / (float(te.item()) / 1e3), "unit": "samples/s",
                    "h2d_bytes_per_step": int(h2d.item()), "d2h_bytes_per_step": int(sum(o.numel() * o.element_size() for o in outs)),
                    "ms_per_step": float(te.item()),
-                   "host_format": (f"hundredths in {host.bits} bits per cell + escape list ({host.esc_cell.numel()} cells), unpacked "
+                   "host_format": (("residuals against the rank-one prediction (sample depth x bin bias)" if host.relative
+                                    else "hundredths") +
+                                   f" in {host.bits} bits per cell + escape list ({host.esc_cell.numel()} cells), unpacked "
                                    "on the device into the " + ("2-byte matrix" if u16_dev else "bit-identical fp32 matrix"))
                    if a.host_format != "f32" else "fp32",
                    # the end-to-end steps went through the host format: same cohort, so the same lists as the checked step

@@ -56,9 +56,9 @@ SIGNATURES = {
     "gridb200_depth_pack_u16": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp]),
     "gridb200_depth_unpack_u16": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _i64, _vp, _vp, _i64, _i64, _vp]),
     "gridb200_depth_packed_row_words": (_i64, [_i64, _i32]),
-    "gridb200_depth_pack_bits": (C.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp]),
-    "gridb200_depth_unpack_bits": (C.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i64, _vp, _vp, _i64, _i64, _vp]),
-    "gridb200_depth_unpack_bits_u16": (C.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _i64, _vp]),
+    "gridb200_depth_pack_bits": (C.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _i64, _i64, _vp, _vp, _i64, _vp, _vp]),
+    "gridb200_depth_unpack_bits": (C.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _i64, _vp, _vp, _i64, _i64, _vp]),
+    "gridb200_depth_unpack_bits_u16": (C.c_int, [_vp, _i64, _i64, _i64, _i32, _vp, _vp, _vp, _i64, _vp]),
     "gridb200_col_row_raw_stats_u16": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp]),
     "gridb200_row_stats_fused_u16": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _sz, _vp]),
     "gridb200_row_means_exact_u16": (C.c_int, [_vp, _i64, _i64, _i64, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -273,7 +273,16 @@ __global__ void k_patch_depth(const int64_t* __restrict__ cell, const float* __r
 // A 30x cohort's hundredths sit below 2^13, so 13 bits per cell carry the matrix and PCIe -- what the end-to-end step is
 // bound by -- moves 19 % fewer bytes.  Layout: a row is a sequence of groups of 32 cells; a group is `bits` 32-bit words
 // holding a little-endian bit stream (cell c of the group at bit c * bits).  The all-ones code is the escape.
+//
+// Relative codes (row_q / col_q given).  Coverage is, to first order, (sample's overall depth) x (bin's bias): with
+// pred(i, j) = (row_q[i] * col_q[j] + 2048) >> 12  (col_q = the bin's mean hundredths, row_q = 4096 x the sample's mean
+// over the cohort mean -- integers, so packer and unpacker agree exactly) a present cell is stored as
+// h - pred + 2^(bits-1); 0 stays "absent" and all-ones the escape.  What is left is the cell's own noise, a few hundred
+// hundredths wide: 11 bits where the absolute value needs 13.
+__device__ __forceinline__ int rel_pred(int rq, int cq) { return (int)(((unsigned)rq * (unsigned)cq + 2048u) >> 12); }
+
 __global__ void __launch_bounds__(256) k_pack_bits(const float* __restrict__ depth, int64_t b, int64_t ld, int bits,
+                                                   const int* __restrict__ row_q, const int* __restrict__ col_q,
                                                    uint32_t* __restrict__ out, int64_t ldw, int64_t row0_global,
                                                    int64_t* __restrict__ esc_cell, float* __restrict__ esc_val,
                                                    int64_t esc_cap, unsigned long long* __restrict__ esc_count) {
@@ -291,7 +300,13 @@ __global__ void __launch_bounds__(256) k_pack_bits(const float* __restrict__ dep
       const float x = p[c];
       const int h = depth_hundredths(x);
       code = (uint32_t)h;
-      if ((uint32_t)h >= esc || !(x < 41943.04f)) {
+      bool out_of_range = (uint32_t)h >= esc || !(x < 41943.04f);
+      if (row_q && h > 0) {  // relative: the residual against the rank-one prediction, biased to the middle of the range
+        const int r = h - rel_pred(row_q[i], col_q[g * 32 + c]) + (1 << (bits - 1));
+        out_of_range = r < 1 || r >= (int)esc || h >= 0xFFFF || !(x < 41943.04f);
+        code = (uint32_t)r;
+      }
+      if (out_of_range) {
         code = esc;
         const unsigned long long slot = atomicAdd(esc_count, 1ULL);
         if ((int64_t)slot < esc_cap) esc_cell[slot] = (row0_global + i) * b + (g * 32 + c), esc_val[slot] = x;
@@ -309,6 +324,7 @@ __global__ void __launch_bounds__(256) k_pack_bits(const float* __restrict__ dep
 
 // thread = 4 consecutive cells -> one float4 store; the codes are read through L1 (adjacent threads share words)
 __global__ void __launch_bounds__(256) k_unpack_bits(const uint32_t* __restrict__ src, int64_t b, int64_t ldw, int bits,
+                                                     const int* __restrict__ row_q, const int* __restrict__ col_q,
                                                      float* __restrict__ depth, int64_t ld) {
   const int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   const int64_t i = blockIdx.y;
@@ -322,7 +338,9 @@ __global__ void __launch_bounds__(256) k_unpack_bits(const uint32_t* __restrict_
     const int w = bit >> 5, sh = bit & 31;
     uint32_t v = __ldg(s + w) >> sh;
     if (sh + bits > 32) v |= __ldg(s + w + 1) << (32 - sh);
-    f[t] = __fdiv_rn((float)(v & mask), 100.0f);   // (the escape code is overwritten by k_patch_depth)
+    v &= mask;
+    if (row_q && v != 0 && v != mask && j + t < b) v = (uint32_t)(rel_pred(row_q[i], col_q[j + t]) + (int)v - (1 << (bits - 1)));
+    f[t] = __fdiv_rn((float)v, 100.0f);   // (the escape code is overwritten by k_patch_depth)
   }
   float* d = depth + i * ld + j;
   if (j + 4 <= b && (reinterpret_cast<uintptr_t>(d) & 15) == 0) *reinterpret_cast<float4*>(d) = make_float4(f[0], f[1], f[2], f[3]);
@@ -333,6 +351,7 @@ __global__ void __launch_bounds__(256) k_unpack_bits(const uint32_t* __restrict_
 // bit-packed codes -> the 2-byte DEVICE matrix (uint16 hundredths; the width's escape code becomes 0xFFFF): what the
 // step-4 kernels read when the matrix is kept in 2 bytes per cell (gridb200_*_u16)
 __global__ void __launch_bounds__(256) k_unpack_bits_u16(const uint32_t* __restrict__ src, int64_t b, int64_t ldw, int bits,
+                                                         const int* __restrict__ row_q, const int* __restrict__ col_q,
                                                          uint16_t* __restrict__ out, int64_t ldo) {
   const int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   const int64_t i = blockIdx.y;
@@ -347,7 +366,9 @@ __global__ void __launch_bounds__(256) k_unpack_bits_u16(const uint32_t* __restr
     uint32_t v = __ldg(s + w) >> sh;
     if (sh + bits > 32) v |= __ldg(s + w + 1) << (32 - sh);
     v &= mask;
-    c[t] = (j + t < b) ? (v == mask ? 0xFFFFu : v) : 0u;
+    const bool is_esc = v == mask;
+    if (row_q && v != 0 && !is_esc && j + t < b) v = (uint32_t)(rel_pred(row_q[i], col_q[j + t]) + (int)v - (1 << (bits - 1)));
+    c[t] = (j + t < b) ? (is_esc ? 0xFFFFu : (v & 0xFFFFu)) : 0u;
   }
   *reinterpret_cast<uint2*>(out + i * ldo + j) = make_uint2(c[0] | (c[1] << 16), c[2] | (c[3] << 16));  // ldo % 4 == 0
 }
@@ -355,13 +376,16 @@ __global__ void __launch_bounds__(256) k_unpack_bits_u16(const uint32_t* __restr
 }  // namespace g2
 
 extern "C" int gridb200_depth_unpack_bits_u16(const uint32_t* src, int64_t n, int64_t b, int64_t ldw, int32_t bits,
-                                              uint16_t* out, int64_t ldo, void* stream) {
+                                              const int32_t* row_q, const int32_t* col_q, uint16_t* out, int64_t ldo,
+                                              void* stream) {
   using namespace g2;
   G2_REQUIRE(src && out && n > 0 && b > 0 && n <= 65535, GRIDB200_EINVAL, "bad argument (rows per call <= 65535)");
+  G2_REQUIRE((row_q == nullptr) == (col_q == nullptr), GRIDB200_EINVAL, "relative codes need both row_q and col_q");
   G2_REQUIRE(bits >= 9 && bits <= 15 && ldw >= ((b + 31) / 32 * bits), GRIDB200_EINVAL, "bits must be 9..15 and ldw cover whole groups");
   G2_REQUIRE(ldo >= (b + 3) / 4 * 4 && ldo % 4 == 0 && (reinterpret_cast<uintptr_t>(out) & 7) == 0, GRIDB200_EINVAL,
              "output rows must be 8-byte aligned with ldo a multiple of 4 and >= roundup4(b)");
-  k_unpack_bits_u16<<<dim3((unsigned)((b + 1023) / 1024), (unsigned)n), 256, 0, as_stream(stream)>>>(src, b, ldw, bits, out, ldo);
+  k_unpack_bits_u16<<<dim3((unsigned)((b + 1023) / 1024), (unsigned)n), 256, 0, as_stream(stream)>>>(src, b, ldw, bits, row_q,
+                                                                                                     col_q, out, ldo);
   G2_LAUNCHED();
   return 0;
 }
@@ -371,10 +395,11 @@ extern "C" int64_t gridb200_depth_packed_row_words(int64_t b, int32_t bits) {
   return ((b + 31) / 32 * bits + 3) / 4 * 4;  // whole groups, rows 16-byte aligned
 }
 
-extern "C" int gridb200_depth_pack_bits(const float* depth, int64_t n, int64_t b, int64_t ld, int32_t bits, uint32_t* out,
-                                        int64_t ldw, int64_t row0, int64_t* esc_cell, float* esc_val, int64_t esc_cap,
-                                        int64_t* esc_count, void* stream) {
+extern "C" int gridb200_depth_pack_bits(const float* depth, int64_t n, int64_t b, int64_t ld, int32_t bits,
+                                        const int32_t* row_q, const int32_t* col_q, uint32_t* out, int64_t ldw, int64_t row0,
+                                        int64_t* esc_cell, float* esc_val, int64_t esc_cap, int64_t* esc_count, void* stream) {
   using namespace g2;
+  G2_REQUIRE((row_q == nullptr) == (col_q == nullptr), GRIDB200_EINVAL, "relative codes need both row_q and col_q");
   G2_REQUIRE(depth && out && esc_count && n > 0 && b > 0 && ld >= b && n <= 65535, GRIDB200_EINVAL,
              "bad argument (rows per call <= 65535)");
   G2_REQUIRE(bits >= 9 && bits <= 15 && ldw >= gridb200_depth_packed_row_words(b, bits), GRIDB200_EINVAL,
@@ -382,21 +407,24 @@ extern "C" int gridb200_depth_pack_bits(const float* depth, int64_t n, int64_t b
   G2_REQUIRE(esc_cap == 0 || (esc_cell && esc_val), GRIDB200_EINVAL, "escape arrays missing");
   const int64_t groups = (b + 31) / 32;
   k_pack_bits<<<dim3((unsigned)((groups + 255) / 256), (unsigned)n), 256, 0, as_stream(stream)>>>(
-      depth, b, ld, bits, out, ldw, row0, esc_cell, esc_val, esc_cap, reinterpret_cast<unsigned long long*>(esc_count));
+      depth, b, ld, bits, row_q, col_q, out, ldw, row0, esc_cell, esc_val, esc_cap,
+      reinterpret_cast<unsigned long long*>(esc_count));
   G2_LAUNCHED();
   return 0;
 }
 
-extern "C" int gridb200_depth_unpack_bits(const uint32_t* src, int64_t n, int64_t b, int64_t ldw, int32_t bits, float* depth,
-                                          int64_t ld, const int64_t* esc_cell, const float* esc_val, int64_t esc_count,
-                                          int64_t row0, void* stream) {
+extern "C" int gridb200_depth_unpack_bits(const uint32_t* src, int64_t n, int64_t b, int64_t ldw, int32_t bits,
+                                          const int32_t* row_q, const int32_t* col_q, float* depth, int64_t ld,
+                                          const int64_t* esc_cell, const float* esc_val, int64_t esc_count, int64_t row0,
+                                          void* stream) {
   using namespace g2;
+  G2_REQUIRE((row_q == nullptr) == (col_q == nullptr), GRIDB200_EINVAL, "relative codes need both row_q and col_q");
   G2_REQUIRE(src && depth && n > 0 && b > 0 && ld >= b && n <= 65535, GRIDB200_EINVAL, "bad argument (rows per call <= 65535)");
   G2_REQUIRE(bits >= 9 && bits <= 15 && ldw >= gridb200_depth_packed_row_words(b, bits), GRIDB200_EINVAL,
              "bits must be 9..15 and ldw at least gridb200_depth_packed_row_words(b, bits)");
   G2_REQUIRE(esc_count == 0 || (esc_cell && esc_val), GRIDB200_EINVAL, "escape arrays missing");
   cudaStream_t st = as_stream(stream);
-  k_unpack_bits<<<dim3((unsigned)((b + 1023) / 1024), (unsigned)n), 256, 0, st>>>(src, b, ldw, bits, depth, ld);
+  k_unpack_bits<<<dim3((unsigned)((b + 1023) / 1024), (unsigned)n), 256, 0, st>>>(src, b, ldw, bits, row_q, col_q, depth, ld);
   G2_LAUNCHED();
   if (esc_count > 0) {
     k_patch_depth<<<(unsigned)((esc_count + 255) / 256), 256, 0, st>>>(esc_cell, esc_val, esc_count, b, row0, n, depth, ld);

@@ -176,11 +176,18 @@ class Depth16:
         if cell.numel() == 0:
             self.esc_key = self.esc_h = self.esc_cols = None
             return
-        hundred = torch.full((1,), 100.0, dtype=torch.float64)
-        h = torch.round(val.cpu().double() * hundred).clamp(max=(1 << 22) - 1).to(torch.int32)
-        key, order = torch.sort(cell.cpu().to(torch.int64))
-        self.esc_key, self.esc_h = key.to(dev), h[order].to(dev)
-        self.esc_cols = torch.unique(key % (self.esc_b or self.b)).to(torch.int32).to(dev)
+        # (on the device: a relative host format can carry millions of escapes; val * 100 is exact in fp64)
+        h = torch.round(val.to(dev, non_blocking=True).double() * 100.0).clamp(max=(1 << 22) - 1).to(torch.int32)
+        self.set_escape_table(cell.to(dev, non_blocking=True).to(torch.int64), h)
+
+    def set_escape_table(self, cell: torch.Tensor, h: torch.Tensor) -> None:
+        """The same from device tensors: cell keys int64 (unsorted), true hundredths int32."""
+        if cell.numel() == 0:
+            self.esc_key = self.esc_h = self.esc_cols = None
+            return
+        key, order = torch.sort(cell)
+        self.esc_key, self.esc_h = key, h[order]
+        self.esc_cols = torch.unique(key % (self.esc_b or self.b)).to(torch.int32)
 
 
 def check_depth(depth, b: int) -> tuple[int, int]:
@@ -804,10 +811,24 @@ class PackedDepth:
     esc_cell: torch.Tensor
     esc_val: torch.Tensor
     bits: int = 16
+    row_q: torch.Tensor | None = None   # relative codes (bits < 16 only): int32 [n] and [b] on the host, see
+    col_q: torch.Tensor | None = None   # gridb200_depth_pack_bits -- a cell travels as its residual against row_q x col_q
+
+    @property
+    def relative(self) -> bool:
+        return self.row_q is not None
+
+    @property
+    def n_big(self) -> int:
+        """Escape cells that do not fit the 2-byte device matrix either (depth >= 655.35); counted once, on the host."""
+        if getattr(self, "_n_big", None) is None:
+            self._n_big = int((self.esc_val >= 655.345).sum()) if self.esc_val.numel() else 0
+        return self._n_big
 
     @property
     def nbytes(self) -> int:
-        return self.codes.numel() * self.codes.element_size() + self.esc_cell.numel() * 12
+        tables = (self.row_q.numel() + self.col_q.numel()) * 4 if self.relative else 0
+        return self.codes.numel() * self.codes.element_size() + self.esc_cell.numel() * 12 + tables
 
 
 def choose_bits(depth: torch.Tensor, b: int, max_escape_frac: float = 2e-4) -> int:
@@ -822,15 +843,65 @@ def choose_bits(depth: torch.Tensor, b: int, max_escape_frac: float = 2e-4) -> i
     return 16
 
 
-def pack_depth(depth: torch.Tensor, b: int, chunk_rows: int = 256, pin: bool = True, bits: int | str = 16) -> PackedDepth:
-    """Device fp32 depth[n, ld] -> PackedDepth on the host (export / side-car / bench set-up).  bits: 16, 9..15, or
-    "auto" (choose_bits)."""
+def rank_one_tables(depth: torch.Tensor, b: int):
+    """(row_q int32 [n], col_q int32 [b]) of the relative host format from the device fp32 matrix: col_q = the bin's mean
+    hundredths over its present cells, row_q = 4096 x (the sample's mean over the cohort mean) -- from the exact integer
+    sums of the raw statistics pass, so pred(i, j) = (row_q[i] * col_q[j] + 2048) >> 12 tracks depth_i x bias_j."""
+    n, ld = check_depth(depth, b)
+    dev = depth.device
+    colsum, colcnt = torch.empty(b, dtype=torch.int64, device=dev), torch.empty(b, dtype=torch.int32, device=dev)
+    rowsum, rowcnt = torch.empty(n, dtype=torch.int64, device=dev), torch.empty(n, dtype=torch.int32, device=dev)
+    _dcall("gridb200_col_row_raw_stats", depth, n, b, ld, ptr(colsum), ptr(colcnt), ptr(rowsum), ptr(rowcnt), _stream())
+    cmean = colsum.double() / colcnt.clamp(min=1).double()
+    rmean = rowsum.double() / rowcnt.clamp(min=1).double()
+    gmean = (rowsum.sum().double() / rowcnt.sum().clamp(min=1).double()).clamp(min=1.0)
+    col_q = torch.round(cmean).clamp(0, 65535).to(torch.int32)
+    row_q = torch.round(rmean / gmean * 4096.0).clamp(0, 32767).to(torch.int32)
+    return row_q, col_q
+
+
+def choose_format(depth: torch.Tensor, b: int, max_escape_frac: float = 2e-3):
+    """(bits, row_q, col_q): the host format with the fewest bytes per cell, judged on a sample of rows -- absolute codes
+    (row_q = col_q = None) or residuals against the rank-one prediction; an escape costs 12 bytes, and at most
+    max_escape_frac of the cells may be escapes (each one is a scattered write on the device)."""
+    n = depth.shape[0]
+    rows = torch.linspace(0, n - 1, min(n, 64)).long().to(depth.device)
+    h = torch.round(depth[rows, :b].double() * 100.0).to(torch.int64)
+    present = h > 0
+    best = (16 / 8.0, 16, None, None)
+    for bits in range(9, 16):
+        frac = float((h >= (1 << bits) - 1).double().mean())
+        if frac <= max_escape_frac and bits / 8.0 + 12.0 * frac < best[0]:
+            best = (bits / 8.0 + 12.0 * frac, bits, None, None)
+    row_q, col_q = rank_one_tables(depth, b)
+    pred = (row_q[rows].to(torch.int64)[:, None] * col_q.to(torch.int64)[None, :] + 2048) >> 12
+    for bits in range(9, 16):
+        r = h - pred + (1 << (bits - 1))
+        bad = present & ((r < 1) | (r >= (1 << bits) - 1) | (h >= 0xFFFF))
+        frac = float(bad.double().mean())
+        if frac <= max_escape_frac and bits / 8.0 + 12.0 * frac < best[0]:
+            best = (bits / 8.0 + 12.0 * frac, bits, row_q, col_q)
+    return best[1], best[2], best[3]
+
+
+def pack_depth(depth: torch.Tensor, b: int, chunk_rows: int = 256, pin: bool = True, bits: int | str = 16,
+               tables: tuple[torch.Tensor, torch.Tensor] | None = None) -> PackedDepth:
+    """Device fp32 depth[n, ld] -> PackedDepth on the host (export / side-car / bench set-up).  bits: 16, 9..15, "auto"
+    (choose_bits: absolute codes) or "best" (choose_format: absolute or relative, whichever is smaller); tables =
+    (row_q, col_q) on the device forces relative codes of the given width."""
     n, ld = depth.shape[0], depth.stride(0)
     dev = depth.device
+    row_q = col_q = None
     if bits == "auto":
         bits = choose_bits(depth, b)
+    elif bits == "best":
+        bits, row_q, col_q = choose_format(depth, b)
+    if tables is not None:
+        row_q, col_q = (t.to(dev, torch.int32).contiguous() for t in tables)
+        assert row_q.numel() == n and col_q.numel() == b
     bits = int(bits)
     if bits == 16:
+        assert row_q is None, "relative codes are a bit-packed format (9..15 bits)"
         ldo, dt = (b + 7) // 8 * 8, torch.uint16
     else:
         ldo, dt = int(_lib.load().gridb200_depth_packed_row_words(b, bits)), torch.int32
@@ -849,12 +920,19 @@ def pack_depth(depth: torch.Tensor, b: int, chunk_rows: int = 256, pin: bool = T
                 call("gridb200_depth_pack_u16", depth.data_ptr() + r0 * ld * 4, c, b, ld, ptr(stage), ldo, r0, ptr(esc_cell),
                      ptr(esc_val), cap, ptr(cnt), _stream())
             else:
-                call("gridb200_depth_pack_bits", depth.data_ptr() + r0 * ld * 4, c, b, ld, bits, ptr(stage), ldo, r0,
+                call("gridb200_depth_pack_bits", depth.data_ptr() + r0 * ld * 4, c, b, ld, bits,
+                     (row_q.data_ptr() + r0 * 4) if row_q is not None else None, ptr(col_q), ptr(stage), ldo, r0,
                      ptr(esc_cell), ptr(esc_val), cap, ptr(cnt), _stream())
             codes[r0:r0 + c].copy_(stage[:c])
         m = int(cnt.item())
         if m <= cap:
-            return PackedDepth(codes, n, b, esc_cell[:m].cpu(), esc_val[:m].cpu(), bits)
+            def host(t):  # (the escape list and the tables travel with every upload: pinned like the codes)
+                out = torch.empty(t.shape, dtype=t.dtype, pin_memory=pin)
+                out.copy_(t)
+                return out
+
+            return PackedDepth(codes, n, b, host(esc_cell[:m]), host(esc_val[:m]), bits,
+                               host(row_q) if row_q is not None else None, host(col_q) if col_q is not None else None)
         cap = m
 
 
@@ -877,6 +955,8 @@ def upload_packed(packed: PackedDepth, depth: torch.Tensor, chunk_rows: int = 12
     n_esc = packed.esc_cell.numel()
     esc_cell = packed.esc_cell.to(dev, non_blocking=True) if n_esc else None
     esc_val = packed.esc_val.to(dev, non_blocking=True) if n_esc else None
+    row_q = packed.row_q.to(dev, non_blocking=True) if packed.relative else None
+    col_q = packed.col_q.to(dev, non_blocking=True) if packed.relative else None
     for s in range(2):
         st["free"][s].record(main)
     for t, r0 in enumerate(range(0, n, chunk_rows)):
@@ -890,7 +970,8 @@ def upload_packed(packed: PackedDepth, depth: torch.Tensor, chunk_rows: int = 12
             call("gridb200_depth_unpack_u16", ptr(st["stage"][s]), c, b, lds, depth.data_ptr() + r0 * ld * 4, ld,
                  ptr(esc_cell), ptr(esc_val), n_esc, r0, main.cuda_stream)
         else:
-            call("gridb200_depth_unpack_bits", ptr(st["stage"][s]), c, b, lds, packed.bits, depth.data_ptr() + r0 * ld * 4, ld,
+            call("gridb200_depth_unpack_bits", ptr(st["stage"][s]), c, b, lds, packed.bits,
+                 (row_q.data_ptr() + r0 * 4) if row_q is not None else None, ptr(col_q), depth.data_ptr() + r0 * ld * 4, ld,
                  ptr(esc_cell), ptr(esc_val), n_esc, r0, main.cuda_stream)
         st["free"][s].record(main)
     return depth
@@ -906,8 +987,8 @@ def upload_packed16(packed: PackedDepth, out: Depth16, chunk_rows: int = 128) ->
     assert codes.shape[0] == n and out.b == b
     main = torch.cuda.current_stream(dev)
     out.row0, out.esc_b = 0, b
-    out.set_escapes(packed.esc_cell, packed.esc_val)
     if packed.bits == 16:
+        out.set_escapes(packed.esc_cell, packed.esc_val)
         assert packed.codes.stride(0) == ldo, "16-bit host codes are copied as they are: same leading dimension"
         codes.copy_(packed.codes, non_blocking=True)
         return out
@@ -921,6 +1002,8 @@ def upload_packed16(packed: PackedDepth, out: Depth16, chunk_rows: int = 128) ->
               "free": [torch.cuda.Event() for _ in range(2)]}
         _UPLOAD_STATE.clear()
         _UPLOAD_STATE[key] = st
+    row_q = packed.row_q.to(dev, non_blocking=True) if packed.relative else None
+    col_q = packed.col_q.to(dev, non_blocking=True) if packed.relative else None
     for s_ in range(2):
         st["free"][s_].record(main)
     for t, r0 in enumerate(range(0, n, chunk_rows)):
@@ -930,17 +1013,24 @@ def upload_packed16(packed: PackedDepth, out: Depth16, chunk_rows: int = 128) ->
             st["stage"][s_][:c].copy_(packed.codes[r0:r0 + c], non_blocking=True)
             st["done"][s_].record(st["copy"])
         main.wait_event(st["done"][s_])
-        call("gridb200_depth_unpack_bits_u16", ptr(st["stage"][s_]), c, b, lds, packed.bits, codes.data_ptr() + r0 * ldo * 2,
-             ldo, main.cuda_stream)
+        call("gridb200_depth_unpack_bits_u16", ptr(st["stage"][s_]), c, b, lds, packed.bits,
+             (row_q.data_ptr() + r0 * 4) if row_q is not None else None, ptr(col_q), codes.data_ptr() + r0 * ldo * 2, ldo,
+             main.cuda_stream)
         st["free"][s_].record(main)
-    if out.n_esc:  # escapes of the narrow host width that DO fit 16 bits go back into the matrix; the rest stay in the table
-        fits = out.esc_h < 0xFFFF
-        if bool(fits.any()):
-            k = out.esc_key[fits]
-            codes.view(torch.int16).view(-1)[(k // b) * ldo + (k % b)] = out.esc_h[fits].to(torch.int16)   # (wraps: bit pattern)
-            keep = ~fits
-            out.esc_key, out.esc_h = (out.esc_key[keep], out.esc_h[keep]) if bool(keep.any()) else (None, None)
-            out.esc_cols = None if out.esc_key is None else torch.unique(out.esc_key % b).to(torch.int32)
+    # escapes of the narrow host width that DO fit 16 bits go back into the matrix (a scatter); the rest -- depths from
+    # 655.35 up, counted once on the host -- form the device's escape table
+    out.esc_key = out.esc_h = out.esc_cols = None
+    if packed.esc_cell.numel():
+        cell = packed.esc_cell.to(dev, non_blocking=True)
+        h = torch.round(packed.esc_val.to(dev, non_blocking=True).double() * 100.0).clamp(max=(1 << 22) - 1).to(torch.int32)
+        flat = codes.view(torch.int16).view(-1)
+        if packed.n_big == 0:
+            flat[(cell // b) * ldo + (cell % b)] = h.to(torch.int16)   # (wraps: bit pattern)
+        else:
+            fits = h < 0xFFFF
+            k = cell[fits]
+            flat[(k // b) * ldo + (k % b)] = h[fits].to(torch.int16)
+            out.set_escape_table(cell[~fits], h[~fits])
     return out
 
 

@@ -310,14 +310,20 @@ GRIDB200_API int gridb200_depth_unpack_u16(const uint16_t* src, int64_t n, int64
 /* The same with `bits` (9..15) per cell: a 30x cohort's hundredths sit below 2^13, and the end-to-end step is bound by
  * PCIe.  A row is a sequence of groups of 32 cells, a group `bits` little-endian 32-bit words (cell c at bit c*bits);
  * the all-ones code is the escape; rows are ldw words apart, ldw >= gridb200_depth_packed_row_words(b, bits)
- * (whole groups, 16-byte aligned).  Unpacking yields the same bit-identical fp32 matrix. */
+ * (whole groups, 16-byte aligned).  Unpacking yields the same bit-identical fp32 matrix.
+ * row_q [n] / col_q [b] (both or neither; NULL = absolute codes): RELATIVE codes.  Coverage is to first order
+ * (sample's depth) x (bin's bias), so with pred(i, j) = (row_q[i] * col_q[j] + 2048) >> 12 -- col_q = the bin's mean
+ * hundredths (<= 65535), row_q = 4096 x the sample's mean over the cohort mean (< 32768), integers so that packer and
+ * unpacker agree exactly -- a present cell travels as h - pred + 2^(bits-1); 0 stays "absent", all-ones the escape
+ * (residual out of range, or h >= 65535).  A 30x cohort then needs 11 bits where the absolute value needs 13. */
 GRIDB200_API int64_t gridb200_depth_packed_row_words(int64_t b, int32_t bits);
-GRIDB200_API int gridb200_depth_pack_bits(const float* depth, int64_t n, int64_t b, int64_t ld, int32_t bits, uint32_t* out,
-                             int64_t ldw, int64_t row0, int64_t* esc_cell, float* esc_val, int64_t esc_cap,
-                             int64_t* esc_count, void* stream);
+GRIDB200_API int gridb200_depth_pack_bits(const float* depth, int64_t n, int64_t b, int64_t ld, int32_t bits,
+                             const int32_t* row_q, const int32_t* col_q, uint32_t* out, int64_t ldw, int64_t row0,
+                             int64_t* esc_cell, float* esc_val, int64_t esc_cap, int64_t* esc_count, void* stream);
 GRIDB200_API int gridb200_depth_unpack_bits(const uint32_t* src, int64_t n, int64_t b, int64_t ldw, int32_t bits,
-                               float* depth, int64_t ld, const int64_t* esc_cell, const float* esc_val,
-                               int64_t esc_count, int64_t row0, void* stream);
+                               const int32_t* row_q, const int32_t* col_q, float* depth, int64_t ld,
+                               const int64_t* esc_cell, const float* esc_val, int64_t esc_count, int64_t row0,
+                               void* stream);
 
 /* ---- the depth matrix in 2 bytes per cell ON THE DEVICE ------------------------------------------------------------
  * uint16 hundredths, 0 = absent, rows ld elements apart (ld % 4 == 0, 8-byte aligned rows): the three step-4 passes then
@@ -329,7 +335,8 @@ GRIDB200_API int gridb200_depth_unpack_bits(const uint32_t* src, int64_t n, int6
  * lines) and the hot loops carry no escape test.  gridb200_depth_pack_u16 produces the
  * matrix from fp32, gridb200_depth_unpack_bits_u16 from the bit-packed host format (its escape code becomes 0xFFFF). */
 GRIDB200_API int gridb200_depth_unpack_bits_u16(const uint32_t* src, int64_t n, int64_t b, int64_t ldw, int32_t bits,
-                                   uint16_t* out, int64_t ldo, void* stream);
+                                   const int32_t* row_q, const int32_t* col_q, uint16_t* out, int64_t ldo,
+                                   void* stream);
 GRIDB200_API int gridb200_col_row_raw_stats_u16(const uint16_t* depth, int64_t n, int64_t b, int64_t ld,
                                    const int64_t* esc_key, const int32_t* esc_h, int64_t n_esc, int64_t esc_row0,
                                    int64_t esc_b, int64_t* colsum, int32_t* colcnt, int64_t* rowsum_all,

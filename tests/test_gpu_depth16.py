@@ -101,3 +101,49 @@ def test_chain_and_host_upload_through_u16(eng):
         torch.cuda.synchronize()
         assert torch.equal(out.codes.view(torch.int16)[:, :b], d16.codes.view(torch.int16)[:, :b])
         assert torch.equal(out.esc_key, d16.esc_key) and torch.equal(out.esc_h, d16.esc_h)
+
+
+@pytest.mark.parametrize("bits", ["best", 10, 11, 12])
+def test_relative_host_format_round_trips_into_both_device_forms(eng, bits):
+    """Residuals against the rank-one prediction (sample depth x bin bias) in 9..15 bits: the same fp32 matrix and the same
+    2-byte matrix + escape table come back, whatever the width -- a width that is too narrow only lengthens the escape
+    list.  Absent cells, cells far from the prediction, depths beyond the 2-byte range, a sample without data and a bin
+    without data are all in the cohort."""
+    n, b = 150, 4099
+    depth = eng.synth_depth(31, n, b)
+    depth[3, 40] = 0.0                    # absent
+    depth[4, 41] = 0.01                   # far below the prediction
+    depth[5, 42] = 399.5                  # far above it (an escape at every width), still a 2-byte value
+    depth[6, 4098] = 12345.67             # beyond the 2-byte range too
+    depth[9, :] = 0.0                     # a sample without data: row_q = 0
+    depth[:, 77] = 0.0                    # a bin without data: col_q = 0
+    depth[20, 77] = 31.25                 # ... but for one cell
+    want = depth.clone()
+    d16 = eng.to_depth16(depth, b)
+    if bits == "best":
+        packed = eng.pack_depth(depth, b, chunk_rows=64, bits="best")
+        assert packed.relative and packed.bits <= 12, "a 30x cohort is smaller as residuals (11-12 bits against 13)"
+    else:
+        packed = eng.pack_depth(depth, b, chunk_rows=64, bits=bits, tables=eng.rank_one_tables(depth, b))
+        assert packed.relative and packed.bits == bits
+    assert packed.row_q.dtype == torch.int32 and packed.col_q.numel() == b and int(packed.row_q[9]) == 0
+    cells = set(packed.esc_cell.tolist())
+    assert {5 * b + 42, 6 * b + 4098} <= cells and (3 * b + 40) not in cells
+    assert packed.n_big == 1
+    out = torch.full_like(depth, -1.0)
+    eng.upload_packed(packed, out, chunk_rows=37)
+    torch.cuda.synchronize()
+    assert torch.equal(out[:, :b].view(torch.int32), want[:, :b].view(torch.int32))
+    o16 = eng.Depth16(torch.full(d16.codes.shape, 7, dtype=torch.int16, device="cuda").view(torch.uint16), b)
+    eng.upload_packed16(packed, o16, chunk_rows=77)
+    torch.cuda.synchronize()
+    assert torch.equal(o16.codes.view(torch.int16)[:, :b], d16.codes.view(torch.int16)[:, :b])
+    assert torch.equal(o16.esc_key, d16.esc_key) and torch.equal(o16.esc_h, d16.esc_h)
+    assert torch.equal(o16.esc_cols, d16.esc_cols)
+    # without a cell beyond the 2-byte range every escape folds back into the matrix and no table is left
+    depth[6, 4098] = 30.0
+    p2 = eng.pack_depth(depth, b, bits=packed.bits, tables=(packed.row_q, packed.col_q))
+    assert p2.n_big == 0 and p2.esc_cell.numel() > 0
+    eng.upload_packed16(p2, o16)
+    torch.cuda.synchronize()
+    assert o16.esc_key is None and torch.equal(o16.codes.view(torch.int16)[:, :b], eng.to_depth16(depth, b).codes.view(torch.int16)[:, :b])
