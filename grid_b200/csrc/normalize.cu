@@ -942,7 +942,8 @@ __device__ __forceinline__ void transform_batch(const typename Cells<T>::Raw (&v
 }
 
 template <bool kZq, bool kZh, typename T>
-__global__ void __launch_bounds__(kThreads, 2) k_transform(const T* __restrict__ depth, const Esc esc, int64_t n, int64_t b,
+// (2-byte cells need half the row registers: three blocks fit an SM without spills, -2 %; four spill and lose 17 %)
+__global__ void __launch_bounds__(kThreads, (sizeof(T) == 2 && !kZq) ? 3 : 2) k_transform(const T* __restrict__ depth, const Esc esc, int64_t n, int64_t b,
                                                            int64_t ld, const double* __restrict__ row_factor,
                                                            const double* __restrict__ mu,
                                                            const int32_t* __restrict__ sel_pos,
