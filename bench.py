@@ -493,6 +493,18 @@ def ring_subrecord(a, dev, group, peaks):
            "gram_tflops_rank0_full_equiv": full / (gram_ms * 1e-3) / 1e12 if gram_ms else None,
            "hbm_gb_peak_rank0": round(torch.cuda.max_memory_allocated() / 1e9, 1),
            "depth_regenerated_outside_timed_region": bool(a.ring_regen)}
+    if a.timeline:
+        res = idx = d2 = cn = None
+        if a.ring_regen:
+            depth = engine.synth_depth(SEED, cnt[rank], b, off[rank], 0, device=dev)
+        barrier()
+        engine.TIMELINE = []
+        engine._tick("step >")
+        res, idx, d2, cn = step()
+        engine._tick("step <")
+        torch.cuda.synchronize()
+        rec["timeline"] = {"columns": ["label", "device ms", "host ms"], "rank": 0, "points": engine.timeline_summary()}
+        engine.TIMELINE = None
     if not a.no_check:
         rec["parity_check"] = parity_check(n_total, b, dict(num_neighbors=p.num_neighbors, n_nbr=p.n_nbr), dev, group, "rows",
                                            (off[rank], off[rank] + cnt[rank]), None, max(2, a.check_rows // world), res, idx, d2,

@@ -39,15 +39,25 @@ class HalfRingOps:
     new_lists(nrows) -> (d2 int64 [nrows, k], idx int32 [nrows, k]), empty (d2 = +inf, idx = -1)
     merge(row_lo, d2, idx)    merge candidate lists for the rows row_lo.. of the CURRENT REFERENCE BLOCK of this rank
                               (= all its rows in the in-core ring) into its running lists
+    before_hop(step)          optional: called at the start of every hop BEFORE the next shard's transfer is issued --
+                              the place for any small collective the hop's block needs (a collective issued later
+                              queues behind the multi-GB transfer on the communicator's stream and the block waits for
+                              the whole shard: 23 ms per hop at 25 000 x 1e6 on 4 GPUs, 50 ms at config 3)
     """
 
-    def __init__(self, new_lists, merge):
-        self.new_lists, self.merge = new_lists, merge
+    def __init__(self, new_lists, merge, before_hop=None):
+        self.new_lists, self.merge, self.before_hop = new_lists, merge, before_hop
 
 
 def half_ring_hops(world: int) -> int:
     """Last hop of the half ring: every unordered pair of ranks meets once within hops 0..world // 2."""
     return world // 2
+
+
+def _tick(label: str) -> None:
+    from . import engine as E
+
+    E._tick(label)
 
 
 def ring_knn(shard: torch.Tensor, shard_rows_max: int, counts: list[int], offsets: list[int], group, block_fn,
@@ -94,6 +104,8 @@ def ring_knn(shard: torch.Tensor, shard_rows_max: int, counts: list[int], offset
     for step in range(hops + 1):
         src = ring_source(rank, step, world)
         works = []
+        if half is not None and half.before_hop is not None:
+            half.before_hop(step)
         if step < hops:
             # pass the resident shard on and receive the next one into the other buffer WHILE this hop computes;
             # the collective library orders the transfer after everything already queued on the current stream,
@@ -103,6 +115,7 @@ def ring_knn(shard: torch.Tensor, shard_rows_max: int, counts: list[int], offset
             send_view = cur[: counts[src] * flat_per_row]
             ops = [dist.P2POp(dist.isend, send_view, nxt_rank, group), dist.P2POp(dist.irecv, recv_view, prv_rank, group)]
             works = dist.batch_isend_irecv(ops)
+            _tick(f"hop {step}: shard transfer issued")
         view = cur[: counts[src] * flat_per_row]
         if half is None:
             block_fn(step, src, view, counts[src], offsets[src])
@@ -135,8 +148,10 @@ def ring_knn(shard: torch.Tensor, shard_rows_max: int, counts: list[int], offset
                 ops += [dist.P2POp(dist.irecv, x, dist.get_global_rank(group, dst), group) for x in got]
             if ops:
                 pending.append((dist.batch_isend_irecv(ops), recv_rows, got, out))
+        _tick(f"hop {step}: block enqueued")
         for w in works:
             w.wait()
+        _tick(f"hop {step}: next shard here")
         # lists that arrived for the PREVIOUS hop are merged now, behind this hop's kernels: nobody waits for a peer
         while len(pending) > (1 if step < hops else 0):
             lw, rows, got, _keep = pending.pop(0)
@@ -182,10 +197,9 @@ def knn_rows(zh: torch.Tensor, kdim: int, norms: torch.Tensor, counts: list[int]
     def block(step, src, flat, n_ref, r_gid0, q_range=None, r_range=None, t_lists=None):
         ref = zh if step == 0 else flat.view(kdim // 64, n_ref, 64)  # hop 0 is the symmetric (same-operand) case
         tau_r = None
-        if t_lists is not None and E.fused_mode() != "0":
+        if t_lists is not None and tau_all[0] is not None:
             # the shard owner's current k-th best distances: what the fused epilogue filters the peer's candidates against
-            # (every rank is at the same hop; a value that is a hop stale only lets a few more candidates through)
-            tau_r = _all_gather_rows(best_d2[:, k - 1].contiguous(), counts, group)[r_gid0:r_gid0 + n_ref]
+            tau_r = tau_all[0][r_gid0:r_gid0 + n_ref]
         E.knn_block_auto(zh, norms, offsets[rank], ref, norms_all[r_gid0:r_gid0 + n_ref], r_gid0, kdim, vmax, best_d2,
                          best_idx, impl=impl, q_range=q_range, r_range=r_range, t_lists=t_lists, tau_r=tau_r,
                          symmetric=step == 0)
@@ -193,6 +207,15 @@ def knn_rows(zh: torch.Tensor, kdim: int, norms: torch.Tensor, counts: list[int]
     def merge(lo, d2_in, idx_in):
         with E._mark("merge_lists"):
             E.merge_lists(d2_in, idx_in, best_d2[lo:lo + d2_in.shape[0]], best_idx[lo:lo + d2_in.shape[0]])
+
+    tau_all = [None]
+
+    def before_hop(step):
+        # every rank's current k-th best distances, gathered BEFORE this hop's shard transfer is queued (every rank is at
+        # the same hop; a value that is a hop stale would only let a few more candidates through)
+        tau_all[0] = None
+        if step >= 1 and E.fused_mode() != "0":
+            tau_all[0] = _all_gather_rows(best_d2[:, k - 1].contiguous(), counts, group)
 
     # The Gram kernel shares the GPU with NCCL's send/recv kernel while a transfer is in flight.  Its default
     # schedule (cluster launch control) adapts to the SMs it gets.  GRIDB200_RING_COMM_SMS=<n> instead selects the
@@ -202,7 +225,7 @@ def knn_rows(zh: torch.Tensor, kdim: int, norms: torch.Tensor, counts: list[int]
     comm_sms = int(os.environ.get("GRIDB200_RING_COMM_SMS", "0")) if world > 1 else 0
     sms = torch.cuda.get_device_properties(dev).multi_processor_count
     full_ring = os.environ.get("GRIDB200_RING", "half") == "full"
-    half = None if full_ring else HalfRingOps(lambda m: E.knn_init(m, k, dev), merge)
+    half = None if full_ring else HalfRingOps(lambda m: E.knn_init(m, k, dev), merge, before_hop)
     extra.update(ring_schedule="full" if full_ring else "half", ring_hops=(world - 1) if full_ring else half_ring_hops(world))
     call("gridb200_gram_set_max_pairs", max(1, (sms - comm_sms) // 2) if comm_sms else 0)
     try:
