@@ -147,3 +147,57 @@ def test_relative_host_format_round_trips_into_both_device_forms(eng, bits):
     eng.upload_packed16(p2, o16)
     torch.cuda.synchronize()
     assert o16.esc_key is None and torch.equal(o16.codes.view(torch.int16)[:, :b], eng.to_depth16(depth, b).codes.view(torch.int16)[:, :b])
+
+
+def _decode_row(words, b, bits, row_q, col_q):
+    """The bit-packed host format restated in plain Python from include/gridb200.h: groups of 32 cells, `bits` 32-bit
+    little-endian words per group, cell c at bit c * bits; 0 = absent, all-ones = escape (returned as -1); relative codes
+    add pred = (row_q * col_q[j] + 2048) >> 12 and subtract the bias 2^(bits-1)."""
+    mask = (1 << bits) - 1
+    out = []
+    for g in range((b + 31) // 32):
+        stream = 0
+        for w in range(bits):
+            stream |= (int(words[g * bits + w]) & 0xFFFFFFFF) << (32 * w)
+        for c in range(32):
+            j = g * 32 + c
+            if j >= b:
+                break
+            v = (stream >> (c * bits)) & mask
+            if v == 0 or v == mask:
+                out.append(0 if v == 0 else -1)
+            elif row_q is None:
+                out.append(v)
+            else:
+                out.append(((row_q * int(col_q[j]) + 2048) >> 12) + v - (1 << (bits - 1)))
+    return out
+
+
+@pytest.mark.parametrize("relative", [False, True])
+def test_bit_packed_codes_decode_as_the_header_says(eng, relative):
+    """Not a round trip through our own unpacker: the packed words are decoded by the plain-Python restatement of the
+    documented layout and must give the cohort's hundredths (escapes aside, which must be exactly the listed cells)."""
+    from grid_b200 import synth
+
+    n, b = 6, 1000
+    depth = eng.synth_depth(31, n, b)
+    depth[2, 7] = 0.0
+    depth[3, 999] = 400.0
+    h = synth.depth_hundredths(31, n, b)
+    h[2, 7], h[3, 999] = 0, 40000
+    if relative:
+        packed = eng.pack_depth(depth, b, bits=11, tables=eng.rank_one_tables(depth, b))
+        rq, cq = packed.row_q.tolist(), packed.col_q.tolist()
+    else:
+        packed = eng.pack_depth(depth, b, bits=13)
+        rq, cq = [None] * n, None
+    esc = set(packed.esc_cell.tolist())
+    words = packed.codes.numpy()
+    for i in range(n):
+        got = _decode_row(words[i], b, packed.bits, rq[i], cq)
+        for j in range(b):
+            if got[j] < 0:
+                assert i * b + j in esc, (i, j)
+            else:
+                assert i * b + j not in esc and got[j] == int(h[i, j]), (i, j, got[j], int(h[i, j]))
+    assert 3 * b + 999 in esc and abs(float(packed.esc_val[packed.esc_cell.tolist().index(3 * b + 999)]) - 400.0) < 1e-3
