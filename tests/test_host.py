@@ -207,3 +207,58 @@ def test_handoff_entries_are_tied_to_the_file(tmp_path):
     H.put(tmp_path / "link.gz", x=4)
     assert H.take(q) == {"x": 4}                                 # keyed by real path
     assert H.enabled({}) and H.enabled({"gpu": None}) and not H.enabled({"gpu": {"device_handoff": False}})
+
+
+def test_multi_gpu_host_helpers():
+    """Pure host logic of the multi-GPU paths: bin slices (contiguous, quantum-aligned, covering), the device list of the
+    additive `gpu` config key, the sharding rule, and the Gram tile count bench.py's roofline uses."""
+    torch = pytest.importorskip("torch")
+    from grid_b200 import engine, multigpu
+
+    for b, world, q in ((2_900_000, 8, 64), (1000, 3, 4), (63, 4, 64), (1, 2, 4)):
+        sl = multigpu.bin_slices(b, world, q)
+        assert len(sl) == world and sl[0][0] == 0 and sl[-1][1] == b
+        assert all(a <= z for a, z in sl) and all(sl[r][1] == sl[r + 1][0] for r in range(world - 1))
+        assert all(a % q == 0 for a, _ in sl if a < b)
+    assert multigpu.configured_devices({}) is None
+    if torch.cuda.device_count() >= 1:
+        assert multigpu.configured_devices({"gpu": {"devices": [0]}}) is None   # one device = the single-GPU path
+    else:
+        with pytest.raises(ValueError):                                            # an index beyond the visible devices
+            multigpu.configured_devices({"gpu": {"devices": [0]}})
+    with pytest.raises(ValueError):
+        multigpu.configured_devices({"gpu": {"devices": "some"}})
+    assert multigpu.knn_sharding({}, 3202) == "bins" and multigpu.knn_sharding({}, 50_000) == "rows"
+    assert multigpu.knn_sharding({"gpu": {"sharding": "rows"}}, 100) == "rows"
+    with pytest.raises(ValueError):
+        multigpu.knn_sharding({"gpu": {"sharding": "columns"}}, 100)
+    # 3202 rows = 13 tile rows of 256 (the last 130 high): upper triangle incl. the diagonal, clipped to the matrix
+    sizes = [256] * 12 + [130]
+    want = sum(sizes[i] * sizes[j] for i in range(13) for j in range(i, 13))
+    assert engine.gram_tile_elems(3202, 3202, True) == want == 5_528_068
+    assert engine.gram_tile_elems(3202, 1000, False) == 3_202_000
+    # the host format's byte count: codes + 12 bytes per escape + the two tables of a relative format
+    pk = engine.PackedDepth(torch.zeros((4, 44), dtype=torch.int32), 4, 100, torch.tensor([7, 9]), torch.tensor([1.5, 700.0]),
+                            11, torch.zeros(4, dtype=torch.int32), torch.zeros(100, dtype=torch.int32))
+    assert pk.relative and pk.nbytes == 4 * 44 * 4 + 2 * 12 + (4 + 100) * 4 and pk.n_big == 1
+    assert not engine.PackedDepth(torch.zeros((4, 104), dtype=torch.int16), 4, 100, torch.zeros(0, dtype=torch.int64),
+                                  torch.zeros(0), 16).relative
+
+
+def test_bench_cli_and_numa_binding_degrade_gracefully(monkeypatch):
+    """bench.py's argument surface the docs name, and the NUMA binding helper on a box without NVML / GPUs: it reports, it
+    does not raise, and it leaves the affinity alone."""
+    import os
+
+    import bench
+
+    monkeypatch.setattr(sys, "argv", ["bench.py", "--gpus", "1", "--host-format", "abs", "--device-format", "f32", "--timeline",
+                                      "--ring-bins", "2900000", "--ring-regen"])
+    a = bench.parse_args()
+    assert a.host_format == "abs" and a.device_format == "f32" and a.timeline and a.ring_regen and a.ring_bins == 2_900_000
+    before = os.sched_getaffinity(0)
+    out = bench.bind_to_gpu_numa_node(0)
+    assert out is None or "error" in out or out["cpus"] >= 1
+    if out is None or "error" in out:
+        assert os.sched_getaffinity(0) == before
+    os.sched_setaffinity(0, before)
