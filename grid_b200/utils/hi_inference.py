@@ -74,6 +74,17 @@ def _load_ibs_neighbors(neighbors_file, IDtoInd, MAX_NBR):
     return lists
 
 
+def _columns(line: str, need: int):
+    """Fields of one iLASH line -- tab-separated, or any whitespace when that yields too few -- or None for a blank or
+    short line (what hi_inference.py:117-124 accepts)."""
+    line = line.strip()
+    for sep in ("\t", None):
+        parts = line.split(sep) if line else []
+        if len(parts) >= need:
+            return parts
+    return None
+
+
 def _load_ibd_neighbors(ilash_file, IDtoInd, MAX_NBR, region_start, region_end, min_length=0.5, min_match=0.70,
                         weighted=False, weight_scale=1_000_000):
     """iLASH output -> lists of (neighbour haplotype, weight): both directions of every kept segment, the MAX_NBR
@@ -81,15 +92,9 @@ def _load_ibd_neighbors(ilash_file, IDtoInd, MAX_NBR, region_start, region_end, 
     (hi_inference.py:78-176)."""
     cand: dict[int, list] = {}
     with open_maybe_gz(ilash_file) as fh:
-        for line in fh:
-            line = line.strip()
-            if not line:
+        for parts in (_columns(line, 11) for line in fh):
+            if parts is None:
                 continue
-            parts = line.split("\t")
-            if len(parts) < 11:
-                parts = line.split()
-                if len(parts) < 11:
-                    continue
             try:
                 bp1, bp2 = int(parts[5]), int(parts[6])
                 length, match = float(parts[9]), float(parts[10])
@@ -206,57 +211,65 @@ def _run_phasing(IRRs, hap_nbrs, MIN_NBR, N_ITERS, console):
     return d["val"].cpu().numpy(), mean_irr, imp.cpu().numpy()
 
 
+class _Settings:
+    """The step's knobs, read with the reference's keys and in-function defaults (hi_inference.py:265-280)."""
+
+    def __init__(self, config):
+        sec = config.get("compute_haploid_genotypes", {})
+        ext = config.get("output_file_type", "tsv")
+        folder = config.get("output_dir", ".")
+        self.section = sec
+        self.out_path = Path(f"{folder}/{sec.get('output_file_prefix', 'haploid_genotypes')}.{ext}")
+        self.dipcn_path = Path(f"{folder}/{config['compute_diploid_genotypes'].get('output_file_prefix')}.{ext}")
+        self.method = sec.get("method", "ibs").lower()
+        self.min_nbr, self.max_nbr, self.sweeps = sec.get("min_neighbors", 1), sec.get("max_neighbors", 10), sec.get("n_iters", 100)
+        self.window = (config.get("start_bp"), config.get("end_bp"))
+
+
+def _neighbours_for(s: _Settings, index, console):
+    """Haplotype neighbour lists by the configured method, or None after logging the reference's config error."""
+    source_key = {"ibs": "ibs_output", "ibd": "ibd_output"}.get(s.method)
+    if source_key is None:
+        log(console, f"Config error: unknown method '{s.method}', must be 'ibs' or 'ibd'", style="danger")
+        return None
+    source = s.section.get(source_key)
+    if not source:
+        log(console, f"Config error: {source_key} required for method='{s.method}'", style="danger")
+        return None
+    if s.method == "ibs":
+        log(console, f"Loading IBS neighbors from {source}")
+        return _load_ibs_neighbors(source, index, s.max_nbr)
+    weighted = s.section.get("weighted", False)
+    log(console, f"Loading IBD neighbors from {source} (weighted={weighted})")
+    return _load_ibd_neighbors(source, index, s.max_nbr, s.window[0], s.window[1],
+                               min_length=s.section.get("min_length", 0.5), min_match=s.section.get("min_match", 0.70),
+                               weighted=weighted, weight_scale=s.section.get("weight_scale", 1_000_000))
+
+
 def hi_inference(config, console):
-    """Same contract as the reference's hi_inference(config, console) (hi_inference.py:259-339)."""
+    """Same contract as the reference's hi_inference(config, console) (hi_inference.py:259-339): same config keys and
+    defaults, same log lines, same output table."""
     try:
-        hi_cfg = config.get("compute_haploid_genotypes", {})
-        output_file_prefix = hi_cfg.get("output_file_prefix", "haploid_genotypes")
-        output_file_type = config.get("output_file_type", "tsv")
-        output_dir = config.get("output_dir", ".")
-        output_file = Path(f"{output_dir}/{output_file_prefix}.{output_file_type}")
-        dip_cn_file_prefix = config["compute_diploid_genotypes"].get("output_file_prefix")
-        dip_cn_file = Path(f"{output_dir}/{dip_cn_file_prefix}.{output_file_type}")
-        method = hi_cfg.get("method", "ibs").lower()
-        MIN_NBR = hi_cfg.get("min_neighbors", 1)
-        MAX_NBR = hi_cfg.get("max_neighbors", 10)
-        N_ITERS = hi_cfg.get("n_iters", 100)
+        s = _Settings(config)
     except Exception as e:
         log(console, f"Config error: {e}", style="danger")
         return
 
-    IDs, IRRs, IDtoInd = _read_dip_cn_file(dip_cn_file)
-    N = len(IRRs)
-    log(console, f"Read diploid IRR data for {N} samples", style="success")
-    if len(IDtoInd) != N:
+    ids, irr, index = _read_dip_cn_file(s.dipcn_path)
+    n = len(irr)
+    log(console, f"Read diploid IRR data for {n} samples", style="success")
+    if len(index) != n:
         # a repeated id: the reference sizes its neighbour table by distinct ids and then indexes it by row -- it
         # fails with an IndexError; so do we, with a message
-        raise IndexError(f"{dip_cn_file}: {N - len(IDtoInd)} repeated sample id(s)")
+        raise IndexError(f"{s.dipcn_path}: {n - len(index)} repeated sample id(s)")
 
-    if method == "ibs":
-        ibs_output = hi_cfg.get("ibs_output")
-        if not ibs_output:
-            log(console, "Config error: ibs_output required for method='ibs'", style="danger")
-            return
-        log(console, f"Loading IBS neighbors from {ibs_output}")
-        hap_nbrs = _load_ibs_neighbors(ibs_output, IDtoInd, MAX_NBR)
-    elif method == "ibd":
-        ibd_output = hi_cfg.get("ibd_output")
-        if not ibd_output:
-            log(console, "Config error: ibd_output required for method='ibd'", style="danger")
-            return
-        weighted = hi_cfg.get("weighted", False)
-        log(console, f"Loading IBD neighbors from {ibd_output} (weighted={weighted})")
-        hap_nbrs = _load_ibd_neighbors(ibd_output, IDtoInd, MAX_NBR, config.get("start_bp"), config.get("end_bp"),
-                                       min_length=hi_cfg.get("min_length", 0.5), min_match=hi_cfg.get("min_match", 0.70),
-                                       weighted=weighted, weight_scale=hi_cfg.get("weight_scale", 1_000_000))
-    else:
-        log(console, f"Config error: unknown method '{method}', must be 'ibs' or 'ibd'", style="danger")
+    hap_nbrs = _neighbours_for(s, index, console)
+    if hap_nbrs is None:
         return
-
-    hap_IRRs, mean_IRRs, imp = _run_phasing(IRRs, hap_nbrs, MIN_NBR, N_ITERS, console)
-    with open_maybe_gz(output_file, "wt") as fout:
+    phased, _mean, imputed = _run_phasing(irr, hap_nbrs, s.min_nbr, s.sweeps, console)
+    h, m = phased.tolist(), imputed.tolist()
+    with open_maybe_gz(s.out_path, "wt") as fout:
         fout.write("ID\tIRRs\thap1phased\thap2phased\thap1imp\thap2imp\n")
-        h, m = hap_IRRs.tolist(), imp.tolist()
-        for i in range(N):
-            fout.write(f"{IDs[i]}\t{IRRs[i]:.2f}\t{h[2 * i]:.2f}\t{h[2 * i + 1]:.2f}\t{m[2 * i]:.2f}\t{m[2 * i + 1]:.2f}\n")
-    log(console, f"Haploid genotypes written to {output_file}", style="success")
+        fout.writelines(f"{ids[i]}\t{irr[i]:.2f}\t{h[2 * i]:.2f}\t{h[2 * i + 1]:.2f}\t{m[2 * i]:.2f}\t{m[2 * i + 1]:.2f}\n"
+                        for i in range(n))
+    log(console, f"Haploid genotypes written to {s.out_path}", style="success")
